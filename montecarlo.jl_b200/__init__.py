@@ -1,0 +1,8 @@
+"""B200-native DQMC / Ising sweep engine behind MonteCarlo.jl's flavor/model API.
+
+Host-side mirror of the reference interface (Python stands in for the Julia host,
+which is absent from this image); all compute goes through the C ABI of
+csrc/libmcb200.so (include/mcb200.h). There is no CPU fallback.
+"""
+from .lattices import SquareLattice  # noqa: F401
+from .models import HubbardModelAttractive, IsingModel, IsingTc  # noqa: F401

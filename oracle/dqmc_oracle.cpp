@@ -1,0 +1,487 @@
+// ORACLE (test infrastructure only — never linked into the product library).
+//
+// Single-chain CPU restatement of MonteCarlo.jl's DQMC sweep for
+// DQMC{HubbardModelAttractive, CheckerboardFalse}: immediate rank-1 updates,
+// materialised slice matrices, unblocked pivoted Householder UDT with norm
+// recomputation, 5-GEMM calculate_greens — i.e. the reference's own algorithmic
+// choices, loop nest by loop nest. Paths cited are relative to /root/reference.
+//
+// Parity status: the reference is Julia and cannot run here (no julia binary,
+// SURVEY.md §8c). The reference's tests for this path are property tests on
+// random inputs (test/slice_matrices.jl:141-235, test/flavortests_DQMC.jl:44-69);
+// tests/test_oracle_*.py restate them against numpy/scipy. Trajectory-level
+// goldens seeded with Julia's MersenneTwister are "parity unpinned"
+// (statistical agreement only).
+#include "linalg_ref.h"
+#include "philox_ref.h"
+#include <stdlib.h>
+#include <vector>
+
+namespace {
+
+struct Oracle {
+    int N, M, safe_mult, n_elements;
+    double dtau, U, lambda;
+    uint64_t seed;
+    uint32_t chain;
+    // hopping exponentials (stack.jl:167-181): e^{-dtau T/2}, e^{+dtau T/2}, and their squares
+    std::vector<double> eT, eTinv, eT2, eTinv2;
+    std::vector<int8_t> conf; // conf[i + l*N]  (HubbardModel.jl:4)
+    // DQMCStack fields (stack.jl:1-85)
+    std::vector<std::vector<double>> u_stack, d_stack, t_stack;
+    std::vector<double> greens, greens_temp, Ul, Ur, Tl, Tr, Dl, Dr, tmp1, tmp2, curr_U, eV, tempv;
+    std::vector<int64_t> pivot;
+    int current_slice, direction;
+    // DQMCAnalysis counters (DQMC.jl:36-47)
+    int64_t prop_local, acc_local;
+    double max_prop_err;
+    int check_propagation;
+    // RNG position
+    uint64_t update_count; // number of update() calls so far
+    // injected uniforms (optional): if non-empty, consumed in order instead of Philox
+    std::vector<double> injected;
+    size_t injected_pos;
+};
+
+// HubbardModelAttractive.jl:100-110
+void interaction_matrix_exp(Oracle& o, int slice /*1-based*/, double power)
+{
+    const double sgn = power > 0 ? 1.0 : (power < 0 ? -1.0 : 0.0);
+    const int8_t* c = o.conf.data() + (size_t)(slice - 1) * o.N;
+    for (int i = 0; i < o.N; ++i) o.eV[i] = exp(sgn * o.lambda * c[i]);
+}
+
+// slice_matrices.jl:23-39 : result = eT2 * diag(eV) (power>0) or diag(eV) * eTinv2
+void slice_matrix(Oracle& o, int slice, double power, double* result)
+{
+    interaction_matrix_exp(o, slice, power);
+    if (power > 0) ref_vmul_nd(result, o.eT2.data(), o.eV.data(), o.N);
+    else ref_vmul_dn(result, o.eV.data(), o.eTinv2.data(), o.N);
+}
+
+// slice_matrices.jl:42-76
+void mul_slice_left(Oracle& o, int slice, double* Mx)
+{
+    slice_matrix(o, slice, 1.0, o.tmp2.data());
+    ref_vmul_nn(o.tmp1.data(), o.tmp2.data(), Mx, o.N);
+    ref_copy(Mx, o.tmp1.data(), o.N);
+}
+void mul_slice_right(Oracle& o, int slice, double* Mx)
+{
+    slice_matrix(o, slice, 1.0, o.tmp2.data());
+    ref_vmul_nn(o.tmp1.data(), Mx, o.tmp2.data(), o.N);
+    ref_copy(Mx, o.tmp1.data(), o.N);
+}
+void mul_slice_inv_right(Oracle& o, int slice, double* Mx)
+{
+    slice_matrix(o, slice, -1.0, o.tmp2.data());
+    ref_vmul_nn(o.tmp1.data(), Mx, o.tmp2.data(), o.N);
+    ref_copy(Mx, o.tmp1.data(), o.N);
+}
+void mul_slice_inv_left(Oracle& o, int slice, double* Mx)
+{
+    slice_matrix(o, slice, -1.0, o.tmp2.data());
+    ref_vmul_nn(o.tmp1.data(), o.tmp2.data(), Mx, o.N);
+    ref_copy(Mx, o.tmp1.data(), o.N);
+}
+void mul_daggered_slice_left(Oracle& o, int slice, double* Mx)
+{
+    slice_matrix(o, slice, 1.0, o.tmp2.data());
+    ref_vmul_tn(o.tmp1.data(), o.tmp2.data(), Mx, o.N);
+    ref_copy(Mx, o.tmp1.data(), o.N);
+}
+
+// stack.jl:491-500
+void wrap_greens(Oracle& o, double* gf, int curr_slice, int direction)
+{
+    if (direction == -1) {
+        mul_slice_inv_left(o, curr_slice - 1, gf);
+        mul_slice_right(o, curr_slice - 1, gf);
+    } else {
+        mul_slice_left(o, curr_slice, gf);
+        mul_slice_inv_right(o, curr_slice, gf);
+    }
+}
+
+// stack.jl:272-287 ; idx is 1-based, ranges[idx] = 1+(idx-1)s : idx*s
+void add_slice_sequence_left(Oracle& o, int idx)
+{
+    const int n = o.N;
+    ref_copy(o.curr_U.data(), o.u_stack[idx - 1].data(), n);
+    for (int slice = 1 + (idx - 1) * o.safe_mult; slice <= idx * o.safe_mult; ++slice)
+        mul_slice_left(o, slice, o.curr_U.data());
+    ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.d_stack[idx - 1].data(), n);
+    ref_udt_pivot(o.u_stack[idx].data(), o.d_stack[idx].data(), o.tmp1.data(), o.pivot.data(),
+                  o.tempv.data(), n, 1);
+    ref_vmul_nn(o.t_stack[idx].data(), o.tmp1.data(), o.t_stack[idx - 1].data(), n);
+}
+// stack.jl:296-311
+void add_slice_sequence_right(Oracle& o, int idx)
+{
+    const int n = o.N;
+    ref_copy(o.curr_U.data(), o.u_stack[idx].data(), n);
+    for (int slice = idx * o.safe_mult; slice >= 1 + (idx - 1) * o.safe_mult; --slice)
+        mul_daggered_slice_left(o, slice, o.curr_U.data());
+    ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.d_stack[idx].data(), n);
+    ref_udt_pivot(o.u_stack[idx - 1].data(), o.d_stack[idx - 1].data(), o.tmp1.data(),
+                  o.pivot.data(), o.tempv.data(), n, 1);
+    ref_vmul_nn(o.t_stack[idx - 1].data(), o.tmp1.data(), o.t_stack[idx].data(), n);
+}
+
+void slot_identity(Oracle& o, int k)
+{
+    ref_eye(o.u_stack[k].data(), o.N);
+    for (int i = 0; i < o.N; ++i) o.d_stack[k][i] = 1.0;
+    ref_eye(o.t_stack[k].data(), o.N);
+}
+
+// stack.jl:242-255
+void build_stack(Oracle& o)
+{
+    slot_identity(o, 0);
+    for (int i = 1; i <= o.n_elements - 1; ++i) add_slice_sequence_left(o, i);
+    o.current_slice = o.M + 1;
+    o.direction = -1;
+}
+
+void calc_greens(Oracle& o, double* out)
+{
+    ref_calculate_greens(o.Ul.data(), o.Dl.data(), o.Tl.data(), o.Ur.data(), o.Dr.data(),
+                         o.Tr.data(), out, o.pivot.data(), o.tempv.data(), o.N);
+}
+
+void load_l(Oracle& o, int k)
+{
+    o.Ul = o.u_stack[k]; o.Dl = o.d_stack[k]; o.Tl = o.t_stack[k];
+}
+void load_r(Oracle& o, int k)
+{
+    o.Ur = o.u_stack[k]; o.Dr = o.d_stack[k]; o.Tr = o.t_stack[k];
+}
+
+void record_prop_err(Oracle& o)
+{
+    double d = 0.0;
+    for (size_t i = 0; i < o.greens.size(); ++i) {
+        double e = fabs(o.greens_temp[i] - o.greens[i]);
+        if (e > d) d = e;
+    }
+    if (d > o.max_prop_err) o.max_prop_err = d;
+}
+
+// stack.jl:502-631
+void propagate(Oracle& o)
+{
+    const int s = o.safe_mult, M = o.M;
+    if (o.direction == 1) {
+        if (o.current_slice % s == 0) {
+            o.current_slice += 1;
+            if (o.current_slice == 1) {
+                load_r(o, 0);
+                slot_identity(o, 0);
+                load_l(o, 0);
+                calc_greens(o, o.greens.data());
+            } else if (o.current_slice > 1 && o.current_slice <= M) {
+                const int idx = (o.current_slice - 1) / s;
+                load_r(o, idx);
+                add_slice_sequence_left(o, idx);
+                load_l(o, idx);
+                if (o.check_propagation) {
+                    // the reference wraps greens_temp unconditionally (stack.jl:534-536); its
+                    // value only matters when the check is on, so the wasted wrap is skipped.
+                    o.greens_temp = o.greens;
+                    wrap_greens(o, o.greens_temp.data(), o.current_slice - 1, 1);
+                }
+                calc_greens(o, o.greens.data());
+                if (o.check_propagation) record_prop_err(o);
+            } else {
+                const int idx = o.n_elements - 1;
+                add_slice_sequence_left(o, idx);
+                o.direction = -1;
+                o.current_slice = M + 1;
+                propagate(o);
+            }
+        } else {
+            wrap_greens(o, o.greens.data(), o.current_slice, 1);
+            o.current_slice += 1;
+        }
+    } else {
+        if ((o.current_slice - 1) % s == 0) {
+            o.current_slice -= 1;
+            if (o.current_slice == M) {
+                const int last = o.n_elements - 1;
+                load_l(o, last);
+                slot_identity(o, last);
+                load_r(o, last);
+                calc_greens(o, o.greens.data());
+                wrap_greens(o, o.greens.data(), o.current_slice + 1, -1);
+            } else if (o.current_slice > 0 && o.current_slice < M) {
+                const int idx = o.current_slice / s + 1; // 1-based
+                load_l(o, idx - 1);
+                add_slice_sequence_right(o, idx);
+                load_r(o, idx - 1);
+                if (o.check_propagation) o.greens_temp = o.greens;
+                calc_greens(o, o.greens.data());
+                if (o.check_propagation) record_prop_err(o);
+                wrap_greens(o, o.greens.data(), o.current_slice + 1, -1);
+            } else {
+                add_slice_sequence_right(o, 1);
+                o.direction = 1;
+                o.current_slice = 0;
+                propagate(o);
+            }
+        } else {
+            wrap_greens(o, o.greens.data(), o.current_slice, -1);
+            o.current_slice -= 1;
+        }
+    }
+}
+
+double next_uniform(Oracle& o, uint32_t sweep, uint32_t visit, uint32_t site)
+{
+    if (!o.injected.empty()) return o.injected[o.injected_pos++ % o.injected.size()];
+    return dqmc_uniform_ref(o.seed, o.chain, sweep, visit, site);
+}
+
+// DQMC.jl:546-582 with propose_local / accept_local! (HubbardModelAttractive.jl:113-155)
+void sweep_spatial(Oracle& o)
+{
+    const int n = o.N;
+    const int slice = o.current_slice;
+    int8_t* c = o.conf.data() + (size_t)(slice - 1) * n;
+    double* G = o.greens.data();
+    const uint32_t sweep = (uint32_t)(o.update_count / (uint64_t)(2 * o.M));
+    const uint32_t visit = (uint32_t)(o.update_count % (uint64_t)(2 * o.M));
+    std::vector<double> IG(n), Gr(n);
+    for (int i = 0; i < n; ++i) {
+        const double dE = -2.0 * o.lambda * c[i];
+        const double gamma = exp(dE) - 1.0;
+        const double r = 1.0 + gamma * (1.0 - G[IDX(i, i, n)]);
+        const double detratio = r * r;
+        o.prop_local += 1;
+        const double p = exp(-dE) * detratio;
+        // the uniform is indexed, not sequential: drawing it unconditionally is
+        // equivalent to the reference's short-circuit `p > 1 || rand() < p`.
+        const double u = next_uniform(o, sweep, visit, (uint32_t)i);
+        if (p > 1.0 || u < p) {
+            for (int j = 0; j < n; ++j) { IG[j] = -G[IDX(j, i, n)]; Gr[j] = G[IDX(i, j, n)]; }
+            IG[i] += 1.0;
+            const double x = gamma / (1.0 + gamma * IG[i]);
+            for (int l = 0; l < n; ++l) {
+                const double xv = x * Gr[l];
+                double* g = G + IDX(0, l, n);
+#pragma omp simd
+                for (int k = 0; k < n; ++k) g[k] -= IG[k] * xv;
+            }
+            c[i] = (int8_t)-c[i];
+            o.acc_local += 1;
+        }
+    }
+}
+
+// DQMC.jl:523-538
+void update(Oracle& o)
+{
+    propagate(o);
+    sweep_spatial(o);
+    o.update_count += 1;
+}
+
+} // namespace
+
+extern "C" {
+
+void* orc_create(int N, int M, int safe_mult, double dtau, double U, const double* eT_half_minus,
+                 const double* eT_half_plus, const double* eT_minus, const double* eT_plus,
+                 const int8_t* conf, uint64_t seed, uint32_t chain, int check_propagation)
+{
+    if (M % safe_mult != 0) return nullptr; // stack.jl:115 convert(Int, slices/safe_mult) throws
+    Oracle* o = new Oracle();
+    o->N = N; o->M = M; o->safe_mult = safe_mult; o->dtau = dtau; o->U = U;
+    o->lambda = acosh(exp(0.5 * U * dtau));
+    o->seed = seed; o->chain = chain;
+    o->n_elements = M / safe_mult + 1;
+    const size_t nn = (size_t)N * N;
+    o->eT.assign(eT_half_minus, eT_half_minus + nn);
+    o->eTinv.assign(eT_half_plus, eT_half_plus + nn);
+    o->eT2.assign(eT_minus, eT_minus + nn);
+    o->eTinv2.assign(eT_plus, eT_plus + nn);
+    o->conf.assign(conf, conf + (size_t)N * M);
+    o->u_stack.assign(o->n_elements, std::vector<double>(nn));
+    o->t_stack.assign(o->n_elements, std::vector<double>(nn));
+    o->d_stack.assign(o->n_elements, std::vector<double>(N, 0.0));
+    for (auto* v : {&o->greens, &o->greens_temp, &o->Ul, &o->Ur, &o->Tl, &o->Tr, &o->tmp1, &o->tmp2,
+                    &o->curr_U})
+        v->assign(nn, 0.0);
+    ref_eye(o->Ul.data(), N); ref_eye(o->Ur.data(), N);
+    ref_eye(o->Tl.data(), N); ref_eye(o->Tr.data(), N);
+    o->Dl.assign(N, 1.0); o->Dr.assign(N, 1.0);
+    o->eV.assign(N, 1.0); o->tempv.assign(N, 0.0);
+    o->pivot.assign(N, 0);
+    o->current_slice = 0; o->direction = 1;
+    o->prop_local = o->acc_local = 0;
+    o->max_prop_err = 0.0;
+    o->check_propagation = check_propagation;
+    o->update_count = 0;
+    o->injected_pos = 0;
+    return o;
+}
+void orc_destroy(void* h) { delete (Oracle*)h; }
+
+void orc_set_conf(void* h, const int8_t* conf)
+{
+    Oracle& o = *(Oracle*)h;
+    o.conf.assign(conf, conf + (size_t)o.N * o.M);
+}
+void orc_get_conf(void* h, int8_t* conf)
+{
+    Oracle& o = *(Oracle*)h;
+    memcpy(conf, o.conf.data(), o.conf.size());
+}
+void orc_set_uniforms(void* h, const double* u, int64_t n)
+{
+    Oracle& o = *(Oracle*)h;
+    o.injected.assign(u, u + n);
+    o.injected_pos = 0;
+}
+// run!'s prologue: build_stack + propagate (DQMC.jl:412-414)
+void orc_build_stack(void* h)
+{
+    Oracle& o = *(Oracle*)h;
+    build_stack(o);
+    propagate(o);
+}
+void orc_update(void* h, int64_t n)
+{
+    Oracle& o = *(Oracle*)h;
+    for (int64_t i = 0; i < n; ++i) update(o);
+}
+void orc_sweep(void* h, int64_t n) { orc_update(h, n * 2 * ((Oracle*)h)->M); }
+void orc_propagate_only(void* h) { propagate(*(Oracle*)h); }
+
+// physical != 0 applies _greens! (DQMC.jl:721-730): e^{+dtau T/2} G e^{-dtau T/2}
+void orc_get_greens(void* h, double* out, int physical)
+{
+    Oracle& o = *(Oracle*)h;
+    if (!physical) { ref_copy(out, o.greens.data(), o.N); return; }
+    std::vector<double> t((size_t)o.N * o.N);
+    ref_vmul_nn(t.data(), o.greens.data(), o.eT.data(), o.N);
+    ref_vmul_nn(out, o.eTinv.data(), t.data(), o.N);
+}
+void orc_get_state(void* h, int64_t* out /*[5]*/, double* max_prop_err)
+{
+    Oracle& o = *(Oracle*)h;
+    out[0] = o.current_slice; out[1] = o.direction; out[2] = o.prop_local; out[3] = o.acc_local;
+    out[4] = (int64_t)o.update_count;
+    *max_prop_err = o.max_prop_err;
+}
+
+// calculate_greens(mc, slice) from scratch (stack.jl:422-480). Does not touch the stack.
+void orc_calculate_greens_at(void* h, int slice, double* out)
+{
+    Oracle& o = *(Oracle*)h;
+    const int n = o.N, s = o.safe_mult, M = o.M;
+    ref_eye(o.curr_U.data(), n); ref_eye(o.Ur.data(), n); ref_eye(o.Tr.data(), n);
+    for (int i = 0; i < n; ++i) o.Dr[i] = 1.0;
+    if (slice + 1 <= M) {
+        for (int k = M; k >= slice + 1; --k) {
+            mul_daggered_slice_left(o, k, o.curr_U.data());
+            if (k % s == 0) {
+                ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.Dr.data(), n);
+                ref_udt_pivot(o.curr_U.data(), o.Dr.data(), o.tmp1.data(), o.pivot.data(),
+                              o.tempv.data(), n, 1);
+                ref_copy(o.tmp2.data(), o.Tr.data(), n);
+                ref_vmul_nn(o.Tr.data(), o.tmp1.data(), o.tmp2.data(), n);
+            }
+        }
+        ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.Dr.data(), n);
+        ref_udt_pivot(o.Ur.data(), o.Dr.data(), o.tmp1.data(), o.pivot.data(), o.tempv.data(), n, 1);
+        ref_copy(o.tmp2.data(), o.Tr.data(), n);
+        ref_vmul_nn(o.Tr.data(), o.tmp1.data(), o.tmp2.data(), n);
+    }
+    ref_eye(o.curr_U.data(), n); ref_eye(o.Ul.data(), n); ref_eye(o.Tl.data(), n);
+    for (int i = 0; i < n; ++i) o.Dl[i] = 1.0;
+    if (slice >= 1) {
+        for (int k = 1; k <= slice; ++k) {
+            mul_slice_left(o, k, o.curr_U.data());
+            if (k % s == 0) {
+                ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.Dl.data(), n);
+                ref_udt_pivot(o.curr_U.data(), o.Dl.data(), o.tmp1.data(), o.pivot.data(),
+                              o.tempv.data(), n, 1);
+                ref_copy(o.tmp2.data(), o.Tl.data(), n);
+                ref_vmul_nn(o.Tl.data(), o.tmp1.data(), o.tmp2.data(), n);
+            }
+        }
+        ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.Dl.data(), n);
+        ref_udt_pivot(o.Ul.data(), o.Dl.data(), o.tmp1.data(), o.pivot.data(), o.tempv.data(), n, 1);
+        ref_copy(o.tmp2.data(), o.Tl.data(), n);
+        ref_vmul_nn(o.Tl.data(), o.tmp1.data(), o.tmp2.data(), n);
+    }
+    calc_greens(o, out);
+}
+
+// ---- bare linear-algebra entry points for the property tests (test/slice_matrices.jl:141-235)
+void orc_vmul(double* C, const double* A, const double* B, int n, int mode)
+{
+    switch (mode) {
+    case 0: ref_vmul_nn(C, A, B, n); break;
+    case 1: ref_vmul_nt(C, A, B, n); break;
+    case 2: ref_vmul_tn(C, A, B, n); break;
+    case 3: ref_vmul_nd(C, A, B, n); break; // B is a length-n diagonal
+    case 4: ref_vmul_dn(C, A, B, n); break; // A is a length-n diagonal
+    }
+}
+void orc_udt_pivot(double* U, double* D, double* A, int64_t* pivot, int n, int apply_pivot)
+{
+    std::vector<double> temp(n);
+    ref_udt_pivot(U, D, A, pivot, temp.data(), n, apply_pivot);
+}
+void orc_rdivp(double* A, const double* T, const int64_t* pivot, int n)
+{
+    std::vector<double> O((size_t)n * n);
+    ref_rdivp(A, T, O.data(), pivot, n);
+}
+void orc_calculate_greens_udt(double* Ul, double* Dl, double* Tl, double* Ur, double* Dr, double* Tr,
+                              double* G, int n)
+{
+    std::vector<int64_t> pivot(n);
+    std::vector<double> temp(n);
+    ref_calculate_greens(Ul, Dl, Tl, Ur, Dr, Tr, G, pivot.data(), temp.data(), n);
+}
+// slice-matrix multiplies on an arbitrary matrix (test/slice_matrices.jl:36-82)
+// mode: 0 left, 1 right, 2 inv_left, 3 inv_right, 4 daggered_left
+void orc_multiply_slice(void* h, int slice, double* Mx, int mode)
+{
+    Oracle& o = *(Oracle*)h;
+    switch (mode) {
+    case 0: mul_slice_left(o, slice, Mx); break;
+    case 1: mul_slice_right(o, slice, Mx); break;
+    case 2: mul_slice_inv_left(o, slice, Mx); break;
+    case 3: mul_slice_inv_right(o, slice, Mx); break;
+    case 4: mul_daggered_slice_left(o, slice, Mx); break;
+    }
+}
+double orc_uniform(uint64_t seed, uint32_t chain, uint32_t sweep, uint32_t visit, uint32_t site)
+{
+    return dqmc_uniform_ref(seed, chain, sweep, visit, site);
+}
+void orc_philox(const uint32_t* ctr, const uint32_t* key, uint32_t* out)
+{
+    philox4x32_10_ref(ctr, key, out);
+}
+
+} // extern "C"
+
+// CPU-baseline helper for bench.py: one independent chain per host thread
+// ("one Julia process per core", the reference's only form of parallelism).
+#include <thread>
+extern "C" void orc_sweep_many(void** handles, int n_handles, int64_t n_sweeps, int n_threads)
+{
+    if (n_threads < 1) n_threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < n_threads; ++t)
+        pool.emplace_back([=]() {
+            for (int i = t; i < n_handles; i += n_threads) orc_sweep(handles[i], n_sweeps);
+        });
+    for (auto& th : pool) th.join();
+}

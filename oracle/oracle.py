@@ -1,0 +1,201 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so).
+
+ORACLE = test infrastructure. Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this module. The product package
+(montecarlo.jl_b200/) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBS = {}
+
+_f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_i8p = np.ctypeslib.ndpointer(dtype=np.int8, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+
+
+def build(native=False, force=False):
+    """Compile the oracle with the committed Makefile. Returns the .so path."""
+    out = "liboracle_native.so" if native else "liboracle.so"
+    path = os.path.join(_HERE, out)
+    srcs = [os.path.join(_HERE, f) for f in
+            ("dqmc_oracle.cpp", "ising_oracle.cpp", "linalg_ref.h", "philox_ref.h")]
+    stale = (not os.path.exists(path)) or any(
+        os.path.getmtime(s) > os.path.getmtime(path) for s in srcs)
+    if stale or force:
+        cmd = ["make", "-C", _HERE, "OUT=" + out]
+        if native:
+            cmd.append("ARCH=native")
+        subprocess.run(cmd, check=True, capture_output=True)
+    return path
+
+
+def lib(native=False):
+    key = bool(native)
+    if key in _LIBS:
+        return _LIBS[key]
+    L = C.CDLL(build(native))
+    L.orc_create.restype = C.c_void_p
+    L.orc_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _f64p, _f64p, _f64p,
+                             _f64p, _i8p, C.c_uint64, C.c_uint32, C.c_int]
+    L.orc_destroy.argtypes = [C.c_void_p]
+    L.orc_set_conf.argtypes = [C.c_void_p, _i8p]
+    L.orc_get_conf.argtypes = [C.c_void_p, _i8p]
+    L.orc_set_uniforms.argtypes = [C.c_void_p, _f64p, C.c_int64]
+    L.orc_build_stack.argtypes = [C.c_void_p]
+    L.orc_update.argtypes = [C.c_void_p, C.c_int64]
+    L.orc_sweep.argtypes = [C.c_void_p, C.c_int64]
+    L.orc_propagate_only.argtypes = [C.c_void_p]
+    L.orc_get_greens.argtypes = [C.c_void_p, _f64p, C.c_int]
+    L.orc_get_state.argtypes = [C.c_void_p, _i64p, _f64p]
+    L.orc_calculate_greens_at.argtypes = [C.c_void_p, C.c_int, _f64p]
+    L.orc_vmul.argtypes = [_f64p, _f64p, _f64p, C.c_int, C.c_int]
+    L.orc_udt_pivot.argtypes = [_f64p, _f64p, _f64p, _i64p, C.c_int, C.c_int]
+    L.orc_rdivp.argtypes = [_f64p, _f64p, _i64p, C.c_int]
+    L.orc_calculate_greens_udt.argtypes = [_f64p] * 7 + [C.c_int]
+    L.orc_multiply_slice.argtypes = [C.c_void_p, C.c_int, _f64p, C.c_int]
+    L.orc_uniform.restype = C.c_double
+    L.orc_uniform.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    L.orc_philox.argtypes = [_u32p, _u32p, _u32p]
+    L.orc_sweep_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int]
+    # Ising
+    L.ising_energy_cubic.restype = C.c_double
+    L.ising_energy_cubic.argtypes = [_i64p, C.c_int, C.c_int]
+    L.ising_energy_square.restype = C.c_double
+    L.ising_energy_square.argtypes = [_i64p, C.c_int]
+    L.ising_delta_e_square.restype = C.c_double
+    L.ising_delta_e_square.argtypes = [_i64p, C.c_int, C.c_int64]
+    L.ising_thresholds.argtypes = [C.c_double, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    L.ising_site_random.restype = C.c_uint32
+    L.ising_site_random.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int,
+                                    C.c_int]
+    L.ising_checkerboard_sweeps.argtypes = [_i8p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint64,
+                                            C.c_uint32, C.c_uint32, C.c_int]
+    L.ising_sequential_sweeps.restype = C.c_int64
+    L.ising_sequential_sweeps.argtypes = [_i8p, C.c_int, C.c_double, C.c_uint64, C.c_uint32,
+                                          C.c_uint32, C.c_int, C.POINTER(C.c_double)]
+    L.ising_energy_magnetization.argtypes = [_i8p, C.c_int, C.POINTER(C.c_int64),
+                                             C.POINTER(C.c_int64)]
+    L.ising_random_spins.argtypes = [_i8p, C.c_int, C.c_uint64, C.c_uint32]
+    _LIBS[key] = L
+    return L
+
+
+def fmat(a):
+    """Julia (column-major) matrix -> flat C buffer. a[i, j] ends up at i + j*n."""
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64).T).reshape(-1)
+
+
+def unfmat(buf, n):
+    return np.asarray(buf, dtype=np.float64).reshape(n, n).T.copy()
+
+
+class OracleDQMC:
+    """One Markov chain of DQMC{HubbardModelAttractive, CheckerboardFalse} on the CPU.
+
+    conf has shape (N, M) like the reference's HubbardConf (HubbardModel.jl:4).
+    """
+
+    def __init__(self, N, M, safe_mult, dtau, U, hop, conf, seed=123, chain=0,
+                 check_propagation=False, native=False):
+        self.L = lib(native)
+        self.N, self.M = N, M
+        eTm, eTp, eT2m, eT2p = hop
+        cbuf = np.ascontiguousarray(np.asarray(conf, dtype=np.int8).T).reshape(-1)
+        self.h = self.L.orc_create(N, M, safe_mult, dtau, U, fmat(eTm), fmat(eTp), fmat(eT2m),
+                                   fmat(eT2p), cbuf, seed, chain, int(check_propagation))
+        if not self.h:
+            raise ValueError("slices must be a multiple of safe_mult (stack.jl:115)")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_destroy(self.h)
+            self.h = None
+
+    def build_stack(self):
+        self.L.orc_build_stack(self.h)
+
+    def update(self, n=1):
+        self.L.orc_update(self.h, n)
+
+    def sweep(self, n=1):
+        self.L.orc_sweep(self.h, n)
+
+    def greens(self, physical=False):
+        out = np.empty(self.N * self.N)
+        self.L.orc_get_greens(self.h, out, int(physical))
+        return unfmat(out, self.N)
+
+    def greens_at(self, slice_):
+        out = np.empty(self.N * self.N)
+        self.L.orc_calculate_greens_at(self.h, slice_, out)
+        return unfmat(out, self.N)
+
+    def conf(self):
+        out = np.empty(self.N * self.M, dtype=np.int8)
+        self.L.orc_get_conf(self.h, out)
+        return out.reshape(self.M, self.N).T.copy()
+
+    def set_conf(self, conf):
+        self.L.orc_set_conf(self.h, np.ascontiguousarray(np.asarray(conf, dtype=np.int8).T).reshape(-1))
+
+    def set_uniforms(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        self.L.orc_set_uniforms(self.h, u, u.size)
+
+    def state(self):
+        st = np.zeros(5, dtype=np.int64)
+        err = np.zeros(1)
+        self.L.orc_get_state(self.h, st, err)
+        return dict(current_slice=int(st[0]), direction=int(st[1]), prop_local=int(st[2]),
+                    acc_local=int(st[3]), updates=int(st[4]), max_prop_err=float(err[0]))
+
+    def multiply_slice(self, slice_, Mx, mode):
+        buf = fmat(Mx)
+        self.L.orc_multiply_slice(self.h, slice_, buf, mode)
+        return unfmat(buf, self.N)
+
+
+def sweep_many(chains, n_sweeps, n_threads):
+    arr = (C.c_void_p * len(chains))(*[c.h for c in chains])
+    chains[0].L.orc_sweep_many(arr, len(chains), n_sweeps, n_threads)
+
+
+def vmul(A, B, mode):
+    n = A.shape[-1]
+    a = fmat(A) if A.ndim == 2 else np.ascontiguousarray(A, dtype=np.float64)
+    b = fmat(B) if B.ndim == 2 else np.ascontiguousarray(B, dtype=np.float64)
+    c = np.empty(n * n)
+    lib().orc_vmul(c, a, b, n, mode)
+    return unfmat(c, n)
+
+
+def udt_pivot(X, apply_pivot=True):
+    """Returns U, D, T, pivot (0-based) of udt_AVX_pivot! (UDT.jl:192-281)."""
+    n = X.shape[0]
+    a = fmat(X)
+    u = np.empty(n * n)
+    d = np.empty(n)
+    p = np.empty(n, dtype=np.int64)
+    lib().orc_udt_pivot(u, d, a, p, n, int(apply_pivot))
+    return unfmat(u, n), d, unfmat(a, n), p
+
+
+def rdivp(A, T, pivot):
+    n = A.shape[0]
+    a = fmat(A)
+    lib().orc_rdivp(a, fmat(T), np.ascontiguousarray(pivot, dtype=np.int64), n)
+    return unfmat(a, n)
+
+
+def calculate_greens_udt(Ul, Dl, Tl, Ur, Dr, Tr):
+    n = Ul.shape[0]
+    g = np.empty(n * n)
+    lib().orc_calculate_greens_udt(fmat(Ul), np.array(Dl, dtype=np.float64), fmat(Tl), fmat(Ur),
+                                   np.array(Dr, dtype=np.float64), fmat(Tr), g, n)
+    return unfmat(g, n)
