@@ -1,0 +1,168 @@
+/* mcb200.h — C ABI of the B200-native DQMC / Ising sweep engine (libmcb200.so, sm_100a).
+ *
+ * The reference (ffreyer/MonteCarlo.jl) is pure Julia and has no FFI of its own; its
+ * "plugin API" is multiple dispatch on the flavor/model types. The entry points below are
+ * what a Julia host binds with `ccall` to replace the hot path of
+ *   DQMC{HubbardModelAttractive, CheckerboardFalse}  and  MC{IsingModel{SquareLattice}}
+ * (see INTEGRATION.md for the Julia-side methods). Every function cites the reference
+ * function(s) it replaces, paths relative to the reference repository root.
+ *
+ * Conventions
+ *  - all pointers are HOST pointers owned by the caller and only valid during the call;
+ *    the library owns all device memory (freed by *_destroy)
+ *  - matrices are column-major (Julia layout): G[i,j] at i + j*N; batched arrays put the
+ *    chain / replica index slowest
+ *  - return value 0 = ok, negative = error; mcb_last_error() gives a thread-local message
+ *  - a handle is bound to one device and one stream and is not thread-safe; calls are
+ *    synchronous (they return after the stream has drained)
+ *  - there is no CPU fallback: without a CUDA device *_create fails with MCB_ERR_CUDA
+ */
+#ifndef MCB200_H
+#define MCB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCB_OK 0
+#define MCB_ERR_ARG (-1)
+#define MCB_ERR_CUDA (-2)
+#define MCB_ERR_STATE (-3)
+
+const char* mcb_last_error(void);
+/* "major.minor sm_100a" */
+const char* mcb_version(void);
+
+/* ------------------------------------------------------------------ DQMC ---- */
+
+typedef struct mcb_dqmc mcb_dqmc;
+
+/* Mirrors DQMCParameters (src/flavors/DQMC/DQMC.jl:52-125) + model constants
+ * (src/models/HubbardModel/HubbardModelAttractive.jl:27-40). */
+typedef struct {
+    int32_t n_sites;           /* N = length(lattice) */
+    int32_t n_slices;          /* M = beta / delta_tau ; must be a multiple of safe_mult (stack.jl:115) */
+    int32_t safe_mult;         /* DQMC.jl:79 */
+    int32_t n_chains;          /* independent Markov chains in this handle */
+    double delta_tau;          /* DQMC.jl:85 */
+    double U;                  /* |U| of the attractive model */
+    uint64_t seed;             /* Philox key word 0 */
+    uint32_t chain_offset;     /* global id of chain 0 (Philox key word 1 = chain_offset + c) */
+    int32_t device_id;
+    int32_t check_propagation; /* DQMCParameters.check_propagation_error (stack.jl:540-550) */
+    int32_t delay_k;           /* delayed-update rank (0 = library default) */
+} mcb_dqmc_params;
+
+typedef struct {
+    int64_t current_slice; /* mc.s.current_slice (stack.jl) */
+    int64_t direction;     /* mc.s.direction */
+    int64_t n_updates;     /* update() calls so far; sweep = n_updates / 2M */
+    int64_t n_measurements;
+} mcb_dqmc_state;
+
+/* per chain: DQMCAnalysis (DQMC.jl:36-47) */
+typedef struct {
+    int64_t prop_local;
+    int64_t acc_local;
+    double max_propagation_error;
+    int64_t n_negative; /* proposals with detratio < 0 (DQMC.jl:562-568); always 0 for this model */
+    int64_t n_nonfinite; /* updates after which G contained NaN/Inf */
+} mcb_dqmc_chain_stats;
+
+/* DQMC(model; kwargs...) constructor + initialize_stack (DQMC.jl:250-289, stack.jl:108-159) */
+int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out);
+int mcb_dqmc_destroy(mcb_dqmc* h);
+
+/* init_hopping_matrix_exp (stack.jl:167-181): the four N x N matrices
+ * exp(-dtau T/2), exp(+dtau T/2), exp(-dtau T/2)^2, exp(+dtau T/2)^2 computed by the host
+ * exactly as the reference does, shared by all chains. */
+int mcb_dqmc_set_hopping(mcb_dqmc* h, const double* eT_half_minus, const double* eT_half_plus,
+                         const double* eT_minus, const double* eT_plus);
+
+/* mc.conf (HubbardModel.jl:4): int8 +-1, layout [chain][slice][site] */
+int mcb_dqmc_set_conf(mcb_dqmc* h, const int8_t* conf);
+int mcb_dqmc_get_conf(mcb_dqmc* h, int8_t* conf);
+
+/* run!'s prologue: build_stack(mc, mc.s); propagate(mc)  (DQMC.jl:412-414, stack.jl:242-255).
+ * Resets the update counter's slice position to (M, -1); G = G_M afterwards. */
+int mcb_dqmc_build_stack(mcb_dqmc* h);
+
+/* n x update(mc, i) = propagate + sweep_spatial  (DQMC.jl:523-582, stack.jl:502-631).
+ * If measure_every > 0 the built-in observables are accumulated after every update that ends at
+ * current_slice == 1 && direction == +1 and whose sweep index is a multiple of measure_every
+ * (DQMC.jl:429-436). */
+int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every);
+/* n_sweeps * 2M updates (the body of run!'s sweep loop, DQMC.jl:420-438) */
+int mcb_dqmc_sweep(mcb_dqmc* h, int64_t n_sweeps, int32_t measure_every);
+
+/* mc.s.greens (physical == 0) or greens(mc) = e^{+dtau T/2} G e^{-dtau T/2} (DQMC.jl:711-730);
+ * layout [chain][col][row] */
+int mcb_dqmc_get_greens(mcb_dqmc* h, double* G, int32_t physical);
+/* calculate_greens(mc, slice) from scratch, stack untouched (stack.jl:422-480);
+ * overwrites the handle's current G like the reference does. */
+int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G);
+
+int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st);
+int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* per_chain);
+
+/* Observables (measurement kernels; src/flavors/DQMC/measurements/measurements.jl:31-44,
+ * src/models/HubbardModel/HubbardModelAttractive.jl:221-245).
+ * dir_of_pair: N*N int32, dir_of_pair[src + trg*N] = direction index of EachSitePairByDistance
+ * (lattice_iterators.jl:131-221), n_dirs directions; hop: N x N hopping matrix T (for E_kin). */
+int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* dir_of_pair, int32_t n_dirs,
+                                    const double* hop);
+/* accumulate the observables of the current G now (what apply!(groups) does, generic.jl:194-243) */
+int mcb_dqmc_measure(mcb_dqmc* h);
+int mcb_dqmc_reset_observables(mcb_dqmc* h);
+/* Length of one chain's scalar observable record, and the record itself: per chain the SUM over
+ * measurements of [occupation n = 2(1-G_ii) avg over sites, double occupancy, E_kin/N, E_int/N,
+ * cdc[0..n_dirs), swave_pairing[0..n_dirs)] followed by the count. */
+int32_t mcb_dqmc_observable_len(mcb_dqmc* h);
+int mcb_dqmc_get_observables(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t* count);
+/* per chain SUM over measurements of G_phys, [chain][col][row] */
+int mcb_dqmc_get_greens_sum(mcb_dqmc* h, double* Gsum);
+
+/* --------------------------------------------------- batched linear algebra ---- *
+ * Kernel-level entry points (the methods a custom matrix type overloads in the
+ * reference, cf. src/linalg/blockdiagonal.jl:156-428). Host buffers, [batch][col][row].   */
+
+/* vmul!: mode 0 C=A*B, 1 C=A*B', 2 C=A'*B  (src/linalg/general.jl:7-45) */
+int mcb_linalg_vmul(int32_t n, int32_t batch, const double* A, const double* B, double* C,
+                    int32_t mode, int32_t device_id);
+/* udt_AVX_pivot!(U, D, T, pivot, temp, Val(apply_pivot)) (src/linalg/UDT.jl:192-306);
+ * X is the input, T the output; pivot is 0-based int32 */
+int mcb_linalg_udt(int32_t n, int32_t batch, const double* X, double* U, double* D, double* T,
+                   int32_t* pivot, int32_t apply_pivot, int32_t device_id);
+/* rdivp!(A, T, O, pivot): A <- A[:,pivot] * triu(T)^-1 (src/linalg/general.jl:138-166) */
+int mcb_linalg_rdivp(int32_t n, int32_t batch, double* A, const double* T, const int32_t* pivot,
+                     int32_t device_id);
+/* calculate_greens_AVX!(Ul,Dl,Tl,Ur,Dr,Tr,G) (src/flavors/DQMC/stack.jl:337-393); inputs are NOT
+ * clobbered here */
+int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, const double* Dl,
+                                const double* Tl, const double* Ur, const double* Dr,
+                                const double* Tr, double* G, int32_t device_id);
+
+/* ----------------------------------------------------------------- Ising ---- */
+
+typedef struct mcb_ising mcb_ising;
+
+/* MC(IsingModel(L=L, dims=2); beta) (src/flavors/MC/MC.jl:50-80). L even. Checkerboard schedule
+ * and Philox stream as specified in SURVEY.md Appendix D. */
+int mcb_ising_create(int32_t L, double beta, int32_t n_replicas, uint64_t seed,
+                     uint32_t replica_offset, int32_t device_id, mcb_ising** out);
+int mcb_ising_destroy(mcb_ising* h);
+/* mc.conf (IsingModel.jl:3-5): int8 +-1, layout [replica][y][x] (site index x + y*L) */
+int mcb_ising_set_spins(mcb_ising* h, const int8_t* spins);
+int mcb_ising_get_spins(mcb_ising* h, int8_t* spins);
+/* n x sweep(mc) (MC.jl:316-332) */
+int mcb_ising_sweep(mcb_ising* h, int64_t n_sweeps);
+/* energy(mc, m, conf) (IsingModel.jl:177-185) and sum(conf) (Ising/measurements.jl:72-78) */
+int mcb_ising_measure(mcb_ising* h, int64_t* E, int64_t* Msum);
+/* sweeps done so far (Philox counter word 0) */
+int64_t mcb_ising_sweep_count(mcb_ising* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCB200_H */

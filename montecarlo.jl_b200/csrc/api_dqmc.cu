@@ -1,0 +1,269 @@
+// extern "C" entry points of the DQMC engine and of the batched linear algebra (include/mcb200.h).
+#include "dqmc_engine.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace mcb {
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+} // namespace mcb
+
+using namespace mcb;
+
+#define API_TRY(expr)                        \
+    do {                                     \
+        const int rc__ = (expr);             \
+        if (rc__ != 0) return rc__;          \
+    } while (0)
+#define REQUIRE(cond, msg)                   \
+    do {                                     \
+        if (!(cond)) { set_error(msg); return MCB_ERR_ARG; } \
+    } while (0)
+
+static int use_device(int dev)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        set_error("no CUDA device: libmcb200 has no CPU fallback");
+        return MCB_ERR_CUDA;
+    }
+    MCB_CUDA(cudaSetDevice(dev));
+    static bool inited[64] = {};
+    if (dev >= 0 && dev < 64 && !inited[dev]) {
+        API_TRY(init_udt_kernels());
+        API_TRY(init_sweep_kernels());
+        inited[dev] = true;
+    }
+    return 0;
+}
+
+extern "C" {
+
+const char* mcb_last_error(void) { return g_error.c_str(); }
+const char* mcb_version(void) { return "0.1 sm_100a"; }
+
+int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
+{
+    REQUIRE(p && out, "null argument");
+    REQUIRE(p->n_sites > 0 && p->n_slices > 0 && p->safe_mult > 0 && p->n_chains > 0, "non-positive size");
+    REQUIRE(p->n_slices % p->safe_mult == 0,
+            "n_slices must be a multiple of safe_mult (stack.jl:115)");
+    REQUIRE(p->U >= 0.0, "U must be positive (HubbardModelAttractive.jl:31)");
+    REQUIRE(p->n_chains <= 65535, "at most 65535 chains per handle");
+    API_TRY(use_device(p->device_id));
+    mcb_dqmc* h = new mcb_dqmc();
+    h->p = *p;
+    h->N = p->n_sites; h->M = p->n_slices; h->s = p->safe_mult; h->C = p->n_chains;
+    h->ne = h->M / h->s + 1;
+    h->nn = (size_t)h->N * h->N;
+    h->mat = h->nn * h->C;
+    h->vec = (size_t)h->N * h->C;
+    h->lambda = acosh(exp(0.5 * p->U * p->delta_tau)); // HubbardModelAttractive.jl:103
+    h->eVp[0] = exp(1.0 * h->lambda * 1.0);  h->eVp[1] = exp(1.0 * h->lambda * -1.0);
+    h->eVm[0] = exp(-1.0 * h->lambda * 1.0); h->eVm[1] = exp(-1.0 * h->lambda * -1.0);
+    if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error("cudaStreamCreate failed");
+        delete h;
+        return MCB_ERR_CUDA;
+    }
+    const int rc = engine_alloc(h);
+    if (rc != 0) { engine_free(h); cudaStreamDestroy(h->st); delete h; return rc; }
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    *out = h;
+    return MCB_OK;
+}
+
+int mcb_dqmc_destroy(mcb_dqmc* h)
+{
+    if (!h) return MCB_OK;
+    cudaSetDevice(h->p.device_id);
+    cudaStreamSynchronize(h->st);
+    engine_free(h);
+    cudaStreamDestroy(h->st);
+    delete h;
+    return MCB_OK;
+}
+
+int mcb_dqmc_set_hopping(mcb_dqmc* h, const double* eT_half_minus, const double* eT_half_plus,
+                         const double* eT_minus, const double* eT_plus)
+{
+    REQUIRE(h && eT_half_minus && eT_half_plus && eT_minus && eT_plus, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    const double* src[4] = {eT_half_minus, eT_half_plus, eT_minus, eT_plus};
+    for (int i = 0; i < 4; ++i)
+        MCB_CUDA(cudaMemcpyAsync(h->hop[i], src[i], h->nn * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->hopping_set = true;
+    return MCB_OK;
+}
+
+int mcb_dqmc_set_conf(mcb_dqmc* h, const int8_t* conf)
+{
+    REQUIRE(h && conf, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(h->conf, conf, (size_t)h->C * h->M * h->N, cudaMemcpyHostToDevice, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->conf_set = true;
+    h->stack_built = false;
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_conf(mcb_dqmc* h, int8_t* conf)
+{
+    REQUIRE(h && conf, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(conf, h->conf, (size_t)h->C * h->M * h->N, cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_build_stack(mcb_dqmc* h)
+{
+    REQUIRE(h, "null handle");
+    if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    API_TRY(engine_build_stack(h));
+    API_TRY(engine_propagate(h));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->stack_built = true;
+    return MCB_OK;
+}
+
+int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every)
+{
+    REQUIRE(h && n_updates >= 0, "bad argument");
+    if (!h->stack_built) { set_error("build_stack first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    for (int64_t u = 0; u < n_updates; ++u) {
+        API_TRY(engine_update(h));
+        if (measure_every > 0 && h->current_slice == 1 && h->direction == 1) {
+            const int64_t sweep = (h->n_updates - 1) / (2 * (int64_t)h->M) + 1; // 1-based like DQMC.jl:420
+            if (sweep % measure_every == 0) API_TRY(engine_measure(h));
+        }
+    }
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_sweep(mcb_dqmc* h, int64_t n_sweeps, int32_t measure_every)
+{
+    REQUIRE(h && n_sweeps >= 0, "bad argument");
+    return mcb_dqmc_update(h, n_sweeps * 2 * (int64_t)h->M, measure_every);
+}
+
+int mcb_dqmc_get_greens(mcb_dqmc* h, double* G, int32_t physical)
+{
+    REQUIRE(h && G, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    const double* src = h->G;
+    if (physical) { API_TRY(engine_physical_greens(h, h->W[1])); src = h->W[1]; }
+    MCB_CUDA(cudaMemcpyAsync(G, src, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G)
+{
+    REQUIRE(h && G && slice >= 0 && slice <= h->M, "bad argument");
+    if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    API_TRY(engine_calculate_greens_at(h, slice));
+    MCB_CUDA(cudaMemcpyAsync(G, h->G, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st)
+{
+    REQUIRE(h && st, "null argument");
+    st->current_slice = h->current_slice;
+    st->direction = h->direction;
+    st->n_updates = h->n_updates;
+    st->n_measurements = h->n_meas;
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* out)
+{
+    REQUIRE(h && out, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    std::vector<long long> acc(h->C), prop(h->C), nf(h->C);
+    std::vector<double> pe(h->C);
+    MCB_CUDA(cudaMemcpyAsync(acc.data(), h->acc, h->C * sizeof(long long), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaMemcpyAsync(prop.data(), h->prop, h->C * sizeof(long long), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaMemcpyAsync(nf.data(), h->nonfinite, h->C * sizeof(long long), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaMemcpyAsync(pe.data(), h->prop_err, h->C * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    for (int c = 0; c < h->C; ++c) {
+        out[c].prop_local = prop[c];
+        out[c].acc_local = acc[c];
+        out[c].max_propagation_error = pe[c];
+        out[c].n_negative = 0;
+        out[c].n_nonfinite = nf[c];
+    }
+    return MCB_OK;
+}
+
+int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* dir_of_pair, int32_t n_dirs, const double* hop)
+{
+    REQUIRE(h && dir_of_pair && hop && n_dirs > 0, "bad argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    for (size_t e = 0; e < h->nn; ++e) REQUIRE(dir_of_pair[e] >= 0 && dir_of_pair[e] < n_dirs, "direction out of range");
+    cudaFree(h->dir_of_pair); cudaFree(h->hopT); cudaFree(h->obs); cudaFree(h->Gsum);
+    h->dir_of_pair = nullptr; h->hopT = nullptr; h->obs = nullptr; h->Gsum = nullptr;
+    h->n_dirs = n_dirs;
+    MCB_CUDA(cudaMalloc(&h->dir_of_pair, h->nn * sizeof(int32_t)));
+    MCB_CUDA(cudaMalloc(&h->hopT, h->nn * sizeof(double)));
+    MCB_CUDA(cudaMalloc(&h->obs, (size_t)h->C * h->obs_len() * sizeof(double)));
+    MCB_CUDA(cudaMalloc(&h->Gsum, h->mat * sizeof(double)));
+    MCB_CUDA(cudaMemcpyAsync(h->dir_of_pair, dir_of_pair, h->nn * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    MCB_CUDA(cudaMemcpyAsync(h->hopT, hop, h->nn * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return mcb_dqmc_reset_observables(h);
+}
+
+int mcb_dqmc_reset_observables(mcb_dqmc* h)
+{
+    REQUIRE(h, "null handle");
+    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemsetAsync(h->obs, 0, (size_t)h->C * h->obs_len() * sizeof(double), h->st));
+    MCB_CUDA(cudaMemsetAsync(h->Gsum, 0, h->mat * sizeof(double), h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->n_meas = 0;
+    return MCB_OK;
+}
+
+int mcb_dqmc_measure(mcb_dqmc* h)
+{
+    REQUIRE(h, "null handle");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    API_TRY(engine_measure(h));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int32_t mcb_dqmc_observable_len(mcb_dqmc* h) { return h ? h->obs_len() : 0; }
+
+int mcb_dqmc_get_observables(mcb_dqmc* h, double* sums, int64_t* count)
+{
+    REQUIRE(h && sums && count, "null argument");
+    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(sums, h->obs, (size_t)h->C * h->obs_len() * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    *count = h->n_meas;
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_greens_sum(mcb_dqmc* h, double* Gsum)
+{
+    REQUIRE(h && Gsum, "null argument");
+    if (!h->Gsum) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(Gsum, h->Gsum, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+} // extern "C"

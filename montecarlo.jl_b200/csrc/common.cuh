@@ -1,0 +1,103 @@
+// Shared device/host helpers of libmcb200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+namespace mcb {
+
+void set_error(const std::string& msg);
+
+#define MCB_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t err__ = (call);                                                             \
+        if (err__ != cudaSuccess) {                                                             \
+            char buf__[512];                                                                    \
+            snprintf(buf__, sizeof(buf__), "%s:%d: %s -> %s", __FILE__, __LINE__, #call,        \
+                     cudaGetErrorString(err__));                                                \
+            mcb::set_error(buf__);                                                              \
+            return -2;                                                                          \
+        }                                                                                       \
+    } while (0)
+
+// A diagonal scaling applied inside a kernel. Either a double vector (optionally inverted), or
+// the Hubbard-Stratonovich field of one time slice: value(i) = conf[i] > 0 ? ep : em, i.e.
+// exp(+-lambda * s_i) of interaction_matrix_exp! (HubbardModelAttractive.jl:100-110) as a
+// sign-select between two host-computed constants.
+struct Scale {
+    const double* d = nullptr;  // [batch][n] (stride_d per chain) or null
+    const int8_t* s = nullptr;  // conf row of the slice: [batch] stride_s, or null
+    long long stride_d = 0;
+    long long stride_s = 0;
+    double ep = 1.0, em = 1.0;
+    int inv = 0;
+
+    __host__ __device__ bool active() const { return d != nullptr || s != nullptr; }
+    __device__ __forceinline__ double at(int chain, int i) const
+    {
+        if (d) {
+            const double v = d[(long long)chain * stride_d + i];
+            return inv ? 1.0 / v : v;
+        }
+        if (s) return s[(long long)chain * stride_s + i] > 0 ? ep : em;
+        return 1.0;
+    }
+};
+
+// ---------------------------------------------------------------- Philox4x32-10
+// Stream specification: SURVEY.md §8(d) / Appendix D.
+__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2,
+                                                       uint32_t c3, uint32_t k0, uint32_t k1,
+                                                       uint32_t out[4])
+{
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+#ifdef __CUDA_ARCH__
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+#else
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
+        const uint32_t hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+#endif
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__host__ __device__ __forceinline__ uint32_t seed_key0(uint64_t seed)
+{
+    return (uint32_t)seed ^ (uint32_t)(seed >> 32);
+}
+
+// acceptance uniform of (sweep, visit, site) for chain key k1: 53-bit, [0,1)
+__device__ __forceinline__ double dqmc_uniform(uint32_t k0, uint32_t k1, uint32_t sweep,
+                                               uint32_t visit, uint32_t site)
+{
+    uint32_t o[4];
+    philox4x32_10(sweep, visit, site, 0u, k0, k1, o);
+    const uint64_t x = ((uint64_t)o[1] << 32) | o[0];
+    return (double)(x >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// ---------------------------------------------------------------- FP64 tensor core
+// mma.sync m8n8k4 f64 (SASS: DMMA.8x8x4). Fragment ownership for lane l:
+//   a = A[l/4][l%4]   b = B[l%4][l/4]   c0,c1 = C[l/4][2*(l%4) + {0,1}]
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+} // namespace mcb

@@ -1,0 +1,90 @@
+// sweep_spatial (src/flavors/DQMC/DQMC.jl:546-582) with propose_local / accept_local!
+// (src/models/HubbardModel/HubbardModelAttractive.jl:113-155), one CTA per chain.
+// G is held in shared memory for the whole site loop when it fits (N <= ~165 on B200),
+// otherwise the rank-1 updates run on the L2-resident copy.
+#include "sweep.cuh"
+
+namespace mcb {
+
+namespace {
+
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+__global__ void sweep_kernel(SweepArgs a, int in_smem)
+{
+    extern __shared__ double sm[];
+    const int n = a.n, chain = blockIdx.x, tid = threadIdx.x;
+    const size_t nn = (size_t)n * n;
+    double* u = sm;
+    double* v = u + n;
+    double* unif = v + n;
+    int8_t* sconf = (int8_t*)(unif + n);
+    double* Gs = unif + n + (n + 7) / 8;
+    double* Gg = a.G + (size_t)chain * a.sG;
+    double* G = in_smem ? Gs : Gg;
+    int8_t* cg = a.conf + (size_t)chain * a.sConf;
+
+    if (in_smem)
+        for (size_t e = tid; e < nn; e += blockDim.x) G[e] = Gg[e];
+    for (int i = tid; i < n; i += blockDim.x) {
+        sconf[i] = cg[i];
+        unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
+    }
+    __syncthreads();
+
+    int nacc = 0;
+    for (int i = 0; i < n; ++i) {
+        const double gii = G[i + (size_t)i * n];
+        const int s = sconf[i];
+        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+        const double efac = s > 0 ? a.efac_p : a.efac_m;
+        const double r = 1.0 + gamma * (1.0 - gii);
+        const double p = efac * (r * r);
+        if (p > 1.0 || unif[i] < p) { // uniform over the CTA: every thread sees the same G_ii
+            for (int k = tid; k < n; k += blockDim.x) {
+                double uk = -G[k + (size_t)i * n];
+                if (k == i) uk += 1.0;
+                u[k] = uk;
+                v[k] = G[i + (size_t)k * n];
+            }
+            __syncthreads();
+            const double x = gamma / (1.0 + gamma * u[i]);
+            for (size_t e = tid; e < nn; e += blockDim.x) {
+                const int k = (int)(e % n), l = (int)(e / n);
+                G[e] -= u[k] * (x * v[l]);
+            }
+            if (tid == 0) sconf[i] = (int8_t)-s;
+            ++nacc;
+            __syncthreads();
+        }
+    }
+    bool bad = false;
+    if (in_smem) {
+        for (size_t e = tid; e < nn; e += blockDim.x) { const double g = G[e]; Gg[e] = g; bad |= !isfinite(g); }
+    }
+    for (int i = tid; i < n; i += blockDim.x) cg[i] = sconf[i];
+    if (__syncthreads_or(bad) && tid == 0) a.nonfinite[chain] += 1;
+    if (tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
+}
+
+} // namespace
+
+int init_sweep_kernels()
+{
+    MCB_CUDA(cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    return 0;
+}
+
+int launch_sweep_spatial(const SweepArgs& a, cudaStream_t st)
+{
+    const int n = a.n;
+    const size_t hdr = (size_t)(3 * n + (n + 7) / 8) * sizeof(double);
+    const size_t mat = (size_t)n * n * sizeof(double);
+    const int in_smem = hdr + mat <= (size_t)SMEM_LIMIT;
+    const int threads = n <= 32 ? 128 : (n <= 96 ? 256 : (n <= 200 ? 512 : 1024));
+    sweep_kernel<<<a.batch, threads, in_smem ? hdr + mat : hdr, st>>>(a, in_smem);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace mcb

@@ -1,0 +1,20 @@
+// Batched UDT (column-pivoted Householder QR) and pivoted right triangular solve.
+#pragma once
+#include "common.cuh"
+
+namespace mcb {
+
+// udt_AVX_pivot! (src/linalg/UDT.jl:192-306): per chain, X -> U (explicit Q), D = |diag R|,
+// T = D^-1 R P' (apply_pivot) or the "dirty" D^-1 R (upper triangle valid) + pivot.
+// X is clobbered (workspace). pivot is 0-based int32.
+int launch_udt(int n, int batch, double* X, long long sX, double* U, long long sU, double* D,
+               long long sD, double* T, long long sT, int* pivot, long long sP, int apply_pivot,
+               cudaStream_t st);
+
+// rdivp! (src/linalg/general.jl:138-166): out = in[:, pivot] * triu(T)^-1  (out != in)
+int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out, long long sOut,
+                 const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st);
+
+int init_udt_kernels();
+
+} // namespace mcb

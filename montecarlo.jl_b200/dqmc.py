@@ -1,0 +1,194 @@
+"""DQMC flavor (host side): mirrors `DQMC(model; kwargs...)`, `run!`, `greens`, `replay!`-style
+from-scratch G and the measurement accessors of src/flavors/DQMC/DQMC.jl, for a *batch* of
+independent Markov chains that live on one B200. All numerics happen in libmcb200.so.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+from .models import HubbardModelAttractive
+
+
+class DQMCParameters:
+    """DQMCParameters (DQMC.jl:52-125): beta / delta_tau / slices consistency rules included."""
+
+    def __init__(self, thermalization=100, sweeps=100, safe_mult=10, measure_rate=10,
+                 check_propagation_error=True, check_sign_problem=True, silent=True, **kw):
+        keys = set(kw)
+        if keys == {"beta"}:
+            kw["delta_tau"] = 0.1
+            keys = set(kw)
+        if keys == {"delta_tau", "beta", "slices"}:
+            delta_tau, beta = kw["delta_tau"], kw["beta"]
+            slices = int(round(beta / delta_tau))
+            if slices != kw["slices"]:
+                raise ValueError(f"Given slices ({kw['slices']}) does not match calculated slices "
+                                 f"beta/delta_tau ~ {slices}")
+        elif keys == {"beta", "slices"}:
+            beta, slices = kw["beta"], int(kw["slices"])
+            delta_tau = beta / slices
+        elif keys == {"delta_tau", "slices"}:
+            delta_tau, slices = kw["delta_tau"], int(kw["slices"])
+            beta = delta_tau * slices
+        elif keys == {"delta_tau", "beta"}:
+            delta_tau, beta = kw["delta_tau"], kw["beta"]
+            slices = int(round(beta / delta_tau))
+        else:
+            raise ValueError(f"Invalid keyword arguments to DQMCParameters {sorted(keys)}")
+        self.thermalization, self.sweeps = int(thermalization), int(sweeps)
+        self.safe_mult, self.measure_rate = int(safe_mult), int(measure_rate)
+        self.check_propagation_error = bool(check_propagation_error)
+        self.check_sign_problem, self.silent = bool(check_sign_problem), bool(silent)
+        self.delta_tau, self.beta, self.slices = float(delta_tau), float(beta), slices
+
+
+class DQMC:
+    """`DQMC(model; beta, ...)` for a batch of `n_chains` chains (global ids chain_offset + c).
+
+    conf has shape (n_chains, N, M): conf[c] is the reference's HubbardConf (HubbardModel.jl:4).
+    """
+
+    def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, **kwargs):
+        if not isinstance(model, HubbardModelAttractive):
+            raise TypeError("the B200 engine implements DQMC{HubbardModelAttractive, CheckerboardFalse}")
+        self.model = model
+        self.p = DQMCParameters(**kwargs)
+        self.n_chains, self.seed, self.chain_offset, self.device = int(n_chains), int(seed), int(chain_offset), int(device)
+        self.N, self.M = len(model.l), self.p.slices
+        if self.M % self.p.safe_mult != 0:
+            raise ValueError("slices must be a multiple of safe_mult (stack.jl:115)")
+        self.L = _lib.lib()
+        prm = _lib.DqmcParams(self.N, self.M, self.p.safe_mult, self.n_chains, self.p.delta_tau, model.U,
+                              self.seed, self.chain_offset, self.device,
+                              int(self.p.check_propagation_error), 0)
+        self.h = C.c_void_p()
+        _lib.check(self.L.mcb_dqmc_create(C.byref(prm), C.byref(self.h)))
+        self.hop = model.hopping_exponentials(self.p.delta_tau)
+        _lib.check(self.L.mcb_dqmc_set_hopping(self.h, *[self._fm(a) for a in self.hop]))
+        if conf is None:
+            conf = np.stack([model.rand_conf(self.M, self.seed, self.chain_offset + c)
+                             for c in range(self.n_chains)])
+        self.set_conf(conf)
+        self.last_sweep = 0
+        self._tables = False
+
+    # -- layout helpers: numpy [i, j] (row-major view of Julia semantics) <-> column-major buffers
+    @staticmethod
+    def _fm(a):
+        return np.ascontiguousarray(np.asarray(a, dtype=np.float64).T).reshape(-1)
+
+    def _unbatch(self, buf):
+        return buf.reshape(self.n_chains, self.N, self.N).transpose(0, 2, 1).copy()
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.L.mcb_dqmc_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_conf(self, conf):
+        conf = np.asarray(conf, dtype=np.int8)
+        if conf.shape != (self.n_chains, self.N, self.M):
+            raise ValueError(f"conf must have shape {(self.n_chains, self.N, self.M)}")
+        buf = np.ascontiguousarray(conf.transpose(0, 2, 1)).reshape(-1)
+        _lib.check(self.L.mcb_dqmc_set_conf(self.h, buf))
+
+    def conf(self):
+        buf = np.empty(self.n_chains * self.N * self.M, dtype=np.int8)
+        _lib.check(self.L.mcb_dqmc_get_conf(self.h, buf))
+        return buf.reshape(self.n_chains, self.M, self.N).transpose(0, 2, 1).copy()
+
+    def build_stack(self):
+        """init! + build_stack + propagate (DQMC.jl:412-414)."""
+        _lib.check(self.L.mcb_dqmc_build_stack(self.h))
+
+    def update(self, n=1, measure_every=0):
+        _lib.check(self.L.mcb_dqmc_update(self.h, n, measure_every))
+
+    def sweep(self, n=1, measure_every=0):
+        _lib.check(self.L.mcb_dqmc_sweep(self.h, n, measure_every))
+
+    def greens(self, physical=True):
+        """greens(mc) (DQMC.jl:711-730); physical=False returns mc.s.greens. Shape (C, N, N)."""
+        buf = np.empty(self.n_chains * self.N * self.N)
+        _lib.check(self.L.mcb_dqmc_get_greens(self.h, buf, int(physical)))
+        return self._unbatch(buf)
+
+    def greens_at(self, slice_):
+        """calculate_greens(mc, slice) (stack.jl:422-480). Shape (C, N, N)."""
+        buf = np.empty(self.n_chains * self.N * self.N)
+        _lib.check(self.L.mcb_dqmc_calculate_greens_at(self.h, slice_, buf))
+        return self._unbatch(buf)
+
+    def state(self):
+        st = _lib.DqmcState()
+        _lib.check(self.L.mcb_dqmc_get_state(self.h, C.byref(st)))
+        return dict(current_slice=st.current_slice, direction=st.direction, n_updates=st.n_updates,
+                    n_measurements=st.n_measurements)
+
+    def stats(self):
+        arr = (_lib.DqmcChainStats * self.n_chains)()
+        _lib.check(self.L.mcb_dqmc_get_stats(self.h, arr))
+        return dict(prop_local=np.array([a.prop_local for a in arr]),
+                    acc_local=np.array([a.acc_local for a in arr]),
+                    max_propagation_error=np.array([a.max_propagation_error for a in arr]),
+                    n_nonfinite=np.array([a.n_nonfinite for a in arr]))
+
+    # -- measurements ---------------------------------------------------------------------
+    def enable_measurements(self):
+        if not self._tables:
+            dir_of, dirs = self.model.l.pair_direction_table()
+            self.directions = dirs
+            self.n_dirs = len(dirs)
+            # dir_of[src, trg] -> buffer index src + trg*N
+            tab = np.ascontiguousarray(dir_of.T.astype(np.int32)).reshape(-1)
+            _lib.check(self.L.mcb_dqmc_set_measurement_tables(self.h, tab, self.n_dirs,
+                                                              self._fm(self.model.hopping_matrix())))
+            self._tables = True
+
+    def measure(self):
+        _lib.check(self.L.mcb_dqmc_measure(self.h))
+
+    def observables(self):
+        """Per-chain means over measurements. Returns dict of arrays with leading chain axis."""
+        n = self.L.mcb_dqmc_observable_len(self.h)
+        buf = np.empty(self.n_chains * n)
+        cnt = C.c_int64()
+        _lib.check(self.L.mcb_dqmc_get_observables(self.h, buf, C.byref(cnt)))
+        gs = np.empty(self.n_chains * self.N * self.N)
+        _lib.check(self.L.mcb_dqmc_get_greens_sum(self.h, gs))
+        k = max(cnt.value, 1)
+        rec = buf.reshape(self.n_chains, n) / k
+        nd = self.n_dirs
+        return dict(count=cnt.value, occupation=rec[:, 0], double_occupancy=rec[:, 1],
+                    e_kin=rec[:, 2], e_int=rec[:, 3], energy=rec[:, 2] + rec[:, 3],
+                    cdc=rec[:, 4:4 + nd], swave_pairing=rec[:, 4 + nd:4 + 2 * nd],
+                    G=self._unbatch(gs) / k)
+
+    def run(self, thermalization=None, sweeps=None):
+        """run!(mc) (DQMC.jl:369-515): thermalise, then sweep with measurements every measure_rate."""
+        th = self.p.thermalization if thermalization is None else thermalization
+        sw = self.p.sweeps if sweeps is None else sweeps
+        self.enable_measurements()
+        self.build_stack()
+        if th:
+            self.sweep(th, 0)
+        if sw:
+            self.sweep(sw, self.p.measure_rate)
+        self.last_sweep += th + sw
+        return self.observables()
+
+
+def mean_and_error(per_chain):
+    """Mean over chains and its standard error (chains are independent Markov chains)."""
+    a = np.asarray(per_chain, dtype=np.float64)
+    m = a.mean(axis=0)
+    e = a.std(axis=0, ddof=1) / math.sqrt(a.shape[0]) if a.shape[0] > 1 else np.zeros_like(m)
+    return m, e

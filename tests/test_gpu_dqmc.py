@@ -1,0 +1,229 @@
+"""GPU parity tests of the DQMC path: libmcb200 (through the C ABI) against the CPU oracle.
+
+P1 kernel level  : vmul / udt / rdivp / calculate_greens on random inputs
+                   (test/slice_matrices.jl:141-235 restated on the batched entry points)
+P2 state level   : same (hopping, conf, Philox stream) -> after every update() of a sweep
+                   max|G_gpu - G_oracle| / max|G_oracle| <= 1e-10 and identical HS fields
+                   (tolerance from BASELINE.json north_star)
+"""
+import numpy as np
+import pytest
+
+import montecarlo_jl_b200 as mcb
+from montecarlo_jl_b200 import _lib
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL_G = 1e-10  # north_star: per-slice Green's functions within 1e-10 relative max-norm
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+def _cm(a):  # batch of numpy matrices -> [batch][col][row] buffer
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64).transpose(0, 2, 1)).reshape(-1)
+
+
+def _uncm(buf, b, n):
+    return buf.reshape(b, n, n).transpose(0, 2, 1).copy()
+
+
+@pytest.mark.parametrize("n", [4, 16, 37, 64, 144])
+def test_vmul_modes(n):
+    rng = np.random.default_rng(n)
+    b = 3
+    A, B = rng.standard_normal((b, n, n)), rng.standard_normal((b, n, n))
+    L = _lib.lib()
+    for mode, want in ((0, A @ B), (1, A @ B.transpose(0, 2, 1)), (2, A.transpose(0, 2, 1) @ B)):
+        out = np.empty(b * n * n)
+        _lib.check(L.mcb_linalg_vmul(n, b, _cm(A), _cm(B), out, mode, 0))
+        assert relerr(_uncm(out, b, n), want) < 1e-13
+        for k in range(b):
+            assert relerr(_uncm(out, b, n)[k], orc.vmul(A[k], B[k], mode)) < 1e-13
+
+
+@pytest.mark.parametrize("n", [4, 16, 64, 100, 144, 200])
+@pytest.mark.parametrize("apply_pivot", [1, 0])
+def test_udt_contract(n, apply_pivot):
+    rng = np.random.default_rng(100 + n)
+    b = 2
+    X = rng.standard_normal((b, n, n))
+    X[1] = X[1] @ np.diag(np.logspace(0, -12, n))  # graded columns, like a long B-chain
+    L = _lib.lib()
+    U, T = np.empty(b * n * n), np.empty(b * n * n)
+    D, piv = np.empty(b * n), np.empty(b * n, dtype=np.int32)
+    _lib.check(L.mcb_linalg_udt(n, b, _cm(X), U, D, T, piv, apply_pivot, 0))
+    U, T = _uncm(U, b, n), _uncm(T, b, n)
+    D, piv = D.reshape(b, n), piv.reshape(b, n)
+    for k in range(b):
+        assert np.abs(U[k] @ U[k].T - np.eye(n)).max() < 1e-12
+        scale = np.abs(X[k]).max()
+        if apply_pivot:
+            assert np.abs(U[k] @ np.diag(D[k]) @ T[k] - X[k]).max() < 1e-12 * scale * n
+        else:
+            P = np.zeros((n, n))
+            P[np.arange(n), piv[k]] = 1.0
+            assert np.abs(U[k] @ np.diag(D[k]) @ np.triu(T[k]) @ P - X[k]).max() < 1e-12 * scale * n
+        Uo, Do, To, po = orc.udt_pivot(X[k], bool(apply_pivot))
+        assert np.allclose(D[k], Do, rtol=1e-9)
+        if np.array_equal(po, piv[k]):
+            assert np.abs(U[k] - Uo).max() < 1e-9
+
+
+@pytest.mark.parametrize("n", [4, 16, 64, 144])
+def test_rdivp(n):
+    rng = np.random.default_rng(7 + n)
+    b = 2
+    X = rng.standard_normal((b, n, n))
+    A = rng.standard_normal((b, n, n))
+    L = _lib.lib()
+    out = _cm(A).copy()
+    Ts, Ps = [], []
+    for k in range(b):
+        _, _, T, p = orc.udt_pivot(X[k], False)
+        Ts.append(T)
+        Ps.append(p)
+    _lib.check(L.mcb_linalg_rdivp(n, b, out, _cm(np.array(Ts)), np.array(Ps, dtype=np.int32).reshape(-1), 0))
+    got = _uncm(out, b, n)
+    for k in range(b):
+        assert relerr(got[k], orc.rdivp(A[k], Ts[k], Ps[k])) < 1e-10
+
+
+@pytest.mark.parametrize("n", [16, 64])
+def test_calculate_greens_from_udts(n):
+    rng = np.random.default_rng(n)
+    b = 2
+    trip = []
+    for side in range(2):
+        Us, Ds, Ts = [], [], []
+        for k in range(b):
+            X = rng.standard_normal((n, n)) @ np.diag(np.logspace(2, -6, n))
+            U, D, T, _ = orc.udt_pivot(X, True)
+            Us.append(U); Ds.append(D); Ts.append(T)
+        trip.append((np.array(Us), np.array(Ds), np.array(Ts)))
+    (Ul, Dl, Tl), (Ur, Dr, Tr) = trip
+    L = _lib.lib()
+    G = np.empty(b * n * n)
+    _lib.check(L.mcb_linalg_calculate_greens(n, b, _cm(Ul), np.ascontiguousarray(Dl).reshape(-1), _cm(Tl),
+                                             _cm(Ur), np.ascontiguousarray(Dr).reshape(-1), _cm(Tr), G, 0))
+    G = _uncm(G, b, n)
+    for k in range(b):
+        want = orc.calculate_greens_udt(Ul[k], Dl[k], Tl[k], Ur[k], Dr[k], Tr[k])
+        assert relerr(G[k], want) < RTOL_G
+        direct = np.linalg.inv(np.eye(n) + Ul[k] @ np.diag(Dl[k]) @ Tl[k] @ Tr[k].T @ np.diag(Dr[k]) @ Ur[k].T)
+        assert relerr(G[k], direct) < 1e-8
+
+
+def _pair(L, U, beta, dtau, safe_mult, n_chains, seed=123, check=False, chain_offset=0):
+    model = mcb.HubbardModelAttractive(L=L, U=U)
+    mc = mcb.DQMC(model, n_chains=n_chains, seed=seed, chain_offset=chain_offset, beta=beta, delta_tau=dtau,
+                  safe_mult=safe_mult, check_propagation_error=check)
+    conf0 = mc.conf()
+    oracles = [orc.OracleDQMC(L * L, mc.M, safe_mult, dtau, U, mc.hop, conf0[c], seed=seed,
+                              chain=chain_offset + c, check_propagation=check) for c in range(n_chains)]
+    return mc, oracles
+
+
+@pytest.mark.parametrize("L,U,beta,safe_mult,chains", [(2, 1.0, 1.0, 5, 2), (4, 1.0, 1.0, 5, 3), (4, 4.0, 2.0, 10, 2)])
+def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains):
+    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, chains, check=True)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    G = mc.greens(physical=False)
+    for c, o in enumerate(oracles):
+        assert relerr(G[c], o.greens()) < RTOL_G
+    for u in range(2 * mc.M + 3):
+        mc.update(1)
+        G = mc.greens(physical=False)
+        st = mc.state()
+        conf = mc.conf()
+        for c, o in enumerate(oracles):
+            o.update(1)
+            so = o.state()
+            assert (st["current_slice"], st["direction"]) == (so["current_slice"], so["direction"])
+            assert relerr(G[c], o.greens()) < RTOL_G, (u, c)
+            assert np.array_equal(conf[c], o.conf()), (u, c)
+    stats = mc.stats()
+    for c, o in enumerate(oracles):
+        so = o.state()
+        assert stats["acc_local"][c] == so["acc_local"] and stats["prop_local"][c] == so["prop_local"]
+        assert stats["max_propagation_error"][c] < 1e-7
+    Gp = mc.greens(physical=True)
+    for c, o in enumerate(oracles):
+        assert relerr(Gp[c], o.greens(physical=True)) < RTOL_G
+    mc.close()
+
+
+def test_config_a_8x8_beta8_full_sweep_matches_oracle():
+    """BASELINE.json configs[0]/[1] physics: 8x8, U=1, beta=8, dtau=0.1, safe_mult=10."""
+    mc, oracles = _pair(8, 1.0, 8.0, 0.1, 10, 2)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    checkpoints = [1, 9, 10, 11, 79, 80, 81, 120, 159, 160]
+    done = 0
+    for cp in checkpoints:
+        mc.update(cp - done)
+        G = mc.greens(physical=False)
+        conf = mc.conf()
+        for c, o in enumerate(oracles):
+            o.update(cp - done)
+            assert relerr(G[c], o.greens()) < RTOL_G, (cp, c)
+            assert np.array_equal(conf[c], o.conf()), (cp, c)
+        done = cp
+    mc.close()
+
+
+def test_config_c_12x12_u4_beta10_partial_sweep_matches_oracle():
+    """BASELINE.json configs[2] physics (N=144): first 25 updates incl. two stabilisations."""
+    mc, oracles = _pair(12, 4.0, 10.0, 0.1, 10, 2)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    done = 0
+    for cp in (1, 10, 11, 25):
+        mc.update(cp - done)
+        G = mc.greens(physical=False)
+        conf = mc.conf()
+        for c, o in enumerate(oracles):
+            o.update(cp - done)
+            assert relerr(G[c], o.greens()) < RTOL_G, (cp, c)
+            assert np.array_equal(conf[c], o.conf()), (cp, c)
+        done = cp
+    mc.close()
+
+
+def test_greens_from_scratch_at_every_slice():
+    """test/flavortests_DQMC.jl:60-69: calculate_greens(mc, k) for k in 0:M against the oracle."""
+    mc, oracles = _pair(4, 1.0, 2.0, 0.1, 5, 2)
+    for k in range(0, mc.M + 1):
+        G = mc.greens_at(k)
+        for c, o in enumerate(oracles):
+            assert relerr(G[c], o.greens_at(k)) < RTOL_G, k
+    mc.close()
+
+
+def test_chain_ids_are_global():
+    """Chains keyed by global id: a handle with chain_offset=2 reproduces chains 2,3 of a 4-chain handle."""
+    full, _ = _pair(4, 1.0, 1.0, 0.1, 5, 4)
+    part, _ = _pair(4, 1.0, 1.0, 0.1, 5, 2, chain_offset=2)
+    assert np.array_equal(full.conf()[2:], part.conf())
+    for mc in (full, part):
+        mc.build_stack()
+        mc.sweep(1)
+    assert np.array_equal(full.conf()[2:], part.conf())
+    assert np.array_equal(full.greens()[2:], part.greens())
+    full.close(); part.close()
+
+
+def test_errors_are_reported():
+    L = _lib.lib()
+    model = mcb.HubbardModelAttractive(L=4)
+    with pytest.raises(ValueError):
+        mcb.DQMC(model, beta=1.0, delta_tau=0.1, safe_mult=3)
+    mc = mcb.DQMC(model, beta=1.0, delta_tau=0.1, safe_mult=5)
+    with pytest.raises(mcb.McbError):
+        mc.update(1)  # build_stack first
+    mc.close()
