@@ -51,7 +51,8 @@ typedef struct {
     uint32_t chain_offset;     /* global id of chain 0 (Philox key word 1 = chain_offset + c) */
     int32_t device_id;
     int32_t check_propagation; /* DQMCParameters.check_propagation_error (stack.jl:540-550) */
-    int32_t delay_k;           /* delayed-update rank (0 = library default) */
+    int32_t general_path;      /* 0 = library default (chain-resident kernels where N allows);
+                                  1 = force the general any-N kernels (testing / comparison) */
 } mcb_dqmc_params;
 
 typedef struct {
@@ -123,6 +124,18 @@ int mcb_dqmc_get_observables(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t
 /* per chain SUM over measurements of G_phys, [chain][col][row] */
 int mcb_dqmc_get_greens_sum(mcb_dqmc* h, double* Gsum);
 
+/* Launch accounting and device timing (the role of the reference's @bm / TimerOutputs hooks,
+ * src/helpers.jl:160-236). Launch classes, in order: gemm, udt, rdivp, sweep_spatial, fused
+ * wrap+sweep, measure, misc, ising  (MCB_N_LAUNCH_CLASSES entries per output array).
+ * mcb_dqmc_profile: enable_timing != 0 brackets every launch with CUDA events on the handle's
+ * stream; reset != 0 clears all counters. get_profile: launches since reset, event-timed ms and
+ * number of timed launches, algorithmic FP64 flop per class. */
+#define MCB_N_LAUNCH_CLASSES 8
+int mcb_dqmc_profile(mcb_dqmc* h, int32_t enable_timing, int32_t reset);
+int mcb_dqmc_get_profile(mcb_dqmc* h, int64_t* launches, double* ms, int64_t* timed, double* flops);
+/* device time (CUDA events on the handle's stream) of the last mcb_dqmc_update / _sweep call */
+double mcb_dqmc_last_elapsed_ms(mcb_dqmc* h);
+
 /* --------------------------------------------------- batched linear algebra ---- *
  * Kernel-level entry points (the methods a custom matrix type overloads in the
  * reference, cf. src/linalg/blockdiagonal.jl:156-428). Host buffers, [batch][col][row].   */
@@ -161,6 +174,10 @@ int mcb_ising_sweep(mcb_ising* h, int64_t n_sweeps);
 int mcb_ising_measure(mcb_ising* h, int64_t* E, int64_t* Msum);
 /* sweeps done so far (Philox counter word 0) */
 int64_t mcb_ising_sweep_count(mcb_ising* h);
+/* device time (CUDA events on the handle's stream) of the last mcb_ising_sweep call, and the number
+ * of kernel launches since create */
+double mcb_ising_last_elapsed_ms(mcb_ising* h);
+int64_t mcb_ising_launch_count(mcb_ising* h);
 
 #ifdef __cplusplus
 }

@@ -10,6 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libmcb200.so")
 _LIB = None
+LAUNCH_CLASSES = ("gemm", "udt", "rdivp", "sweep_spatial", "fused", "measure", "misc", "ising")
 
 
 class McbError(RuntimeError):
@@ -20,7 +21,7 @@ class DqmcParams(C.Structure):
     _fields_ = [("n_sites", C.c_int32), ("n_slices", C.c_int32), ("safe_mult", C.c_int32),
                 ("n_chains", C.c_int32), ("delta_tau", C.c_double), ("U", C.c_double),
                 ("seed", C.c_uint64), ("chain_offset", C.c_uint32), ("device_id", C.c_int32),
-                ("check_propagation", C.c_int32), ("delay_k", C.c_int32)]
+                ("check_propagation", C.c_int32), ("general_path", C.c_int32)]
 
 
 class DqmcState(C.Structure):
@@ -61,6 +62,11 @@ SIGNATURES = {
     "mcb_dqmc_observable_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_get_observables": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_get_greens_sum": (C.c_int, [C.c_void_p, _f64]),
+    "mcb_dqmc_profile": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "mcb_dqmc_get_profile": (C.c_int, [C.c_void_p, _i64, _f64, _i64, _f64]),
+    "mcb_dqmc_last_elapsed_ms": (C.c_double, [C.c_void_p]),
+    "mcb_ising_last_elapsed_ms": (C.c_double, [C.c_void_p]),
+    "mcb_ising_launch_count": (C.c_int64, [C.c_void_p]),
     "mcb_linalg_vmul": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, C.c_int32, C.c_int32]),
     "mcb_linalg_udt": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, _f64, _i32, C.c_int32,
                                  C.c_int32]),

@@ -32,10 +32,18 @@ static int use_device(int dev)
     if (dev >= 0 && dev < 64 && !inited[dev]) {
         API_TRY(init_udt_kernels());
         API_TRY(init_sweep_kernels());
+        API_TRY(init_segment_kernels());
         inited[dev] = true;
     }
     return 0;
 }
+
+namespace {
+struct ProfBind {
+    explicit ProfBind(mcb_dqmc* h) { set_current_profiler(&h->prof); }
+    ~ProfBind() { set_current_profiler(nullptr); }
+};
+} // namespace
 
 extern "C" {
 
@@ -55,6 +63,7 @@ int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
     h->p = *p;
     h->N = p->n_sites; h->M = p->n_slices; h->s = p->safe_mult; h->C = p->n_chains;
     h->ne = h->M / h->s + 1;
+    h->use_panel = segment_supported(h->N) && p->general_path == 0;
     h->nn = (size_t)h->N * h->N;
     h->mat = h->nn * h->C;
     h->vec = (size_t)h->N * h->C;
@@ -63,6 +72,12 @@ int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
     h->eVm[0] = exp(-1.0 * h->lambda * 1.0); h->eVm[1] = exp(-1.0 * h->lambda * -1.0);
     if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("cudaStreamCreate failed");
+        delete h;
+        return MCB_ERR_CUDA;
+    }
+    if (cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+        set_error("cudaEventCreate failed");
+        cudaStreamDestroy(h->st);
         delete h;
         return MCB_ERR_CUDA;
     }
@@ -78,7 +93,10 @@ int mcb_dqmc_destroy(mcb_dqmc* h)
     if (!h) return MCB_OK;
     cudaSetDevice(h->p.device_id);
     cudaStreamSynchronize(h->st);
+    h->prof.collect();
     engine_free(h);
+    cudaEventDestroy(h->ev0);
+    cudaEventDestroy(h->ev1);
     cudaStreamDestroy(h->st);
     delete h;
     return MCB_OK;
@@ -122,8 +140,9 @@ int mcb_dqmc_build_stack(mcb_dqmc* h)
     REQUIRE(h, "null handle");
     if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
     API_TRY(engine_build_stack(h));
-    API_TRY(engine_propagate(h));
+    API_TRY(engine_propagate(h, false, nullptr));
     MCB_CUDA(cudaStreamSynchronize(h->st));
     h->stack_built = true;
     return MCB_OK;
@@ -134,14 +153,20 @@ int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every)
     REQUIRE(h && n_updates >= 0, "bad argument");
     if (!h->stack_built) { set_error("build_stack first"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
-    for (int64_t u = 0; u < n_updates; ++u) {
-        API_TRY(engine_update(h));
+    ProfBind bind(h);
+    MCB_CUDA(cudaEventRecord(h->ev0, h->st));
+    for (int64_t left = n_updates; left > 0;) {
+        int64_t done = 0;
+        API_TRY(engine_update_batch(h, left, measure_every > 0, &done));
+        left -= done;
         if (measure_every > 0 && h->current_slice == 1 && h->direction == 1) {
             const int64_t sweep = (h->n_updates - 1) / (2 * (int64_t)h->M) + 1; // 1-based like DQMC.jl:420
             if (sweep % measure_every == 0) API_TRY(engine_measure(h));
         }
     }
+    MCB_CUDA(cudaEventRecord(h->ev1, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
+    MCB_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
     return MCB_OK;
 }
 
@@ -156,6 +181,7 @@ int mcb_dqmc_get_greens(mcb_dqmc* h, double* G, int32_t physical)
     REQUIRE(h && G, "null argument");
     MCB_CUDA(cudaSetDevice(h->p.device_id));
     const double* src = h->G;
+    ProfBind bind(h);
     if (physical) { API_TRY(engine_physical_greens(h, h->W[1])); src = h->W[1]; }
     MCB_CUDA(cudaMemcpyAsync(G, src, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
@@ -167,6 +193,7 @@ int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G)
     REQUIRE(h && G && slice >= 0 && slice <= h->M, "bad argument");
     if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
     API_TRY(engine_calculate_greens_at(h, slice));
     MCB_CUDA(cudaMemcpyAsync(G, h->G, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
@@ -238,10 +265,38 @@ int mcb_dqmc_measure(mcb_dqmc* h)
 {
     REQUIRE(h, "null handle");
     MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
     API_TRY(engine_measure(h));
     MCB_CUDA(cudaStreamSynchronize(h->st));
     return MCB_OK;
 }
+
+int mcb_dqmc_profile(mcb_dqmc* h, int32_t enable_timing, int32_t reset)
+{
+    REQUIRE(h, "null handle");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    if (reset) h->prof.reset();
+    h->prof.timing = enable_timing != 0;
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_profile(mcb_dqmc* h, int64_t* launches, double* ms, int64_t* timed, double* flops)
+{
+    REQUIRE(h && launches && ms && timed && flops, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->prof.collect();
+    for (int i = 0; i < LC_COUNT; ++i) {
+        launches[i] = h->prof.launches[i];
+        ms[i] = h->prof.ms[i];
+        timed[i] = h->prof.timed[i];
+        flops[i] = h->prof.flops[i];
+    }
+    return MCB_OK;
+}
+
+double mcb_dqmc_last_elapsed_ms(mcb_dqmc* h) { return h ? (double)h->last_ms : -1.0; }
 
 int32_t mcb_dqmc_observable_len(mcb_dqmc* h) { return h ? h->obs_len() : 0; }
 

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include "prof.cuh"
 
 namespace mcb {
 

@@ -49,6 +49,7 @@ __global__ void max_abs_diff_kernel(const double* A, const double* B, double* ou
 
 int set_identity(mcb_dqmc* h, double* U, double* T, double* D)
 {
+    LaunchScope scope(LC_MISC, h->st, 0.0);
     set_identity_kernel<<<296, 256, 0, h->st>>>(U, T, D, h->N, h->mat);
     MCB_CUDA(cudaGetLastError());
     return 0;
@@ -205,6 +206,7 @@ int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
 
 int record_prop_err(mcb_dqmc* h)
 {
+    LaunchScope scope(LC_MISC, h->st, 0.0);
     max_abs_diff_kernel<<<h->C, 256, 0, h->st>>>(h->Gtmp, h->G, h->prop_err, h->nn);
     MCB_CUDA(cudaGetLastError());
     return 0;
@@ -275,8 +277,9 @@ int engine_build_stack(mcb_dqmc* h)
 
 // propagate (stack.jl:502-631); slots are 0-based here: slot k = udt(B_{ks}...B_1) while moving up,
 // udt(B'_{ks+1}...B'_M) while moving down.
-int engine_propagate(mcb_dqmc* h)
+int engine_propagate(mcb_dqmc* h, bool defer_wrap, bool* wrap_pending)
 {
+    if (wrap_pending) *wrap_pending = false;
     const int s = h->s, M = h->M;
     double* wrap_tmp = h->W[6];
     if (h->direction == 1) {
@@ -304,7 +307,7 @@ int engine_propagate(mcb_dqmc* h)
                 std::swap(h->slot[k], h->spare);
                 h->direction = -1;
                 h->current_slice = M + 1;
-                return engine_propagate(h);
+                return engine_propagate(h, defer_wrap, wrap_pending);
             }
         } else {
             MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice, 1));
@@ -318,7 +321,8 @@ int engine_propagate(mcb_dqmc* h)
                 MCB_TRY(set_identity(h, h->bufU[h->spare], h->bufT[h->spare], h->bufD[h->spare]));
                 std::swap(h->slot[last], h->spare); // spare = old left decomposition, slot = identity
                 MCB_TRY(calc_greens(h, h->spare, h->slot[last], h->G));
-                MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice + 1, -1));
+                if (defer_wrap) *wrap_pending = true;
+                else MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice + 1, -1));
             } else if (h->current_slice > 0) {
                 const int k = h->current_slice / s;
                 MCB_TRY(advance(h, false, h->slot[k + 1], h->spare, k * s + 1, (k + 1) * s));
@@ -328,13 +332,14 @@ int engine_propagate(mcb_dqmc* h)
                                              cudaMemcpyDeviceToDevice, h->st));
                 MCB_TRY(calc_greens(h, h->spare, h->slot[k], h->G));
                 if (h->p.check_propagation) MCB_TRY(record_prop_err(h));
-                MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice + 1, -1));
+                if (defer_wrap) *wrap_pending = true;
+                else MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice + 1, -1));
             } else {
                 MCB_TRY(advance(h, false, h->slot[1], h->spare, 1, s));
                 std::swap(h->slot[0], h->spare);
                 h->direction = 1;
                 h->current_slice = 0;
-                return engine_propagate(h);
+                return engine_propagate(h, defer_wrap, wrap_pending);
             }
         } else {
             MCB_TRY(wrap_greens(h, h->G, wrap_tmp, h->current_slice, -1));
@@ -344,10 +349,10 @@ int engine_propagate(mcb_dqmc* h)
     return 0;
 }
 
-// update (DQMC.jl:523-538) = propagate + sweep_spatial
+// update (DQMC.jl:523-538) = propagate + sweep_spatial, general path (any N): separate launches
 int engine_update(mcb_dqmc* h)
 {
-    MCB_TRY(engine_propagate(h));
+    MCB_TRY(engine_propagate(h, false, nullptr));
     SweepArgs a;
     a.n = h->N; a.batch = h->C;
     a.G = h->G; a.sG = (long long)h->nn;
@@ -363,6 +368,51 @@ int engine_update(mcb_dqmc* h)
     a.acc = h->acc; a.prop = h->prop; a.nonfinite = h->nonfinite;
     MCB_TRY(launch_sweep_spatial(a, h->st));
     h->n_updates += 1;
+    return 0;
+}
+
+// A run of update() calls on the chain-resident path (segment.cu): the stabilisation part of
+// propagate (if the next update needs one) runs through the stack kernels, then ONE launch does
+// [wrap +] sweep_spatial for this update and for every following update that is a plain wrap in the
+// same direction (at most safe_mult - 1 of them), up to max_updates.
+int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_point, int64_t* done)
+{
+    *done = 0;
+    if (max_updates <= 0) return 0;
+    if (!h->use_panel) {
+        MCB_TRY(engine_update(h));
+        *done = 1;
+        return 0;
+    }
+    const int s = h->s;
+    const bool plain = h->direction == 1 ? (h->current_slice % s != 0) : ((h->current_slice - 1) % s != 0);
+    bool first_wrap = true;
+    if (plain) h->current_slice += h->direction;
+    else MCB_TRY(engine_propagate(h, true, &first_wrap));
+    const int start = h->current_slice, d = h->direction;
+    int64_t further = d == 1 ? (start % s == 0 ? 0 : s - start % s) : (start - 1) % s;
+    if (stop_at_measure_point && start == 1 && d == 1) further = 0;
+    const int64_t visits = 1 + further < max_updates ? 1 + further : max_updates;
+
+    SegmentArgs a;
+    a.n = h->N; a.batch = h->C;
+    a.G = h->G; a.sG = (long long)h->nn;
+    a.conf = h->conf; a.sConf = (long long)h->M * h->N;
+    a.eT2 = h->hop[2]; a.eTinv2 = h->hop[3];
+    a.n_slices = h->M;
+    a.start_slice = start; a.direction = d; a.n_visits = (int)visits; a.first_wrap = first_wrap ? 1 : 0;
+    a.eVp[0] = h->eVp[0]; a.eVp[1] = h->eVp[1]; a.eVm[0] = h->eVm[0]; a.eVm[1] = h->eVm[1];
+    const double dEp = -2.0 * h->lambda * 1.0, dEm = -2.0 * h->lambda * -1.0;
+    a.gamma_p = exp(dEp) - 1.0; a.efac_p = exp(-dEp);
+    a.gamma_m = exp(dEm) - 1.0; a.efac_m = exp(-dEm);
+    a.key0 = seed_key0(h->p.seed);
+    a.chain_offset = h->p.chain_offset;
+    a.n_updates0 = h->n_updates;
+    a.acc = h->acc; a.prop = h->prop; a.nonfinite = h->nonfinite;
+    MCB_TRY(launch_segment(a, h->st));
+    h->current_slice = start + d * (int)(visits - 1);
+    h->n_updates += visits;
+    *done = visits;
     return 0;
 }
 
@@ -495,6 +545,7 @@ int engine_measure(mcb_dqmc* h)
     if (!h->dir_of_pair) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_TRY(engine_physical_greens(h, h->W[1]));
     const size_t smem = (size_t)(2 * h->n_dirs + 4) * sizeof(double);
+    LaunchScope scope(LC_MEASURE, h->st, 0.0);
     measure_kernel<<<h->C, 256, smem, h->st>>>(h->W[1], h->dir_of_pair, h->hopT, h->N, h->n_dirs, h->p.U,
                                                h->obs, h->Gsum);
     MCB_CUDA(cudaGetLastError());

@@ -6,6 +6,7 @@
 #include "common.cuh"
 #include "gemm.cuh"
 #include "sweep.cuh"
+#include "segment.cuh"
 #include "udt.cuh"
 #include <vector>
 
@@ -43,6 +44,10 @@ struct mcb_dqmc {
     // schedule state
     int current_slice = 0, direction = 1;
     int64_t n_updates = 0;
+    mcb::Profiler prof;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    bool use_panel = false; // chain-resident kernels (panel.cuh) exist for this N
     bool hopping_set = false, conf_set = false, stack_built = false;
 
     int obs_len() const { return 4 + 2 * n_dirs; }
@@ -52,8 +57,9 @@ namespace mcb {
 int engine_alloc(mcb_dqmc* h);
 void engine_free(mcb_dqmc* h);
 int engine_build_stack(mcb_dqmc* h);
-int engine_propagate(mcb_dqmc* h);
+int engine_propagate(mcb_dqmc* h, bool defer_wrap, bool* wrap_pending);
 int engine_update(mcb_dqmc* h);
+int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_point, int64_t* done);
 int engine_calculate_greens_at(mcb_dqmc* h, int slice);
 int engine_physical_greens(mcb_dqmc* h, double* out_dev);
 int engine_measure(mcb_dqmc* h);

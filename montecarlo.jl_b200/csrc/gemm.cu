@@ -145,6 +145,7 @@ int launch_gemm(const GemmArgs& g, cudaStream_t st)
     if (g.C == g.A || g.C == g.B) { set_error("gemm: output aliases an input"); return -1; }
     const int tiles = (g.n + BM - 1) / BM;
     dim3 grid(tiles * tiles, g.batch);
+    LaunchScope scope(LC_GEMM, st, 2.0 * g.n * (double)g.n * g.n * g.batch);
     if (!g.transA && !g.transB) gemm_kernel<false, false><<<grid, THREADS, 0, st>>>(g);
     else if (!g.transA && g.transB) gemm_kernel<false, true><<<grid, THREADS, 0, st>>>(g);
     else if (g.transA && !g.transB) gemm_kernel<true, false><<<grid, THREADS, 0, st>>>(g);

@@ -29,6 +29,9 @@ struct mcb_ising {
     int8_t* spins_dev = nullptr;  // [R][L][L] staging for set/get
     unsigned long long* red = nullptr; // [R][2] : aligned-bond count, up-spin count
     int64_t sweeps_done = 0;
+    int64_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
     bool spins_set = false;
 };
 
@@ -202,6 +205,8 @@ int mcb_ising_create(int32_t L, double beta, int32_t n_replicas, uint64_t seed, 
     MCB_CUDA(cudaMalloc(&h->planes, (size_t)h->R * 2 * h->L * h->W * sizeof(uint64_t)));
     MCB_CUDA(cudaMalloc(&h->spins_dev, (size_t)h->R * h->L * h->L));
     MCB_CUDA(cudaMalloc(&h->red, (size_t)h->R * 2 * sizeof(unsigned long long)));
+    MCB_CUDA(cudaEventCreate(&h->ev0));
+    MCB_CUDA(cudaEventCreate(&h->ev1));
     *out = h;
     return MCB_OK;
 }
@@ -212,6 +217,7 @@ int mcb_ising_destroy(mcb_ising* h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->st);
     cudaFree(h->planes); cudaFree(h->spins_dev); cudaFree(h->red);
+    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
     cudaStreamDestroy(h->st);
     delete h;
     return MCB_OK;
@@ -247,15 +253,19 @@ int mcb_ising_sweep(mcb_ising* h, int64_t n_sweeps)
     MCB_CUDA(cudaSetDevice(h->device));
     const size_t total = (size_t)h->R * h->L * h->W;
     const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    MCB_CUDA(cudaEventRecord(h->ev0, h->st));
     for (int64_t s = 0; s < n_sweeps; ++s) {
         for (int colour = 0; colour < 2; ++colour)
             ising_halfsweep_kernel<<<blocks, 256, 0, h->st>>>(h->planes, geom(h), colour,
                                                               (uint32_t)h->sweeps_done, seed_key0(h->seed),
                                                               h->replica_offset, h->thr4, h->thr8);
         h->sweeps_done += 1;
+        h->launches += 2;
     }
     MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(cudaEventRecord(h->ev1, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
+    MCB_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
     return MCB_OK;
 }
 
@@ -287,5 +297,7 @@ int mcb_ising_measure(mcb_ising* h, int64_t* E, int64_t* Msum)
 }
 
 int64_t mcb_ising_sweep_count(mcb_ising* h) { return h ? h->sweeps_done : -1; }
+double mcb_ising_last_elapsed_ms(mcb_ising* h) { return h ? (double)h->last_ms : -1.0; }
+int64_t mcb_ising_launch_count(mcb_ising* h) { return h ? h->launches : -1; }
 
 } // extern "C"

@@ -82,6 +82,7 @@ int launch_sweep_spatial(const SweepArgs& a, cudaStream_t st)
     const size_t mat = (size_t)n * n * sizeof(double);
     const int in_smem = hdr + mat <= (size_t)SMEM_LIMIT;
     const int threads = n <= 32 ? 128 : (n <= 96 ? 256 : (n <= 200 ? 512 : 1024));
+    LaunchScope scope(LC_SWEEP, st, 0.0);
     sweep_kernel<<<a.batch, threads, in_smem ? hdr + mat : hdr, st>>>(a, in_smem);
     MCB_CUDA(cudaGetLastError());
     return 0;

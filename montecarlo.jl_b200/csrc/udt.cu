@@ -232,6 +232,7 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
     if (hdr + 2 * mat <= (size_t)SMEM_LIMIT) { a.mode = 2; smem = hdr + 2 * mat; }
     else if (hdr + mat <= (size_t)SMEM_LIMIT) { a.mode = 1; smem = hdr + mat; }
     const int threads = n <= 32 ? 128 : (n <= 96 ? 256 : (n <= 200 ? 512 : 1024));
+    LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
     udt_kernel<<<batch, threads, smem, st>>>(a);
     MCB_CUDA(cudaGetLastError());
     return 0;
@@ -248,6 +249,7 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
     if (hdr + 2 * mat <= (size_t)SMEM_LIMIT) { a.mode = 2; smem = hdr + 2 * mat; }
     else if (hdr + mat <= (size_t)SMEM_LIMIT) { a.mode = 1; smem = hdr + mat; }
     const int threads = n <= 32 ? 128 : (n <= 96 ? 256 : (n <= 200 ? 512 : 1024));
+    LaunchScope scope(LC_RDIVP, st, 1.0 * n * (double)n * n * batch);
     rdivp_kernel<<<batch, threads, smem, st>>>(a);
     MCB_CUDA(cudaGetLastError());
     return 0;

@@ -50,7 +50,8 @@ class DQMC:
     conf has shape (n_chains, N, M): conf[c] is the reference's HubbardConf (HubbardModel.jl:4).
     """
 
-    def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, **kwargs):
+    def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, general_path=False,
+                 **kwargs):
         if not isinstance(model, HubbardModelAttractive):
             raise TypeError("the B200 engine implements DQMC{HubbardModelAttractive, CheckerboardFalse}")
         self.model = model
@@ -62,7 +63,7 @@ class DQMC:
         self.L = _lib.lib()
         prm = _lib.DqmcParams(self.N, self.M, self.p.safe_mult, self.n_chains, self.p.delta_tau, model.U,
                               self.seed, self.chain_offset, self.device,
-                              int(self.p.check_propagation_error), 0)
+                              int(self.p.check_propagation_error), int(general_path))
         self.h = C.c_void_p()
         _lib.check(self.L.mcb_dqmc_create(C.byref(prm), C.byref(self.h)))
         self.hop = model.hopping_exponentials(self.p.delta_tau)

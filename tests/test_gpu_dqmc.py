@@ -115,19 +115,20 @@ def test_calculate_greens_from_udts(n):
         assert relerr(G[k], direct) < 1e-8
 
 
-def _pair(L, U, beta, dtau, safe_mult, n_chains, seed=123, check=False, chain_offset=0):
+def _pair(L, U, beta, dtau, safe_mult, n_chains, seed=123, check=False, chain_offset=0, general=False):
     model = mcb.HubbardModelAttractive(L=L, U=U)
     mc = mcb.DQMC(model, n_chains=n_chains, seed=seed, chain_offset=chain_offset, beta=beta, delta_tau=dtau,
-                  safe_mult=safe_mult, check_propagation_error=check)
+                  safe_mult=safe_mult, check_propagation_error=check, general_path=general)
     conf0 = mc.conf()
     oracles = [orc.OracleDQMC(L * L, mc.M, safe_mult, dtau, U, mc.hop, conf0[c], seed=seed,
                               chain=chain_offset + c, check_propagation=check) for c in range(n_chains)]
     return mc, oracles
 
 
+@pytest.mark.parametrize("general", [False, True])
 @pytest.mark.parametrize("L,U,beta,safe_mult,chains", [(2, 1.0, 1.0, 5, 2), (4, 1.0, 1.0, 5, 3), (4, 4.0, 2.0, 10, 2)])
-def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains):
-    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, chains, check=True)
+def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains, general):
+    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, chains, check=True, general=general)
     mc.build_stack()
     for o in oracles:
         o.build_stack()
@@ -156,9 +157,10 @@ def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains):
     mc.close()
 
 
-def test_config_a_8x8_beta8_full_sweep_matches_oracle():
+@pytest.mark.parametrize("general", [False, True])
+def test_config_a_8x8_beta8_full_sweep_matches_oracle(general):
     """BASELINE.json configs[0]/[1] physics: 8x8, U=1, beta=8, dtau=0.1, safe_mult=10."""
-    mc, oracles = _pair(8, 1.0, 8.0, 0.1, 10, 2)
+    mc, oracles = _pair(8, 1.0, 8.0, 0.1, 10, 2, general=general)
     mc.build_stack()
     for o in oracles:
         o.build_stack()
@@ -203,6 +205,30 @@ def test_greens_from_scratch_at_every_slice():
         for c, o in enumerate(oracles):
             assert relerr(G[c], o.greens_at(k)) < RTOL_G, k
     mc.close()
+
+
+@pytest.mark.parametrize("L", [4, 8])
+def test_batched_updates_equal_single_updates(L):
+    """update(n) runs many slice visits per launch on the chain-resident path; the trajectory must be
+    bit-identical to n single update() calls and (HS field) to the general any-N kernels."""
+    a, _ = _pair(L, 2.0, 2.0, 0.1, 5, 3, seed=5)
+    b, _ = _pair(L, 2.0, 2.0, 0.1, 5, 3, seed=5)
+    c, _ = _pair(L, 2.0, 2.0, 0.1, 5, 3, seed=5, general=True)
+    for mc in (a, b, c):
+        mc.build_stack()
+    n = 2 * a.M + 7
+    a.update(n)
+    for _ in range(n):
+        b.update(1)
+    c.update(n)
+    assert a.state() == b.state() == c.state()
+    assert np.array_equal(a.conf(), b.conf()) and np.array_equal(a.greens(False), b.greens(False))
+    assert np.array_equal(a.conf(), c.conf())
+    assert relerr(a.greens(False), c.greens(False)) < RTOL_G
+    sa, sc = a.stats(), c.stats()
+    assert np.array_equal(sa["acc_local"], sc["acc_local"]) and np.array_equal(sa["prop_local"], sc["prop_local"])
+    for mc in (a, b, c):
+        mc.close()
 
 
 def test_chain_ids_are_global():
