@@ -358,7 +358,7 @@ def run_dqmc(args, w, rank, local_rank, world):
         "wall_s_timed_region": wall,
     }
     k = shares[top]
-    if top in ("gemm", "udt", "rdivp", "fused"):
+    if top in ("gemm", "udt", "rdivp", "fused", "advance", "greens"):
         line["roofline"] = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": fp64_peak,
                             "unit": "TFLOP/s", "frac": (k["tflops"] or 0.0) / fp64_peak,
                             "traffic": traffic_for(top), "avg_launch_us": k["avg_us"], "share_of_step": k["share"],

@@ -126,11 +126,12 @@ int mcb_dqmc_get_greens_sum(mcb_dqmc* h, double* Gsum);
 
 /* Launch accounting and device timing (the role of the reference's @bm / TimerOutputs hooks,
  * src/helpers.jl:160-236). Launch classes, in order: gemm, udt, rdivp, sweep_spatial, fused
- * wrap+sweep, measure, misc, ising  (MCB_N_LAUNCH_CLASSES entries per output array).
+ * wrap+sweep, measure, misc, ising, chain-resident add_slice_sequence, chain-resident
+ * calculate_greens  (MCB_N_LAUNCH_CLASSES entries per output array).
  * mcb_dqmc_profile: enable_timing != 0 brackets every launch with CUDA events on the handle's
  * stream; reset != 0 clears all counters. get_profile: launches since reset, event-timed ms and
  * number of timed launches, algorithmic FP64 flop per class. */
-#define MCB_N_LAUNCH_CLASSES 8
+#define MCB_N_LAUNCH_CLASSES 10
 int mcb_dqmc_profile(mcb_dqmc* h, int32_t enable_timing, int32_t reset);
 int mcb_dqmc_get_profile(mcb_dqmc* h, int64_t* launches, double* ms, int64_t* timed, double* flops);
 /* device time (CUDA events on the handle's stream) of the last mcb_dqmc_update / _sweep call */
@@ -139,6 +140,10 @@ double mcb_dqmc_last_elapsed_ms(mcb_dqmc* h);
 /* --------------------------------------------------- batched linear algebra ---- *
  * Kernel-level entry points (the methods a custom matrix type overloads in the
  * reference, cf. src/linalg/blockdiagonal.jl:156-428). Host buffers, [batch][col][row].   */
+
+/* Testing aid: on != 0 makes the entry points below use the general any-N kernels even where a
+ * chain-resident (register/shared-memory) kernel exists for n; default 0. Process-wide. */
+int mcb_linalg_force_general(int32_t on);
 
 /* vmul!: mode 0 C=A*B, 1 C=A*B', 2 C=A'*B  (src/linalg/general.jl:7-45) */
 int mcb_linalg_vmul(int32_t n, int32_t batch, const double* A, const double* B, double* C,

@@ -10,7 +10,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libmcb200.so")
 _LIB = None
-LAUNCH_CLASSES = ("gemm", "udt", "rdivp", "sweep_spatial", "fused", "measure", "misc", "ising")
+LAUNCH_CLASSES = ("gemm", "udt", "rdivp", "sweep_spatial", "fused", "measure", "misc", "ising", "advance",
+                  "greens")
 
 
 class McbError(RuntimeError):
@@ -67,6 +68,7 @@ SIGNATURES = {
     "mcb_dqmc_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_launch_count": (C.c_int64, [C.c_void_p]),
+    "mcb_linalg_force_general": (C.c_int, [C.c_int32]),
     "mcb_linalg_vmul": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, C.c_int32, C.c_int32]),
     "mcb_linalg_udt": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, _f64, _i32, C.c_int32,
                                  C.c_int32]),

@@ -33,6 +33,7 @@ static int use_device(int dev)
         API_TRY(init_udt_kernels());
         API_TRY(init_sweep_kernels());
         API_TRY(init_segment_kernels());
+        API_TRY(init_stab_kernels());
         inited[dev] = true;
     }
     return 0;
@@ -63,7 +64,7 @@ int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
     h->p = *p;
     h->N = p->n_sites; h->M = p->n_slices; h->s = p->safe_mult; h->C = p->n_chains;
     h->ne = h->M / h->s + 1;
-    h->use_panel = segment_supported(h->N) && p->general_path == 0;
+    h->use_panel = segment_supported(h->N) && stab_supported(h->N) && p->general_path == 0;
     h->nn = (size_t)h->N * h->N;
     h->mat = h->nn * h->C;
     h->vec = (size_t)h->N * h->C;

@@ -28,8 +28,12 @@ int prepare(int dev)
     }
     MCB_CUDA(cudaSetDevice(dev));
     if (init_udt_kernels() != 0) return MCB_ERR_CUDA;
+    if (init_stab_kernels() != 0) return MCB_ERR_CUDA;
     return 0;
 }
+
+bool g_force_general = false;
+bool use_panel(int n) { return !g_force_general && stab_supported(n); }
 
 #define CHECK_ALLOC(p) do { if (!(p)) { set_error("cudaMalloc failed"); return MCB_ERR_CUDA; } } while (0)
 #define L_TRY(expr) do { const int rc__ = (expr); if (rc__ != 0) return rc__; } while (0)
@@ -37,6 +41,12 @@ int prepare(int dev)
 } // namespace
 
 extern "C" {
+
+int mcb_linalg_force_general(int32_t on)
+{
+    g_force_general = on != 0;
+    return MCB_OK;
+}
 
 int mcb_linalg_vmul(int32_t n, int32_t batch, const double* A, const double* B, double* C, int32_t mode,
                     int32_t device_id)
@@ -71,8 +81,10 @@ int mcb_linalg_udt(int32_t n, int32_t batch, const double* X, double* U, double*
     double* dD = d.alloc<double>(vcnt); int* dP = d.alloc<int>(vcnt);
     CHECK_ALLOC(dX && dU && dT && dD && dP);
     MCB_CUDA(cudaMemcpy(dX, X, cnt * sizeof(double), cudaMemcpyHostToDevice));
-    L_TRY(launch_udt(n, batch, dX, (long long)n * n, dU, (long long)n * n, dD, n, dT, (long long)n * n, dP, n,
-                     apply_pivot, 0));
+    if (use_panel(n)) L_TRY(launch_udt_panel(n, batch, dX, dU, dD, dT, dP, apply_pivot, 0));
+    else
+        L_TRY(launch_udt(n, batch, dX, (long long)n * n, dU, (long long)n * n, dD, n, dT, (long long)n * n, dP, n,
+                         apply_pivot, 0));
     MCB_CUDA(cudaDeviceSynchronize());
     MCB_CUDA(cudaMemcpy(U, dU, cnt * sizeof(double), cudaMemcpyDeviceToHost));
     MCB_CUDA(cudaMemcpy(T, dT, cnt * sizeof(double), cudaMemcpyDeviceToHost));
@@ -119,7 +131,13 @@ int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, cons
     int* piv = d.alloc<int>(vcnt); CHECK_ALLOC(piv);
     for (int i = 0; i < 4; ++i) MCB_CUDA(cudaMemcpy(m[i], hm[i], cnt * sizeof(double), cudaMemcpyHostToDevice));
     for (int i = 0; i < 2; ++i) MCB_CUDA(cudaMemcpy(v[i], hv[i], vcnt * sizeof(double), cudaMemcpyHostToDevice));
-    L_TRY(calc_greens_raw(n, batch, m[0], v[0], m[1], m[2], v[1], m[3], m[4], W, Dw, piv, 0));
+    if (use_panel(n)) {
+        GreensArgs a;
+        a.n = n; a.batch = batch;
+        a.Ul = m[0]; a.Dl = v[0]; a.Tl = m[1]; a.Ur = m[2]; a.Dr = v[1]; a.Tr = m[3]; a.G = m[4];
+        L_TRY(launch_greens_panel(a, 0));
+    } else
+        L_TRY(calc_greens_raw(n, batch, m[0], v[0], m[1], m[2], v[1], m[3], m[4], W, Dw, piv, 0));
     MCB_CUDA(cudaDeviceSynchronize());
     MCB_CUDA(cudaMemcpy(G, m[4], cnt * sizeof(double), cudaMemcpyDeviceToHost));
     return MCB_OK;

@@ -176,6 +176,14 @@ namespace {
 
 int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 {
+    if (h->use_panel) {
+        GreensArgs a;
+        a.n = h->N; a.batch = h->C;
+        a.Ul = h->bufU[physL]; a.Dl = h->bufD[physL]; a.Tl = h->bufT[physL];
+        a.Ur = h->bufU[physR]; a.Dr = h->bufD[physR]; a.Tr = h->bufT[physR];
+        a.G = out;
+        return launch_greens_panel(a, h->st);
+    }
     return calc_greens_raw(h->N, h->C, h->bufU[physL], h->bufD[physL], h->bufT[physL], h->bufU[physR],
                            h->bufD[physR], h->bufT[physR], out, h->W, h->Dw, h->pivot, h->st);
 }
@@ -184,6 +192,17 @@ int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 // add_slice_sequence_right (stack.jl:296-311) for left == false (daggered, descending slices)
 int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
 {
+    if (h->use_panel) {
+        AdvanceArgs a;
+        a.n = h->N; a.batch = h->C;
+        a.Usrc = h->bufU[src]; a.Dsrc = h->bufD[src]; a.Tsrc = h->bufT[src];
+        a.Udst = h->bufU[dst]; a.Ddst = h->bufD[dst]; a.Tdst = h->bufT[dst];
+        a.eT2 = h->hop[2];
+        a.conf = h->conf; a.sConf = (long long)h->M * h->N;
+        a.lo = lo; a.hi = hi; a.left = left ? 1 : 0;
+        a.ep = h->eVp[0]; a.em = h->eVp[1];
+        return launch_advance_panel(a, h->st);
+    }
     const double* cur = h->bufU[src];
     const Scale dcol = vec_scale(h->bufD[src], h->N);
     int pp = 0;

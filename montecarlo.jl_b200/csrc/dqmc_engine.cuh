@@ -7,6 +7,7 @@
 #include "gemm.cuh"
 #include "sweep.cuh"
 #include "segment.cuh"
+#include "stab.cuh"
 #include "udt.cuh"
 #include <vector>
 

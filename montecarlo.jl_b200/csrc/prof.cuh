@@ -8,7 +8,7 @@
 
 namespace mcb {
 
-enum LaunchClass { LC_GEMM = 0, LC_UDT, LC_RDIVP, LC_SWEEP, LC_FUSED, LC_MEASURE, LC_MISC, LC_ISING, LC_COUNT };
+enum LaunchClass { LC_GEMM = 0, LC_UDT, LC_RDIVP, LC_SWEEP, LC_FUSED, LC_MEASURE, LC_MISC, LC_ISING, LC_ADVANCE, LC_GREENS, LC_COUNT };
 
 struct Profiler {
     bool timing = false;

@@ -1,0 +1,38 @@
+// Chain-resident stabilisation kernels (one CTA per Markov chain, matrices in registers / shared
+// memory, see panel.cuh and panel_qr.cuh). They replace, for the matrix sizes the register layout
+// supports, the general-path sequences of dqmc_engine.cu:
+//   advance  = add_slice_sequence_left / _right            src/flavors/DQMC/stack.jl:272-311
+//   greens   = calculate_greens_AVX!                        src/flavors/DQMC/stack.jl:337-393
+//   udt      = udt_AVX_pivot!                               src/linalg/UDT.jl:192-306
+#pragma once
+#include "common.cuh"
+
+namespace mcb {
+
+struct AdvanceArgs {
+    int n = 0, batch = 0;
+    const double* Usrc = nullptr; const double* Dsrc = nullptr; const double* Tsrc = nullptr;
+    double* Udst = nullptr; double* Ddst = nullptr; double* Tdst = nullptr; // strides n*n / n per chain
+    const double* eT2 = nullptr;       // e^{-dtau T}, shared by all chains
+    const int8_t* conf = nullptr; long long sConf = 0; // [chain][slice][site]
+    int lo = 0, hi = 0;                // 1-based slice range of the sequence
+    int left = 1;                      // 1: B_hi ... B_lo (ascending) ; 0: B'_lo ... B'_hi (descending, daggered)
+    double ep = 1.0, em = 1.0;         // exp(+lambda s) for s = +1 / -1
+};
+
+struct GreensArgs {
+    int n = 0, batch = 0;
+    const double *Ul = nullptr, *Dl = nullptr, *Tl = nullptr, *Ur = nullptr, *Dr = nullptr, *Tr = nullptr;
+    double* G = nullptr;
+};
+
+bool stab_supported(int n);
+int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st);
+int launch_greens_panel(const GreensArgs& a, cudaStream_t st);
+// X -> U, D, T (= D^-1 R P' when apply_pivot, else the reference's "dirty" upper triangle in
+// position order) and the 0-based pivot vector; same contract as launch_udt (udt.cuh)
+int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, double* T, int* pivot,
+                     int apply_pivot, cudaStream_t st);
+int init_stab_kernels();
+
+} // namespace mcb

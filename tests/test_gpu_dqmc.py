@@ -43,9 +43,19 @@ def test_vmul_modes(n):
             assert relerr(_uncm(out, b, n)[k], orc.vmul(A[k], B[k], mode)) < 1e-13
 
 
-@pytest.mark.parametrize("n", [4, 16, 64, 100, 144, 200])
+@pytest.fixture
+def linalg_path(request):
+    """general=True forces the any-N kernels where a chain-resident kernel exists (N = 16, 32, 64)."""
+    L = _lib.lib()
+    L.mcb_linalg_force_general(int(request.param))
+    yield request.param
+    L.mcb_linalg_force_general(0)
+
+
+@pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
+@pytest.mark.parametrize("n", [4, 16, 32, 64, 100, 144, 200])
 @pytest.mark.parametrize("apply_pivot", [1, 0])
-def test_udt_contract(n, apply_pivot):
+def test_udt_contract(n, apply_pivot, linalg_path):
     rng = np.random.default_rng(100 + n)
     b = 2
     X = rng.standard_normal((b, n, n))
@@ -90,8 +100,9 @@ def test_rdivp(n):
         assert relerr(got[k], orc.rdivp(A[k], Ts[k], Ps[k])) < 1e-10
 
 
-@pytest.mark.parametrize("n", [16, 64])
-def test_calculate_greens_from_udts(n):
+@pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
+@pytest.mark.parametrize("n", [16, 32, 64])
+def test_calculate_greens_from_udts(n, linalg_path):
     rng = np.random.default_rng(n)
     b = 2
     trip = []
