@@ -84,81 +84,91 @@ __device__ __forceinline__ void qr_pivot(double (&A)[Geo<N>::MT][2], QrSmem<N>& 
         for (int m = 0; m < MT; ++m) s += A[m][c] * A[m][c];
         nrm[c] = col_sum(s);
     }
-    for (int j = 0; j < N; ++j) {
-        const int buf = j & 1;
-        // ---- best remaining column of this warp
-        double bv = done[0] ? -1.0 : nrm[0];
-        int bk = (curpos[0] << 16) | col0;
-        {
-            const double v1 = done[1] ? -1.0 : nrm[1];
-            const int k1 = (curpos[1] << 16) | (col0 + 1);
-            if (v1 > bv || (v1 == bv && k1 < bk)) { bv = v1; bk = k1; }
-        }
 #pragma unroll
-        for (int o = 1; o <= 2; o <<= 1) {
-            const double ov = __shfl_xor_sync(FULL, bv, o);
-            const int ok = __shfl_xor_sync(FULL, bk, o);
-            if (ov > bv || (ov == bv && ok < bk)) { bv = ov; bk = ok; }
-        }
-        {
-            const int bc = bk & 0xffff;
-            if (bc == col0 || bc == col0 + 1) {
-                const int c = bc - col0;
-#pragma unroll
-                for (int m = 0; m < MT; ++m) qs.cand[buf][t.w][8 * m + t.r] = c ? A[m][1] : A[m][0];
+    for (int mj = 0; mj < MT; ++mj) { // row block of the step: rows below 8*mj are finished (compile time)
+#pragma unroll 1
+        for (int rj = 0; rj < 8; ++rj) {
+            const int j = 8 * mj + rj;
+            const int buf = j & 1;
+            // ---- best remaining column of this warp
+            double bv = done[0] ? -1.0 : nrm[0];
+            int bk = (curpos[0] << 16) | col0;
+            {
+                const double v1 = done[1] ? -1.0 : nrm[1];
+                const int k1 = (curpos[1] << 16) | (col0 + 1);
+                if (v1 > bv || (v1 == bv && k1 < bk)) { bv = v1; bk = k1; }
             }
-            if (t.l == 0) { qs.cval[buf][t.w] = bv; qs.ckey[buf][t.w] = bk; }
-        }
-        __syncthreads();
-        // ---- global winner (every thread evaluates the same NW candidates)
-        double maxval = qs.cval[buf][0];
-        int key = qs.ckey[buf][0], wb = 0;
 #pragma unroll
-        for (int w = 1; w < NW; ++w) {
-            const double v = qs.cval[buf][w];
-            const int k = qs.ckey[buf][w];
-            if (v > maxval || (v == maxval && k < key)) { maxval = v; key = k; wb = w; }
-        }
-        const int pj = key & 0xffff, jm = key >> 16;
-        // ---- reflector! (UDT.jl:133-148)
-        const double* x = qs.cand[buf][wb];
-        const double xj = x[j];
-        double nu = 0.0, tj = 0.0, inv = 0.0;
-        if (maxval > 0.0) {
-            nu = copysign(sqrt(maxval), xj);
-            const double xjn = xj + nu;
-            tj = xjn / nu;
-            inv = 1.0 / xjn;
-        }
-        double v[MT];
-#pragma unroll
-        for (int m = 0; m < MT; ++m) {
-            const int i = 8 * m + t.r;
-            v[m] = i < j ? 0.0 : (i == j ? (maxval > 0.0 ? 1.0 : 0.0) : x[i] * inv);
-        }
-        // ---- reflectorApply! on the remaining columns (UDT.jl:32-50) + fresh trailing norms
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const bool is_piv = (col0 + c == pj);
-            double dot = 0.0;
-#pragma unroll
-            for (int m = 0; m < MT; ++m) dot += v[m] * A[m][c];
-            dot = col_sum(dot);
-            const double s = (done[c] || is_piv) ? 0.0 : tj * dot;
-            double nn = 0.0;
-#pragma unroll
-            for (int m = 0; m < MT; ++m) {
-                const int i = 8 * m + t.r;
-                double a = A[m][c] - s * v[m];
-                if (is_piv && maxval > 0.0) a = i < j ? a : (i == j ? -nu : v[m]);
-                A[m][c] = a;
-                nn += i > j ? a * a : 0.0;
+            for (int o = 1; o <= 2; o <<= 1) {
+                const double ov = __shfl_xor_sync(FULL, bv, o);
+                const int ok = __shfl_xor_sync(FULL, bk, o);
+                if (ov > bv || (ov == bv && ok < bk)) { bv = ov; bk = ok; }
             }
-            nrm[c] = col_sum(nn);
-            if (is_piv) done[c] = true;
-            else if (!done[c] && curpos[c] == j) curpos[c] = jm; // the swap j <-> jm (UDT.jl:219-231)
+            {
+                const int bc = bk & 0xffff;
+                if (bc == col0 || bc == col0 + 1) {
+                    const int c = bc - col0;
+#pragma unroll
+                    for (int m = mj; m < MT; ++m) qs.cand[buf][t.w][8 * m + t.r] = c ? A[m][1] : A[m][0];
+                }
+                if (t.l == 0) { qs.cval[buf][t.w] = bv; qs.ckey[buf][t.w] = bk; }
+            }
+            __syncthreads();
+            // ---- global winner (every thread evaluates the same NW candidates)
+            double maxval = qs.cval[buf][0];
+            int key = qs.ckey[buf][0], wb = 0;
+#pragma unroll
+            for (int w = 1; w < NW; ++w) {
+                const double v = qs.cval[buf][w];
+                const int k = qs.ckey[buf][w];
+                if (v > maxval || (v == maxval && k < key)) { maxval = v; key = k; wb = w; }
+            }
+            const int pj = key & 0xffff, jm = key >> 16;
+            // ---- reflector! (UDT.jl:133-148)
+            const double* x = qs.cand[buf][wb];
+            const double xj = x[j];
+            double nu = 0.0, tj = 0.0, inv = 0.0;
+            const bool live = maxval > 0.0;
+            if (live) {
+                nu = copysign(sqrt(maxval), xj);
+                const double xjn = xj + nu;
+                tj = xjn / nu;
+                inv = 1.0 / xjn;
+            }
+            // v = (0 .. 0, 1, x[j+1:] / (x_j + nu)); only the row blocks m >= mj are touched
+            double v[MT];
+            v[mj] = t.r < rj ? 0.0 : (t.r == rj ? (live ? 1.0 : 0.0) : x[8 * mj + t.r] * inv);
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m) v[m] = x[8 * m + t.r] * inv;
+            // ---- reflectorApply! on the remaining columns (UDT.jl:32-50) + fresh trailing norms
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const bool is_piv = (col0 + c == pj);
+                double dot = 0.0;
+#pragma unroll
+                for (int m = mj; m < MT; ++m) dot += v[m] * A[m][c];
+                dot = col_sum(dot);
+                const double s = (done[c] || is_piv) ? 0.0 : tj * dot;
+                double nn = 0.0;
+                {
+                    double a = A[mj][c] - s * v[mj];
+                    if (is_piv && live) a = t.r < rj ? a : (t.r == rj ? -nu : v[mj]);
+                    A[mj][c] = a;
+                    nn = t.r > rj ? a * a : 0.0;
+                }
+#pragma unroll
+                for (int m = mj + 1; m < MT; ++m) {
+                    double a = A[m][c] - s * v[m];
+                    if (is_piv && live) a = v[m];
+                    A[m][c] = a;
+                    nn += a * a;
+                }
+                nrm[c] = col_sum(nn);
+                if (is_piv) done[c] = true;
+                else if (!done[c] && curpos[c] == j) curpos[c] = jm; // the swap j <-> jm (UDT.jl:219-231)
+            }
+            if (t.tid == 0) { qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j; }
         }
-        if (t.tid == 0) { qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j; }
     }
     __syncthreads();
 }
@@ -176,24 +186,27 @@ __device__ __forceinline__ void form_q(double (&Q)[Geo<N>::MT][2], const double*
         Q[m][0] = (8 * m + t.r == col0) ? 1.0 : 0.0;
         Q[m][1] = (8 * m + t.r == col0 + 1) ? 1.0 : 0.0;
     }
-    for (int k = N - 1; k >= 0; --k) {
-        if (8 * t.w + 7 < k) continue; // columns left of k are still unit vectors: H_k leaves them alone
-        const double* x = F + (size_t)qs.piv[k] * LD;
-        const double tk = qs.tau[k];
-        double v[MT];
 #pragma unroll
-        for (int m = 0; m < MT; ++m) {
-            const int i = 8 * m + t.r;
-            v[m] = i < k ? 0.0 : (i == k ? 1.0 : x[i]);
-        }
+    for (int mk = MT - 1; mk >= 0; --mk) {
+#pragma unroll 1
+        for (int rk = 7; rk >= 0; --rk) {
+            const int k = 8 * mk + rk;
+            if (8 * t.w + 7 < k) continue; // columns left of k are still unit vectors: H_k leaves them alone
+            const double* x = F + (size_t)qs.piv[k] * LD;
+            const double tk = qs.tau[k];
+            double v[MT];
+            v[mk] = t.r < rk ? 0.0 : (t.r == rk ? 1.0 : x[8 * mk + t.r]);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            double dot = 0.0;
+            for (int m = mk + 1; m < MT; ++m) v[m] = x[8 * m + t.r];
 #pragma unroll
-            for (int m = 0; m < MT; ++m) dot += v[m] * Q[m][c];
-            const double s = tk * col_sum(dot);
+            for (int c = 0; c < 2; ++c) {
+                double dot = 0.0;
 #pragma unroll
-            for (int m = 0; m < MT; ++m) Q[m][c] -= s * v[m];
+                for (int m = mk; m < MT; ++m) dot += v[m] * Q[m][c];
+                const double s = tk * col_sum(dot);
+#pragma unroll
+                for (int m = mk; m < MT; ++m) Q[m][c] -= s * v[m];
+            }
         }
     }
 }
