@@ -1,53 +1,231 @@
 // wrap_greens! (src/flavors/DQMC/stack.jl:491-500) + sweep_spatial (src/flavors/DQMC/DQMC.jl:546-582)
 // with propose_local / accept_local! (src/models/HubbardModel/HubbardModelAttractive.jl:113-155),
-// fused over a run of consecutive time slices. One CTA per chain; G stays in registers (panel.cuh).
+// fused over a run of consecutive time slices.
 //
-// Wrap: the two N^3 products run on the FP64 tensor pipe from shared-memory operands; the slice
-// matrices B_l = e^{-dtau T} diag(e^{lambda s}) are never materialised (slice_matrices.jl:23-39):
-// the diagonal factor is applied while G is staged to shared memory.
-// Local updates: one __syncthreads per site. The owners of row i and column i publish them
-// (double-buffered), every thread then evaluates the Metropolis decision redundantly from G_ii and
-// applies the rank-1 update G -= (e_i - G[:,i]) x G[i,:] to its 16 register elements.
-#include "panel.cuh"
+// Geometry: a CTA works on CH = 4 Markov chains at once; each chain belongs to NWC = N/16 warps and its
+// Green's function stays in their REGISTERS for the whole run of slices, in the accumulator layout of
+// the FP64 tensor-core instruction (DMMA m8n8k4):
+//     warp wl of the chain owns the 16 columns [16 wl, 16 wl + 16), all N rows;
+//     lane l (r = l>>2, q = l&3): acc[m][cw][c] = G[8m + r][16 wl + 8 cw + 2q + c].
+// The hopping exponentials e^{-+dtau T} are staged ONCE per CTA in shared memory and shared by its four
+// chains; each chain has a private staging matrix X for the operand that has to cross warps. Chains
+// synchronise on their own named barrier, never CTA-wide, so the four latency chains of the strictly
+// sequential site loop interleave on one SM.
+//
+// Wrap: two N^3 products on the FP64 tensor pipe; the slice matrices B_l = e^{-dtau T} diag(e^{lambda s})
+// are never materialised (slice_matrices.jl:23-39): the diagonal factor is applied in registers.
+// Local updates: ONE barrier per site. The warp that owns column i takes G_ii by shuffle, evaluates
+// the Metropolis decision and publishes x (e_i - G[:,i]) with x = gamma / (1 + gamma (1 - G_ii)); the
+// holders of row i publish it; after the barrier every thread applies the rank-1 update to its 32
+// register elements. Publication buffers are double-buffered over sites.
 #include "segment.cuh"
 
 namespace mcb {
 
 namespace {
 
-using namespace panel;
+constexpr int CH = 4; // chains per CTA
+constexpr int CW = 2; // 8-column blocks per warp
 
 template <int N>
-struct SegSmem {
-    static constexpr int LD = Geo<N>::LD;
-    double eT2[N * LD];
-    double eTinv2[N * LD];
-    double X[N * LD];
-    double colbuf[2][N];
-    double rowbuf[2][N];
+struct SGeo {
+    static_assert(N % 16 == 0, "chain-resident kernels need N to be a multiple of 16");
+    static constexpr int MT = N / 8;         // 8-row blocks
+    static constexpr int NWC = N / (8 * CW); // warps per chain
+    static constexpr int TPC = NWC * 32;     // threads per chain
+    static constexpr int THREADS = CH * TPC;
+    static constexpr int LD = N + 4;         // LD % 16 == 4: conflict-free DMMA fragment loads
+};
+
+template <int N>
+struct alignas(16) ChainSmem {
+    double X[N * SGeo<N>::LD];
+    double ux[2][N];   // x * (e_i - G[:, i])
+    double row[2][N];  // G[i, :]
     double unif[N];
     double sc_row[N];
     double sc_col[N];
+    int accept[2];
     int8_t s_in[N];
     int8_t s_out[N];
 };
 
 template <int N>
-__global__ void __launch_bounds__(Geo<N>::THREADS) segment_kernel(SegmentArgs a)
+struct SegSmem {
+    double eT2[N * SGeo<N>::LD];
+    double eTinv2[N * SGeo<N>::LD];
+    ChainSmem<N> ch[CH];
+};
+
+__device__ __forceinline__ void chain_sync(int id, int nthreads)
 {
-    constexpr int MT = Geo<N>::MT, TH = Geo<N>::THREADS;
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+struct CLane {
+    int ctid, wl, l, r, q, col0; // thread in chain, warp in chain, lane, row-in-block, quad, first column
+    __device__ __forceinline__ CLane(int tid_in_chain)
+    {
+        ctid = tid_in_chain; wl = ctid >> 5; l = ctid & 31; r = l >> 2; q = l & 3;
+        col0 = 8 * CW * wl + 2 * q;
+    }
+};
+
+template <int N>
+__device__ __forceinline__ void r2s(const double (&acc)[SGeo<N>::MT][CW][2], double* S, const CLane& t)
+{
+    constexpr int LD = SGeo<N>::LD;
+#pragma unroll
+    for (int m = 0; m < SGeo<N>::MT; ++m)
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw)
+#pragma unroll
+            for (int c = 0; c < 2; ++c) S[(8 * m + t.r) + (t.col0 + 8 * cw + c) * LD] = acc[m][cw][c];
+}
+
+// acc = A * B, both in shared memory (ld = LD), column-major
+template <int N>
+__device__ __forceinline__ void gemm(double (&acc)[SGeo<N>::MT][CW][2], const double* As, const double* Bs,
+                                     const CLane& t)
+{
+    constexpr int LD = SGeo<N>::LD, MT = SGeo<N>::MT;
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw) acc[m][cw][0] = acc[m][cw][1] = 0.0;
+    const double* ap = As + t.r + t.q * LD;
+    const double* bp = Bs + t.q + (8 * CW * t.wl + t.r) * LD;
+#pragma unroll 4
+    for (int k0 = 0; k0 < N; k0 += 4) {
+        double b[CW];
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw) b[cw] = bp[k0 + 8 * cw * LD];
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+            const double a = ap[8 * m + k0 * LD];
+#pragma unroll
+            for (int cw = 0; cw < CW; ++cw) dmma884(acc[m][cw][0], acc[m][cw][1], a, b[cw]);
+        }
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void scale_rows(double (&acc)[SGeo<N>::MT][CW][2], const double* v, const CLane& t)
+{
+#pragma unroll
+    for (int m = 0; m < SGeo<N>::MT; ++m) {
+        const double s = v[8 * m + t.r];
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw) { acc[m][cw][0] *= s; acc[m][cw][1] *= s; }
+    }
+}
+template <int N>
+__device__ __forceinline__ void scale_cols(double (&acc)[SGeo<N>::MT][CW][2], const double* v, const CLane& t)
+{
+#pragma unroll
+    for (int cw = 0; cw < CW; ++cw) {
+        const double s0 = v[t.col0 + 8 * cw], s1 = v[t.col0 + 8 * cw + 1];
+#pragma unroll
+        for (int m = 0; m < SGeo<N>::MT; ++m) { acc[m][cw][0] *= s0; acc[m][cw][1] *= s1; }
+    }
+}
+
+// one site of sweep_spatial; IT = row block of site i, RR = i % 8 (compile time)
+template <int N, int IT, int RR>
+__device__ __forceinline__ void site_update(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,
+                                            const SegmentArgs& a, const CLane& t, int bar_id, int& nacc)
+{
+    constexpr int MT = SGeo<N>::MT;
+    constexpr int i = 8 * IT + RR;
+    constexpr int WI = i / (8 * CW), CWI = (i / 8) % CW, QI = (i % 8) / 2, CI = i % 2; // owner of column i
+    constexpr int buf = RR & 1;
+    double* ux = cs.ux[buf];
+    double* row = cs.row[buf];
+    if (t.wl == WI) {
+        // G_ii sits in lane (r = RR, q = QI) of this warp
+        const double gii = __shfl_sync(0xffffffffu, acc[IT][CWI][CI], RR * 4 + QI);
+        const int s = cs.s_in[i];
+        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+        const double efac = s > 0 ? a.efac_p : a.efac_m;
+        const double rt = 1.0 + gamma * (1.0 - gii);       // propose_local: detratio = rt^2
+        const double p = efac * (rt * rt);                  // DQMC.jl:570
+        const bool accept = (p > 1.0 || cs.unif[i] < p);    // DQMC.jl:573
+        if (accept && t.q == QI) {
+            const double x = gamma / rt;                    // accept_local!: gamma / (1 + gamma u_i)
+#pragma unroll
+            for (int m = 0; m < MT; ++m)
+                ux[8 * m + t.r] = x * (((8 * m + t.r) == i ? 1.0 : 0.0) - acc[m][CWI][CI]);
+        }
+        if (t.l == 0) { cs.accept[buf] = accept; cs.s_out[i] = (int8_t)(accept ? -s : s); }
+    }
+    if (t.r == RR) {
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw)
+            *reinterpret_cast<double2*>(row + t.col0 + 8 * cw) = make_double2(acc[IT][cw][0], acc[IT][cw][1]);
+    }
+    chain_sync(bar_id, SGeo<N>::TPC);
+    if (cs.accept[buf]) {
+        double2 v[CW];
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw) v[cw] = *reinterpret_cast<const double2*>(row + t.col0 + 8 * cw);
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+            const double u = ux[8 * m + t.r];
+#pragma unroll
+            for (int cw = 0; cw < CW; ++cw) {
+                acc[m][cw][0] -= u * v[cw].x;
+                acc[m][cw][1] -= u * v[cw].y;
+            }
+        }
+        ++nacc;
+    }
+}
+
+template <int N, int IT>
+__device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,
+                                           const SegmentArgs& a, const CLane& t, int bar_id, int& nacc)
+{
+    site_update<N, IT, 0>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 1>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 2>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 3>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 4>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 5>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 6>(acc, cs, a, t, bar_id, nacc);
+    site_update<N, IT, 7>(acc, cs, a, t, bar_id, nacc);
+    if constexpr (IT + 1 < SGeo<N>::MT) site_block<N, IT + 1>(acc, cs, a, t, bar_id, nacc);
+}
+
+template <int N>
+__global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArgs a)
+{
+    constexpr int MT = SGeo<N>::MT, TPC = SGeo<N>::TPC, LD = SGeo<N>::LD;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SegSmem<N>& sm = *reinterpret_cast<SegSmem<N>*>(smem_raw);
-    const Lane t;
-    const int chain = blockIdx.x;
+    // the hopping exponentials, once per CTA
+    for (int e = threadIdx.x; e < N * N; e += SGeo<N>::THREADS) {
+        const int i = e % N, j = e / N;
+        sm.eT2[i + j * LD] = a.eT2[e];
+        sm.eTinv2[i + j * LD] = a.eTinv2[e];
+    }
+    __syncthreads();
+    const int cl = threadIdx.x / TPC; // chain within the CTA
+    const int chain = blockIdx.x * CH + cl;
+    if (chain >= a.batch) return; // whole chains leave together; they only use their own barrier below
+    const CLane t(threadIdx.x % TPC);
+    const int bar_id = 1 + cl;
+    ChainSmem<N>& cs = sm.ch[cl];
     double* Gg = a.G + (size_t)chain * a.sG;
     int8_t* cg = a.conf + (size_t)chain * a.sConf;
     const uint32_t k1 = a.chain_offset + (uint32_t)chain;
 
-    double acc[MT][2];
-    g2r<N>(acc, Gg, t);
-    g2s<N, false>(sm.eT2, a.eT2, t.tid);
-    g2s<N, false>(sm.eTinv2, a.eTinv2, t.tid);
+    double acc[MT][CW][2];
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw)
+#pragma unroll
+            for (int c = 0; c < 2; ++c) acc[m][cw][c] = Gg[(8 * m + t.r) + (size_t)(t.col0 + 8 * cw + c) * N];
 
     int nacc = 0;
     for (int v = 0; v < a.n_visits; ++v) {
@@ -55,99 +233,67 @@ __global__ void __launch_bounds__(Geo<N>::THREADS) segment_kernel(SegmentArgs a)
         if (v > 0 || a.first_wrap) {
             // ---- wrap_greens!
             const int l = a.direction > 0 ? slice - 1 : slice; // slice matrix B_l
-            __syncthreads();
-            for (int i = t.tid; i < N; i += TH) {
+            for (int i = t.ctid; i < N; i += TPC) {
                 const int s = cg[(size_t)(l - 1) * N + i];
-                if (a.direction > 0) { sm.sc_row[i] = s > 0 ? a.eVp[0] : a.eVp[1]; sm.sc_col[i] = s > 0 ? a.eVm[0] : a.eVm[1]; }
-                else { sm.sc_row[i] = s > 0 ? a.eVm[0] : a.eVm[1]; sm.sc_col[i] = s > 0 ? a.eVp[0] : a.eVp[1]; }
+                const double ep = s > 0 ? a.eVp[0] : a.eVp[1], em = s > 0 ? a.eVm[0] : a.eVm[1];
+                cs.sc_row[i] = a.direction > 0 ? ep : em;
+                cs.sc_col[i] = a.direction > 0 ? em : ep;
             }
-            __syncthreads();
+            chain_sync(bar_id, TPC);
             if (a.direction > 0) {
                 // G <- e^{-dtau T} diag(e^{+lambda s}) G diag(e^{-lambda s}) e^{+dtau T}
-                scale_rows<N>(acc, sm.sc_row, t);
-                r2s<N, false>(acc, sm.X, t);
-                __syncthreads();
-                gemm<N, false, false>(acc, sm.eT2, sm.X, t);
-                __syncthreads();
-                scale_cols<N>(acc, sm.sc_col, t);
-                r2s<N, false>(acc, sm.X, t);
-                __syncthreads();
-                gemm<N, false, false>(acc, sm.X, sm.eTinv2, t);
+                scale_rows<N>(acc, cs.sc_row, t);
+                r2s<N>(acc, cs.X, t);
+                chain_sync(bar_id, TPC);
+                gemm<N>(acc, sm.eT2, cs.X, t);
+                chain_sync(bar_id, TPC);
+                scale_cols<N>(acc, cs.sc_col, t);
+                r2s<N>(acc, cs.X, t);
+                chain_sync(bar_id, TPC);
+                gemm<N>(acc, cs.X, sm.eTinv2, t);
             } else {
                 // G <- diag(e^{-lambda s}) e^{+dtau T} G e^{-dtau T} diag(e^{+lambda s})
-                r2s<N, false>(acc, sm.X, t);
-                __syncthreads();
-                gemm<N, false, false>(acc, sm.eTinv2, sm.X, t);
-                __syncthreads();
-                scale_rows<N>(acc, sm.sc_row, t);
-                r2s<N, false>(acc, sm.X, t);
-                __syncthreads();
-                gemm<N, false, false>(acc, sm.X, sm.eT2, t);
-                scale_cols<N>(acc, sm.sc_col, t);
+                r2s<N>(acc, cs.X, t);
+                chain_sync(bar_id, TPC);
+                gemm<N>(acc, sm.eTinv2, cs.X, t);
+                chain_sync(bar_id, TPC);
+                scale_rows<N>(acc, cs.sc_row, t);
+                r2s<N>(acc, cs.X, t);
+                chain_sync(bar_id, TPC);
+                gemm<N>(acc, cs.X, sm.eT2, t);
+                scale_cols<N>(acc, cs.sc_col, t);
             }
         }
         // ---- sweep_spatial of `slice`
         const long long upd = a.n_updates0 + v;
         const uint32_t sweep = (uint32_t)(upd / (2LL * a.n_slices));
         const uint32_t visit = (uint32_t)(upd % (2LL * a.n_slices));
-        __syncthreads();
-        for (int i = t.tid; i < N; i += TH) {
-            sm.s_in[i] = cg[(size_t)(slice - 1) * N + i];
-            sm.unif[i] = dqmc_uniform(a.key0, k1, sweep, visit, (uint32_t)i);
+        for (int i = t.ctid; i < N; i += TPC) {
+            cs.s_in[i] = cg[(size_t)(slice - 1) * N + i];
+            cs.unif[i] = dqmc_uniform(a.key0, k1, sweep, visit, (uint32_t)i);
         }
-        // (the first __syncthreads of the site loop orders these writes before their reads)
-#pragma unroll
-        for (int it = 0; it < MT; ++it) {
-#pragma unroll
-            for (int rr = 0; rr < 8; ++rr) {
-                const int i = 8 * it + rr;
-                double* colb = sm.colbuf[rr & 1];
-                double* rowb = sm.rowbuf[rr & 1];
-                if (t.w == it && t.q == (rr >> 1)) {
-#pragma unroll
-                    for (int m = 0; m < MT; ++m) {
-                        const double g = (rr & 1) ? acc[m][1] : acc[m][0];
-                        colb[8 * m + t.r] = ((8 * m + t.r) == i ? 1.0 : 0.0) - g;
-                    }
-                }
-                if (t.r == rr) {
-                    rowb[8 * t.w + 2 * t.q] = acc[it][0];
-                    rowb[8 * t.w + 2 * t.q + 1] = acc[it][1];
-                }
-                __syncthreads();
-                const double gii = rowb[i];
-                const int s = sm.s_in[i];
-                const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
-                const double efac = s > 0 ? a.efac_p : a.efac_m;
-                const double rt = 1.0 + gamma * (1.0 - gii);
-                const double p = efac * (rt * rt);
-                const bool accept = (p > 1.0 || sm.unif[i] < p);
-                if (accept) {
-                    const double x = gamma / (1.0 + gamma * colb[i]);
-                    const double v0 = x * rowb[8 * t.w + 2 * t.q], v1 = x * rowb[8 * t.w + 2 * t.q + 1];
-#pragma unroll
-                    for (int m = 0; m < MT; ++m) {
-                        const double u = colb[8 * m + t.r];
-                        acc[m][0] -= u * v0;
-                        acc[m][1] -= u * v1;
-                    }
-                    ++nacc;
-                }
-                if (t.tid == 0) sm.s_out[i] = (int8_t)(accept ? -s : s);
-            }
-        }
-        __syncthreads();
-        for (int i = t.tid; i < N; i += TH) cg[(size_t)(slice - 1) * N + i] = sm.s_out[i];
+        chain_sync(bar_id, TPC);
+        site_block<N, 0>(acc, cs, a, t, bar_id, nacc);
+        chain_sync(bar_id, TPC);
+        for (int i = t.ctid; i < N; i += TPC) cg[(size_t)(slice - 1) * N + i] = cs.s_out[i];
     }
     bool bad = false;
 #pragma unroll
-    for (int m = 0; m < MT; ++m) bad |= !isfinite(acc[m][0]) || !isfinite(acc[m][1]);
-    r2g<N>(acc, Gg, t);
-    const int anybad = __syncthreads_or(bad);
-    if (t.tid == 0) {
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+        for (int cw = 0; cw < CW; ++cw)
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const double g = acc[m][cw][c];
+                bad |= !isfinite(g);
+                Gg[(8 * m + t.r) + (size_t)(t.col0 + 8 * cw + c) * N] = g;
+            }
+    if (bad) cs.accept[0] = -1; // (benign race: any writer flags the chain)
+    chain_sync(bar_id, TPC);
+    if (t.ctid == 0) {
         a.acc[chain] += nacc;
         a.prop[chain] += (long long)N * a.n_visits;
-        if (anybad) a.nonfinite[chain] += 1;
+        if (cs.accept[0] == -1) a.nonfinite[chain] += 1;
     }
 }
 
@@ -158,7 +304,7 @@ int launch_t(const SegmentArgs& a, cudaStream_t st)
     // acceptance counters
     const int wraps = a.n_visits - 1 + (a.first_wrap ? 1 : 0);
     LaunchScope scope(LC_FUSED, st, 4.0 * N * (double)N * N * wraps * a.batch);
-    segment_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(SegSmem<N>), st>>>(a);
+    segment_kernel<N><<<(a.batch + CH - 1) / CH, SGeo<N>::THREADS, sizeof(SegSmem<N>), st>>>(a);
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
