@@ -9,3 +9,4 @@ from .models import HubbardModelAttractive, IsingModel, IsingTc  # noqa: F401
 from .dqmc import DQMC, DQMCParameters, mean_and_error  # noqa: F401
 from .mc import MC  # noqa: F401
 from ._lib import McbError  # noqa: F401
+from .sharding import ShardedDQMC, shard, reduce_observables  # noqa: F401

@@ -264,3 +264,20 @@ def test_errors_are_reported():
     with pytest.raises(mcb.McbError):
         mc.update(1)  # build_stack first
     mc.close()
+
+
+def test_sharded_run_equals_plain_run_on_one_gpu():
+    """ShardedDQMC (the multi-GPU driver) with world_size 1: same chains, same observables."""
+    model = mcb.HubbardModelAttractive(L=4, U=2.0)
+    kw = dict(beta=1.0, delta_tau=0.1, safe_mult=5, thermalization=2, sweeps=6, measure_rate=2)
+    mc = mcb.DQMC(model, n_chains=6, seed=5, **kw)
+    obs = mc.run()
+    mc.close()
+    sh = mcb.ShardedDQMC(model, 6, seed=5, **kw)
+    res, n = sh.run()
+    sh.close()
+    assert n == 6
+    for key in ("occupation", "double_occupancy", "energy", "cdc", "swave_pairing", "G"):
+        mean, err = mcb.mean_and_error(obs[key])
+        assert np.allclose(res[key][0], mean, rtol=1e-12, atol=1e-14)
+        assert np.allclose(res[key][1], err, rtol=1e-8, atol=1e-14)
