@@ -32,6 +32,7 @@ static int use_device(int dev)
     if (dev >= 0 && dev < 64 && !inited[dev]) {
         API_TRY(init_udt_kernels());
         API_TRY(init_sweep_kernels());
+        API_TRY(init_sweep_delayed_kernels());
         API_TRY(init_segment_kernels());
         API_TRY(init_stab_kernels());
         inited[dev] = true;

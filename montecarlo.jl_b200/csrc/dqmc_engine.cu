@@ -385,7 +385,9 @@ int engine_update(mcb_dqmc* h)
     a.sweep = (uint32_t)(h->n_updates / (2 * (int64_t)h->M));
     a.visit = (uint32_t)(h->n_updates % (2 * (int64_t)h->M));
     a.acc = h->acc; a.prop = h->prop; a.nonfinite = h->nonfinite;
-    MCB_TRY(launch_sweep_spatial(a, h->st));
+    // immediate rank-1 updates only where the whole update is a handful of elements per thread
+    if (h->N >= 16) MCB_TRY(launch_sweep_delayed(a, h->st));
+    else MCB_TRY(launch_sweep_spatial(a, h->st));
     h->n_updates += 1;
     return 0;
 }

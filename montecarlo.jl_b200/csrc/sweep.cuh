@@ -19,5 +19,8 @@ struct SweepArgs {
 
 int launch_sweep_spatial(const SweepArgs& a, cudaStream_t st);
 int init_sweep_kernels();
+// same contract, delayed rank-k updates flushed on the FP64 tensor pipe (sweep_delayed.cu)
+int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st);
+int init_sweep_delayed_kernels();
 
 } // namespace mcb

@@ -1,0 +1,241 @@
+// sweep_spatial (src/flavors/DQMC/DQMC.jl:546-582) with propose_local / accept_local!
+// (src/models/HubbardModel/HubbardModelAttractive.jl:113-155) for any N, with DELAYED rank-k
+// Green's-function updates: one CTA per chain, G stays in global memory (L2).
+//
+// The sites of a slice are processed in blocks of K. For a block starting at site i0 the CTA holds
+// in shared memory the K current columns Cc = G[:, i0:i0+K) and the K current rows Rc = G[i0:i0+K, :].
+// An accepted flip at site i = i0 + j is the rank-1 update G -= u v' with u = x (e_i - G[:, i]),
+// v = G[i, :], x = gamma / (1 + gamma (1 - G_ii))  (accept_local!, :142-153). It is applied at once
+// only to the columns j' > j of Cc and the rows k > j of Rc (2 K N flop instead of 2 N^2); u is
+// recorded in U[:, j], v stays frozen in Rc[j, :]. After the block the whole matrix is brought up to
+// date with ONE product G -= U * Rc (N x K x N) on the FP64 tensor pipe. The Metropolis decisions see
+// exactly the Green's function the immediate updates would give (the arithmetic is re-associated only).
+// One barrier per site: the next site's G_ii is published by the thread that owns its row.
+#include "sweep.cuh"
+
+namespace mcb {
+
+namespace {
+
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+struct DelayedGeom {
+    int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
+    size_t smem;
+};
+
+__host__ __device__ inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+DelayedGeom delayed_geom(int n)
+{
+    DelayedGeom g;
+    g.n = n;
+    g.np = round_up(n, 8);
+    g.ld = g.np + ((20 - g.np % 16) % 16 == 0 ? 16 : (20 - g.np % 16) % 16); // ld % 16 == 4, ld > np
+    const size_t hdr = (size_t)(2 * n + 16) * sizeof(double) + 2 * (size_t)round_up(n, 8);
+    int K = (int)((SMEM_LIMIT - 2048 - hdr) / (3 * (size_t)g.ld * sizeof(double)));
+    K = K / 4 * 4;
+    if (K > 32) K = 32;
+    if (K > round_up(n, 4)) K = round_up(n, 4);
+    g.K = K;
+    g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
+    g.smem = hdr + 3 * (size_t)K * g.ld * sizeof(double);
+    return g;
+}
+
+// 1/x to ~1 ulp: hardware seed + two Newton steps (x is 1 + gamma (1 - G_ii), never subnormal here)
+__device__ __forceinline__ double fast_rcp(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
+}
+
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, DelayedGeom g)
+{
+    extern __shared__ __align__(16) double sm[];
+    const int n = g.n, ld = g.ld, K = g.K;
+    const int chain = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    double* unif = sm;                  // [n]
+    double* gnext = unif + n;           // [2] G_ii of the next site (double buffered)
+    double* Cc = gnext + 16;            // [K][ld]  column j of the block at Cc + j*ld
+    double* Rc = Cc + (size_t)K * ld;   // [K][ld]  row k of the block at Rc + k*ld
+    double* U = Rc + (size_t)K * ld;    // [K][ld]  recorded u of site j at U + j*ld (zero if rejected)
+    int8_t* s_in = (int8_t*)(U + (size_t)K * ld);
+    int8_t* s_out = s_in + round_up(n, 8);
+    double* Gg = a.G + (size_t)chain * a.sG;
+    int8_t* cg = a.conf + (size_t)chain * a.sConf;
+
+    for (int i = tid; i < n; i += T) {
+        s_in[i] = cg[i];
+        unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
+    }
+    int nacc = 0;
+    const int nv = round_up(n, 32);                 // threads per group (whole warps)
+    // groups of nv threads that share the per-site work; more groups shorten the loops but every
+    // extra warp repeats the fixed per-site instructions, so two groups at most
+    const int ngrp = T / nv >= 2 ? 2 : 1;
+    const int warp = tid >> 5, lane = tid & 31, r = lane >> 2, q = lane & 3, nwarps = T >> 5;
+
+    // thread = (element e of a length-n vector, group grp): the groups stride over the remaining
+    // columns / rows of the block so that all threads have work
+    const int e = tid % nv, grp = tid / nv;
+    const bool worker = grp < ngrp && e < n;
+    const int gstep = ngrp * ld;
+
+    for (int i0 = 0; i0 < n; i0 += K) {
+        const int kb = min(K, n - i0);
+        const int kb4 = round_up(kb, 4);
+        __syncthreads(); // previous flush done (G up to date, buffers free)
+        // ---- load the block's columns and rows; zero the padding the flush will read
+        for (int j = warp; j < kb4; j += nwarps) {
+            const double* gcol = Gg + (size_t)(i0 + j) * n;
+            for (int row = lane; row < ld; row += 32) {
+                Cc[j * ld + row] = (j < kb && row < n) ? gcol[row] : 0.0;
+                U[j * ld + row] = 0.0;
+            }
+        }
+        for (int l = warp; l < ld; l += nwarps) {
+            const double* gcol = Gg + (size_t)l * n + i0;
+            for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
+        }
+        if (tid == 0) gnext[0] = Gg[i0 + (size_t)i0 * n];
+        for (int j = 0; j < kb; ++j) {
+            __syncthreads();
+            if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
+            const int i = i0 + j;
+            const double gii = gnext[j & 1];
+            const int s = s_in[i];
+            const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+            const double efac = s > 0 ? a.efac_p : a.efac_m;
+            const double rt = 1.0 + gamma * (1.0 - gii);
+            const double p = efac * (rt * rt);
+            const bool accept = (p > 1.0 || unif[i] < p); // uniform over the CTA
+            const double* cj = Cc + j * ld;
+            const double* vj = Rc + j * ld;
+            if (accept) {
+                const double x = gamma * fast_rcp(rt);
+                if (worker) {
+                    // columns j' > j of the block: element (row e, column j')
+                    const double u = x * ((e == i ? 1.0 : 0.0) - cj[e]);
+                    if (grp == 0) U[j * ld + e] = u;
+                    const int first = j + 1 + grp;
+                    double* cp = Cc + first * ld + e;
+                    const double* vp = vj + i0 + first;
+                    if (grp == 0 && e == i + 1 && first < kb) {
+                        const double cnew = *cp - u * *vp;
+                        gnext[(j + 1) & 1] = cnew;
+                    }
+                    // (operands are fetched four iterations at a time: the compiler cannot prove that
+                    // the stores do not alias the next loads)
+                    const double xv = x * vj[e];
+                    double* rp = Rc + first * ld + e;
+                    const double* up = cj + i0 + first;
+                    for (int jp = first; jp < kb; jp += 4 * ngrp) {
+                        double c[4], v[4], rr[4], uu[4];
+#pragma unroll
+                        for (int z = 0; z < 4; ++z) {
+                            const bool ok = jp + z * ngrp < kb;
+                            c[z] = ok ? cp[z * gstep] : 0.0;
+                            v[z] = ok ? vp[z * ngrp] : 0.0;
+                            rr[z] = ok ? rp[z * gstep] : 0.0;
+                            uu[z] = ok ? up[z * ngrp] : 0.0;
+                        }
+#pragma unroll
+                        for (int z = 0; z < 4; ++z) {
+                            if (jp + z * ngrp < kb) {
+                                cp[z * gstep] = c[z] - u * v[z];    // columns j' > j: element (row e, column j')
+                                rp[z * gstep] = rr[z] + uu[z] * xv; // rows k > j: element (row k, column e), u_k = -x G[i0+k, i]
+                            }
+                        }
+                        cp += 4 * gstep; vp += 4 * ngrp; rp += 4 * gstep; up += 4 * ngrp;
+                    }
+                }
+                ++nacc;
+            } else if (j + 1 < kb) {
+                if (tid == 0) gnext[(j + 1) & 1] = Cc[(j + 1) * ld + i + 1];
+            }
+            if (tid == 0) s_out[i] = (int8_t)(accept ? -s : s);
+        }
+        __syncthreads();
+        // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
+        const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
+        for (int tile = warp; tile < tm * tn; tile += nwarps) {
+            const int row0 = (tile % tm) * 32, col0 = (tile / tm) * 16;
+            // rows / columns past the padded size are clamped: their products are never stored
+            const double* ua[4];
+            const double* rb[2];
+#pragma unroll
+            for (int x = 0; x < 4; ++x) ua[x] = U + q * ld + min(row0 + 8 * x + r, g.np - 1);
+#pragma unroll
+            for (int y = 0; y < 2; ++y) rb[y] = Rc + q * ld + min(col0 + 8 * y + r, g.np - 1);
+            double c[4][2][2];
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 2; ++y) c[x][y][0] = c[x][y][1] = 0.0;
+            for (int k0 = 0; k0 < kb4; k0 += 4) {
+                double av[4], bv[2];
+#pragma unroll
+                for (int x = 0; x < 4; ++x) av[x] = ua[x][k0 * ld];
+#pragma unroll
+                for (int y = 0; y < 2; ++y) bv[y] = rb[y][k0 * ld];
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 2; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
+            }
+            // read-modify-write of the tile: all loads first, then the stores
+            double gold[4][2][2];
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 2; ++y)
+#pragma unroll
+                    for (int cc = 0; cc < 2; ++cc) {
+                        const int row = row0 + 8 * x + r, col = col0 + 8 * y + 2 * q + cc;
+                        gold[x][y][cc] = (row < n && col < n) ? Gg[row + (size_t)col * n] : 0.0;
+                    }
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 2; ++y)
+#pragma unroll
+                    for (int cc = 0; cc < 2; ++cc) {
+                        const int row = row0 + 8 * x + r, col = col0 + 8 * y + 2 * q + cc;
+                        if (row < n && col < n) Gg[row + (size_t)col * n] = gold[x][y][cc] - c[x][y][cc];
+                    }
+        }
+    }
+    __syncthreads();
+    bool bad = false;
+    for (size_t e = tid; e < (size_t)n * n; e += T) bad |= !isfinite(Gg[e]);
+    for (int i = tid; i < n; i += T) cg[i] = s_out[i];
+    if (__syncthreads_or(bad) && tid == 0) a.nonfinite[chain] += 1;
+    if (tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
+}
+
+} // namespace
+
+int init_sweep_delayed_kernels()
+{
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    return 0;
+}
+
+int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
+{
+    const DelayedGeom g = delayed_geom(a.n);
+    if (g.K < 4) { set_error("delayed sweep: matrix too large for one CTA's shared memory"); return -1; }
+    LaunchScope scope(LC_SWEEP, st, 0.0);
+    if (g.threads <= 512) sweep_delayed_kernel<512><<<a.batch, g.threads, g.smem, st>>>(a, g);
+    else sweep_delayed_kernel<1024><<<a.batch, g.threads, g.smem, st>>>(a, g);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace mcb
