@@ -106,10 +106,13 @@ __device__ __forceinline__ void qr_pivot(double (&A)[Geo<N>::MT][2], QrSmem<N>& 
             }
             {
                 const int bc = bk & 0xffff;
-                if (bc == col0 || bc == col0 + 1) {
-                    const int c = bc - col0;
+                double* cd = qs.cand[buf][t.w] + t.r;
+                if (bc == col0) {
 #pragma unroll
-                    for (int m = mj; m < MT; ++m) qs.cand[buf][t.w][8 * m + t.r] = c ? A[m][1] : A[m][0];
+                    for (int m = mj; m < MT; ++m) cd[8 * m] = A[m][0];
+                } else if (bc == col0 + 1) {
+#pragma unroll
+                    for (int m = mj; m < MT; ++m) cd[8 * m] = A[m][1];
                 }
                 if (t.l == 0) { qs.cval[buf][t.w] = bv; qs.ckey[buf][t.w] = bk; }
             }
@@ -149,23 +152,24 @@ __device__ __forceinline__ void qr_pivot(double (&A)[Geo<N>::MT][2], QrSmem<N>& 
                 for (int m = mj; m < MT; ++m) dot += v[m] * A[m][c];
                 dot = col_sum(dot);
                 const double s = (done[c] || is_piv) ? 0.0 : tj * dot;
-                double nn = 0.0;
-                {
-                    double a = A[mj][c] - s * v[mj];
-                    if (is_piv && live) a = t.r < rj ? a : (t.r == rj ? -nu : v[mj]);
-                    A[mj][c] = a;
-                    nn = t.r > rj ? a * a : 0.0;
-                }
 #pragma unroll
-                for (int m = mj + 1; m < MT; ++m) {
-                    double a = A[m][c] - s * v[m];
-                    if (is_piv && live) a = v[m];
-                    A[m][c] = a;
-                    nn += a * a;
-                }
+                for (int m = mj; m < MT; ++m) A[m][c] -= s * v[m];
+                double nn = t.r > rj ? A[mj][c] * A[mj][c] : 0.0;
+#pragma unroll
+                for (int m = mj + 1; m < MT; ++m) nn += A[m][c] * A[m][c];
                 nrm[c] = col_sum(nn);
                 if (is_piv) done[c] = true;
                 else if (!done[c] && curpos[c] == j) curpos[c] = jm; // the swap j <-> jm (UDT.jl:219-231)
+            }
+            // the pivot column keeps R above the diagonal, -nu on it and the Householder vector below
+            if (live && col0 == pj) {
+                if (t.r >= rj) A[mj][0] = t.r == rj ? -nu : v[mj];
+#pragma unroll
+                for (int m = mj + 1; m < MT; ++m) A[m][0] = v[m];
+            } else if (live && col0 + 1 == pj) {
+                if (t.r >= rj) A[mj][1] = t.r == rj ? -nu : v[mj];
+#pragma unroll
+                for (int m = mj + 1; m < MT; ++m) A[m][1] = v[m];
             }
             if (t.tid == 0) { qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j; }
         }

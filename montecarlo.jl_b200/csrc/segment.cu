@@ -14,10 +14,12 @@
 //
 // Wrap: two N^3 products on the FP64 tensor pipe; the slice matrices B_l = e^{-dtau T} diag(e^{lambda s})
 // are never materialised (slice_matrices.jl:23-39): the diagonal factor is applied in registers.
-// Local updates: ONE barrier per site. The warp that owns column i takes G_ii by shuffle, evaluates
-// the Metropolis decision and publishes x (e_i - G[:,i]) with x = gamma / (1 + gamma (1 - G_ii)); the
-// holders of row i publish it; after the barrier every thread applies the rank-1 update to its 32
-// register elements. Publication buffers are double-buffered over sites.
+// Local updates: DELAYED rank-8 updates, two barriers per block of 8 sites. All warps publish the 8
+// rows of the block; the ONE warp that owns its 8 columns then runs the 8 strictly sequential
+// Metropolis decisions on private copies of those rows and columns (warp-local: shuffles and
+// __syncwarp only), recording  -x (e_i - G[:,i])  and  G[i,:]  of every accepted flip
+// (accept_local!, x = gamma / (1 + gamma (1 - G_ii))); after the second barrier every warp applies
+// G += NUX * V (N x 8 x N) to its registers on the FP64 tensor pipe.
 #include "segment.cuh"
 
 namespace mcb {
@@ -39,15 +41,19 @@ struct SGeo {
 
 template <int N>
 struct alignas(16) ChainSmem {
-    double X[N * SGeo<N>::LD];
-    double ux[2][N];   // x * (e_i - G[:, i])
-    double row[2][N];  // G[i, :]
+    static constexpr int LD = SGeo<N>::LD;
+    static constexpr int XSIZE = N * LD > 24 * LD ? N * LD : 24 * LD;
+    double X[XSIZE];   // wrap: staging matrix; site loop: Rb | NUX | V (8 x LD each)
     double unif[N];
     double sc_row[N];
     double sc_col[N];
-    int accept[2];
+    int flag;
+    int nacc;
     int8_t s_in[N];
     int8_t s_out[N];
+    __device__ double* Rb() { return X; }            // rows of the current block, Rb[k*LD + col]
+    __device__ double* NUX() { return X + 8 * LD; }  // -x (e_i - G[:, i]) of site j at NUX[j*LD + row]
+    __device__ double* V() { return X + 16 * LD; }   // G[i, :] of site j at V[j*LD + col]
 };
 
 template <int N>
@@ -130,70 +136,112 @@ __device__ __forceinline__ void scale_cols(double (&acc)[SGeo<N>::MT][CW][2], co
     }
 }
 
-// one site of sweep_spatial; IT = row block of site i, RR = i % 8 (compile time)
-template <int N, int IT, int RR>
-__device__ __forceinline__ void site_update(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,
-                                            const SegmentArgs& a, const CLane& t, int bar_id, int& nacc)
+// 1/x to ~1 ulp: hardware seed + two Newton steps (x = 1 + gamma (1 - G_ii) is never subnormal)
+__device__ __forceinline__ double fast_rcp(double x)
 {
-    constexpr int MT = SGeo<N>::MT;
-    constexpr int i = 8 * IT + RR;
-    constexpr int WI = i / (8 * CW), CWI = (i / 8) % CW, QI = (i % 8) / 2, CI = i % 2; // owner of column i
-    constexpr int buf = RR & 1;
-    double* ux = cs.ux[buf];
-    double* row = cs.row[buf];
-    if (t.wl == WI) {
-        // G_ii sits in lane (r = RR, q = QI) of this warp
-        const double gii = __shfl_sync(0xffffffffu, acc[IT][CWI][CI], RR * 4 + QI);
-        const int s = cs.s_in[i];
-        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
-        const double efac = s > 0 ? a.efac_p : a.efac_m;
-        const double rt = 1.0 + gamma * (1.0 - gii);       // propose_local: detratio = rt^2
-        const double p = efac * (rt * rt);                  // DQMC.jl:570
-        const bool accept = (p > 1.0 || cs.unif[i] < p);    // DQMC.jl:573
-        if (accept && t.q == QI) {
-            const double x = gamma / rt;                    // accept_local!: gamma / (1 + gamma u_i)
-#pragma unroll
-            for (int m = 0; m < MT; ++m)
-                ux[8 * m + t.r] = x * (((8 * m + t.r) == i ? 1.0 : 0.0) - acc[m][CWI][CI]);
-        }
-        if (t.l == 0) { cs.accept[buf] = accept; cs.s_out[i] = (int8_t)(accept ? -s : s); }
-    }
-    if (t.r == RR) {
-#pragma unroll
-        for (int cw = 0; cw < CW; ++cw)
-            *reinterpret_cast<double2*>(row + t.col0 + 8 * cw) = make_double2(acc[IT][cw][0], acc[IT][cw][1]);
-    }
-    chain_sync(bar_id, SGeo<N>::TPC);
-    if (cs.accept[buf]) {
-        double2 v[CW];
-#pragma unroll
-        for (int cw = 0; cw < CW; ++cw) v[cw] = *reinterpret_cast<const double2*>(row + t.col0 + 8 * cw);
-#pragma unroll
-        for (int m = 0; m < MT; ++m) {
-            const double u = ux[8 * m + t.r];
-#pragma unroll
-            for (int cw = 0; cw < CW; ++cw) {
-                acc[m][cw][0] -= u * v[cw].x;
-                acc[m][cw][1] -= u * v[cw].y;
-            }
-        }
-        ++nacc;
-    }
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
 }
 
+// sites 8 IT .. 8 IT + 7 of sweep_spatial
 template <int N, int IT>
 __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,
                                            const SegmentArgs& a, const CLane& t, int bar_id, int& nacc)
 {
-    site_update<N, IT, 0>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 1>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 2>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 3>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 4>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 5>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 6>(acc, cs, a, t, bar_id, nacc);
-    site_update<N, IT, 7>(acc, cs, a, t, bar_id, nacc);
-    if constexpr (IT + 1 < SGeo<N>::MT) site_block<N, IT + 1>(acc, cs, a, t, bar_id, nacc);
+    constexpr int MT = SGeo<N>::MT, LD = SGeo<N>::LD, TPC = SGeo<N>::TPC;
+    constexpr int WI = IT / CW, CWI = IT % CW;  // owner of the block's 8 columns
+    constexpr int NH = (N + 31) / 32;           // row-vector elements per lane
+    constexpr int HB = (8 * IT) / 32;           // which of them holds the block's own columns
+    double* Rb = cs.Rb();
+    double* NUX = cs.NUX();
+    double* V = cs.V();
+    // ---- phase 1: everybody publishes its part of the rows 8 IT .. 8 IT + 7
+#pragma unroll
+    for (int cw = 0; cw < CW; ++cw)
+        *reinterpret_cast<double2*>(Rb + t.r * LD + t.col0 + 8 * cw) = make_double2(acc[IT][cw][0], acc[IT][cw][1]);
+    chain_sync(bar_id, TPC);
+    // ---- phase 2: the column owner decides the 8 sites
+    if (t.wl == WI) {
+        // the block's own 8 columns are updated in place (phase 3 leaves them alone)
+        double rb[8][NH];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int h = 0; h < NH; ++h) rb[k][h] = Rb[k * LD + min(t.l + 32 * h, N - 1)];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int i = 8 * IT + j;
+            const double gii = __shfl_sync(0xffffffffu, acc[IT][CWI][j & 1], j * 4 + (j >> 1));
+            const int s = cs.s_in[i];
+            const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+            const double efac = s > 0 ? a.efac_p : a.efac_m;
+            const double rt = 1.0 + gamma * (1.0 - gii);       // propose_local: detratio = rt^2
+            const double p = efac * (rt * rt);                  // DQMC.jl:570
+            const bool accept = (p > 1.0 || cs.unif[i] < p);    // DQMC.jl:573 (uniform over the warp)
+#pragma unroll
+            for (int h = 0; h < NH; ++h)
+                if (t.l + 32 * h < N) V[j * LD + t.l + 32 * h] = rb[j][h];
+            if (accept) {
+                const double x = gamma * fast_rcp(rt);          // accept_local!: gamma / (1 + gamma u_i)
+                if (t.q == (j >> 1)) {
+#pragma unroll
+                    for (int m = 0; m < MT; ++m)
+                        NUX[j * LD + 8 * m + t.r] = x * (acc[m][CWI][j & 1] - ((8 * m + t.r) == i ? 1.0 : 0.0));
+                }
+                __syncwarp();
+                // columns of the block: G[:, 8 IT + 2q + c] += nux * v[8 IT + 2q + c]
+                const int src = (8 * IT + 2 * t.q) & 31;
+                const double v0 = __shfl_sync(0xffffffffu, rb[j][HB], src);
+                const double v1 = __shfl_sync(0xffffffffu, rb[j][HB], src + 1);
+#pragma unroll
+                for (int m = 0; m < MT; ++m) {
+                    const double nu = NUX[j * LD + 8 * m + t.r];
+                    acc[m][CWI][0] += nu * v0;
+                    acc[m][CWI][1] += nu * v1;
+                }
+                // rows of the block: rb[k, :] += nux[8 IT + k] * v
+                if (j < 7) {
+                    double vh[NH];
+#pragma unroll
+                    for (int h = 0; h < NH; ++h) vh[h] = rb[j][h];
+#pragma unroll
+                    for (int k = j + 1; k < 8; ++k) {
+                        const double nk = NUX[j * LD + 8 * IT + k];
+#pragma unroll
+                        for (int h = 0; h < NH; ++h) rb[k][h] += nk * vh[h];
+                    }
+                }
+                ++nacc;
+            } else if (t.q == (j >> 1)) {
+#pragma unroll
+                for (int m = 0; m < MT; ++m) NUX[j * LD + 8 * m + t.r] = 0.0;
+            }
+            if (t.l == 0) cs.s_out[i] = (int8_t)(accept ? -s : s);
+        }
+    }
+    chain_sync(bar_id, TPC);
+    // ---- phase 3: G += NUX * V on the tensor pipe (k = 8)
+    {
+        const double* ap = NUX + t.q * LD + t.r;
+        const double* bp = V + t.q * LD + 8 * CW * t.wl + t.r;
+#pragma unroll
+        for (int k0 = 0; k0 < 8; k0 += 4) {
+            double b[CW];
+#pragma unroll
+            for (int cw = 0; cw < CW; ++cw) b[cw] = bp[k0 * LD + 8 * cw];
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                const double av = ap[k0 * LD + 8 * m];
+#pragma unroll
+                for (int cw = 0; cw < CW; ++cw)
+                    if (!(cw == CWI && t.wl == WI)) dmma884(acc[m][cw][0], acc[m][cw][1], av, b[cw]);
+            }
+        }
+    }
+    if constexpr (IT + 1 < MT) site_block<N, IT + 1>(acc, cs, a, t, bar_id, nacc);
 }
 
 template <int N>
@@ -227,7 +275,8 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
 #pragma unroll
             for (int c = 0; c < 2; ++c) acc[m][cw][c] = Gg[(8 * m + t.r) + (size_t)(t.col0 + 8 * cw + c) * N];
 
-    int nacc = 0;
+    int nacc = 0; // accepted flips decided by this warp
+    if (t.ctid == 0) { cs.flag = 0; cs.nacc = 0; }
     for (int v = 0; v < a.n_visits; ++v) {
         const int slice = a.start_slice + a.direction * v;
         if (v > 0 || a.first_wrap) {
@@ -288,12 +337,13 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
                 bad |= !isfinite(g);
                 Gg[(8 * m + t.r) + (size_t)(t.col0 + 8 * cw + c) * N] = g;
             }
-    if (bad) cs.accept[0] = -1; // (benign race: any writer flags the chain)
+    if (bad) cs.flag = -1; // (benign race: any writer flags the chain)
+    if (t.l == 0 && nacc) atomicAdd(&cs.nacc, nacc);
     chain_sync(bar_id, TPC);
     if (t.ctid == 0) {
-        a.acc[chain] += nacc;
+        a.acc[chain] += cs.nacc;
         a.prop[chain] += (long long)N * a.n_visits;
-        if (cs.accept[0] == -1) a.nonfinite[chain] += 1;
+        if (cs.flag == -1) a.nonfinite[chain] += 1;
     }
 }
 
