@@ -370,6 +370,14 @@ def run_dqmc(args, w, rank, local_rank, world):
         line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
                             "frac": gbs / hbm_peak, "traffic": traffic_for(top), "avg_launch_us": k["avg_us"],
                             "share_of_step": k["share"], "peak_source": hbm_src}
+    # the one collective of the path: all-reduce of per-chain moments over the ranks (NCCL when
+    # world > 1). Not timed: it happens once per run, after the sweeps.
+    from montecarlo_jl_b200 import sharding
+    rate = (st1["acc_local"] - st0["acc_local"]) / np.maximum(1, st1["prop_local"] - st0["prop_local"])
+    red, n_red = sharding.reduce_observables({"acceptance": rate}, device=dev)
+    line["observable_reduction"] = {"chains": n_red, "acceptance_mean": float(red["acceptance"][0]),
+                                    "acceptance_stderr": float(red["acceptance"][1]),
+                                    "collective": "nccl all_reduce(sum) of moments" if world > 1 else "none (1 rank)"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         b = cpu_dqmc_baseline(w)
         line["cpu_baseline"] = {k2: b[k2] for k2 in ("value", "unit", "cores", "kind", "sample")}

@@ -94,6 +94,26 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "d"(a), "d"(b));
 }
 
+// 1/x and 1/sqrt(x) to ~1 ulp for normal, positive-magnitude x: hardware seed (20 mantissa bits) and
+// two Newton steps; no special-case branches (callers guard x == 0 themselves).
+__device__ __forceinline__ double fast_rcp(double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
+}
+__device__ __forceinline__ double fast_rsqrt(double x)
+{
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double hx = 0.5 * x;
+    r = fma(fma(-hx * r, r, 0.5), r, r);
+    r = fma(fma(-hx * r, r, 0.5), r, r);
+    return r;
+}
+
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll

@@ -133,10 +133,13 @@ __device__ __forceinline__ void qr_pivot(double (&A)[Geo<N>::MT][2], QrSmem<N>& 
             double nu = 0.0, tj = 0.0, inv = 0.0;
             const bool live = maxval > 0.0;
             if (live) {
-                nu = copysign(sqrt(maxval), xj);
+                // nu = copysign(||x||, x_j), tau = (x_j + nu) / nu, inv = 1 / (x_j + nu), from one
+                // reciprocal square root and one reciprocal (Newton-refined hardware seeds)
+                const double rs = fast_rsqrt(maxval);
+                nu = copysign(maxval * rs, xj);
                 const double xjn = xj + nu;
-                tj = xjn / nu;
-                inv = 1.0 / xjn;
+                tj = xjn * copysign(rs, xj);
+                inv = fast_rcp(xjn);
             }
             // v = (0 .. 0, 1, x[j+1:] / (x_j + nu)); only the row blocks m >= mj are touched
             double v[MT];
@@ -264,7 +267,7 @@ __device__ __forceinline__ void rsolve_t(double (&B)[Geo<N>::MT][2], double (&Y)
                 if (pm == m) { s0 = B[m][0]; s1 = B[m][1]; }
             const int src = ((p & 7) << 2) | t.q;
             const double* trow = Tt + (size_t)j * LD;
-            const double rinv = 1.0 / trow[p];
+            const double rinv = fast_rcp(trow[p]);
             const double y0 = __shfl_sync(FULL, s0, src) * rinv;
             const double y1 = __shfl_sync(FULL, s1, src) * rinv;
             if (t.r == rj) { Y[mj][0] = y0; Y[mj][1] = y1; }

@@ -136,16 +136,6 @@ __device__ __forceinline__ void scale_cols(double (&acc)[SGeo<N>::MT][CW][2], co
     }
 }
 
-// 1/x to ~1 ulp: hardware seed + two Newton steps (x = 1 + gamma (1 - G_ii) is never subnormal)
-__device__ __forceinline__ double fast_rcp(double x)
-{
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-    r = fma(fma(-x, r, 1.0), r, r);
-    r = fma(fma(-x, r, 1.0), r, r);
-    return r;
-}
-
 // sites 8 IT .. 8 IT + 7 of sweep_spatial
 template <int N, int IT>
 __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,

@@ -43,16 +43,6 @@ DelayedGeom delayed_geom(int n)
     return g;
 }
 
-// 1/x to ~1 ulp: hardware seed + two Newton steps (x is 1 + gamma (1 - G_ii), never subnormal here)
-__device__ __forceinline__ double fast_rcp(double x)
-{
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-    r = fma(fma(-x, r, 1.0), r, r);
-    r = fma(fma(-x, r, 1.0), r, r);
-    return r;
-}
-
 template <int MAXT>
 __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, DelayedGeom g)
 {
