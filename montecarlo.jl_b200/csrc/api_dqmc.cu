@@ -30,6 +30,7 @@ static int use_device(int dev)
     MCB_CUDA(cudaSetDevice(dev));
     static bool inited[64] = {};
     if (dev >= 0 && dev < 64 && !inited[dev]) {
+        API_TRY(init_gemm_kernels());
         API_TRY(init_udt_kernels());
         API_TRY(init_sweep_kernels());
         API_TRY(init_sweep_delayed_kernels());

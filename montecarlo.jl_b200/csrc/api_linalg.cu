@@ -27,6 +27,7 @@ int prepare(int dev)
         return MCB_ERR_CUDA;
     }
     MCB_CUDA(cudaSetDevice(dev));
+    if (init_gemm_kernels() != 0) return MCB_ERR_CUDA;
     if (init_udt_kernels() != 0) return MCB_ERR_CUDA;
     if (init_stab_kernels() != 0) return MCB_ERR_CUDA;
     return 0;

@@ -1,26 +1,34 @@
-// Batched FP64 DMMA GEMM, tile 64x64x16, 4 warps (2x2) of 32x32, register-staged double
-// buffering (global loads of tile k+1 are in flight while tile k is multiplied).
+// Batched FP64 DMMA GEMM, square tile T x T x 16 with T in {48, 64, 80} chosen so that it divides the
+// matrix size (12x12 lattice -> 48, 8x8 -> 64, 20x20 -> 80; no padded tiles), 4 warps (2x2) of
+// T/2 x T/2, register-staged double buffering (global loads of tile k+1 are in flight while tile k
+// is multiplied).
 #include "gemm.cuh"
 
 namespace mcb {
 
 namespace {
 
-constexpr int BM = 64, BN = 64, BK = 16;
+constexpr int BK = 16;
 constexpr int THREADS = 128;
-constexpr int LDX = BM + 4;  // [k][x] layout: conflict-free fragment reads need ld % 16 == 4
 constexpr int LDK = BK + 4;  // [x][k] layout
-constexpr int TILE_ELEMS = BM * BK; // 1024, 8 per thread
-constexpr int PER_THREAD = TILE_ELEMS / THREADS;
-constexpr int SMEM_TILE = (BM * LDK > BK * LDX) ? BM * LDK : BK * LDX; // 1280 doubles
+
+template <int T>
+struct Tile {
+    static constexpr int LDX = T + 4;  // [k][x] layout: conflict-free fragment reads need ld % 16 == 4
+    static constexpr int PER_THREAD = T * BK / THREADS;
+    static constexpr int SMEM_TILE = (T * LDK > BK * LDX) ? T * LDK : BK * LDX;
+    static constexpr int WT = T / 16;  // DMMA tiles per warp in each direction (warp tile T/2 x T/2)
+    static_assert((T * BK) % THREADS == 0 && T % 16 == 0 && LDX % 16 == 4, "unsupported tile");
+};
 
 // XC = the tile is contiguous in its non-K index in global memory (A: !transA, B: transB)
-template <bool XC>
-__device__ __forceinline__ void load_tile(double (&r)[PER_THREAD], const double* __restrict__ P, int n,
+template <int T, bool XC>
+__device__ __forceinline__ void load_tile(double (&r)[Tile<T>::PER_THREAD], const double* __restrict__ P, int n,
                                           int x0, int k0, int tid)
 {
+    constexpr int BM = T;
 #pragma unroll
-    for (int e = 0; e < PER_THREAD; ++e) {
+    for (int e = 0; e < Tile<T>::PER_THREAD; ++e) {
         const int idx = tid + e * THREADS;
         int x, k;
         if (XC) { x = idx % BM; k = idx / BM; }
@@ -32,12 +40,13 @@ __device__ __forceinline__ void load_tile(double (&r)[PER_THREAD], const double*
     }
 }
 
-template <bool XC, bool SCALE>
-__device__ __forceinline__ void store_tile(const double (&r)[PER_THREAD], double* S, int tid,
+template <int T, bool XC, bool SCALE>
+__device__ __forceinline__ void store_tile(const double (&r)[Tile<T>::PER_THREAD], double* S, int tid,
                                            const Scale& mid, int chain, int k0, int n)
 {
+    constexpr int BM = T, LDX = Tile<T>::LDX;
 #pragma unroll
-    for (int e = 0; e < PER_THREAD; ++e) {
+    for (int e = 0; e < Tile<T>::PER_THREAD; ++e) {
         const int idx = tid + e * THREADS;
         int x, k;
         if (XC) { x = idx % BM; k = idx / BM; }
@@ -48,17 +57,19 @@ __device__ __forceinline__ void store_tile(const double (&r)[PER_THREAD], double
     }
 }
 
-template <bool XC>
+template <int T, bool XC>
 __device__ __forceinline__ double frag(const double* S, int x, int k)
 {
-    return XC ? S[k * LDX + x] : S[x * LDK + k];
+    return XC ? S[k * Tile<T>::LDX + x] : S[x * LDK + k];
 }
 
-template <bool TA, bool TB>
+template <int T, bool TA, bool TB>
 __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
 {
-    __shared__ double As[2][SMEM_TILE];
-    __shared__ double Bs[2][SMEM_TILE];
+    constexpr int BM = T, BN = T, WT = Tile<T>::WT, PER_THREAD = Tile<T>::PER_THREAD;
+    extern __shared__ __align__(16) double gemm_smem[];
+    double (*As)[Tile<T>::SMEM_TILE] = reinterpret_cast<double (*)[Tile<T>::SMEM_TILE]>(gemm_smem);
+    double (*Bs)[Tile<T>::SMEM_TILE] = As + 2;
     const int n = g.n;
     const int tiles = (n + BM - 1) / BM;
     const int tm = blockIdx.x % tiles, tn = blockIdx.x / tiles;
@@ -67,63 +78,63 @@ __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
     const double* B = g.B + (size_t)chain * g.strideB;
     double* C = g.C + (size_t)chain * g.strideC;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = (warp & 1) * 32, wn = (warp >> 1) * 32;
+    const int wm = (warp & 1) * (T / 2), wn = (warp >> 1) * (T / 2);
     const int r = lane >> 2, q = lane & 3;
     const int m0 = tm * BM, n0 = tn * BN;
     const bool has_mid = g.mid.active();
 
-    double acc[4][4][2];
+    double acc[WT][WT][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < WT; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < WT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
     double ra[PER_THREAD], rb[PER_THREAD];
     const int nk = (n + BK - 1) / BK;
-    load_tile<!TA>(ra, A, n, m0, 0, tid);
-    load_tile<TB>(rb, B, n, n0, 0, tid);
-    if (has_mid) store_tile<!TA, true>(ra, As[0], tid, g.mid, chain, 0, n);
-    else store_tile<!TA, false>(ra, As[0], tid, g.mid, chain, 0, n);
-    store_tile<TB, false>(rb, Bs[0], tid, g.mid, chain, 0, n);
+    load_tile<T, !TA>(ra, A, n, m0, 0, tid);
+    load_tile<T, TB>(rb, B, n, n0, 0, tid);
+    if (has_mid) store_tile<T, !TA, true>(ra, As[0], tid, g.mid, chain, 0, n);
+    else store_tile<T, !TA, false>(ra, As[0], tid, g.mid, chain, 0, n);
+    store_tile<T, TB, false>(rb, Bs[0], tid, g.mid, chain, 0, n);
     __syncthreads();
 
     for (int kt = 0; kt < nk; ++kt) {
         const int cur = kt & 1;
         if (kt + 1 < nk) {
-            load_tile<!TA>(ra, A, n, m0, (kt + 1) * BK, tid);
-            load_tile<TB>(rb, B, n, n0, (kt + 1) * BK, tid);
+            load_tile<T, !TA>(ra, A, n, m0, (kt + 1) * BK, tid);
+            load_tile<T, TB>(rb, B, n, n0, (kt + 1) * BK, tid);
         }
         const double* as = As[cur];
         const double* bs = Bs[cur];
 #pragma unroll
         for (int kk = 0; kk < BK; kk += 4) {
-            double a[4], b[4];
+            double a[WT], b[WT];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) a[i] = frag<!TA>(as, wm + i * 8 + r, kk + q);
+            for (int i = 0; i < WT; ++i) a[i] = frag<T, !TA>(as, wm + i * 8 + r, kk + q);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = frag<TB>(bs, wn + j * 8 + r, kk + q);
+            for (int j = 0; j < WT; ++j) b[j] = frag<T, TB>(bs, wn + j * 8 + r, kk + q);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < WT; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                for (int j = 0; j < WT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
         if (kt + 1 < nk) {
             const int nxt = cur ^ 1;
-            if (has_mid) store_tile<!TA, true>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
-            else store_tile<!TA, false>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
-            store_tile<TB, false>(rb, Bs[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
+            if (has_mid) store_tile<T, !TA, true>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
+            else store_tile<T, !TA, false>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
+            store_tile<T, TB, false>(rb, Bs[nxt], tid, g.mid, chain, (kt + 1) * BK, n);
         }
         __syncthreads();
     }
 
     const bool has_row = g.row.active(), has_col = g.col.active();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < WT; ++i) {
         const int gm = m0 + wm + i * 8 + r;
         if (gm >= n) continue;
         const double rs = has_row ? g.row.at(chain, gm) : 1.0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < WT; ++j)
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 const int gn = n0 + wn + j * 8 + 2 * q + c;
@@ -137,21 +148,52 @@ __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
     }
 }
 
+template <int T>
+int launch_gemm_t(const GemmArgs& g, cudaStream_t st)
+{
+    const int tiles = (g.n + T - 1) / T;
+    dim3 grid(tiles * tiles, g.batch);
+    constexpr size_t smem = 4 * Tile<T>::SMEM_TILE * sizeof(double);
+    if (!g.transA && !g.transB) gemm_kernel<T, false, false><<<grid, THREADS, smem, st>>>(g);
+    else if (!g.transA && g.transB) gemm_kernel<T, false, true><<<grid, THREADS, smem, st>>>(g);
+    else if (g.transA && !g.transB) gemm_kernel<T, true, false><<<grid, THREADS, smem, st>>>(g);
+    else gemm_kernel<T, true, true><<<grid, THREADS, smem, st>>>(g);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int T>
+int set_gemm_attrs()
+{
+    constexpr int smem = 4 * Tile<T>::SMEM_TILE * (int)sizeof(double);
+    MCB_CUDA(cudaFuncSetAttribute(gemm_kernel<T, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCB_CUDA(cudaFuncSetAttribute(gemm_kernel<T, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCB_CUDA(cudaFuncSetAttribute(gemm_kernel<T, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCB_CUDA(cudaFuncSetAttribute(gemm_kernel<T, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return 0;
+}
+
 } // namespace
+
+int init_gemm_kernels()
+{
+    if (set_gemm_attrs<48>() || set_gemm_attrs<64>() || set_gemm_attrs<80>()) return -2;
+    return 0;
+}
 
 int launch_gemm(const GemmArgs& g, cudaStream_t st)
 {
     if (g.n <= 0 || g.batch <= 0) return 0;
     if (g.C == g.A || g.C == g.B) { set_error("gemm: output aliases an input"); return -1; }
-    const int tiles = (g.n + BM - 1) / BM;
-    dim3 grid(tiles * tiles, g.batch);
     LaunchScope scope(LC_GEMM, st, 2.0 * g.n * (double)g.n * g.n * g.batch);
-    if (!g.transA && !g.transB) gemm_kernel<false, false><<<grid, THREADS, 0, st>>>(g);
-    else if (!g.transA && g.transB) gemm_kernel<false, true><<<grid, THREADS, 0, st>>>(g);
-    else if (g.transA && !g.transB) gemm_kernel<true, false><<<grid, THREADS, 0, st>>>(g);
-    else gemm_kernel<true, true><<<grid, THREADS, 0, st>>>(g);
-    MCB_CUDA(cudaGetLastError());
-    return 0;
+    // the tile that wastes the least padded work
+    auto padded = [&](int t) { const int k = (g.n + t - 1) / t * t; return (long long)k * k; };
+    int best = 64;
+    if (padded(80) < padded(best)) best = 80;
+    if (padded(48) < padded(best)) best = 48;
+    if (best == 48) return launch_gemm_t<48>(g, st);
+    if (best == 80) return launch_gemm_t<80>(g, st);
+    return launch_gemm_t<64>(g, st);
 }
 
 } // namespace mcb

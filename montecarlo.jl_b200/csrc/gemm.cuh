@@ -23,5 +23,6 @@ struct GemmArgs {
 };
 
 int launch_gemm(const GemmArgs& g, cudaStream_t st);
+int init_gemm_kernels();
 
 } // namespace mcb
