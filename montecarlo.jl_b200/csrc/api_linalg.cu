@@ -46,6 +46,7 @@ extern "C" {
 int mcb_linalg_force_general(int32_t on)
 {
     g_force_general = on != 0;
+    set_force_general_udt(on != 0);
     return MCB_OK;
 }
 

@@ -137,42 +137,55 @@ __device__ __forceinline__ void qr_pivot(double (&A)[Geo<N>::MT][2], QrSmem<N>& 
                 // reciprocal square root and one reciprocal (Newton-refined hardware seeds)
                 const double rs = fast_rsqrt(maxval);
                 nu = copysign(maxval * rs, xj);
-                const double xjn = xj + nu;
-                tj = xjn * copysign(rs, xj);
-                inv = fast_rcp(xjn);
+                tj = (xj + nu) * copysign(rs, xj);
+                inv = fast_rcp(xj + nu);
             }
-            // v = (0 .. 0, 1, x[j+1:] / (x_j + nu)); only the row blocks m >= mj are touched
-            double v[MT];
-            v[mj] = t.r < rj ? 0.0 : (t.r == rj ? (live ? 1.0 : 0.0) : x[8 * mj + t.r] * inv);
-#pragma unroll
-            for (int m = mj + 1; m < MT; ++m) v[m] = x[8 * m + t.r] * inv;
+            // v = inv * xt with xt = (0 .. 0, x_j + nu, x[j+1:]); xt is read from the candidate buffer
+            // where it is needed (no register copy), inv is folded into the scalars. Only the row
+            // blocks m >= mj are touched.
+            const double xjn = xj + nu;
+            const double xd = t.r < rj ? 0.0 : (t.r == rj ? (live ? xjn : 0.0) : x[8 * mj + t.r]);
             // ---- reflectorApply! on the remaining columns (UDT.jl:32-50) + fresh trailing norms
+            double dot0 = xd * A[mj][0], dot1 = xd * A[mj][1];
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const bool is_piv = (col0 + c == pj);
-                double dot = 0.0;
-#pragma unroll
-                for (int m = mj; m < MT; ++m) dot += v[m] * A[m][c];
-                dot = col_sum(dot);
-                const double s = (done[c] || is_piv) ? 0.0 : tj * dot;
-#pragma unroll
-                for (int m = mj; m < MT; ++m) A[m][c] -= s * v[m];
-                double nn = t.r > rj ? A[mj][c] * A[mj][c] : 0.0;
-#pragma unroll
-                for (int m = mj + 1; m < MT; ++m) nn += A[m][c] * A[m][c];
-                nrm[c] = col_sum(nn);
-                if (is_piv) done[c] = true;
-                else if (!done[c] && curpos[c] == j) curpos[c] = jm; // the swap j <-> jm (UDT.jl:219-231)
+            for (int m = mj + 1; m < MT; ++m) {
+                const double xm = x[8 * m + t.r];
+                dot0 += xm * A[m][0];
+                dot1 += xm * A[m][1];
             }
+            dot0 = col_sum(dot0);
+            dot1 = col_sum(dot1);
+            const bool piv0 = (col0 == pj), piv1 = (col0 + 1 == pj);
+            const double tinv2 = tj * inv * inv; // A -= xt * (tau inv^2 (xt . A))
+            const double s0 = (done[0] || piv0) ? 0.0 : tinv2 * dot0;
+            const double s1 = (done[1] || piv1) ? 0.0 : tinv2 * dot1;
+            A[mj][0] -= s0 * xd;
+            A[mj][1] -= s1 * xd;
+            double nn0 = t.r > rj ? A[mj][0] * A[mj][0] : 0.0;
+            double nn1 = t.r > rj ? A[mj][1] * A[mj][1] : 0.0;
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m) {
+                const double xm = x[8 * m + t.r];
+                A[m][0] -= s0 * xm;
+                A[m][1] -= s1 * xm;
+                nn0 += A[m][0] * A[m][0];
+                nn1 += A[m][1] * A[m][1];
+            }
+            nrm[0] = col_sum(nn0);
+            nrm[1] = col_sum(nn1);
+            if (piv0) done[0] = true;
+            else if (!done[0] && curpos[0] == j) curpos[0] = jm; // the swap j <-> jm (UDT.jl:219-231)
+            if (piv1) done[1] = true;
+            else if (!done[1] && curpos[1] == j) curpos[1] = jm;
             // the pivot column keeps R above the diagonal, -nu on it and the Householder vector below
-            if (live && col0 == pj) {
-                if (t.r >= rj) A[mj][0] = t.r == rj ? -nu : v[mj];
+            if (live && piv0) {
+                if (t.r >= rj) A[mj][0] = t.r == rj ? -nu : xd * inv;
 #pragma unroll
-                for (int m = mj + 1; m < MT; ++m) A[m][0] = v[m];
-            } else if (live && col0 + 1 == pj) {
-                if (t.r >= rj) A[mj][1] = t.r == rj ? -nu : v[mj];
+                for (int m = mj + 1; m < MT; ++m) A[m][0] = x[8 * m + t.r] * inv;
+            } else if (live && piv1) {
+                if (t.r >= rj) A[mj][1] = t.r == rj ? -nu : xd * inv;
 #pragma unroll
-                for (int m = mj + 1; m < MT; ++m) A[m][1] = v[m];
+                for (int m = mj + 1; m < MT; ++m) A[m][1] = x[8 * m + t.r] * inv;
             }
             if (t.tid == 0) { qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j; }
         }
@@ -201,18 +214,22 @@ __device__ __forceinline__ void form_q(double (&Q)[Geo<N>::MT][2], const double*
             if (8 * t.w + 7 < k) continue; // columns left of k are still unit vectors: H_k leaves them alone
             const double* x = F + (size_t)qs.piv[k] * LD;
             const double tk = qs.tau[k];
-            double v[MT];
-            v[mk] = t.r < rk ? 0.0 : (t.r == rk ? 1.0 : x[8 * mk + t.r]);
+            const double vd = t.r < rk ? 0.0 : (t.r == rk ? 1.0 : x[8 * mk + t.r]);
+            double dot0 = vd * Q[mk][0], dot1 = vd * Q[mk][1];
 #pragma unroll
-            for (int m = mk + 1; m < MT; ++m) v[m] = x[8 * m + t.r];
+            for (int m = mk + 1; m < MT; ++m) {
+                const double vm = x[8 * m + t.r];
+                dot0 += vm * Q[m][0];
+                dot1 += vm * Q[m][1];
+            }
+            const double s0 = tk * col_sum(dot0), s1 = tk * col_sum(dot1);
+            Q[mk][0] -= s0 * vd;
+            Q[mk][1] -= s1 * vd;
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                double dot = 0.0;
-#pragma unroll
-                for (int m = mk; m < MT; ++m) dot += v[m] * Q[m][c];
-                const double s = tk * col_sum(dot);
-#pragma unroll
-                for (int m = mk; m < MT; ++m) Q[m][c] -= s * v[m];
+            for (int m = mk + 1; m < MT; ++m) {
+                const double vm = x[8 * m + t.r];
+                Q[m][0] -= s0 * vm;
+                Q[m][1] -= s1 * vm;
             }
         }
     }

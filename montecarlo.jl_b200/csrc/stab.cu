@@ -217,6 +217,111 @@ udt_panel_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg
     }
 }
 
+// Same factorisation for matrices that leave room for only ONE shared-memory matrix next to the
+// pivoting buffers (N = 144: 18 warps, the matrix in 72 registers per thread).
+template <int N>
+struct UdtSmem {
+    double F[N * Geo<N>::LD];
+    QrSmem<N> qs;
+};
+
+template <int N>
+__global__ void __launch_bounds__(Geo<N>::THREADS, 1)
+udt_big_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
+{
+    constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    UdtSmem<N>& sm = *reinterpret_cast<UdtSmem<N>*>(smem_raw);
+    const Lane t;
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)N * N;
+    {
+        double X[MT][2];
+        g2r<N>(X, Xg + chain * nn, t);
+        qr_pivot<N>(X, sm.qs, t);
+        r2s<N, false>(X, sm.F, t);
+    }
+    __syncthreads();
+    make_d<N>(sm.F, sm.qs, t);
+    {
+        double Q[MT][2];
+        form_q<N>(Q, sm.F, sm.qs, t);
+        r2g<N>(Q, Ug + chain * nn, t);
+    }
+    __syncthreads();
+    for (int i = t.tid; i < N; i += Geo<N>::THREADS) {
+        Dg[(size_t)chain * N + i] = sm.qs.D[i];
+        pivg[(size_t)chain * N + i] = sm.qs.piv[i];
+    }
+    // T from the shared-memory copy of the factored matrix (UDT.jl:283-306)
+    for (int e = t.tid; e < N * N; e += Geo<N>::THREADS) {
+        const int i = e % N, j = e / N;
+        if (apply_pivot) { // T[:, p] = D^-1 R[:, pos(p)] masked below the position
+            Tg[chain * nn + e] = i <= sm.qs.pos[j] ? sm.F[i + j * LD] * sm.qs.Dinv[i] : 0.0;
+        } else {           // columns in position order
+            Tg[chain * nn + e] = i <= j ? sm.F[i + sm.qs.piv[j] * LD] * sm.qs.Dinv[i] : 0.0;
+        }
+    }
+}
+
+// rdivp!(A, T, O, pivot) (src/linalg/general.jl:138-166) for the same large size: out = A[:, p] triu(T)^-1.
+// Solved in the transposed domain: each warp owns 8 rows of A (= 8 columns of A'), loaded already
+// permuted, and runs the forward substitution over the positions j without block-level barriers;
+// triu(T) is staged transposed in shared memory so that row j is contiguous; x_j goes straight to
+// global memory.
+template <int N>
+__global__ void __launch_bounds__(Geo<N>::THREADS, 1)
+rdivp_big_kernel(const double* Ag, double* Og, const double* Tg, const int* pivg)
+{
+    constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* Tt = reinterpret_cast<double*>(smem_raw);       // T[j][k] at Tt[k + j*LD]
+    int* piv = reinterpret_cast<int*>(Tt + N * LD);
+    const Lane t;
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)N * N;
+    const double* T = Tg + chain * nn;
+    for (int e = t.tid; e < N * N; e += Geo<N>::THREADS) {
+        const int j = e % N, k = e / N; // T[j, k], coalesced over j
+        Tt[k + j * LD] = T[e];
+    }
+    for (int i = t.tid; i < N; i += Geo<N>::THREADS) piv[i] = pivg[(size_t)chain * N + i];
+    __syncthreads();
+    // B(i, c) = A[c, p[i]] for the 2 columns c of the transposed problem this lane holds
+    double B[MT][2];
+    const double* A = Ag + chain * nn;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+        const double2 v = *reinterpret_cast<const double2*>(A + (8 * t.w + 2 * t.q) + (size_t)piv[8 * m + t.r] * N);
+        B[m][0] = v.x; B[m][1] = v.y;
+    }
+    double* O = Og + chain * nn + (8 * t.w + 2 * t.q);
+#pragma unroll
+    for (int mj = 0; mj < MT; ++mj) {
+#pragma unroll
+        for (int rj = 0; rj < 8; ++rj) {
+            const int j = 8 * mj + rj;
+            const double* trow = Tt + j * LD;
+            const double rinv = fast_rcp(trow[j]);
+            const double y0 = __shfl_sync(FULL, B[mj][0], rj * 4 + t.q) * rinv;
+            const double y1 = __shfl_sync(FULL, B[mj][1], rj * 4 + t.q) * rinv;
+            if (t.r == rj) *reinterpret_cast<double2*>(O + (size_t)j * N) = make_double2(y0, y1);
+            // positions j' > j: b[j'] -= T[j, j'] x_j  (the diagonal block masks r <= rj)
+            {
+                const double tv = t.r > rj ? trow[8 * mj + t.r] : 0.0;
+                B[mj][0] -= tv * y0;
+                B[mj][1] -= tv * y1;
+            }
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m) {
+                const double tv = trow[8 * m + t.r];
+                B[m][0] -= tv * y0;
+                B[m][1] -= tv * y1;
+            }
+        }
+    }
+}
+
 template <int N>
 int set_attrs()
 {
@@ -230,10 +335,13 @@ int set_attrs()
 } // namespace
 
 bool stab_supported(int n) { return n == 16 || n == 32 || n == 64; }
+bool udt_panel_supported(int n) { return stab_supported(n) || n == 144; }
 
 int init_stab_kernels()
 {
     if (set_attrs<16>() || set_attrs<32>() || set_attrs<64>()) return -2;
+    MCB_CUDA(cudaFuncSetAttribute(udt_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
+    MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int))));
     return 0;
 }
 
@@ -270,8 +378,26 @@ int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, do
 {
     if (batch <= 0) return 0;
     LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
+    if (n == 144) {
+        udt_big_kernel<144><<<batch, Geo<144>::THREADS, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
+        MCB_CUDA(cudaGetLastError());
+        return 0;
+    }
     STAB_DISPATCH(n, (udt_panel_kernel<N><<<batch, Geo<N>::THREADS, sizeof(StabSmem<N>), st>>>(X, U, D, T, pivot,
                                                                                               apply_pivot)));
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// out = in[:, pivot] * triu(T)^-1 for the sizes with a register-resident solver (udt_panel_supported && n > 64)
+int launch_rdivp_panel(int n, int batch, const double* in, double* out, const double* T, const int* pivot,
+                       cudaStream_t st)
+{
+    if (batch <= 0) return 0;
+    if (n != 144) { set_error("rdivp panel kernel: unsupported matrix size"); return -1; }
+    LaunchScope scope(LC_RDIVP, st, 1.0 * n * (double)n * n * batch);
+    rdivp_big_kernel<144><<<batch, Geo<144>::THREADS, 144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int), st>>>(
+        in, out, T, pivot);
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

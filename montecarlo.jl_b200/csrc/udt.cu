@@ -2,8 +2,11 @@
 // otherwise it is worked on in place in global memory (L2 resident). The code is the same for
 // both: it works through generic pointers.
 #include "udt.cuh"
+#include "stab.cuh"
 
 namespace mcb {
+
+bool force_general_udt();
 
 namespace {
 
@@ -213,6 +216,10 @@ __global__ void rdivp_kernel(RdivpArgs a)
 
 } // namespace
 
+static bool g_force_general_udt = false;
+bool force_general_udt() { return g_force_general_udt; }
+void set_force_general_udt(bool on) { g_force_general_udt = on; }
+
 int init_udt_kernels()
 {
     MCB_CUDA(cudaFuncSetAttribute(udt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
@@ -225,6 +232,10 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
                cudaStream_t st)
 {
     if (X == T || X == U || U == T) { set_error("udt: buffers alias"); return -1; }
+    // sizes beyond the chain-resident path that still fit one SM's registers: register-resident QR
+    if (n > 64 && udt_panel_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
+        sD == n && sP == n)
+        return launch_udt_panel(n, batch, X, U, D, T, pivot, apply_pivot, st);
     UdtArgs a{n, X, sX, U, sU, D, sD, T, sT, pivot, sP, apply_pivot, 0};
     const size_t hdr = (size_t)(3 * n + 2 + (n + 3) / 2 + 2) * sizeof(double);
     const size_t mat = (size_t)n * n * sizeof(double);
@@ -242,6 +253,9 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
                  const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st)
 {
     if (in == out) { set_error("rdivp: in-place call"); return -1; }
+    if (n > 64 && udt_panel_supported(n) && !force_general_udt() && sIn == (long long)n * n && sOut == sIn &&
+        sT == sIn && sP == n)
+        return launch_rdivp_panel(n, batch, in, out, T, pivot, st);
     RdivpArgs a{n, in, sIn, out, sOut, T, sT, pivot, sP, 0};
     const size_t hdr = (size_t)n * sizeof(double);
     const size_t mat = (size_t)n * n * sizeof(double);

@@ -16,5 +16,7 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
                  const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st);
 
 int init_udt_kernels();
+// testing aid: route every size through udt_kernel / rdivp_kernel
+void set_force_general_udt(bool on);
 
 } // namespace mcb

@@ -81,8 +81,9 @@ def test_udt_contract(n, apply_pivot, linalg_path):
             assert np.abs(U[k] - Uo).max() < 1e-9
 
 
+@pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
 @pytest.mark.parametrize("n", [4, 16, 64, 144])
-def test_rdivp(n):
+def test_rdivp(n, linalg_path):
     rng = np.random.default_rng(7 + n)
     b = 2
     X = rng.standard_normal((b, n, n))
