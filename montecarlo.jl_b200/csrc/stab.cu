@@ -322,6 +322,80 @@ rdivp_big_kernel(const double* Ag, double* Og, const double* Tg, const int* pivg
     }
 }
 
+// rdivp! for matrices too large for one CTA: the rows of A are independent, so a CTA takes 32 of them
+// (4 warps x 8 rows, held in registers in the transposed layout) and streams triu(T) through shared
+// memory 8 rows at a time (double buffered). grid = (ceil(N / 32), chains).
+template <int N>
+struct RowsGeo {
+    static constexpr int MT = N / 8, LDT = N + 4, WARPS = 4, THREADS = 128;
+    static constexpr size_t SMEM = 2 * 8 * LDT * sizeof(double) + N * sizeof(int);
+};
+
+// positions 8 MJ .. 8 MJ + 7 (compile-time recursion keeps every register index static)
+template <int N, int MJ>
+__device__ __forceinline__ void rows_block(double (&B)[N / 8][2], double (*Tt)[8][N + 4], const double* T,
+                                           double* O, int tid, int r, int q, bool live)
+{
+    constexpr int MT = N / 8;
+    if constexpr (MJ + 1 < MT) {
+        // prefetch rows 8 (MJ+1) .. of triu(T): 8 consecutive doubles per column k >= 8 (MJ+1)
+        for (int e = tid; e < 8 * (N - 8 * (MJ + 1)); e += 128) {
+            const int rr = e & 7, k = 8 * (MJ + 1) + (e >> 3);
+            Tt[(MJ + 1) & 1][rr][k] = T[(8 * (MJ + 1) + rr) + (size_t)k * N];
+        }
+    }
+#pragma unroll
+    for (int rj = 0; rj < 8; ++rj) {
+        const int j = 8 * MJ + rj;
+        const double* trow = Tt[MJ & 1][rj];
+        const double rinv = fast_rcp(trow[j]);
+        const double y0 = __shfl_sync(FULL, B[MJ][0], rj * 4 + q) * rinv;
+        const double y1 = __shfl_sync(FULL, B[MJ][1], rj * 4 + q) * rinv;
+        if (r == rj && live) *reinterpret_cast<double2*>(O + (size_t)j * N) = make_double2(y0, y1);
+        {
+            const double tv = r > rj ? trow[8 * MJ + r] : 0.0;
+            B[MJ][0] -= tv * y0;
+            B[MJ][1] -= tv * y1;
+        }
+#pragma unroll
+        for (int m = MJ + 1; m < MT; ++m) {
+            const double tv = trow[8 * m + r];
+            B[m][0] -= tv * y0;
+            B[m][1] -= tv * y1;
+        }
+    }
+    __syncthreads();
+    if constexpr (MJ + 1 < MT) rows_block<N, MJ + 1>(B, Tt, T, O, tid, r, q, live);
+}
+
+template <int N>
+__global__ void __launch_bounds__(128, 1)
+rdivp_rows_kernel(const double* Ag, double* Og, const double* Tg, const int* pivg)
+{
+    constexpr int MT = N / 8, LDT = N + 4, WARPS = 4;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double (*Tt)[8][LDT] = reinterpret_cast<double (*)[8][LDT]>(smem_raw); // Tt[buffer][row in block][k]
+    int* piv = reinterpret_cast<int*>(smem_raw + 2 * 8 * LDT * sizeof(double));
+    const int tid = threadIdx.x, wl = tid >> 5, l = tid & 31, r = l >> 2, q = l & 3;
+    const int chain = blockIdx.y;
+    const int row0 = (blockIdx.x * WARPS + wl) * 8 + 2 * q; // first of this lane's two rows of A
+    const bool live = row0 < N;                               // (N % 8 == 0: both rows in range)
+    const size_t nn = (size_t)N * N;
+    const double* T = Tg + chain * nn;
+    for (int i = tid; i < N; i += 128) piv[i] = pivg[(size_t)chain * N + i];
+    for (int e = tid; e < 8 * N; e += 128) Tt[0][e & 7][e >> 3] = T[(e & 7) + (size_t)(e >> 3) * N];
+    __syncthreads();
+    double B[MT][2];
+    const double* A = Ag + chain * nn;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+        double2 v = make_double2(0.0, 0.0);
+        if (live) v = *reinterpret_cast<const double2*>(A + row0 + (size_t)piv[8 * m + r] * N);
+        B[m][0] = v.x; B[m][1] = v.y;
+    }
+    rows_block<N, 0>(B, Tt, T, Og + chain * nn + row0, tid, r, q, live);
+}
+
 template <int N>
 int set_attrs()
 {
@@ -336,11 +410,13 @@ int set_attrs()
 
 bool stab_supported(int n) { return n == 16 || n == 32 || n == 64; }
 bool udt_panel_supported(int n) { return stab_supported(n) || n == 144; }
+bool rdivp_panel_supported(int n) { return n == 144 || n == 400; }
 
 int init_stab_kernels()
 {
     if (set_attrs<16>() || set_attrs<32>() || set_attrs<64>()) return -2;
     MCB_CUDA(cudaFuncSetAttribute(udt_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
+    MCB_CUDA(cudaFuncSetAttribute(rdivp_rows_kernel<400>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * 8 * 404 * sizeof(double) + 400 * sizeof(int))));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int))));
     return 0;
 }
@@ -394,8 +470,13 @@ int launch_rdivp_panel(int n, int batch, const double* in, double* out, const do
                        cudaStream_t st)
 {
     if (batch <= 0) return 0;
-    if (n != 144) { set_error("rdivp panel kernel: unsupported matrix size"); return -1; }
     LaunchScope scope(LC_RDIVP, st, 1.0 * n * (double)n * n * batch);
+    if (n == 400) {
+        rdivp_rows_kernel<400><<<dim3((400 + 31) / 32, batch), 128, 2 * 8 * 404 * sizeof(double) + 400 * sizeof(int), st>>>(in, out, T, pivot);
+        MCB_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (n != 144) { set_error("rdivp panel kernel: unsupported matrix size"); return -1; }
     rdivp_big_kernel<144><<<batch, Geo<144>::THREADS, 144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int), st>>>(
         in, out, T, pivot);
     MCB_CUDA(cudaGetLastError());

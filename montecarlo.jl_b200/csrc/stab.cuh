@@ -27,7 +27,8 @@ struct GreensArgs {
 };
 
 bool stab_supported(int n);
-bool udt_panel_supported(int n); // launch_udt_panel exists for this size
+bool udt_panel_supported(int n);   // launch_udt_panel exists for this size
+bool rdivp_panel_supported(int n); // launch_rdivp_panel exists for this size
 int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st);
 int launch_greens_panel(const GreensArgs& a, cudaStream_t st);
 // X -> U, D, T (= D^-1 R P' when apply_pivot, else the reference's "dirty" upper triangle in

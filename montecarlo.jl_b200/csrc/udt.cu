@@ -253,7 +253,7 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
                  const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st)
 {
     if (in == out) { set_error("rdivp: in-place call"); return -1; }
-    if (n > 64 && udt_panel_supported(n) && !force_general_udt() && sIn == (long long)n * n && sOut == sIn &&
+    if (rdivp_panel_supported(n) && !force_general_udt() && sIn == (long long)n * n && sOut == sIn &&
         sT == sIn && sP == n)
         return launch_rdivp_panel(n, batch, in, out, T, pivot, st);
     RdivpArgs a{n, in, sIn, out, sOut, T, sT, pivot, sP, 0};
