@@ -282,3 +282,60 @@ def test_sharded_run_equals_plain_run_on_one_gpu():
         mean, err = mcb.mean_and_error(obs[key])
         assert np.allclose(res[key][0], mean, rtol=1e-12, atol=1e-14)
         assert np.allclose(res[key][1], err, rtol=1e-8, atol=1e-14)
+
+
+def test_full_size_config_a_512_chains_properties():
+    """BASELINE.json configs[1] at full size (512 chains): size-independent properties.
+    (1) the propagated G agrees with the from-scratch G of the same HS field (the reference's own
+    canary, stack.jl:540-550) for every chain; (2) chains c of the big batch reproduce the oracle run
+    alone; (3) no chain produced a non-finite G; (4) the batch equals two half batches."""
+    model = mcb.HubbardModelAttractive(L=8, U=1.0)
+    kw = dict(beta=8.0, delta_tau=0.1, safe_mult=10, check_propagation_error=True)
+    mc = mcb.DQMC(model, n_chains=512, seed=123, **kw)
+    conf0 = mc.conf()
+    mc.build_stack()
+    mc.sweep(1)
+    st = mc.stats()
+    assert st["max_propagation_error"].max() < 1e-7
+    assert st["n_nonfinite"].sum() == 0
+    assert (st["prop_local"] == 2 * mc.M * mc.N).all()
+    G = mc.greens(physical=False)
+    conf = mc.conf()
+    state = mc.state()
+    assert (state["current_slice"], state["direction"]) == (mc.M, -1)
+    fresh = mc.greens_at(mc.M - 1)  # G_M = [1 + B_{M-1} ... B_1 B_M]^-1 from scratch
+    assert relerr(G, fresh) < 1e-8
+    for c in (0, 255, 511):
+        o = orc.OracleDQMC(64, mc.M, 10, 0.1, 1.0, mc.hop, conf0[c], seed=123, chain=c)
+        o.build_stack()
+        o.update(2 * mc.M)
+        assert np.array_equal(conf[c], o.conf())
+        assert relerr(G[c], o.greens()) < RTOL_G
+    mc.close()
+    half = mcb.DQMC(model, n_chains=256, seed=123, chain_offset=256, **kw)
+    half.build_stack()
+    half.sweep(1)
+    assert np.array_equal(half.conf(), conf[256:])
+    assert np.array_equal(half.greens(physical=False), G[256:])
+    half.close()
+
+
+def test_config_d_20x20_first_updates_match_oracle():
+    """BASELINE.json configs[3] physics (N=400, U=4, dtau=0.05, safe_mult=10) at a reduced number of
+    slices so that the CPU oracle finishes in seconds: the general any-N kernels incl. the row-block
+    rdivp and the delayed-update sweep with K < 32."""
+    mc, oracles = _pair(20, 4.0, 1.0, 0.05, 10, 2)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    done = 0
+    for cp in (1, 10, 11):
+        mc.update(cp - done)
+        G = mc.greens(physical=False)
+        conf = mc.conf()
+        for c, o in enumerate(oracles):
+            o.update(cp - done)
+            assert relerr(G[c], o.greens()) < RTOL_G, (cp, c)
+            assert np.array_equal(conf[c], o.conf()), (cp, c)
+        done = cp
+    mc.close()

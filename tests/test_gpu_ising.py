@@ -83,3 +83,26 @@ def test_errors():
         mcb.MC(mcb.IsingModel(7), beta=0.4)
     with pytest.raises(mcb.McbError):
         mcb.MC(mcb.IsingModel(130), beta=0.4)
+
+
+def test_full_size_L4096_bit_exact_and_conserved_counts():
+    """BASELINE.json configs[4] at full lattice size: 2 of the replicas against the oracle (bit-exact),
+    and the integer observables against a direct count on the downloaded spins."""
+    Ls, R = 4096, 2
+    sim = mcb.MC(mcb.IsingModel(Ls), beta=0.5 * np.log(1 + np.sqrt(2)), n_replicas=R, seed=123, replica_offset=5)
+    s0 = sim.conf()
+    sim.sweep(2)
+    got = sim.conf()
+    E, M = sim.energy_magnetization()
+    L = orc.lib()
+    import ctypes as C
+    t4, t8 = C.c_uint32(), C.c_uint32()
+    L.ising_thresholds(sim.beta, C.byref(t4), C.byref(t8))
+    for r in range(R):
+        s = np.ascontiguousarray(s0[r].T).reshape(-1).copy()
+        L.ising_checkerboard_sweeps(s, Ls, t4.value, t8.value, 123, 5 + r, 0, 2)
+        assert np.array_equal(s.reshape(Ls, Ls).T, got[r])
+        g = got[r].astype(np.int64)
+        assert M[r] == g.sum()
+        assert E[r] == -(g * (np.roll(g, -1, 0) + np.roll(g, -1, 1))).sum()
+    sim.close()
