@@ -176,7 +176,7 @@ namespace {
 
 int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 {
-    if (h->use_panel) {
+    if (h->use_panel && !h->split_stab) {
         GreensArgs a;
         a.n = h->N; a.batch = h->C;
         a.Ul = h->bufU[physL]; a.Dl = h->bufD[physL]; a.Tl = h->bufT[physL];
@@ -201,7 +201,11 @@ int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
         a.conf = h->conf; a.sConf = (long long)h->M * h->N;
         a.lo = lo; a.hi = hi; a.left = left ? 1 : 0;
         a.ep = h->eVp[0]; a.em = h->eVp[1];
-        return launch_advance_panel(a, h->st);
+        if (!h->split_stab) return launch_advance_panel(a, h->st);
+        MCB_TRY(launch_slice_products(a, h->W[0], h->st));
+        MCB_TRY(launch_udt(h->N, h->C, h->W[0], h->nn, h->bufU[dst], h->nn, h->bufD[dst], h->N, h->W[2], h->nn,
+                           h->pivot, h->N, 1, h->st));
+        return launch_gemm(base_gemm(h, h->W[2], false, h->bufT[src], false, h->bufT[dst]), h->st);
     }
     const double* cur = h->bufU[src];
     const Scale dcol = vec_scale(h->bufD[src], h->N);

@@ -1,7 +1,7 @@
 // Chain-resident stabilisation kernels: see stab.cuh. One CTA per chain, N/8 warps; every N x N
 // matrix of the sequence lives in registers (accumulator layout of DMMA m8n8k4) or in one of three
 // shared-memory operand buffers; global memory is touched only for the inputs and the results.
-#include "panel_qr.cuh"
+#include "panel_qr2.cuh"
 #include "stab.cuh"
 
 namespace mcb {
@@ -24,18 +24,42 @@ struct StabSmem {
 };
 
 // X (registers) -> T = D^-1 R P' in X, explicit Q, qs.{D, Dinv, piv, pos}. F: scratch matrix in
-// shared memory that no warp is reading any more. Ends with a block-wide barrier.
+// shared memory that no warp is reading any more. Called by ALL warps of the CTA; the Householder
+// steps themselves run on the first N/16 warps with 16 columns each (panel_qr2.cuh), the matrix
+// changes layout through F. Ends with a block-wide barrier.
 template <int N>
 __device__ __forceinline__ void udt_regs(double (&X)[Geo<N>::MT][2], double (&Q)[Geo<N>::MT][2], double* F,
                                          QrSmem<N>& qs, const Lane& t)
 {
-    qr_pivot<N>(X, qs, t);
+    constexpr int MT = Geo<N>::MT;
     r2s<N, false>(X, F, t);
     __syncthreads();
-    make_d<N>(F, qs, t);
-    form_q<N>(Q, F, qs, t);
+    double Q2[MT][2][2];
+    const bool part = t.w < Geo2<N>::NW;
+    const Lane2 t2;
+    if (part) {
+        {
+            double A2[MT][2][2];
+            s2r2<N>(A2, F, t2);
+            qr_pivot2<N>(A2, qs, t2);
+            r2s2<N>(A2, F, t2);
+        }
+        bar2(Geo2<N>::NT);
+        for (int i = t.tid; i < N; i += Geo2<N>::NT) {
+            const double d = fabs(F[i + (size_t)qs.piv[i] * Geo<N>::LD]);
+            qs.D[i] = d;
+            qs.Dinv[i] = 1.0 / d;
+        }
+        form_q2<N>(Q2, F, qs, t2);
+    }
     __syncthreads();
+    s2r<N>(X, F, t); // the factored matrix, for make_t
+    __syncthreads();
+    if (part) r2s2<N>(Q2, F, t2);
+    __syncthreads();
+    s2r<N>(Q, F, t);
     make_t<N>(X, qs, t);
+    __syncthreads();
 }
 
 template <int N>
@@ -107,6 +131,59 @@ __global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1)) advance_ke
     __syncthreads();
     gemm<N, false, false>(Y, sm.S1, sm.S2, t);
     r2g<N>(Y, a.Tdst + chain * nn, t);
+}
+
+// The slice-matrix products of add_slice_sequence_* alone: Xout = B_hi ... B_lo Usrc diag(Dsrc) (left) or
+// the daggered descending sequence (right). Used when the factorisation runs as a kernel of its own
+// (udt2_kernel, more chains per SM than the fused advance_kernel allows).
+template <int N>
+struct MultSmem {
+    double S0[N * Geo<N>::LD];
+    double d0[N];
+};
+
+template <int N>
+__global__ void __launch_bounds__(Geo<N>::THREADS) slice_products_kernel(AdvanceArgs a, double* Xout)
+{
+    constexpr int MT = Geo<N>::MT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    MultSmem<N>& sm = *reinterpret_cast<MultSmem<N>*>(smem_raw);
+    const Lane t;
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)N * N;
+    const int8_t* cg = a.conf + (size_t)chain * a.sConf;
+    double X[MT][2], Y[MT][2];
+    g2r<N>(X, a.Usrc + chain * nn, t);
+    g2s<N, false>(sm.S0, a.eT2, t.tid);
+    load_vec<N>(sm.d0, a.Dsrc + (size_t)chain * N, t.tid);
+    const int cnt = a.hi - a.lo + 1;
+    double ev[MT];
+    load_ev<N>(ev, cg + (size_t)((a.left ? a.lo : a.hi) - 1) * N, a.ep, a.em, t);
+    __syncthreads();
+    for (int s = 0; s < cnt; ++s) {
+        double evn[MT];
+        if (s + 1 < cnt) {
+            const int nxt = a.left ? a.lo + s + 1 : a.hi - s - 1;
+            load_ev<N>(evn, cg + (size_t)(nxt - 1) * N, a.ep, a.em, t);
+        }
+        if (a.left) {
+#pragma unroll
+            for (int m = 0; m < MT; ++m) { X[m][0] *= ev[m]; X[m][1] *= ev[m]; }
+            gemm_regB<N, false>(Y, sm.S0, X, t);
+#pragma unroll
+            for (int m = 0; m < MT; ++m) { X[m][0] = Y[m][0]; X[m][1] = Y[m][1]; }
+        } else {
+            gemm_regB<N, true>(Y, sm.S0, X, t);
+#pragma unroll
+            for (int m = 0; m < MT; ++m) { X[m][0] = Y[m][0] * ev[m]; X[m][1] = Y[m][1] * ev[m]; }
+        }
+        if (s + 1 < cnt) {
+#pragma unroll
+            for (int m = 0; m < MT; ++m) ev[m] = evn[m];
+        }
+    }
+    scale_cols<N>(X, sm.d0, t);
+    r2g<N>(X, Xout + chain * nn, t);
 }
 
 // ------------------------------------------------------------------ calculate_greens_AVX!
@@ -185,40 +262,9 @@ __global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1)) greens_ker
     r2g<N>(A, a.G + chain * nn, t);
 }
 
-// ------------------------------------------------------------------ udt_AVX_pivot! alone
-template <int N>
-__global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1))
-udt_panel_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
-{
-    constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    StabSmem<N>& sm = *reinterpret_cast<StabSmem<N>*>(smem_raw);
-    const Lane t;
-    const int chain = blockIdx.x;
-    const size_t nn = (size_t)N * N;
-    double X[MT][2], Q[MT][2];
-    g2r<N>(X, Xg + chain * nn, t);
-    udt_regs<N>(X, Q, sm.S0, sm.qs, t);
-    r2g<N>(Q, Ug + chain * nn, t);
-    for (int i = t.tid; i < N; i += Geo<N>::THREADS) {
-        Dg[(size_t)chain * N + i] = sm.qs.D[i];
-        pivg[(size_t)chain * N + i] = sm.qs.piv[i];
-    }
-    if (apply_pivot) {
-        r2g<N>(X, Tg + chain * nn, t);
-    } else {
-        // Val(false): columns in position order, D^-1 R in the upper triangle (UDT.jl:298-306)
-        r2s<N, false>(X, sm.S1, t);
-        __syncthreads();
-        for (int e = t.tid; e < N * N; e += Geo<N>::THREADS) {
-            const int i = e % N, j = e / N;
-            Tg[chain * nn + e] = sm.S1[i + sm.qs.piv[j] * LD];
-        }
-    }
-}
-
-// Same factorisation for matrices that leave room for only ONE shared-memory matrix next to the
-// pivoting buffers (N = 144: 18 warps, the matrix in 72 registers per thread).
+// udt_AVX_pivot! as a kernel of its own: N/16 warps with 16 columns each (panel_qr2.cuh), ONE
+// shared-memory matrix next to the pivoting buffers, so that several chains share an SM (N = 64:
+// 45 KB and 128 threads per chain) and N = 144 fits at all (9 warps, 144 registers of matrix per thread).
 template <int N>
 struct UdtSmem {
     double F[N * Geo<N>::LD];
@@ -226,35 +272,48 @@ struct UdtSmem {
 };
 
 template <int N>
-__global__ void __launch_bounds__(Geo<N>::THREADS, 1)
-udt_big_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
+__global__ void __launch_bounds__(Geo2<N>::NT)
+udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
 {
-    constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
+    constexpr int MT = Geo2<N>::MT, LD = Geo2<N>::LD, NT = Geo2<N>::NT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     UdtSmem<N>& sm = *reinterpret_cast<UdtSmem<N>*>(smem_raw);
-    const Lane t;
+    const Lane2 t;
+    const int tid = threadIdx.x;
     const int chain = blockIdx.x;
     const size_t nn = (size_t)N * N;
     {
-        double X[MT][2];
-        g2r<N>(X, Xg + chain * nn, t);
-        qr_pivot<N>(X, sm.qs, t);
-        r2s<N, false>(X, sm.F, t);
+        double A[MT][2][2];
+        const double* X = Xg + chain * nn;
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                A[m][k >> 1][k & 1] = X[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N];
+        qr_pivot2<N>(A, sm.qs, t);
+        r2s2<N>(A, sm.F, t);
     }
     __syncthreads();
-    make_d<N>(sm.F, sm.qs, t);
-    {
-        double Q[MT][2];
-        form_q<N>(Q, sm.F, sm.qs, t);
-        r2g<N>(Q, Ug + chain * nn, t);
-    }
-    __syncthreads();
-    for (int i = t.tid; i < N; i += Geo<N>::THREADS) {
-        Dg[(size_t)chain * N + i] = sm.qs.D[i];
+    for (int i = tid; i < N; i += NT) {
+        const double d = fabs(sm.F[i + (size_t)sm.qs.piv[i] * LD]);
+        sm.qs.D[i] = d;
+        sm.qs.Dinv[i] = 1.0 / d;
+        Dg[(size_t)chain * N + i] = d;
         pivg[(size_t)chain * N + i] = sm.qs.piv[i];
     }
+    {
+        double Q[MT][2][2];
+        form_q2<N>(Q, sm.F, sm.qs, t);
+        double* U = Ug + chain * nn;
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                U[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N] = Q[m][k >> 1][k & 1];
+    }
+    __syncthreads();
     // T from the shared-memory copy of the factored matrix (UDT.jl:283-306)
-    for (int e = t.tid; e < N * N; e += Geo<N>::THREADS) {
+    for (int e = tid; e < N * N; e += NT) {
         const int i = e % N, j = e / N;
         if (apply_pivot) { // T[:, p] = D^-1 R[:, pos(p)] masked below the position
             Tg[chain * nn + e] = i <= sm.qs.pos[j] ? sm.F[i + j * LD] * sm.qs.Dinv[i] : 0.0;
@@ -402,7 +461,9 @@ int set_attrs()
     const int bytes = (int)sizeof(StabSmem<N>);
     MCB_CUDA(cudaFuncSetAttribute(advance_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     MCB_CUDA(cudaFuncSetAttribute(greens_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    MCB_CUDA(cudaFuncSetAttribute(udt_panel_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    MCB_CUDA(cudaFuncSetAttribute(slice_products_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MultSmem<N>)));
+    MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * Geo<N>::LD * sizeof(double) + N * sizeof(int))));
+    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<N>)));
     return 0;
 }
 
@@ -410,12 +471,12 @@ int set_attrs()
 
 bool stab_supported(int n) { return n == 16 || n == 32 || n == 64; }
 bool udt_panel_supported(int n) { return stab_supported(n) || n == 144; }
-bool rdivp_panel_supported(int n) { return n == 144 || n == 400; }
+bool rdivp_panel_supported(int n) { return stab_supported(n) || n == 144 || n == 400; }
 
 int init_stab_kernels()
 {
     if (set_attrs<16>() || set_attrs<32>() || set_attrs<64>()) return -2;
-    MCB_CUDA(cudaFuncSetAttribute(udt_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
+    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_rows_kernel<400>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * 8 * 404 * sizeof(double) + 400 * sizeof(int))));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int))));
     return 0;
@@ -439,6 +500,16 @@ int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st)
     return 0;
 }
 
+int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st)
+{
+    if (a.batch <= 0) return 0;
+    const double n3 = (double)a.n * a.n * a.n;
+    LaunchScope scope(LC_ADVANCE, st, 2.0 * (a.hi - a.lo + 1) * n3 * a.batch);
+    STAB_DISPATCH(a.n, (slice_products_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(MultSmem<N>), st>>>(a, Xout)));
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int launch_greens_panel(const GreensArgs& a, cudaStream_t st)
 {
     if (a.batch <= 0) return 0;
@@ -455,12 +526,11 @@ int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, do
     if (batch <= 0) return 0;
     LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
     if (n == 144) {
-        udt_big_kernel<144><<<batch, Geo<144>::THREADS, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
+        udt2_kernel<144><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
         MCB_CUDA(cudaGetLastError());
         return 0;
     }
-    STAB_DISPATCH(n, (udt_panel_kernel<N><<<batch, Geo<N>::THREADS, sizeof(StabSmem<N>), st>>>(X, U, D, T, pivot,
-                                                                                              apply_pivot)));
+    STAB_DISPATCH(n, (udt2_kernel<N><<<batch, Geo2<N>::NT, sizeof(UdtSmem<N>), st>>>(X, U, D, T, pivot, apply_pivot)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -476,9 +546,16 @@ int launch_rdivp_panel(int n, int batch, const double* in, double* out, const do
         MCB_CUDA(cudaGetLastError());
         return 0;
     }
-    if (n != 144) { set_error("rdivp panel kernel: unsupported matrix size"); return -1; }
-    rdivp_big_kernel<144><<<batch, Geo<144>::THREADS, 144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int), st>>>(
-        in, out, T, pivot);
+#define RDIVP_CASE(NN)                                                                                  \
+    case NN:                                                                                            \
+        rdivp_big_kernel<NN><<<batch, Geo<NN>::THREADS, NN * Geo<NN>::LD * sizeof(double) + NN * sizeof(int), st>>>( \
+            in, out, T, pivot);                                                                         \
+        break;
+    switch (n) {
+        RDIVP_CASE(16) RDIVP_CASE(32) RDIVP_CASE(64) RDIVP_CASE(144)
+    default: set_error("rdivp panel kernel: unsupported matrix size"); return -1;
+    }
+#undef RDIVP_CASE
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -31,6 +31,8 @@ bool udt_panel_supported(int n);   // launch_udt_panel exists for this size
 bool rdivp_panel_supported(int n); // launch_rdivp_panel exists for this size
 int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st);
 int launch_greens_panel(const GreensArgs& a, cudaStream_t st);
+// only the products of add_slice_sequence_*: Xout = (B chain) * Usrc * diag(Dsrc)
+int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st);
 // X -> U, D, T (= D^-1 R P' when apply_pivot, else the reference's "dirty" upper triangle in
 // position order) and the 0-based pivot vector; same contract as launch_udt (udt.cuh)
 int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, double* T, int* pivot,

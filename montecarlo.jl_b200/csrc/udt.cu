@@ -233,7 +233,7 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
 {
     if (X == T || X == U || U == T) { set_error("udt: buffers alias"); return -1; }
     // sizes beyond the chain-resident path that still fit one SM's registers: register-resident QR
-    if (n > 64 && udt_panel_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
+    if (udt_panel_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
         sD == n && sP == n)
         return launch_udt_panel(n, batch, X, U, D, T, pivot, apply_pivot, st);
     UdtArgs a{n, X, sX, U, sU, D, sD, T, sT, pivot, sP, apply_pivot, 0};
