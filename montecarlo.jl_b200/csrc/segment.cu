@@ -42,8 +42,8 @@ struct SGeo {
 template <int N>
 struct alignas(16) ChainSmem {
     static constexpr int LD = SGeo<N>::LD;
-    static constexpr int XSIZE = N * LD > 24 * LD ? N * LD : 24 * LD;
-    double X[XSIZE];   // wrap: staging matrix; site loop: Rb | NUX | V (8 x LD each)
+    static constexpr int XSIZE = N * LD > 48 * LD + 160 ? N * LD : 48 * LD + 160;
+    double X[XSIZE];   // wrap: staging matrix; site loop: 2 x (Rb | NUX | V) (8 x LD each, by block parity) | block scalars
     double unif[N];
     double sc_row[N];
     double sc_col[N];
@@ -51,9 +51,13 @@ struct alignas(16) ChainSmem {
     int nacc;
     int8_t s_in[N];
     int8_t s_out[N];
-    __device__ double* Rb() { return X; }            // rows of the current block, Rb[k*LD + col]
-    __device__ double* NUX() { return X + 8 * LD; }  // -x (e_i - G[:, i]) of site j at NUX[j*LD + row]
-    __device__ double* V() { return X + 16 * LD; }   // G[i, :] of site j at V[j*LD + col]
+    __device__ double* Rb(int par) { return X + par * 24 * LD; }            // rows of the block, Rb[k*LD + col]
+    __device__ double* NUX(int par) { return X + par * 24 * LD + 8 * LD; }  // -x (e_i - G[:, i]) of site j at NUX[j*LD + row]
+    __device__ double* V(int par) { return X + par * 24 * LD + 16 * LD; }   // G[i, :] of site j at V[j*LD + col]
+    // results of the sequential 8 x 8 decision chain of the block
+    __device__ double* nuS() { return X + 48 * LD; }        // [j][k]: NUX_j at block row k (0 if rejected)
+    __device__ double* rowS() { return X + 48 * LD + 64; }  // [j][k]: V_j at block column k
+    __device__ double* xS() { return X + 48 * LD + 128; }   // [j]: x_j (0 if rejected)
 };
 
 template <int N>
@@ -136,80 +140,99 @@ __device__ __forceinline__ void scale_cols(double (&acc)[SGeo<N>::MT][CW][2], co
     }
 }
 
-// sites 8 IT .. 8 IT + 7 of sweep_spatial
+// sites 8 IT .. 8 IT + 7 of sweep_spatial.
+// The only strictly sequential part of the 8 decisions involves the 8 x 8 diagonal block
+// D = G[blk, blk]: flip j needs D_jj and updates D by a rank-1 term. Phase 2a runs that chain in the
+// warp that owns the block's columns (lane r holds row r of D) and records, per accepted flip j,
+// x_j, nu_j[k] = NUX_j at block row k and row_j[k] = V_j at block column k. With these scalars the
+// full vectors follow from two triangular recurrences without any sequential decision (phase 2b,
+// one row or one column per thread):
+//     NUX_k = x_k (G0[:, k] - e_k + sum_{m<k} NUX_m row_m[k]),   V_k = G0[k, :] + sum_{m<k} nu_m[k] V_m
 template <int N, int IT>
 __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], ChainSmem<N>& cs,
                                            const SegmentArgs& a, const CLane& t, int bar_id, int& nacc)
 {
     constexpr int MT = SGeo<N>::MT, LD = SGeo<N>::LD, TPC = SGeo<N>::TPC;
     constexpr int WI = IT / CW, CWI = IT % CW;  // owner of the block's 8 columns
-    constexpr int NH = (N + 31) / 32;           // row-vector elements per lane
-    constexpr int HB = (8 * IT) / 32;           // which of them holds the block's own columns
-    double* Rb = cs.Rb();
-    double* NUX = cs.NUX();
-    double* V = cs.V();
-    // ---- phase 1: everybody publishes its part of the rows 8 IT .. 8 IT + 7
+    // (block parity: the next block's phase 1 may overlap this block's phase 3 in another warp)
+    double* Rb = cs.Rb(IT & 1);
+    double* NUX = cs.NUX(IT & 1);
+    double* V = cs.V(IT & 1);
+    double* nuS = cs.nuS();
+    double* rowS = cs.rowS();
+    double* xS = cs.xS();
+    // ---- phase 1: publish the rows 8 IT .. 8 IT + 7 (everybody) and the columns (their owner; into NUX)
 #pragma unroll
     for (int cw = 0; cw < CW; ++cw)
         *reinterpret_cast<double2*>(Rb + t.r * LD + t.col0 + 8 * cw) = make_double2(acc[IT][cw][0], acc[IT][cw][1]);
-    chain_sync(bar_id, TPC);
-    // ---- phase 2: the column owner decides the 8 sites
     if (t.wl == WI) {
-        // the block's own 8 columns are updated in place (phase 3 leaves them alone)
-        double rb[8][NH];
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
+        for (int m = 0; m < MT; ++m) {
+            NUX[(2 * t.q) * LD + 8 * m + t.r] = acc[m][CWI][0];
+            NUX[(2 * t.q + 1) * LD + 8 * m + t.r] = acc[m][CWI][1];
+        }
+    }
+    chain_sync(bar_id, TPC);
+    // ---- phase 2a: the sequential decisions on the 8 x 8 diagonal block
+    if (t.wl == WI) {
+        const int r8 = t.l & 7; // lanes 8..31 mirror lanes 0..7
+        double Dr[8];
 #pragma unroll
-            for (int h = 0; h < NH; ++h) rb[k][h] = Rb[k * LD + min(t.l + 32 * h, N - 1)];
+        for (int c = 0; c < 8; ++c) Dr[c] = Rb[r8 * LD + 8 * IT + c];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int i = 8 * IT + j;
-            const double gii = __shfl_sync(0xffffffffu, acc[IT][CWI][j & 1], j * 4 + (j >> 1));
+            const double gii = __shfl_sync(0xffffffffu, Dr[j], j);
+            double rowj[8];
+#pragma unroll
+            for (int c = j + 1; c < 8; ++c) rowj[c] = __shfl_sync(0xffffffffu, Dr[c], j);
             const int s = cs.s_in[i];
             const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
             const double efac = s > 0 ? a.efac_p : a.efac_m;
             const double rt = 1.0 + gamma * (1.0 - gii);       // propose_local: detratio = rt^2
             const double p = efac * (rt * rt);                  // DQMC.jl:570
             const bool accept = (p > 1.0 || cs.unif[i] < p);    // DQMC.jl:573 (uniform over the warp)
-#pragma unroll
-            for (int h = 0; h < NH; ++h)
-                if (t.l + 32 * h < N) V[j * LD + t.l + 32 * h] = rb[j][h];
+            double x = 0.0, nu = 0.0;
             if (accept) {
-                const double x = gamma * fast_rcp(rt);          // accept_local!: gamma / (1 + gamma u_i)
-                if (t.q == (j >> 1)) {
+                x = gamma * fast_rcp(rt);                       // accept_local!: gamma / (1 + gamma u_i)
+                nu = x * (Dr[j] - (r8 == j ? 1.0 : 0.0));
 #pragma unroll
-                    for (int m = 0; m < MT; ++m)
-                        NUX[j * LD + 8 * m + t.r] = x * (acc[m][CWI][j & 1] - ((8 * m + t.r) == i ? 1.0 : 0.0));
-                }
-                __syncwarp();
-                // columns of the block: G[:, 8 IT + 2q + c] += nux * v[8 IT + 2q + c]
-                const int src = (8 * IT + 2 * t.q) & 31;
-                const double v0 = __shfl_sync(0xffffffffu, rb[j][HB], src);
-                const double v1 = __shfl_sync(0xffffffffu, rb[j][HB], src + 1);
-#pragma unroll
-                for (int m = 0; m < MT; ++m) {
-                    const double nu = NUX[j * LD + 8 * m + t.r];
-                    acc[m][CWI][0] += nu * v0;
-                    acc[m][CWI][1] += nu * v1;
-                }
-                // rows of the block: rb[k, :] += nux[8 IT + k] * v
-                if (j < 7) {
-                    double vh[NH];
-#pragma unroll
-                    for (int h = 0; h < NH; ++h) vh[h] = rb[j][h];
-#pragma unroll
-                    for (int k = j + 1; k < 8; ++k) {
-                        const double nk = NUX[j * LD + 8 * IT + k];
-#pragma unroll
-                        for (int h = 0; h < NH; ++h) rb[k][h] += nk * vh[h];
-                    }
-                }
+                for (int c = j + 1; c < 8; ++c) Dr[c] += nu * rowj[c];
                 ++nacc;
-            } else if (t.q == (j >> 1)) {
-#pragma unroll
-                for (int m = 0; m < MT; ++m) NUX[j * LD + 8 * m + t.r] = 0.0;
             }
-            if (t.l == 0) cs.s_out[i] = (int8_t)(accept ? -s : s);
+            if (t.l < 8) nuS[j * 8 + t.l] = nu;
+            if (t.l == 0) {
+                xS[j] = x;
+#pragma unroll
+                for (int c = j + 1; c < 8; ++c) rowS[j * 8 + c] = rowj[c];
+                cs.s_out[i] = (int8_t)(accept ? -s : s);
+            }
+        }
+    }
+    chain_sync(bar_id, TPC);
+    // ---- phase 2b: the vectors of the accepted flips, one row (NUX) or one column (V) per thread
+    if (t.ctid < N) {
+        const int rho = t.ctid;
+        double nux[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            double v = NUX[k * LD + rho] - (rho == 8 * IT + k ? 1.0 : 0.0);
+#pragma unroll
+            for (int m = 0; m < k; ++m) v += nux[m] * rowS[m * 8 + k];
+            nux[k] = xS[k] * v;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) NUX[k * LD + rho] = nux[k];
+    } else if (t.ctid < 2 * N) {
+        const int kap = t.ctid - N;
+        double vv[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            double v = Rb[k * LD + kap];
+#pragma unroll
+            for (int m = 0; m < k; ++m) v += nuS[m * 8 + k] * vv[m];
+            vv[k] = v;
+            V[k * LD + kap] = v;
         }
     }
     chain_sync(bar_id, TPC);
@@ -226,8 +249,7 @@ __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], Ch
             for (int m = 0; m < MT; ++m) {
                 const double av = ap[k0 * LD + 8 * m];
 #pragma unroll
-                for (int cw = 0; cw < CW; ++cw)
-                    if (!(cw == CWI && t.wl == WI)) dmma884(acc[m][cw][0], acc[m][cw][1], av, b[cw]);
+                for (int cw = 0; cw < CW; ++cw) dmma884(acc[m][cw][0], acc[m][cw][1], av, b[cw]);
             }
         }
     }
