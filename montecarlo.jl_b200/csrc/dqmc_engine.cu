@@ -151,6 +151,13 @@ int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const 
         MCB_TRY(launch_gemm(g, st));
     }
     MCB_TRY(launch_udt(n, batch, W[0], nn, W[1], nn, Dw[0], n, W[2], nn, pivot, n, 0, st));
+    if (stab_supported(n) && !force_general_udt()) {
+        // one CTA per chain for everything between and after the factorisations (stab.cuh)
+        MCB_TRY(launch_greens_mid(n, batch, Ul, W[1], W[2], pivot, Dw[0], Ur, W[3], W[4], W[0], st));
+        MCB_TRY(launch_udt(n, batch, W[0], nn, W[1], nn, Dw[1], n, W[2], nn, pivot, n, 0, st));
+        MCB_TRY(launch_greens_end(n, batch, W[3], W[1], W[2], pivot, Dw[1], W[4], G, st));
+        return 0;
+    }
     // B2: W3 = Ul Q1 ; W4 = Ur[:,p] triu(W2)^-1 ; W0 = W3' W4 + diag(D1)   (B3 fused)
     MCB_TRY(launch_gemm(gemm(Ul, false, W[1], false, W[3]), st));
     MCB_TRY(launch_rdivp(n, batch, Ur, nn, W[4], nn, W[2], nn, pivot, n, st));

@@ -179,34 +179,44 @@ __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], Ch
         double Dr[8];
 #pragma unroll
         for (int c = 0; c < 8; ++c) Dr[c] = Rb[r8 * LD + 8 * IT + c];
+        // everything that does not depend on the previous decision is read up front; the chain itself is
+        // branch-free (the update is computed speculatively and masked), because every FP64 instruction
+        // on it queues behind the DMMAs of the other chains of the SM
+        int sgn = 0; // bit j: s_j > 0
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sgn |= (cs.s_in[8 * IT + j] > 0 ? 1 : 0) << j;
+        int flips = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const int i = 8 * IT + j;
             const double gii = __shfl_sync(0xffffffffu, Dr[j], j);
             double rowj[8];
 #pragma unroll
             for (int c = j + 1; c < 8; ++c) rowj[c] = __shfl_sync(0xffffffffu, Dr[c], j);
-            const int s = cs.s_in[i];
-            const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
-            const double efac = s > 0 ? a.efac_p : a.efac_m;
-            const double rt = 1.0 + gamma * (1.0 - gii);       // propose_local: detratio = rt^2
-            const double p = efac * (rt * rt);                  // DQMC.jl:570
-            const bool accept = (p > 1.0 || cs.unif[i] < p);    // DQMC.jl:573 (uniform over the warp)
-            double x = 0.0, nu = 0.0;
-            if (accept) {
-                x = gamma * fast_rcp(rt);                       // accept_local!: gamma / (1 + gamma u_i)
-                nu = x * (Dr[j] - (r8 == j ? 1.0 : 0.0));
+            const bool up = (sgn >> j) & 1;
+            const double gam = up ? a.gamma_p : a.gamma_m;
+            const double efc = up ? a.efac_p : a.efac_m;
+            const double dm = Dr[j] - (r8 == j ? 1.0 : 0.0);
+            const double rt = 1.0 + gam * (1.0 - gii);          // propose_local: detratio = rt^2
+            const double p = efc * (rt * rt);                   // DQMC.jl:570
+            // DQMC.jl:573: p > 1 || rand() < p; the uniform is < 1, so the second test alone decides
+            const bool accept = cs.unif[8 * IT + j] < p;
+            const double xs = gam * fast_rcp(rt);               // accept_local!: gamma / (1 + gamma u_i)
+            const double x = accept ? xs : 0.0;
+            const double nu = accept ? xs * dm : 0.0;
 #pragma unroll
-                for (int c = j + 1; c < 8; ++c) Dr[c] += nu * rowj[c];
-                ++nacc;
-            }
+            for (int c = j + 1; c < 8; ++c) Dr[c] += nu * rowj[c];
+            flips |= (accept ? 1 : 0) << j;
             if (t.l < 8) nuS[j * 8 + t.l] = nu;
             if (t.l == 0) {
                 xS[j] = x;
 #pragma unroll
                 for (int c = j + 1; c < 8; ++c) rowS[j * 8 + c] = rowj[c];
-                cs.s_out[i] = (int8_t)(accept ? -s : s);
             }
+        }
+        nacc += __popc(flips);
+        if (t.l < 8) {
+            const int8_t s = cs.s_in[8 * IT + t.l];
+            cs.s_out[8 * IT + t.l] = ((flips >> t.l) & 1) ? (int8_t)-s : s;
         }
     }
     chain_sync(bar_id, TPC);

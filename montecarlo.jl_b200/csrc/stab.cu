@@ -381,6 +381,134 @@ rdivp_big_kernel(const double* Ag, double* Og, const double* Tg, const int* pivg
     }
 }
 
+// The two halves of calculate_greens_AVX! that sit between / after the factorisations when those run
+// as kernels of their own (udt2_kernel): products and triangular solves of one chain in one CTA, the
+// intermediates in registers / shared memory. T comes "dirty" (position order, apply_pivot = 0).
+template <int N>
+struct GlueSmem {
+    static constexpr int LD = Geo<N>::LD;
+    double S0[N * LD];
+    double S1[N * LD];
+    double Tt[N * LD]; // T[j][k] at Tt[k + j*LD]
+    double d[N];
+    int piv[N];
+};
+
+// x = b[:, p] triu(T)^-1 in the transposed domain (see rdivp_big_kernel); column j of the result, times
+// colscale[j] if given, goes to S[.. + j*LD] and, if Og != nullptr, unscaled to global memory.
+template <int N, bool SCALE>
+__device__ __forceinline__ void solve_perm(const double* __restrict__ A, const GlueSmem<N>& sm, double* S,
+                                           double* Og, const Lane& t)
+{
+    constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
+    double B[MT][2];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+        const double2 v = *reinterpret_cast<const double2*>(A + (8 * t.w + 2 * t.q) + (size_t)sm.piv[8 * m + t.r] * N);
+        B[m][0] = v.x; B[m][1] = v.y;
+    }
+    const int c0 = 8 * t.w + 2 * t.q;
+#pragma unroll
+    for (int mj = 0; mj < MT; ++mj) {
+#pragma unroll
+        for (int rj = 0; rj < 8; ++rj) {
+            const int j = 8 * mj + rj;
+            const double* trow = sm.Tt + j * LD;
+            const double rinv = fast_rcp(trow[j]);
+            const double y0 = __shfl_sync(FULL, B[mj][0], rj * 4 + t.q) * rinv;
+            const double y1 = __shfl_sync(FULL, B[mj][1], rj * 4 + t.q) * rinv;
+            if (t.r == rj) {
+                if (Og) *reinterpret_cast<double2*>(Og + c0 + (size_t)j * N) = make_double2(y0, y1);
+                const double sc = SCALE ? sm.d[j] : 1.0;
+                *reinterpret_cast<double2*>(S + c0 + j * LD) = make_double2(y0 * sc, y1 * sc);
+            }
+            {
+                const double tv = t.r > rj ? trow[8 * mj + t.r] : 0.0;
+                B[mj][0] -= tv * y0;
+                B[mj][1] -= tv * y1;
+            }
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m) {
+                const double tv = trow[8 * m + t.r];
+                B[m][0] -= tv * y0;
+                B[m][1] -= tv * y1;
+            }
+        }
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void load_tt(GlueSmem<N>& sm, const double* __restrict__ T, const int* __restrict__ piv,
+                                        const Lane& t)
+{
+    constexpr int LD = Geo<N>::LD;
+    for (int e = t.tid; e < N * N; e += Geo<N>::THREADS) {
+        const int j = e % N, k = e / N;
+        sm.Tt[k + j * LD] = T[e];
+    }
+    for (int i = t.tid; i < N; i += Geo<N>::THREADS) sm.piv[i] = piv[i];
+}
+
+// W3 = Ul Q1 ; W4 = Ur[:, p1] triu(T1)^-1 ; A2 = W3' W4 + diag(D1)            (stack.jl:360-368)
+template <int N>
+__global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1))
+greens_mid_kernel(const double* Ulg, const double* Q1g, const double* T1g, const int* piv1g, const double* D1g,
+                  const double* Urg, double* W3g, double* W4g, double* A2g)
+{
+    constexpr int MT = Geo<N>::MT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    GlueSmem<N>& sm = *reinterpret_cast<GlueSmem<N>*>(smem_raw);
+    const Lane t;
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)N * N;
+    double Q[MT][2], W[MT][2];
+    g2s<N, false>(sm.S0, Ulg + chain * nn, t.tid);
+    load_tt<N>(sm, T1g + chain * nn, piv1g + (size_t)chain * N, t);
+    load_vec<N>(sm.d, D1g + (size_t)chain * N, t.tid);
+    g2r<N>(Q, Q1g + chain * nn, t);
+    __syncthreads();
+    gemm_regB<N, false>(W, sm.S0, Q, t);
+    r2g<N>(W, W3g + chain * nn, t);
+    solve_perm<N, false>(Urg + chain * nn, sm, sm.S1, W4g + chain * nn, t);
+    __syncthreads();
+    r2s<N, false>(W, sm.S0, t);
+    __syncthreads();
+    gemm<N, true, false>(Q, sm.S0, sm.S1, t);
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+            if (8 * m + t.r == 8 * t.w + 2 * t.q + c) Q[m][c] += sm.d[8 * m + t.r];
+    r2g<N>(Q, A2g + chain * nn, t);
+}
+
+// W0 = W3 Q2 ; W5 = W4[:, p2] triu(T2)^-1 ; G = (W5 diag(1/D2)) W0'            (stack.jl:377-391)
+template <int N>
+__global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1))
+greens_end_kernel(const double* W3g, const double* Q2g, const double* T2g, const int* piv2g, const double* D2g,
+                  const double* W4g, double* Gg)
+{
+    constexpr int MT = Geo<N>::MT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    GlueSmem<N>& sm = *reinterpret_cast<GlueSmem<N>*>(smem_raw);
+    const Lane t;
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)N * N;
+    double Q[MT][2], W[MT][2];
+    g2s<N, false>(sm.S0, W3g + chain * nn, t.tid);
+    load_tt<N>(sm, T2g + chain * nn, piv2g + (size_t)chain * N, t);
+    for (int i = t.tid; i < N; i += Geo<N>::THREADS) sm.d[i] = 1.0 / D2g[(size_t)chain * N + i];
+    g2r<N>(Q, Q2g + chain * nn, t);
+    __syncthreads();
+    gemm_regB<N, false>(W, sm.S0, Q, t);
+    solve_perm<N, true>(W4g + chain * nn, sm, sm.S1, nullptr, t);
+    __syncthreads();
+    r2s<N, false>(W, sm.S0, t);
+    __syncthreads();
+    gemm<N, false, true>(Q, sm.S1, sm.S0, t);
+    r2g<N>(Q, Gg + chain * nn, t);
+}
+
 // rdivp! for matrices too large for one CTA: the rows of A are independent, so a CTA takes 32 of them
 // (4 warps x 8 rows, held in registers in the transposed layout) and streams triu(T) through shared
 // memory 8 rows at a time (double buffered). grid = (ceil(N / 32), chains).
@@ -464,6 +592,8 @@ int set_attrs()
     MCB_CUDA(cudaFuncSetAttribute(slice_products_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MultSmem<N>)));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * Geo<N>::LD * sizeof(double) + N * sizeof(int))));
     MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<N>)));
+    MCB_CUDA(cudaFuncSetAttribute(greens_mid_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GlueSmem<N>)));
+    MCB_CUDA(cudaFuncSetAttribute(greens_end_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GlueSmem<N>)));
     return 0;
 }
 
@@ -516,6 +646,26 @@ int launch_greens_panel(const GreensArgs& a, cudaStream_t st)
     const double n3 = (double)a.n * a.n * a.n;
     LaunchScope scope(LC_GREENS, st, (10.0 + 16.0 / 3.0 + 2.0) * n3 * a.batch);
     STAB_DISPATCH(a.n, (greens_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(StabSmem<N>), st>>>(a)));
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_greens_mid(int n, int batch, const double* Ul, const double* Q1, const double* T1, const int* piv1,
+                      const double* D1, const double* Ur, double* W3, double* W4, double* A2, cudaStream_t st)
+{
+    if (batch <= 0) return 0;
+    LaunchScope scope(LC_GREENS, st, 5.0 * n * (double)n * n * batch);
+    STAB_DISPATCH(n, (greens_mid_kernel<N><<<batch, Geo<N>::THREADS, sizeof(GlueSmem<N>), st>>>(Ul, Q1, T1, piv1, D1, Ur, W3, W4, A2)));
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_greens_end(int n, int batch, const double* W3, const double* Q2, const double* T2, const int* piv2,
+                      const double* D2, const double* W4, double* G, cudaStream_t st)
+{
+    if (batch <= 0) return 0;
+    LaunchScope scope(LC_GREENS, st, 5.0 * n * (double)n * n * batch);
+    STAB_DISPATCH(n, (greens_end_kernel<N><<<batch, Geo<N>::THREADS, sizeof(GlueSmem<N>), st>>>(W3, Q2, T2, piv2, D2, W4, G)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -39,6 +39,13 @@ int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, do
                      int apply_pivot, cudaStream_t st);
 int launch_rdivp_panel(int n, int batch, const double* in, double* out, const double* T, const int* pivot,
                        cudaStream_t st);
+// calculate_greens between / after its two factorisations (T1, T2 "dirty", i.e. apply_pivot = 0):
+//   mid: W3 = Ul Q1, W4 = Ur[:, p1] triu(T1)^-1, A2 = W3' W4 + diag(D1)     stack.jl:360-368
+//   end: G = (W4[:, p2] triu(T2)^-1 diag(1/D2)) (W3 Q2)'                     stack.jl:377-391
+int launch_greens_mid(int n, int batch, const double* Ul, const double* Q1, const double* T1, const int* piv1,
+                      const double* D1, const double* Ur, double* W3, double* W4, double* A2, cudaStream_t st);
+int launch_greens_end(int n, int batch, const double* W3, const double* Q2, const double* T2, const int* piv2,
+                      const double* D2, const double* W4, double* G, cudaStream_t st);
 int init_stab_kernels();
 
 } // namespace mcb

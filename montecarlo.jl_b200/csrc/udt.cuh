@@ -18,5 +18,6 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
 int init_udt_kernels();
 // testing aid: route every size through udt_kernel / rdivp_kernel
 void set_force_general_udt(bool on);
+bool force_general_udt();
 
 } // namespace mcb
