@@ -9,14 +9,16 @@
 #pragma once
 #include "panel_qr.cuh"
 
+
 namespace mcb {
 namespace panel {
 
-template <int N>
+template <int N, int CW_ = 2>
 struct Geo2 {
-    static_assert(N % 16 == 0, "needs N to be a multiple of 16");
-    static constexpr int CW = 2;
-    static constexpr int NW = N / 16;      // participating warps
+    static_assert(N % (8 * CW_) == 0, "needs N to be a multiple of the warp's column count");
+    static constexpr int CW = CW_;         // 8-column blocks per warp
+    static constexpr int KC = 2 * CW_;     // columns per lane
+    static constexpr int NW = N / (8 * CW_); // participating warps
     static constexpr int NT = NW * 32;     // participating threads
     static constexpr int MT = N / 8;
     static constexpr int LD = Geo<N>::LD;
@@ -29,46 +31,52 @@ __device__ __forceinline__ void bar2(int nthreads)
 
 struct Lane2 {
     int w, l, r, q, col0;
-    __device__ __forceinline__ Lane2()
+    __device__ __forceinline__ Lane2(int cw = 2)
     {
-        w = threadIdx.x >> 5; l = threadIdx.x & 31; r = l >> 2; q = l & 3; col0 = 16 * w + 2 * q;
+        w = threadIdx.x >> 5; l = threadIdx.x & 31; r = l >> 2; q = l & 3; col0 = 8 * cw * w + 2 * q;
     }
 };
 
-template <int N>
-__device__ __forceinline__ void s2r2(double (&A)[Geo2<N>::MT][2][2], const double* S, const Lane2& t)
+template <int N, int CW = 2>
+__device__ __forceinline__ void s2r2(double (&A)[Geo2<N>::MT][CW][2], const double* S, const Lane2& t)
 {
     constexpr int LD = Geo2<N>::LD;
 #pragma unroll
     for (int m = 0; m < Geo2<N>::MT; ++m)
 #pragma unroll
-        for (int cw = 0; cw < 2; ++cw)
+        for (int cw = 0; cw < CW; ++cw)
 #pragma unroll
             for (int c = 0; c < 2; ++c) A[m][cw][c] = S[(8 * m + t.r) + (t.col0 + 8 * cw + c) * LD];
 }
 
-template <int N>
-__device__ __forceinline__ void r2s2(const double (&A)[Geo2<N>::MT][2][2], double* S, const Lane2& t)
+template <int N, int CW = 2>
+__device__ __forceinline__ void r2s2(const double (&A)[Geo2<N>::MT][CW][2], double* S, const Lane2& t)
 {
     constexpr int LD = Geo2<N>::LD;
 #pragma unroll
     for (int m = 0; m < Geo2<N>::MT; ++m)
 #pragma unroll
-        for (int cw = 0; cw < 2; ++cw)
+        for (int cw = 0; cw < CW; ++cw)
 #pragma unroll
             for (int c = 0; c < 2; ++c) S[(8 * m + t.r) + (t.col0 + 8 * cw + c) * LD] = A[m][cw][c];
 }
 
 // Column-pivoted Householder QR (see qr_pivot). Called by the first Geo2<N>::NW warps only.
-template <int N>
-__device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][2][2], QrSmem<N>& qs, const Lane2& t)
+// A Householder step is one long dependency chain (pivot search -> barrier -> reflector scalars -> dot
+// products -> update -> fresh norms), so the code is arranged for latency rather than instruction count:
+//  * squared norms are non-negative doubles, so their bit patterns order like integers: the pivot
+//    search compares (hi, lo, key) words on the integer pipe and reduces over the warp with REDUX;
+//  * the pivot column stays untouched in registers; -nu and 1/(x_j + nu) are kept per step
+//    (qs.D / qs.Dinv, overwritten by make_d later) and applied once after the last step.
+template <int N, int CW = 2>
+__device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSmem<N>& qs, const Lane2& t)
 {
-    constexpr int MT = Geo2<N>::MT, NW = Geo2<N>::NW, NT = Geo2<N>::NT;
-    int curpos[4];
-    bool done[4];
-    double nrm[4];
+    constexpr int MT = Geo2<N, CW>::MT, NW = Geo2<N, CW>::NW, NT = Geo2<N, CW>::NT, KC = 2 * CW;
+    int curpos[KC];
+    bool done[KC];
+    double nrm[KC];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < KC; ++k) {
         curpos[k] = t.col0 + 8 * (k >> 1) + (k & 1);
         done[k] = false;
         double s = 0.0;
@@ -82,135 +90,161 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][2][2], QrSmem
         for (int rj = 0; rj < 8; ++rj) {
             const int j = 8 * mj + rj;
             const int buf = j & 1;
-            // ---- best remaining column of this warp
-            double bv = -2.0;
-            int bk = 0;
+            // ---- best remaining column of this warp: max norm, ties to the lowest position
+            int hi[KC], key[KC];
+            unsigned lo[KC];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const double v = done[k] ? -1.0 : nrm[k];
-                const int key = (curpos[k] << 16) | (t.col0 + 8 * (k >> 1) + (k & 1));
-                if (v > bv || (v == bv && key < bk)) { bv = v; bk = key; }
+            for (int k = 0; k < KC; ++k) {
+                hi[k] = done[k] ? -1 : __double2hiint(nrm[k]);
+                lo[k] = (unsigned)__double2loint(nrm[k]);
+                key[k] = (curpos[k] << 16) | (t.col0 + 8 * (k >> 1) + (k & 1));
             }
+            int mh = hi[0];
 #pragma unroll
-            for (int o = 1; o <= 2; o <<= 1) {
-                const double ov = __shfl_xor_sync(FULL, bv, o);
-                const int ok = __shfl_xor_sync(FULL, bk, o);
-                if (ov > bv || (ov == bv && ok < bk)) { bv = ov; bk = ok; }
-            }
+            for (int k = 1; k < KC; ++k) mh = max(mh, hi[k]);
+            mh = __reduce_max_sync(FULL, mh);
+            unsigned ml = 0u;
+#pragma unroll
+            for (int k = 0; k < KC; ++k) ml = max(ml, hi[k] == mh ? lo[k] : 0u);
+            ml = __reduce_max_sync(FULL, ml);
+            int bk = 0x7fffffff;
+#pragma unroll
+            for (int k = 0; k < KC; ++k) bk = min(bk, (hi[k] == mh && lo[k] == ml) ? key[k] : 0x7fffffff);
+            bk = __reduce_min_sync(FULL, bk);
             {
+                // the warp's candidate column (bk is uniform over the warp)
                 const int bc = bk & 0xffff;
                 double* cd = qs.cand[buf][t.w] + t.r;
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (bc == t.col0 + 8 * (k >> 1) + (k & 1)) {
+                for (int k = 0; k < KC; ++k) {
+                    const bool mine = bc == t.col0 + 8 * (k >> 1) + (k & 1);
 #pragma unroll
-                        for (int m = mj; m < MT; ++m) cd[8 * m] = A[m][k >> 1][k & 1];
-                    }
-                if (t.l == 0) { qs.cval[buf][t.w] = bv; qs.ckey[buf][t.w] = bk; }
+                    for (int m = mj; m < MT; ++m)
+                        if (mine) cd[8 * m] = A[m][k >> 1][k & 1];
+                }
+                if (t.l == 0) { qs.cval[buf][t.w] = __hiloint2double(mh, (int)ml); qs.ckey[buf][t.w] = bk; }
             }
             bar2(NT);
             // ---- global winner
-            double maxval = qs.cval[buf][0];
-            int key = qs.ckey[buf][0], wb = 0;
+            int wh[NW], wk[NW];
+            unsigned wl[NW];
 #pragma unroll
-            for (int w = 1; w < NW; ++w) {
+            for (int w = 0; w < NW; ++w) {
                 const double v = qs.cval[buf][w];
-                const int k = qs.ckey[buf][w];
-                if (v > maxval || (v == maxval && k < key)) { maxval = v; key = k; wb = w; }
+                wh[w] = __double2hiint(v); wl[w] = (unsigned)__double2loint(v); wk[w] = qs.ckey[buf][w];
             }
-            const int pj = key & 0xffff, jm = key >> 16;
-            // ---- reflector! (UDT.jl:133-148)
-            const double* x = qs.cand[buf][wb];
+            int gh = wh[0];
+#pragma unroll
+            for (int w = 1; w < NW; ++w) gh = max(gh, wh[w]);
+            unsigned gl = 0u;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) gl = max(gl, wh[w] == gh ? wl[w] : 0u);
+            int gkey = 0x7fffffff;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) gkey = min(gkey, (wh[w] == gh && wl[w] == gl) ? wk[w] : 0x7fffffff);
+            const double maxval = __hiloint2double(gh, (int)gl);
+            const int pj = gkey & 0xffff, jm = gkey >> 16;
+            const double* x = qs.cand[buf][pj / (8 * CW)];
+            const double xlow = t.r > rj ? x[8 * mj + t.r] : 0.0;
+            double xm[MT];
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m) xm[m] = x[8 * m + t.r];
             const double xj = x[j];
-            double nu = 0.0, tj = 0.0, inv = 0.0;
             const bool live = maxval > 0.0;
-            if (live) {
-                const double rs = fast_rsqrt(maxval);
-                nu = copysign(maxval * rs, xj);
-                tj = (xj + nu) * copysign(rs, xj);
-                inv = fast_rcp(xj + nu);
-            }
+            const double rs = live ? fast_rsqrt(maxval) : 0.0;
+            const double nu = copysign(maxval * rs, xj);
             const double xjn = xj + nu;
-            const double xd = t.r < rj ? 0.0 : (t.r == rj ? (live ? xjn : 0.0) : x[8 * mj + t.r]);
-            // ---- reflectorApply! (UDT.jl:32-50) + fresh trailing norms
-            double dot[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) dot[k] = xd * A[mj][k >> 1][k & 1];
-#pragma unroll
-            for (int m = mj + 1; m < MT; ++m) {
-                const double xm = x[8 * m + t.r];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) dot[k] += xm * A[m][k >> 1][k & 1];
-            }
+            const double tj = xjn * copysign(rs, xj);
+            const double inv = live ? fast_rcp(xjn) : 0.0;
             const double tinv2 = tj * inv * inv;
-            double s[4], nn[4];
+            const double xd = t.r == rj ? xjn : xlow;
+            double dot[KC];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < KC; ++k) dot[k] = xd * A[mj][k >> 1][k & 1];
+#pragma unroll
+            for (int m = mj + 1; m < MT; ++m)
+#pragma unroll
+                for (int k = 0; k < KC; ++k) dot[k] += xm[m] * A[m][k >> 1][k & 1];
+#pragma unroll
+            for (int k = 0; k < KC; ++k) dot[k] = col_sum(dot[k]);
+            // ---- reflectorApply! (UDT.jl:32-50) + fresh trailing norms
+            double s[KC], nn[KC];
+#pragma unroll
+            for (int k = 0; k < KC; ++k) {
                 const bool is_piv = (t.col0 + 8 * (k >> 1) + (k & 1) == pj);
-                const double d = col_sum(dot[k]);
-                s[k] = (done[k] || is_piv) ? 0.0 : tinv2 * d;
+                s[k] = (done[k] || is_piv) ? 0.0 : tinv2 * dot[k];
                 A[mj][k >> 1][k & 1] -= s[k] * xd;
                 nn[k] = t.r > rj ? A[mj][k >> 1][k & 1] * A[mj][k >> 1][k & 1] : 0.0;
             }
 #pragma unroll
-            for (int m = mj + 1; m < MT; ++m) {
-                const double xm = x[8 * m + t.r];
+            for (int m = mj + 1; m < MT; ++m)
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    A[m][k >> 1][k & 1] -= s[k] * xm;
+                for (int k = 0; k < KC; ++k) {
+                    A[m][k >> 1][k & 1] -= s[k] * xm[m];
                     nn[k] += A[m][k >> 1][k & 1] * A[m][k >> 1][k & 1];
                 }
-            }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < KC; ++k) nrm[k] = col_sum(nn[k]);
+#pragma unroll
+            for (int k = 0; k < KC; ++k) {
                 const bool is_piv = (t.col0 + 8 * (k >> 1) + (k & 1) == pj);
-                nrm[k] = col_sum(nn[k]);
-                if (is_piv) done[k] = true;
-                else if (!done[k] && curpos[k] == j) curpos[k] = jm; // the swap j <-> jm (UDT.jl:219-231)
-                // the pivot column keeps R above the diagonal, -nu on it and the Householder vector below
-                if (live && is_piv) {
-                    if (t.r >= rj) A[mj][k >> 1][k & 1] = t.r == rj ? -nu : xd * inv;
-#pragma unroll
-                    for (int m = mj + 1; m < MT; ++m) A[m][k >> 1][k & 1] = x[8 * m + t.r] * inv;
-                }
+                // the swap j <-> jm (UDT.jl:219-231); a pivot column remembers its final position
+                curpos[k] = is_piv ? j : ((!done[k] && curpos[k] == j) ? jm : curpos[k]);
+                done[k] = done[k] || is_piv;
             }
-            if (threadIdx.x == 0) { qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j; }
+            if (threadIdx.x == 0) {
+                qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j;
+                qs.D[j] = -nu; qs.Dinv[j] = inv;
+            }
         }
     }
     bar2(NT);
+    // every column keeps R above its position, -nu on it and the Householder vector below
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+        const int pos = curpos[k];
+        const double dg = qs.D[pos], iv = qs.Dinv[pos];
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+            const int i = 8 * m + t.r;
+            const double a = A[m][k >> 1][k & 1];
+            A[m][k >> 1][k & 1] = i < pos ? a : (i == pos ? dg : a * iv);
+        }
+    }
+    bar2(NT); // qs.D / qs.Dinv are free again
 }
 
 // Explicit Q (see form_q); every participating warp builds its own 16 columns.
-template <int N>
-__device__ __forceinline__ void form_q2(double (&Q)[Geo2<N>::MT][2][2], const double* F, const QrSmem<N>& qs,
+template <int N, int CW = 2>
+__device__ __forceinline__ void form_q2(double (&Q)[Geo2<N>::MT][CW][2], const double* F, const QrSmem<N>& qs,
                                         const Lane2& t)
 {
-    constexpr int MT = Geo2<N>::MT, LD = Geo2<N>::LD;
+    constexpr int MT = Geo2<N>::MT, LD = Geo2<N>::LD, KC = 2 * CW;
 #pragma unroll
     for (int m = 0; m < MT; ++m)
 #pragma unroll
-        for (int k = 0; k < 4; ++k) Q[m][k >> 1][k & 1] = (8 * m + t.r == t.col0 + 8 * (k >> 1) + (k & 1)) ? 1.0 : 0.0;
+        for (int k = 0; k < KC; ++k) Q[m][k >> 1][k & 1] = (8 * m + t.r == t.col0 + 8 * (k >> 1) + (k & 1)) ? 1.0 : 0.0;
 #pragma unroll
     for (int mk = MT - 1; mk >= 0; --mk) {
 #pragma unroll 1
         for (int rk = 7; rk >= 0; --rk) {
             const int k = 8 * mk + rk;
-            if (16 * t.w + 15 < k) continue; // columns left of k are still unit vectors
+            if (8 * CW * t.w + 8 * CW - 1 < k) continue; // columns left of k are still unit vectors
             const double* x = F + (size_t)qs.piv[k] * LD;
             const double tk = qs.tau[k];
             const double vd = t.r < rk ? 0.0 : (t.r == rk ? 1.0 : x[8 * mk + t.r]);
-            double dot[4];
+            double dot[KC];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) dot[c] = vd * Q[mk][c >> 1][c & 1];
+            for (int c = 0; c < KC; ++c) dot[c] = vd * Q[mk][c >> 1][c & 1];
 #pragma unroll
             for (int m = mk + 1; m < MT; ++m) {
                 const double vm = x[8 * m + t.r];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) dot[c] += vm * Q[m][c >> 1][c & 1];
+                for (int c = 0; c < KC; ++c) dot[c] += vm * Q[m][c >> 1][c & 1];
             }
-            double s[4];
+            double s[KC];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < KC; ++c) {
                 s[c] = tk * col_sum(dot[c]);
                 Q[mk][c >> 1][c & 1] -= s[c] * vd;
             }
@@ -218,7 +252,7 @@ __device__ __forceinline__ void form_q2(double (&Q)[Geo2<N>::MT][2][2], const do
             for (int m = mk + 1; m < MT; ++m) {
                 const double vm = x[8 * m + t.r];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) Q[m][c >> 1][c & 1] -= s[c] * vm;
+                for (int c = 0; c < KC; ++c) Q[m][c >> 1][c & 1] -= s[c] * vm;
             }
         }
     }

@@ -271,27 +271,27 @@ struct UdtSmem {
     QrSmem<N> qs;
 };
 
-template <int N>
-__global__ void __launch_bounds__(Geo2<N>::NT)
+template <int N, int CW>
+__global__ void __launch_bounds__(Geo2<N, CW>::NT)
 udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
 {
-    constexpr int MT = Geo2<N>::MT, LD = Geo2<N>::LD, NT = Geo2<N>::NT;
+    constexpr int MT = Geo2<N, CW>::MT, LD = Geo2<N, CW>::LD, NT = Geo2<N, CW>::NT, KC = 2 * CW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     UdtSmem<N>& sm = *reinterpret_cast<UdtSmem<N>*>(smem_raw);
-    const Lane2 t;
+    const Lane2 t(CW);
     const int tid = threadIdx.x;
     const int chain = blockIdx.x;
     const size_t nn = (size_t)N * N;
     {
-        double A[MT][2][2];
+        double A[MT][CW][2];
         const double* X = Xg + chain * nn;
 #pragma unroll
         for (int m = 0; m < MT; ++m)
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < KC; ++k)
                 A[m][k >> 1][k & 1] = X[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N];
-        qr_pivot2<N>(A, sm.qs, t);
-        r2s2<N>(A, sm.F, t);
+        qr_pivot2<N, CW>(A, sm.qs, t);
+        r2s2<N, CW>(A, sm.F, t);
     }
     __syncthreads();
     for (int i = tid; i < N; i += NT) {
@@ -302,13 +302,13 @@ udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int
         pivg[(size_t)chain * N + i] = sm.qs.piv[i];
     }
     {
-        double Q[MT][2][2];
-        form_q2<N>(Q, sm.F, sm.qs, t);
+        double Q[MT][CW][2];
+        form_q2<N, CW>(Q, sm.F, sm.qs, t);
         double* U = Ug + chain * nn;
 #pragma unroll
         for (int m = 0; m < MT; ++m)
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < KC; ++k)
                 U[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N] = Q[m][k >> 1][k & 1];
     }
     __syncthreads();
@@ -322,6 +322,11 @@ udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int
         }
     }
 }
+
+// warp width of the stand-alone factorisation per matrix size: fewer, fatter warps execute fewer
+// instructions per Householder step (the per-step scalar work is replicated in every warp)
+template <int N> struct UdtCw { static constexpr int value = 2; };
+template <> struct UdtCw<64> { static constexpr int value = 2; };
 
 // rdivp!(A, T, O, pivot) (src/linalg/general.jl:138-166) for the same large size: out = A[:, p] triu(T)^-1.
 // Solved in the transposed domain: each warp owns 8 rows of A (= 8 columns of A'), loaded already
@@ -591,7 +596,7 @@ int set_attrs()
     MCB_CUDA(cudaFuncSetAttribute(greens_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     MCB_CUDA(cudaFuncSetAttribute(slice_products_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MultSmem<N>)));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * Geo<N>::LD * sizeof(double) + N * sizeof(int))));
-    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<N>)));
+    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<N, UdtCw<N>::value>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<N>)));
     MCB_CUDA(cudaFuncSetAttribute(greens_mid_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GlueSmem<N>)));
     MCB_CUDA(cudaFuncSetAttribute(greens_end_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GlueSmem<N>)));
     return 0;
@@ -606,7 +611,7 @@ bool rdivp_panel_supported(int n) { return stab_supported(n) || n == 144 || n ==
 int init_stab_kernels()
 {
     if (set_attrs<16>() || set_attrs<32>() || set_attrs<64>()) return -2;
-    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
+    MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<144, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<144>)));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_rows_kernel<400>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * 8 * 404 * sizeof(double) + 400 * sizeof(int))));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(144 * Geo<144>::LD * sizeof(double) + 144 * sizeof(int))));
     return 0;
@@ -676,11 +681,11 @@ int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, do
     if (batch <= 0) return 0;
     LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
     if (n == 144) {
-        udt2_kernel<144><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
+        udt2_kernel<144, 2><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
         MCB_CUDA(cudaGetLastError());
         return 0;
     }
-    STAB_DISPATCH(n, (udt2_kernel<N><<<batch, Geo2<N>::NT, sizeof(UdtSmem<N>), st>>>(X, U, D, T, pivot, apply_pivot)));
+    STAB_DISPATCH(n, (udt2_kernel<N, UdtCw<N>::value><<<batch, Geo2<N, UdtCw<N>::value>::NT, sizeof(UdtSmem<N>), st>>>(X, U, D, T, pivot, apply_pivot)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -11,6 +11,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from montecarlo_jl_b200 import _lib  # noqa: E402
 
 op, n, b = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
+if os.environ.get("MCB_LIB"):  # a differently built library (kernel variants under test)
+    _lib.LIB_PATH = os.environ["MCB_LIB"]
 L = _lib.lib()
 if len(sys.argv) > 4:
     L.mcb_linalg_force_general(1)
