@@ -7,6 +7,7 @@
 // 570-594) become pointer swaps, and calculate_greens reads the slots without clobbering them.
 #include "dqmc_engine.cuh"
 #include <math.h>
+#include <stdlib.h>
 #include <utility>
 
 namespace mcb {
@@ -441,6 +442,11 @@ int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_p
     a.chain_offset = h->p.chain_offset;
     a.n_updates0 = h->n_updates;
     a.acc = h->acc; a.prop = h->prop; a.nonfinite = h->nonfinite;
+    {
+        // all chains of a CTA wrap in the same window (segment.cuh); MCB_PHASE_SYNC=0 turns it off
+        const char* ev = getenv("MCB_PHASE_SYNC");
+        a.phase_sync = ((!ev || atoi(ev)) && h->C % 4 == 0) ? 1 : 0;
+    }
     MCB_TRY(launch_segment(a, h->st));
     h->current_slice = start + d * (int)(visits - 1);
     h->n_updates += visits;

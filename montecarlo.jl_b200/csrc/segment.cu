@@ -74,9 +74,10 @@ __device__ __forceinline__ void chain_sync(int id, int nthreads)
 
 struct CLane {
     int ctid, wl, l, r, q, col0; // thread in chain, warp in chain, lane, row-in-block, quad, first column
-    __device__ __forceinline__ CLane(int tid_in_chain)
+    // rot rotates the warp roles, so that the same role of different chains sits on different SMSPs
+    __device__ __forceinline__ CLane(int tid_in_chain, int rot, int nw)
     {
-        ctid = tid_in_chain; wl = ctid >> 5; l = ctid & 31; r = l >> 2; q = l & 3;
+        ctid = tid_in_chain; wl = ((ctid >> 5) + rot) % nw; l = ctid & 31; r = l >> 2; q = l & 3;
         col0 = 8 * CW * wl + 2 * q;
     }
 };
@@ -221,29 +222,32 @@ __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], Ch
     }
     chain_sync(bar_id, TPC);
     // ---- phase 2b: the vectors of the accepted flips, one row (NUX) or one column (V) per thread
+    // (right-looking: a finished vector entry is added to all later sums at once, so that the
+    // dependent chain is one FMA and one product per step; the order of the additions is unchanged)
     if (t.ctid < N) {
         const int rho = t.ctid;
-        double nux[8];
+        double v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = NUX[k * LD + rho] - (rho == 8 * IT + k ? 1.0 : 0.0);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            double v = NUX[k * LD + rho] - (rho == 8 * IT + k ? 1.0 : 0.0);
+            v[k] *= xS[k];
 #pragma unroll
-            for (int m = 0; m < k; ++m) v += nux[m] * rowS[m * 8 + k];
-            nux[k] = xS[k] * v;
+            for (int c = k + 1; c < 8; ++c) v[c] += v[k] * rowS[k * 8 + c];
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) NUX[k * LD + rho] = nux[k];
+        for (int k = 0; k < 8; ++k) NUX[k * LD + rho] = v[k];
     } else if (t.ctid < 2 * N) {
         const int kap = t.ctid - N;
-        double vv[8];
+        double v[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            double v = Rb[k * LD + kap];
+        for (int k = 0; k < 8; ++k) v[k] = Rb[k * LD + kap];
 #pragma unroll
-            for (int m = 0; m < k; ++m) v += nuS[m * 8 + k] * vv[m];
-            vv[k] = v;
-            V[k * LD + kap] = v;
-        }
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int c = k + 1; c < 8; ++c) v[c] += nuS[k * 8 + c] * v[k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) V[k * LD + kap] = v[k];
     }
     chain_sync(bar_id, TPC);
     // ---- phase 3: G += NUX * V on the tensor pipe (k = 8)
@@ -282,7 +286,7 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
     const int cl = threadIdx.x / TPC; // chain within the CTA
     const int chain = blockIdx.x * CH + cl;
     if (chain >= a.batch) return; // whole chains leave together; they only use their own barrier below
-    const CLane t(threadIdx.x % TPC);
+    const CLane t(threadIdx.x % TPC, a.phase_sync ? cl : 0, TPC / 32);
     const int bar_id = 1 + cl;
     ChainSmem<N>& cs = sm.ch[cl];
     double* Gg = a.G + (size_t)chain * a.sG;
@@ -301,8 +305,24 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
     if (t.ctid == 0) { cs.flag = 0; cs.nacc = 0; }
     for (int v = 0; v < a.n_visits; ++v) {
         const int slice = a.start_slice + a.direction * v;
-        if (v > 0 || a.first_wrap) {
+        // the fields and uniforms of this visit's sweep_spatial (read together with the wrap's fields,
+        // one global-memory round trip per visit)
+        const bool wrapping = v > 0 || a.first_wrap;
+        {
+            const long long upd = a.n_updates0 + v;
+            const uint32_t sweep = (uint32_t)(upd / (2LL * a.n_slices));
+            const uint32_t visit = (uint32_t)(upd % (2LL * a.n_slices));
+            for (int i = t.ctid; i < N; i += TPC) {
+                cs.s_in[i] = cg[(size_t)(slice - 1) * N + i];
+                cs.unif[i] = dqmc_uniform(a.key0, k1, sweep, visit, (uint32_t)i);
+            }
+        }
+        if (wrapping) {
             // ---- wrap_greens!
+            // The products saturate the FP64 pipe, and a dependent DFMA of another chain's site loop
+            // that queues behind them takes several times its latency: all chains of the CTA do their
+            // products in the same window and their site loops in the other.
+            if (a.phase_sync) __syncthreads();
             const int l = a.direction > 0 ? slice - 1 : slice; // slice matrix B_l
             for (int i = t.ctid; i < N; i += TPC) {
                 const int s = cg[(size_t)(l - 1) * N + i];
@@ -334,16 +354,10 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
                 gemm<N>(acc, cs.X, sm.eT2, t);
                 scale_cols<N>(acc, cs.sc_col, t);
             }
+            if (a.phase_sync) __syncthreads();
         }
         // ---- sweep_spatial of `slice`
-        const long long upd = a.n_updates0 + v;
-        const uint32_t sweep = (uint32_t)(upd / (2LL * a.n_slices));
-        const uint32_t visit = (uint32_t)(upd % (2LL * a.n_slices));
-        for (int i = t.ctid; i < N; i += TPC) {
-            cs.s_in[i] = cg[(size_t)(slice - 1) * N + i];
-            cs.unif[i] = dqmc_uniform(a.key0, k1, sweep, visit, (uint32_t)i);
-        }
-        chain_sync(bar_id, TPC);
+        if (!wrapping) chain_sync(bar_id, TPC);
         site_block<N, 0>(acc, cs, a, t, bar_id, nacc);
         chain_sync(bar_id, TPC);
         for (int i = t.ctid; i < N; i += TPC) cg[(size_t)(slice - 1) * N + i] = cs.s_out[i];

@@ -23,6 +23,7 @@ struct SegmentArgs {
     long long* acc = nullptr;
     long long* prop = nullptr;
     long long* nonfinite = nullptr;
+    int phase_sync = 0; // CTA-wide barriers around the wrap (all chains of the CTA present: batch % 4 == 0)
 };
 
 // true if a chain-resident instantiation exists for this matrix size

@@ -100,6 +100,40 @@ __global__ void k_bar(double* out, long long* cyc)
     long long t1 = clock64();
     if (threadIdx.x == 0) cyc[0] = t1 - t0;
 }
+__global__ void k_bar_reg(double* out, long long* cyc)
+{
+    const int grp = threadIdx.x >> 7;
+    const int id = 1 + grp;
+    __shared__ double buf[512];
+    long long t0 = clock64();
+#pragma unroll 4
+    for (int i = 0; i < REP; ++i) {
+        buf[threadIdx.x] = i;
+        asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(128) : "memory");
+    }
+    long long t1 = clock64();
+    out[threadIdx.x] = buf[(threadIdx.x + 1) & 511];
+    if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+__global__ void k_bar_one_works(double* out, long long* cyc)
+{
+    // warp 0 of each group does ~200 cycles of dependent work, the other 3 wait
+    const int grp = threadIdx.x >> 7, w = (threadIdx.x >> 5) & 3;
+    const int id = 1 + grp;
+    double x = out[threadIdx.x];
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int i = 0; i < REP; ++i) {
+        if (w == 0) {
+#pragma unroll
+            for (int k = 0; k < 24; ++k) x = fma(x, 1.0000001, 1e-9);
+        }
+        asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(128) : "memory");
+    }
+    long long t1 = clock64();
+    out[threadIdx.x] = x;
+    if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
 template <class F> void run(const char* name, F f, int ops = REP)
 {
     long long* cyc; double* out;
@@ -122,5 +156,9 @@ int main()
     run("MUFU.RCP64H dependent", [](double* o, long long* c) { k_rcp<<<1, 32>>>(o, c); });
     run("LDS dependent", [](double* o, long long* c) { k_lds<<<1, 256>>>(o, c); });
     run("bar.sync 128 thr", [](double* o, long long* c) { k_bar<<<1, 128>>>(o, c); });
+    run("bar.sync reg-id, 4 groups x128 + STS", [](double* o, long long* c) { k_bar_reg<<<1, 512>>>(o, c); });
+    run("bar.sync reg-id, 1 group  x128 + STS", [](double* o, long long* c) { k_bar_reg<<<1, 128>>>(o, c); });
+    run("24 dep DFMA in 1 of 4 warps + bar, 4 grp", [](double* o, long long* c) { k_bar_one_works<<<1, 512>>>(o, c); });
+    run("24 dep DFMA in 1 of 4 warps + bar, 1 grp", [](double* o, long long* c) { k_bar_one_works<<<1, 128>>>(o, c); });
     return 0;
 }
