@@ -144,6 +144,15 @@ int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const 
         g.C = C; g.strideC = nn;
         return g;
     };
+    if (stab_supported(n) && !force_general_udt()) {
+        // one CTA per chain: the scaled product inside the first factorisation, everything between and
+        // after the factorisations in the two glue kernels (stab.cuh)
+        MCB_TRY(launch_udt_of_product(n, batch, Tl, Tr, Dl, Dr, W[1], Dw[0], W[2], pivot, st));
+        MCB_TRY(launch_greens_mid(n, batch, Ul, W[1], W[2], pivot, Dw[0], Ur, W[3], W[4], W[0], st));
+        MCB_TRY(launch_udt(n, batch, W[0], nn, W[1], nn, Dw[1], n, W[2], nn, pivot, n, 0, st));
+        MCB_TRY(launch_greens_end(n, batch, W[3], W[1], W[2], pivot, Dw[1], W[4], G, st));
+        return 0;
+    }
     // B1: W0 = diag(Dl) (Tl Tr') diag(Dr) ; udt -> Q1 = W1, D1 = Dw0, dirty T = W2
     {
         GemmArgs g = gemm(Tl, false, Tr, true, W[0]);
@@ -152,13 +161,6 @@ int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const 
         MCB_TRY(launch_gemm(g, st));
     }
     MCB_TRY(launch_udt(n, batch, W[0], nn, W[1], nn, Dw[0], n, W[2], nn, pivot, n, 0, st));
-    if (stab_supported(n) && !force_general_udt()) {
-        // one CTA per chain for everything between and after the factorisations (stab.cuh)
-        MCB_TRY(launch_greens_mid(n, batch, Ul, W[1], W[2], pivot, Dw[0], Ur, W[3], W[4], W[0], st));
-        MCB_TRY(launch_udt(n, batch, W[0], nn, W[1], nn, Dw[1], n, W[2], nn, pivot, n, 0, st));
-        MCB_TRY(launch_greens_end(n, batch, W[3], W[1], W[2], pivot, Dw[1], W[4], G, st));
-        return 0;
-    }
     // B2: W3 = Ul Q1 ; W4 = Ur[:,p] triu(W2)^-1 ; W0 = W3' W4 + diag(D1)   (B3 fused)
     MCB_TRY(launch_gemm(gemm(Ul, false, W[1], false, W[3]), st));
     MCB_TRY(launch_rdivp(n, batch, Ur, nn, W[4], nn, W[2], nn, pivot, n, st));
@@ -211,6 +213,9 @@ int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
         a.ep = h->eVp[0]; a.em = h->eVp[1];
         if (!h->split_stab) return launch_advance_panel(a, h->st);
         MCB_TRY(launch_slice_products(a, h->W[0], h->st));
+        if (!force_general_udt())
+            return launch_udt_times(h->N, h->C, h->W[0], h->bufU[dst], h->bufD[dst], h->bufT[src], h->bufT[dst],
+                                    h->pivot, h->st);
         MCB_TRY(launch_udt(h->N, h->C, h->W[0], h->nn, h->bufU[dst], h->nn, h->bufD[dst], h->N, h->W[2], h->nn,
                            h->pivot, h->N, 1, h->st));
         return launch_gemm(base_gemm(h, h->W[2], false, h->bufT[src], false, h->bufT[dst]), h->st);

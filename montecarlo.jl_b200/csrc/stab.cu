@@ -265,6 +265,17 @@ __global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1)) greens_ker
 // udt_AVX_pivot! as a kernel of its own: N/16 warps with 16 columns each (panel_qr2.cuh), ONE
 // shared-memory matrix next to the pivoting buffers, so that several chains share an SM (N = 64:
 // 45 KB and 128 threads per chain) and N = 144 fits at all (9 warps, 144 registers of matrix per thread).
+// udt2_kernel arguments. Input: X, or (X == nullptr) the scaled product diag(rs) PA PB' diag(cs).
+// Output: U, D, pivot and T, or (Tsrc != nullptr, apply_pivot form) T * Tsrc in T's place.
+struct UdtFused {
+    const double* X = nullptr;
+    const double *PA = nullptr, *PB = nullptr, *rs = nullptr, *cs = nullptr;
+    double *U = nullptr, *D = nullptr, *T = nullptr;
+    int* piv = nullptr;
+    int apply_pivot = 1;
+    const double* Tsrc = nullptr;
+};
+
 template <int N>
 struct UdtSmem {
     double F[N * Geo<N>::LD];
@@ -272,8 +283,8 @@ struct UdtSmem {
 };
 
 template <int N, int CW>
-__global__ void __launch_bounds__(Geo2<N, CW>::NT)
-udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int apply_pivot)
+__global__ void __launch_bounds__(Geo2<N, CW>::NT, (N <= 64 ? 4 : 1))
+udt2_kernel(UdtFused a)
 {
     constexpr int MT = Geo2<N, CW>::MT, LD = Geo2<N, CW>::LD, NT = Geo2<N, CW>::NT, KC = 2 * CW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -284,12 +295,52 @@ udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int
     const size_t nn = (size_t)N * N;
     {
         double A[MT][CW][2];
-        const double* X = Xg + chain * nn;
+        if (a.X) {
+            const double* X = a.X + chain * nn;
 #pragma unroll
-        for (int m = 0; m < MT; ++m)
+            for (int m = 0; m < MT; ++m)
 #pragma unroll
-            for (int k = 0; k < KC; ++k)
-                A[m][k >> 1][k & 1] = X[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N];
+                for (int k = 0; k < KC; ++k)
+                    A[m][k >> 1][k & 1] = X[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N];
+        } else {
+            // X = diag(rs) (PA PB') diag(cs) computed here (calculate_greens, stack.jl:346-348): PB staged in
+            // F, PA streamed from global memory as DMMA fragments
+            const double* PB = a.PB + chain * nn;
+            for (int e = tid; e < N * N; e += NT) sm.F[(e % N) + (e / N) * LD] = PB[e];
+            __syncthreads();
+            const double* PA = a.PA + chain * nn + t.r + (size_t)t.q * N;
+            const double* bp = sm.F + (8 * CW * t.w + t.r) + t.q * LD;
+#pragma unroll
+            for (int m = 0; m < MT; ++m)
+#pragma unroll
+                for (int cw = 0; cw < CW; ++cw) A[m][cw][0] = A[m][cw][1] = 0.0;
+#pragma unroll 2
+            for (int k0 = 0; k0 < N; k0 += 4) {
+                double av[MT], b[CW];
+#pragma unroll
+                for (int m = 0; m < MT; ++m) av[m] = __ldg(PA + 8 * m + (size_t)k0 * N);
+#pragma unroll
+                for (int cw = 0; cw < CW; ++cw) b[cw] = bp[8 * cw + k0 * LD];
+#pragma unroll
+                for (int m = 0; m < MT; ++m)
+#pragma unroll
+                    for (int cw = 0; cw < CW; ++cw) dmma884(A[m][cw][0], A[m][cw][1], av[m], b[cw]);
+            }
+            const double* rs = a.rs + (size_t)chain * N;
+            const double* cs = a.cs + (size_t)chain * N;
+#pragma unroll
+            for (int k = 0; k < KC; ++k) {
+                const double c = __ldg(cs + t.col0 + 8 * (k >> 1) + (k & 1));
+#pragma unroll
+                for (int m = 0; m < MT; ++m) A[m][k >> 1][k & 1] *= c;
+            }
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                const double r = __ldg(rs + 8 * m + t.r);
+#pragma unroll
+                for (int k = 0; k < KC; ++k) A[m][k >> 1][k & 1] *= r;
+            }
+        }
         qr_pivot2<N, CW>(A, sm.qs, t);
         r2s2<N, CW>(A, sm.F, t);
     }
@@ -298,13 +349,13 @@ udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int
         const double d = fabs(sm.F[i + (size_t)sm.qs.piv[i] * LD]);
         sm.qs.D[i] = d;
         sm.qs.Dinv[i] = 1.0 / d;
-        Dg[(size_t)chain * N + i] = d;
-        pivg[(size_t)chain * N + i] = sm.qs.piv[i];
+        a.D[(size_t)chain * N + i] = d;
+        a.piv[(size_t)chain * N + i] = sm.qs.piv[i];
     }
     {
         double Q[MT][CW][2];
         form_q2<N, CW>(Q, sm.F, sm.qs, t);
-        double* U = Ug + chain * nn;
+        double* U = a.U + chain * nn;
 #pragma unroll
         for (int m = 0; m < MT; ++m)
 #pragma unroll
@@ -312,13 +363,48 @@ udt2_kernel(const double* Xg, double* Ug, double* Dg, double* Tg, int* pivg, int
                 U[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N] = Q[m][k >> 1][k & 1];
     }
     __syncthreads();
+    if (a.Tsrc) {
+        // T = D^-1 R P' materialised in F, then T_out = T * Tsrc (t_stack update, stack.jl:285, 309)
+        for (int e = tid; e < N * N; e += NT) {
+            const int i = e % N, j = e / N;
+            const double v = sm.F[i + j * LD];
+            sm.F[i + j * LD] = i <= sm.qs.pos[j] ? v * sm.qs.Dinv[i] : 0.0;
+        }
+        __syncthreads();
+        double C[MT][CW][2];
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+#pragma unroll
+            for (int cw = 0; cw < CW; ++cw) C[m][cw][0] = C[m][cw][1] = 0.0;
+        const double* ap = sm.F + t.r + t.q * LD;
+        const double* Bg = a.Tsrc + chain * nn + t.q + (size_t)(8 * CW * t.w + t.r) * N;
+#pragma unroll 2
+        for (int k0 = 0; k0 < N; k0 += 4) {
+            double b[CW];
+#pragma unroll
+            for (int cw = 0; cw < CW; ++cw) b[cw] = __ldg(Bg + k0 + (size_t)(8 * cw) * N);
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                const double av = ap[8 * m + k0 * LD];
+#pragma unroll
+                for (int cw = 0; cw < CW; ++cw) dmma884(C[m][cw][0], C[m][cw][1], av, b[cw]);
+            }
+        }
+        double* To = a.T + chain * nn;
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+#pragma unroll
+            for (int k = 0; k < KC; ++k)
+                To[(8 * m + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * N] = C[m][k >> 1][k & 1];
+        return;
+    }
     // T from the shared-memory copy of the factored matrix (UDT.jl:283-306)
     for (int e = tid; e < N * N; e += NT) {
         const int i = e % N, j = e / N;
-        if (apply_pivot) { // T[:, p] = D^-1 R[:, pos(p)] masked below the position
-            Tg[chain * nn + e] = i <= sm.qs.pos[j] ? sm.F[i + j * LD] * sm.qs.Dinv[i] : 0.0;
-        } else {           // columns in position order
-            Tg[chain * nn + e] = i <= j ? sm.F[i + sm.qs.piv[j] * LD] * sm.qs.Dinv[i] : 0.0;
+        if (a.apply_pivot) { // T[:, p] = D^-1 R[:, pos(p)] masked below the position
+            a.T[chain * nn + e] = i <= sm.qs.pos[j] ? sm.F[i + j * LD] * sm.qs.Dinv[i] : 0.0;
+        } else {             // columns in position order
+            a.T[chain * nn + e] = i <= j ? sm.F[i + sm.qs.piv[j] * LD] * sm.qs.Dinv[i] : 0.0;
         }
     }
 }
@@ -675,19 +761,42 @@ int launch_greens_end(int n, int batch, const double* W3, const double* Q2, cons
     return 0;
 }
 
-int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, double* T, int* pivot,
-                     int apply_pivot, cudaStream_t st)
+static int launch_udt2(int n, int batch, const UdtFused& a, double flops, cudaStream_t st)
 {
     if (batch <= 0) return 0;
-    LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
+    LaunchScope scope(LC_UDT, st, flops * batch);
     if (n == 144) {
-        udt2_kernel<144, 2><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(X, U, D, T, pivot, apply_pivot);
+        udt2_kernel<144, 2><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(a);
         MCB_CUDA(cudaGetLastError());
         return 0;
     }
-    STAB_DISPATCH(n, (udt2_kernel<N, UdtCw<N>::value><<<batch, Geo2<N, UdtCw<N>::value>::NT, sizeof(UdtSmem<N>), st>>>(X, U, D, T, pivot, apply_pivot)));
+    STAB_DISPATCH(n, (udt2_kernel<N, UdtCw<N>::value><<<batch, Geo2<N, UdtCw<N>::value>::NT, sizeof(UdtSmem<N>), st>>>(a)));
     MCB_CUDA(cudaGetLastError());
     return 0;
+}
+
+int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, double* T, int* pivot,
+                     int apply_pivot, cudaStream_t st)
+{
+    UdtFused a;
+    a.X = X; a.U = U; a.D = D; a.T = T; a.piv = pivot; a.apply_pivot = apply_pivot;
+    return launch_udt2(n, batch, a, 8.0 / 3.0 * n * (double)n * n, st);
+}
+
+int launch_udt_of_product(int n, int batch, const double* PA, const double* PB, const double* rs, const double* cs,
+                          double* U, double* D, double* T, int* pivot, cudaStream_t st)
+{
+    UdtFused a;
+    a.PA = PA; a.PB = PB; a.rs = rs; a.cs = cs; a.U = U; a.D = D; a.T = T; a.piv = pivot; a.apply_pivot = 0;
+    return launch_udt2(n, batch, a, (2.0 + 8.0 / 3.0) * n * (double)n * n, st);
+}
+
+int launch_udt_times(int n, int batch, const double* X, double* U, double* D, const double* Tsrc, double* Tout,
+                     int* pivot, cudaStream_t st)
+{
+    UdtFused a;
+    a.X = X; a.U = U; a.D = D; a.T = Tout; a.piv = pivot; a.apply_pivot = 1; a.Tsrc = Tsrc;
+    return launch_udt2(n, batch, a, (2.0 + 8.0 / 3.0) * n * (double)n * n, st);
 }
 
 // out = in[:, pivot] * triu(T)^-1 for the sizes with a register-resident solver (udt_panel_supported && n > 64)

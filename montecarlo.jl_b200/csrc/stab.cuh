@@ -37,6 +37,13 @@ int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st);
 // position order) and the 0-based pivot vector; same contract as launch_udt (udt.cuh)
 int launch_udt_panel(int n, int batch, const double* X, double* U, double* D, double* T, int* pivot,
                      int apply_pivot, cudaStream_t st);
+// the same factorisation with the product that feeds it / consumes it done by the same CTA (stab_supported sizes):
+//   _of_product: X = diag(rs) (PA PB') diag(cs), T "dirty"            calculate_greens, stack.jl:346-349
+//   _times:      T_out = (D^-1 R P') * Tsrc instead of T              add_slice_sequence_*, stack.jl:285, 309
+int launch_udt_of_product(int n, int batch, const double* PA, const double* PB, const double* rs, const double* cs,
+                          double* U, double* D, double* T, int* pivot, cudaStream_t st);
+int launch_udt_times(int n, int batch, const double* X, double* U, double* D, const double* Tsrc, double* Tout,
+                     int* pivot, cudaStream_t st);
 int launch_rdivp_panel(int n, int batch, const double* in, double* out, const double* T, const int* pivot,
                        cudaStream_t st);
 // calculate_greens between / after its two factorisations (T1, T2 "dirty", i.e. apply_pivot = 0):
