@@ -60,6 +60,69 @@ __global__ void k_chain(double* out, long long* cyc, double gp, double gm, doubl
     if (threadIdx.x == 0) cyc[0] = t1 - t0;
 }
 
+// the same chain with G_ii of the next site taken from shuffles issued before 1/R is known (segment.cu as built)
+__global__ void k_chain2(double* out, long long* cyc, double gp, double gm, double ep, double em)
+{
+    __shared__ double unif[64], nuS[8][64], rowS[8][64], xS[8][8];
+    __shared__ int8_t s_in[64];
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, r8 = l & 7;
+    if (threadIdx.x < 64) { unif[threadIdx.x] = 0.37 + 0.001 * threadIdx.x; s_in[threadIdx.x] = (threadIdx.x & 1) ? 1 : -1; }
+    __syncthreads();
+    double Dr[8];
+    for (int c = 0; c < 8; ++c) Dr[c] = out[r8 * 8 + c];
+    int nacc = 0;
+    long long t0 = clock64();
+    for (int rep = 0; rep < REP; ++rep) {
+        int sgn = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sgn |= (s_in[j] > 0 ? 1 : 0) << j;
+        int flips = 0;
+        double gii = __shfl_sync(0xffffffffu, Dr[0], 0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            double rowj[8];
+#pragma unroll
+            for (int c = j + 1; c < 8; ++c) rowj[c] = __shfl_sync(0xffffffffu, Dr[c], j);
+            double a1 = 0.0, q1 = 0.0;
+            if (j < 7) {
+                a1 = __shfl_sync(0xffffffffu, Dr[j], j + 1);
+                q1 = __shfl_sync(0xffffffffu, Dr[j < 7 ? j + 1 : 7], j + 1);
+            }
+            const bool up = (sgn >> j) & 1;
+            const double gam = up ? gp : gm;
+            const double efc = up ? ep : em;
+            const double dm = Dr[j] - (r8 == j ? 1.0 : 0.0);
+            const double rt = 1.0 + gam * (1.0 - gii);
+            const double p = efc * (rt * rt);
+            const bool accept = unif[j] < p;
+            const double xs = gam * fast_rcp(rt);
+            const double x = accept ? xs : 0.0;
+            const double nu = accept ? xs * dm : 0.0;
+            if (j < 7) {
+                const double nu1 = accept ? xs * a1 : 0.0;
+                gii = fma(nu1, rowj[j < 7 ? j + 1 : 7], q1);
+            }
+#pragma unroll
+            for (int c = j + 1; c < 8; ++c) Dr[c] += nu * rowj[c];
+            flips |= (accept ? 1 : 0) << j;
+            if (l < 8) nuS[w][j * 8 + l] = nu;
+            if (l == 0) {
+                xS[w][j] = x;
+#pragma unroll
+                for (int c = j + 1; c < 8; ++c) rowS[w][j * 8 + c] = rowj[c];
+            }
+        }
+        nacc += __popc(flips);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) Dr[c] = Dr[c] * 0.5 + 0.01 * (c + r8);
+    }
+    long long t1 = clock64();
+    double s = nacc;
+    for (int c = 0; c < 8; ++c) s += Dr[c];
+    out[threadIdx.x] = s;
+    if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+
 // the decision chain in warp 0 of every group of 4 warps; the other 3 wait at the group's named barrier
 __global__ void k_chain_wait(double* out, long long* cyc, double gp, double gm, double ep, double em, int nregs_dummy)
 {
@@ -169,6 +232,12 @@ int main()
         k_chain<<<1, 32 * warps>>>(out, cyc, 0.7, -0.4, 1.2, 0.8);
         long long c; cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
         printf("decision chain, %d warp(s): %.1f cycles per site (%s)\n", warps, (double)c / (REP * 8), cudaGetErrorString(cudaGetLastError()));
+    }
+    {
+        cudaMemcpy(out, h, sizeof(h), cudaMemcpyHostToDevice);
+        k_chain2<<<1, 32>>>(out, cyc, 0.7, -0.4, 1.2, 0.8);
+        long long c; cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
+        printf("decision chain with early next-G_ii shuffles, 1 warp: %.1f cycles per site (%s)\n", (double)c / (REP * 8), cudaGetErrorString(cudaGetLastError()));
     }
     for (int groups = 1; groups <= 4; groups *= 2) {
         cudaMemcpy(out, h, sizeof(h), cudaMemcpyHostToDevice);
