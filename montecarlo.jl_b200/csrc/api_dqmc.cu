@@ -68,7 +68,6 @@ int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
     h->N = p->n_sites; h->M = p->n_slices; h->s = p->safe_mult; h->C = p->n_chains;
     h->ne = h->M / h->s + 1;
     h->use_panel = segment_supported(h->N) && stab_supported(h->N) && p->general_path == 0;
-    { const char* e = getenv("MCB_STAB"); h->split_stab = !(e && strcmp(e, "fused") == 0); }
     h->nn = (size_t)h->N * h->N;
     h->mat = h->nn * h->C;
     h->vec = (size_t)h->N * h->C;

@@ -186,14 +186,6 @@ namespace {
 
 int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 {
-    if (h->use_panel && !h->split_stab) {
-        GreensArgs a;
-        a.n = h->N; a.batch = h->C;
-        a.Ul = h->bufU[physL]; a.Dl = h->bufD[physL]; a.Tl = h->bufT[physL];
-        a.Ur = h->bufU[physR]; a.Dr = h->bufD[physR]; a.Tr = h->bufT[physR];
-        a.G = out;
-        return launch_greens_panel(a, h->st);
-    }
     return calc_greens_raw(h->N, h->C, h->bufU[physL], h->bufD[physL], h->bufT[physL], h->bufU[physR],
                            h->bufD[physR], h->bufT[physR], out, h->W, h->Dw, h->pivot, h->st);
 }
@@ -211,7 +203,6 @@ int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
         a.conf = h->conf; a.sConf = (long long)h->M * h->N;
         a.lo = lo; a.hi = hi; a.left = left ? 1 : 0;
         a.ep = h->eVp[0]; a.em = h->eVp[1];
-        if (!h->split_stab) return launch_advance_panel(a, h->st);
         MCB_TRY(launch_slice_products(a, h->W[0], h->st));
         if (!force_general_udt())
             return launch_udt_times(h->N, h->C, h->W[0], h->bufU[dst], h->bufD[dst], h->bufT[src], h->bufT[dst],

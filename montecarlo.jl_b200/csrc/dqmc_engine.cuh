@@ -49,7 +49,6 @@ struct mcb_dqmc {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
     bool use_panel = false; // chain-resident kernels (panel.cuh) exist for this N
-    bool split_stab = false; // stabilisation as separate kernels (products, UDT at high occupancy, solves)
     bool hopping_set = false, conf_set = false, stack_built = false;
 
     int obs_len() const { return 4 + 2 * n_dirs; }

@@ -1,14 +1,12 @@
-// The Householder steps of panel_qr.cuh on HALF the warps: the first N/16 warps of the CTA hold the
-// matrix with 16 columns per warp,
-//     lane l (r = l>>2, q = l&3): A[m][cw][c] = X[8m + r][16 w + 8 cw + 2q + c],
-// the other warps wait. The per-step work that does not shrink with the warp count (pivot search,
-// reflector scalars, barrier) is replicated in every participating warp, so fewer, fatter warps
-// execute about half the instructions per Householder step. The participating warps synchronise on
-// named barrier 1; everything else (pivot rule, reflector, storage of R / v / tau / piv / pos in
-// QrSmem) is identical to qr_pivot / form_q.
+// Column-pivoted Householder QR (udt_AVX_pivot!, src/linalg/UDT.jl:192-266) of a register-resident matrix:
+// a CTA's N / (8 CW) warps hold CW 8-column blocks each,
+//     lane l (r = l>>2, q = l&3): A[m][cw][c] = X[8m + r][8 CW w + 8 cw + 2q + c].
+// The per-step work that does not shrink with the warp count (pivot search, reflector scalars, barrier)
+// is replicated in every warp, the per-column work grows with CW: CW = 2 is the measured optimum at
+// N = 64 (CW = 1: 8.8 ms, CW = 2: 6.05 ms, CW = 4: 7.6 ms of factorisations per dqmc_A512 sweep).
+// The warps synchronise on named barrier 1; pivoting state (tau, piv, pos) lives in QrSmem.
 #pragma once
 #include "panel_qr.cuh"
-
 
 namespace mcb {
 namespace panel {
@@ -38,18 +36,6 @@ struct Lane2 {
 };
 
 template <int N, int CW = 2>
-__device__ __forceinline__ void s2r2(double (&A)[Geo2<N>::MT][CW][2], const double* S, const Lane2& t)
-{
-    constexpr int LD = Geo2<N>::LD;
-#pragma unroll
-    for (int m = 0; m < Geo2<N>::MT; ++m)
-#pragma unroll
-        for (int cw = 0; cw < CW; ++cw)
-#pragma unroll
-            for (int c = 0; c < 2; ++c) A[m][cw][c] = S[(8 * m + t.r) + (t.col0 + 8 * cw + c) * LD];
-}
-
-template <int N, int CW = 2>
 __device__ __forceinline__ void r2s2(const double (&A)[Geo2<N>::MT][CW][2], double* S, const Lane2& t)
 {
     constexpr int LD = Geo2<N>::LD;
@@ -61,7 +47,10 @@ __device__ __forceinline__ void r2s2(const double (&A)[Geo2<N>::MT][CW][2], doub
             for (int c = 0; c < 2; ++c) S[(8 * m + t.r) + (t.col0 + 8 * cw + c) * LD] = A[m][cw][c];
 }
 
-// Column-pivoted Householder QR (see qr_pivot). Called by the first Geo2<N>::NW warps only.
+// Column-pivoted Householder QR, in place. On return the physical column k = qs.piv[j] holds R[0..j, j] in
+// rows <= j and the Householder vector of step j in rows > j (implicit leading 1), qs.tau[j] its factor.
+// Pivot rule of indmaxcolumn (UDT.jl:151-168): first strict maximum of the freshly recomputed trailing
+// column norms, in the column order the reference's swaps would have produced (tracked as `curpos`).
 // A Householder step is one long dependency chain (pivot search -> barrier -> reflector scalars -> dot
 // products -> update -> fresh norms), so the code is arranged for latency rather than instruction count:
 //  * squared norms are non-negative doubles, so their bit patterns order like integers: the pivot
@@ -214,7 +203,8 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSme
     bar2(NT); // qs.D / qs.Dinv are free again
 }
 
-// Explicit Q (see form_q); every participating warp builds its own 16 columns.
+// Q = H_0 H_1 ... H_{N-1} (explicit, UDT.jl:250-266). F = the factored matrix in shared memory (ld = LD);
+// every warp builds its own columns independently.
 template <int N, int CW = 2>
 __device__ __forceinline__ void form_q2(double (&Q)[Geo2<N>::MT][CW][2], const double* F, const QrSmem<N>& qs,
                                         const Lane2& t)

@@ -1,6 +1,8 @@
-// Chain-resident stabilisation kernels: see stab.cuh. One CTA per chain, N/8 warps; every N x N
-// matrix of the sequence lives in registers (accumulator layout of DMMA m8n8k4) or in one of three
-// shared-memory operand buffers; global memory is touched only for the inputs and the results.
+// Chain-resident stabilisation kernels: see stab.cuh. One CTA per chain; the N x N matrices of a step live
+// in registers (accumulator layout of DMMA m8n8k4) or in shared-memory operand buffers, global memory is
+// touched for the inputs and the results of a kernel. Products (FP64-pipe bound) and factorisations
+// (latency bound) are separate kernels on purpose: a dependent DFMA that queues behind another warp's
+// DMMAs takes several times its latency (profiles/microbench), so the two kinds must not share an SM.
 #include "panel_qr2.cuh"
 #include "stab.cuh"
 
@@ -9,58 +11,6 @@ namespace mcb {
 namespace {
 
 using namespace panel;
-
-template <int N>
-struct StabSmem {
-    static constexpr int LD = Geo<N>::LD;
-    double S0[N * LD];
-    double S1[N * LD];
-    double S2[N * LD];
-    QrSmem<N> qs;
-    // two scaling vectors, consumed before a factorisation starts: they alias the second candidate
-    // buffer of qr_pivot (first written after that routine's first barrier)
-    __device__ double* d0() { return qs.cand[1][0]; }
-    __device__ double* d1() { return qs.cand[1][0] + N; }
-};
-
-// X (registers) -> T = D^-1 R P' in X, explicit Q, qs.{D, Dinv, piv, pos}. F: scratch matrix in
-// shared memory that no warp is reading any more. Called by ALL warps of the CTA; the Householder
-// steps themselves run on the first N/16 warps with 16 columns each (panel_qr2.cuh), the matrix
-// changes layout through F. Ends with a block-wide barrier.
-template <int N>
-__device__ __forceinline__ void udt_regs(double (&X)[Geo<N>::MT][2], double (&Q)[Geo<N>::MT][2], double* F,
-                                         QrSmem<N>& qs, const Lane& t)
-{
-    constexpr int MT = Geo<N>::MT;
-    r2s<N, false>(X, F, t);
-    __syncthreads();
-    double Q2[MT][2][2];
-    const bool part = t.w < Geo2<N>::NW;
-    const Lane2 t2;
-    if (part) {
-        {
-            double A2[MT][2][2];
-            s2r2<N>(A2, F, t2);
-            qr_pivot2<N>(A2, qs, t2);
-            r2s2<N>(A2, F, t2);
-        }
-        bar2(Geo2<N>::NT);
-        for (int i = t.tid; i < N; i += Geo2<N>::NT) {
-            const double d = fabs(F[i + (size_t)qs.piv[i] * Geo<N>::LD]);
-            qs.D[i] = d;
-            qs.Dinv[i] = 1.0 / d;
-        }
-        form_q2<N>(Q2, F, qs, t2);
-    }
-    __syncthreads();
-    s2r<N>(X, F, t); // the factored matrix, for make_t
-    __syncthreads();
-    if (part) r2s2<N>(Q2, F, t2);
-    __syncthreads();
-    s2r<N>(Q, F, t);
-    make_t<N>(X, qs, t);
-    __syncthreads();
-}
 
 template <int N>
 __device__ __forceinline__ void load_vec(double* dst, const double* __restrict__ src, int tid)
@@ -78,61 +28,6 @@ __device__ __forceinline__ void load_ev(double (&ev)[Geo<N>::MT], const int8_t* 
 }
 
 // ------------------------------------------------------------------ add_slice_sequence_*
-template <int N>
-__global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1)) advance_kernel(AdvanceArgs a)
-{
-    constexpr int MT = Geo<N>::MT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    StabSmem<N>& sm = *reinterpret_cast<StabSmem<N>*>(smem_raw);
-    const Lane t;
-    const int chain = blockIdx.x;
-    const size_t nn = (size_t)N * N;
-    const int8_t* cg = a.conf + (size_t)chain * a.sConf;
-
-    double X[MT][2], Y[MT][2];
-    g2r<N>(X, a.Usrc + chain * nn, t);
-    g2s<N, false>(sm.S0, a.eT2, t.tid);
-    g2s<N, false>(sm.S2, a.Tsrc + chain * nn, t.tid);
-    load_vec<N>(sm.d0(), a.Dsrc + (size_t)chain * N, t.tid);
-    const int cnt = a.hi - a.lo + 1;
-    double ev[MT];
-    load_ev<N>(ev, cg + (size_t)((a.left ? a.lo : a.hi) - 1) * N, a.ep, a.em, t);
-    __syncthreads();
-    for (int s = 0; s < cnt; ++s) {
-        double evn[MT];
-        if (s + 1 < cnt) {
-            const int nxt = a.left ? a.lo + s + 1 : a.hi - s - 1;
-            load_ev<N>(evn, cg + (size_t)(nxt - 1) * N, a.ep, a.em, t);
-        }
-        if (a.left) {
-            // multiply_slice_matrix_left!: X <- e^{-dtau T} diag(e^{lambda s}) X   (slice_matrices.jl:42-48)
-#pragma unroll
-            for (int m = 0; m < MT; ++m) { X[m][0] *= ev[m]; X[m][1] *= ev[m]; }
-            gemm_regB<N, false>(Y, sm.S0, X, t);
-#pragma unroll
-            for (int m = 0; m < MT; ++m) { X[m][0] = Y[m][0]; X[m][1] = Y[m][1]; }
-        } else {
-            // multiply_daggered_slice_matrix_left!: X <- diag(e^{lambda s}) (e^{-dtau T})' X   (:70-76)
-            gemm_regB<N, true>(Y, sm.S0, X, t);
-#pragma unroll
-            for (int m = 0; m < MT; ++m) { X[m][0] = Y[m][0] * ev[m]; X[m][1] = Y[m][1] * ev[m]; }
-        }
-        if (s + 1 < cnt) {
-#pragma unroll
-            for (int m = 0; m < MT; ++m) ev[m] = evn[m];
-        }
-    }
-    scale_cols<N>(X, sm.d0(), t); // tmp1 = curr_U * Diagonal(d)   (stack.jl:279, 303)
-    udt_regs<N>(X, Y, sm.S1, sm.qs, t);
-    r2g<N>(Y, a.Udst + chain * nn, t);
-    load_vec<N>(a.Ddst + (size_t)chain * N, sm.qs.D, t.tid);
-    // t_stack[idx+1] = T * t_stack[idx]   (stack.jl:285, 309)
-    r2s<N, false>(X, sm.S1, t);
-    __syncthreads();
-    gemm<N, false, false>(Y, sm.S1, sm.S2, t);
-    r2g<N>(Y, a.Tdst + chain * nn, t);
-}
-
 // The slice-matrix products of add_slice_sequence_* alone: Xout = B_hi ... B_lo Usrc diag(Dsrc) (left) or
 // the daggered descending sequence (right). Used when the factorisation runs as a kernel of its own
 // (udt2_kernel, more chains per SM than the fused advance_kernel allows).
@@ -186,82 +81,7 @@ __global__ void __launch_bounds__(Geo<N>::THREADS) slice_products_kernel(Advance
     r2g<N>(X, Xout + chain * nn, t);
 }
 
-// ------------------------------------------------------------------ calculate_greens_AVX!
-// G = [1 + Ul Dl Tl Tr' Dr Ur']^-1 in the reference's operation order (stack.jl:337-393).
-template <int N>
-__global__ void __launch_bounds__(Geo<N>::THREADS, (N <= 64 ? 2 : 1)) greens_kernel(GreensArgs a)
-{
-    constexpr int MT = Geo<N>::MT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    StabSmem<N>& sm = *reinterpret_cast<StabSmem<N>*>(smem_raw);
-    const Lane t;
-    const int chain = blockIdx.x;
-    const size_t nn = (size_t)N * N;
-    double A[MT][2], Q[MT][2];
-
-    // 1. A = diag(Dl) (Tl Tr') diag(Dr)                                            (:346-348)
-    g2s<N, false>(sm.S0, a.Tl + chain * nn, t.tid);
-    g2s<N, false>(sm.S1, a.Tr + chain * nn, t.tid);
-    load_vec<N>(sm.d0(), a.Dl + (size_t)chain * N, t.tid);
-    load_vec<N>(sm.d1(), a.Dr + (size_t)chain * N, t.tid);
-    __syncthreads();
-    gemm<N, false, true>(A, sm.S0, sm.S1, t);
-    scale_rows<N>(A, sm.d0(), t);
-    scale_cols<N>(A, sm.d1(), t);
-    __syncthreads();
-    // 2. udt: Q1, D1, T1                                                            (:349)
-    udt_regs<N>(A, Q, sm.S2, sm.qs, t);
-    // 3. W3 = Ul Q1  -> S0                                                           (:360)
-    g2s<N, false>(sm.S0, a.Ul + chain * nn, t.tid);
-    r2s<N, true>(A, sm.S2, t); // T1, stored transposed for the row-wise solve
-    __syncthreads();
-    {
-        double W3[MT][2];
-        gemm_regB<N, false>(W3, sm.S0, Q, t);
-        __syncthreads();
-        r2s<N, false>(W3, sm.S0, t);
-    }
-    // 4. W4 = Ur T1^-1  (rdivp!, :361) -> S1
-    {
-        double B[MT][2];
-        g2r_t<N>(B, a.Ur + chain * nn, t);
-        rsolve_t<N>(B, Q, sm.S2, sm.qs, t);
-        r2s<N, true>(Q, sm.S1, t);
-    }
-    __syncthreads();
-    // 5. A = W3' W4 + diag(D1)                                                       (:362-368)
-    gemm<N, true, false>(A, sm.S0, sm.S1, t);
-#pragma unroll
-    for (int m = 0; m < MT; ++m)
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-            if (8 * m + t.r == 8 * t.w + 2 * t.q + c) A[m][c] += sm.qs.D[8 * m + t.r];
-    __syncthreads(); // D1 consumed before the second factorisation overwrites qs
-    // 6. udt: Q2, D2, T2                                                            (:376)
-    udt_regs<N>(A, Q, sm.S2, sm.qs, t);
-    // 7. W0 = W3 Q2 -> S0 (read transposed by the last product)                      (:378)
-    {
-        double W0[MT][2];
-        gemm_regB<N, false>(W0, sm.S0, Q, t);
-        r2s<N, true>(A, sm.S2, t); // T2 transposed
-        __syncthreads();
-        r2s<N, false>(W0, sm.S0, t);
-    }
-    // 8. W5 = W4 T2^-1 (:377), scaled by 1/D2 (:382-387) -> S1
-    {
-        double B[MT][2];
-        s2r_t<N>(B, sm.S1, t);
-        rsolve_t<N>(B, Q, sm.S2, sm.qs, t);
-        scale_rows<N>(Q, sm.qs.Dinv, t);
-        __syncthreads();
-        r2s<N, true>(Q, sm.S1, t);
-    }
-    __syncthreads();
-    // 9. G = (W5 D2^-1) W0'                                                          (:391)
-    gemm<N, false, true>(A, sm.S1, sm.S0, t);
-    r2g<N>(A, a.G + chain * nn, t);
-}
-
+// ------------------------------------------------------------------ udt_AVX_pivot!, calculate_greens_AVX!
 // udt_AVX_pivot! as a kernel of its own: N/16 warps with 16 columns each (panel_qr2.cuh), ONE
 // shared-memory matrix next to the pivoting buffers, so that several chains share an SM (N = 64:
 // 45 KB and 128 threads per chain) and N = 144 fits at all (9 warps, 144 registers of matrix per thread).
@@ -677,9 +497,6 @@ rdivp_rows_kernel(const double* Ag, double* Og, const double* Tg, const int* piv
 template <int N>
 int set_attrs()
 {
-    const int bytes = (int)sizeof(StabSmem<N>);
-    MCB_CUDA(cudaFuncSetAttribute(advance_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    MCB_CUDA(cudaFuncSetAttribute(greens_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     MCB_CUDA(cudaFuncSetAttribute(slice_products_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MultSmem<N>)));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_big_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(N * Geo<N>::LD * sizeof(double) + N * sizeof(int))));
     MCB_CUDA(cudaFuncSetAttribute(udt2_kernel<N, UdtCw<N>::value>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UdtSmem<N>)));
@@ -711,32 +528,12 @@ int init_stab_kernels()
     default: set_error("chain-resident kernels: unsupported matrix size"); return -1;  \
     }
 
-int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st)
-{
-    if (a.batch <= 0) return 0;
-    const double n3 = (double)a.n * a.n * a.n;
-    LaunchScope scope(LC_ADVANCE, st, (2.0 * (a.hi - a.lo + 1) + 2.0 + 8.0 / 3.0) * n3 * a.batch);
-    STAB_DISPATCH(a.n, (advance_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(StabSmem<N>), st>>>(a)));
-    MCB_CUDA(cudaGetLastError());
-    return 0;
-}
-
 int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st)
 {
     if (a.batch <= 0) return 0;
     const double n3 = (double)a.n * a.n * a.n;
     LaunchScope scope(LC_ADVANCE, st, 2.0 * (a.hi - a.lo + 1) * n3 * a.batch);
     STAB_DISPATCH(a.n, (slice_products_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(MultSmem<N>), st>>>(a, Xout)));
-    MCB_CUDA(cudaGetLastError());
-    return 0;
-}
-
-int launch_greens_panel(const GreensArgs& a, cudaStream_t st)
-{
-    if (a.batch <= 0) return 0;
-    const double n3 = (double)a.n * a.n * a.n;
-    LaunchScope scope(LC_GREENS, st, (10.0 + 16.0 / 3.0 + 2.0) * n3 * a.batch);
-    STAB_DISPATCH(a.n, (greens_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(StabSmem<N>), st>>>(a)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -1,9 +1,10 @@
 // Chain-resident stabilisation kernels (one CTA per Markov chain, matrices in registers / shared
-// memory, see panel.cuh and panel_qr.cuh). They replace, for the matrix sizes the register layout
+// memory, see panel.cuh and panel_qr2.cuh). They replace, for the matrix sizes the register layout
 // supports, the general-path sequences of dqmc_engine.cu:
-//   advance  = add_slice_sequence_left / _right            src/flavors/DQMC/stack.jl:272-311
-//   greens   = calculate_greens_AVX!                        src/flavors/DQMC/stack.jl:337-393
-//   udt      = udt_AVX_pivot!                               src/linalg/UDT.jl:192-306
+//   slice products + udt(_times)        = add_slice_sequence_left / _right   src/flavors/DQMC/stack.jl:272-311
+//   udt_of_product, greens_mid, udt, greens_end = calculate_greens_AVX!      src/flavors/DQMC/stack.jl:337-393
+//   udt                                 = udt_AVX_pivot!                      src/linalg/UDT.jl:192-306
+//   rdivp                               = rdivp!                              src/linalg/general.jl:138-166
 #pragma once
 #include "common.cuh"
 
@@ -20,17 +21,9 @@ struct AdvanceArgs {
     double ep = 1.0, em = 1.0;         // exp(+lambda s) for s = +1 / -1
 };
 
-struct GreensArgs {
-    int n = 0, batch = 0;
-    const double *Ul = nullptr, *Dl = nullptr, *Tl = nullptr, *Ur = nullptr, *Dr = nullptr, *Tr = nullptr;
-    double* G = nullptr;
-};
-
 bool stab_supported(int n);
 bool udt_panel_supported(int n);   // launch_udt_panel exists for this size
 bool rdivp_panel_supported(int n); // launch_rdivp_panel exists for this size
-int launch_advance_panel(const AdvanceArgs& a, cudaStream_t st);
-int launch_greens_panel(const GreensArgs& a, cudaStream_t st);
 // only the products of add_slice_sequence_*: Xout = (B chain) * Usrc * diag(Dsrc)
 int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st);
 // X -> U, D, T (= D^-1 R P' when apply_pivot, else the reference's "dirty" upper triangle in
