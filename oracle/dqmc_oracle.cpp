@@ -41,6 +41,11 @@ struct Oracle {
     // injected uniforms (optional): if non-empty, consumed in order instead of Philox
     std::vector<double> injected;
     size_t injected_pos;
+    // UnequalTimeStack (unequal_time_stack.jl:1-37): forward B_{ns}..B_1, backward B^T_{ns+1}..B^T_M,
+    // inverse blocks B^-1_{ns+1}..B^-1_{(n+1)s}, and the work matrices of calculate_greens(k, l)
+    std::vector<std::vector<double>> ut_fu, ut_fd, ut_ft, ut_bu, ut_bd, ut_bt, ut_iu, ut_id, ut_it;
+    std::vector<double> ut_greens, ut_U, ut_D, ut_T;
+    bool ut_built = false;
 };
 
 // HubbardModelAttractive.jl:100-110
@@ -287,6 +292,220 @@ void update(Oracle& o)
     o.update_count += 1;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Unequal-time Green's functions (src/flavors/DQMC/unequal_time_stack.jl). Stack index idx is
+// 1-based as in the reference; ranges[idx] = 1+(idx-1)s : idx*s.
+
+// initialize_stack + build_stack(mc, s::UnequalTimeStack)   unequal_time_stack.jl:54-166
+// (the lazy_build_* variants compute the same slots on demand)
+void ut_build(Oracle& o)
+{
+    const int n = o.N, s = o.safe_mult, R = o.n_elements - 1, Mst = o.n_elements;
+    const size_t nn = (size_t)n * n;
+    auto mats = [&](std::vector<std::vector<double>>& v, int cnt) { v.assign(cnt, std::vector<double>(nn, 0.0)); };
+    auto vecs = [&](std::vector<std::vector<double>>& v, int cnt) { v.assign(cnt, std::vector<double>(n, 0.0)); };
+    mats(o.ut_fu, Mst); vecs(o.ut_fd, Mst); mats(o.ut_ft, Mst);
+    mats(o.ut_bu, Mst); vecs(o.ut_bd, Mst); mats(o.ut_bt, Mst);
+    mats(o.ut_iu, R); vecs(o.ut_id, R); mats(o.ut_it, R);
+    o.ut_greens.assign(nn, 0.0); o.ut_U.assign(nn, 0.0); o.ut_T.assign(nn, 0.0); o.ut_D.assign(n, 0.0);
+    ref_eye(o.ut_fu[0].data(), n); ref_eye(o.ut_ft[0].data(), n);
+    ref_eye(o.ut_bu[Mst - 1].data(), n); ref_eye(o.ut_bt[Mst - 1].data(), n);
+    for (int i = 0; i < n; ++i) { o.ut_fd[0][i] = 1.0; o.ut_bd[Mst - 1][i] = 1.0; }
+    // forward (:113-126)
+    for (int idx = 1; idx <= R; ++idx) {
+        ref_copy(o.curr_U.data(), o.ut_fu[idx - 1].data(), n);
+        for (int slice = 1 + (idx - 1) * s; slice <= idx * s; ++slice) mul_slice_left(o, slice, o.curr_U.data());
+        ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.ut_fd[idx - 1].data(), n);
+        ref_udt_pivot(o.ut_fu[idx].data(), o.ut_fd[idx].data(), o.tmp1.data(), o.pivot.data(), o.tempv.data(), n, 1);
+        ref_vmul_nn(o.ut_ft[idx].data(), o.tmp1.data(), o.ut_ft[idx - 1].data(), n);
+    }
+    // backward (:129-142)
+    for (int idx = R; idx >= 1; --idx) {
+        ref_copy(o.curr_U.data(), o.ut_bu[idx].data(), n);
+        for (int slice = idx * s; slice >= 1 + (idx - 1) * s; --slice) mul_daggered_slice_left(o, slice, o.curr_U.data());
+        ref_vmul_nd(o.tmp1.data(), o.curr_U.data(), o.ut_bd[idx].data(), n);
+        ref_udt_pivot(o.ut_bu[idx - 1].data(), o.ut_bd[idx - 1].data(), o.tmp1.data(), o.pivot.data(), o.tempv.data(), n, 1);
+        ref_vmul_nn(o.ut_bt[idx - 1].data(), o.tmp1.data(), o.ut_bt[idx].data(), n);
+    }
+    // inverse (:146-157)
+    for (int idx = 1; idx <= R; ++idx) {
+        ref_eye(o.ut_it[idx - 1].data(), n);
+        for (int slice = idx * s; slice >= 1 + (idx - 1) * s; --slice) mul_slice_inv_left(o, slice, o.ut_it[idx - 1].data());
+        ref_udt_pivot(o.ut_iu[idx - 1].data(), o.ut_id[idx - 1].data(), o.ut_it[idx - 1].data(), o.pivot.data(),
+                      o.tempv.data(), n, 1);
+    }
+    o.ut_built = true;
+}
+
+// Julia's div (truncation toward zero; all operands here are >= 0 except low+1+s-2 >= 0)
+inline int jdiv(int a, int b) { return a / b; }
+
+// compute_inverse_udt_block!   unequal_time_stack.jl:326-378 : U D T = B_{low+1}^-1 ... B_high^-1
+void ut_inverse_block(Oracle& o, int low, int high)
+{
+    const int n = o.N, s = o.safe_mult;
+    double *U = o.ut_U.data(), *D = o.ut_D.data(), *T = o.ut_T.data(), *tmp1 = o.tmp1.data(), *tmp2 = o.tmp2.data();
+    const int lower = jdiv(low + 1 + s - 2, s) + 1;
+    const int upper = jdiv(high, s);
+    ref_eye(U, n); ref_eye(T, n);
+    for (int i = 0; i < n; ++i) D[i] = 1.0;
+    for (int idx = lower; idx <= upper; ++idx) {
+        ref_vmul_nn(tmp1, T, o.ut_iu[idx - 1].data(), n);
+        ref_vmul_dn(tmp2, D, tmp1, n);
+        ref_vmul_nd(tmp1, tmp2, o.ut_id[idx - 1].data(), n);
+        ref_udt_pivot(tmp2, D, tmp1, o.pivot.data(), o.tempv.data(), n, 1);
+        ref_vmul_nn(T, tmp1, o.ut_it[idx - 1].data(), n);
+        ref_vmul_nn(tmp1, U, tmp2, n);
+        ref_copy(U, tmp1, n);
+    }
+    const int lower_slice = (lower - 1) * s + 1;
+    const int upper_slice = upper * s;
+    const int top = lower_slice - 1 < high ? lower_slice - 1 : high; // min(lower_slice-1, high)
+    // (mul_slice_inv_left uses o.tmp1 / o.tmp2 as scratch, like the reference's multiply_* do)
+    for (int slice = top; slice >= low + 1; --slice) mul_slice_inv_left(o, slice, U);
+    if (top >= low + 1) {
+        ref_vmul_nd(tmp1, U, D, n);
+        ref_udt_pivot(U, D, tmp1, o.pivot.data(), o.tempv.data(), n, 1);
+        ref_vmul_nn(tmp2, tmp1, T, n);
+        ref_copy(T, tmp2, n);
+    }
+    const int from = upper_slice + 1 > top + 1 ? upper_slice + 1 : top + 1; // max(upper_slice+1, top+1)
+    for (int slice = from; slice <= high; ++slice) mul_slice_inv_right(o, slice, T);
+}
+
+// compute_forward_udt_block!   :391-408 : Ul Dl Tl = B_slice ... B_1
+void ut_forward_block(Oracle& o, int slice)
+{
+    const int n = o.N, s = o.safe_mult;
+    const int idx = jdiv(slice - 1, s); // slice = 0 -> div(-1, s) = 0 in Julia (truncation)
+    ref_copy(o.Tl.data(), o.ut_fu[idx].data(), n);
+    for (int l = s * idx + 1; l <= slice; ++l) mul_slice_left(o, l, o.Tl.data());
+    std::vector<double> tmp((size_t)n * n);
+    ref_vmul_nd(tmp.data(), o.Tl.data(), o.ut_fd[idx].data(), n);
+    ref_udt_pivot(o.Ul.data(), o.Dl.data(), tmp.data(), o.pivot.data(), o.tempv.data(), n, 1);
+    ref_vmul_nn(o.Tl.data(), tmp.data(), o.ut_ft[idx].data(), n);
+}
+
+// compute_backward_udt_block!  :422-439 : (Ur Dr Tr)^T = B_M ... B_{slice+1}
+void ut_backward_block(Oracle& o, int slice)
+{
+    const int n = o.N, s = o.safe_mult;
+    const int idx = jdiv(slice + s - 1, s);
+    ref_copy(o.Ur.data(), o.ut_bu[idx].data(), n);
+    for (int l = s * idx; l >= slice + 1; --l) mul_daggered_slice_left(o, l, o.Ur.data());
+    std::vector<double> tmp((size_t)n * n);
+    ref_vmul_nd(tmp.data(), o.Ur.data(), o.ut_bd[idx].data(), n);
+    ref_udt_pivot(o.Ur.data(), o.Dr.data(), tmp.data(), o.pivot.data(), o.tempv.data(), n, 1);
+    ref_vmul_nn(o.Tr.data(), tmp.data(), o.ut_bt[idx].data(), n);
+}
+
+inline void v_maxinv(double* v, const double* w, int n) { for (int i = 0; i < n; ++i) v[i] = 1.0 / (w[i] > 1.0 ? w[i] : 1.0); }
+inline void v_min(double* v, const double* w, int n) { for (int i = 0; i < n; ++i) v[i] = w[i] < 1.0 ? w[i] : 1.0; }
+inline void v_inv(double* v, int n) { for (int i = 0; i < n; ++i) v[i] = 1.0 / v[i]; }
+inline void diag_matrix(double* A, const double* d, int n)
+{
+    for (size_t e = 0; e < (size_t)n * n; ++e) A[e] = 0.0;
+    for (int i = 0; i < n; ++i) A[IDX(i, i, n)] = d[i];
+}
+
+// calculate_greens_full1!  unequal_time_stack.jl:443-525 : G(slice1 <- slice2), slice1 >= slice2
+void ut_full1(Oracle& o, int slice1, int slice2)
+{
+    const int n = o.N;
+    const size_t nn = (size_t)n * n;
+    ut_inverse_block(o, slice2, slice1);
+    ut_forward_block(o, slice2);
+    ut_backward_block(o, slice1);
+    double *G = o.ut_greens.data(), *U = o.ut_U.data(), *D = o.ut_D.data(), *T = o.ut_T.data();
+    double *Ul = o.Ul.data(), *Dl = o.Dl.data(), *Tl = o.Tl.data(), *Ur = o.Ur.data(), *Dr = o.Dr.data(), *Tr = o.Tr.data();
+    double* tmp1 = o.tmp1.data();
+    // B1
+    ref_vmul_nt(G, Tl, Tr, n);
+    ref_vmul_nd(tmp1, G, Dr, n);
+    ref_vmul_dn(G, Dl, tmp1, n);
+    // udt
+    ref_udt_pivot(Tr, Dr, G, o.pivot.data(), o.tempv.data(), n, 0);
+    // B2
+    ref_vmul_nn(Tl, Ul, Tr, n);
+    ref_rdivp(Ur, G, Ul, o.pivot.data(), n);
+    // B3
+    ref_vmul_tn(Tr, U, Tl, n);
+    v_maxinv(Dl, D, n);
+    ref_vmul_dn(tmp1, Dl, Tr, n);
+    v_min(Dl, Dr, n);
+    ref_vmul_nd(Tr, tmp1, Dl, n);
+    // B4
+    ref_vmul_nn(Tl, T, Ur, n);
+    v_min(Dl, D, n);
+    ref_vmul_dn(tmp1, Dl, Tl, n);
+    v_maxinv(Dl, Dr, n);
+    ref_vmul_nd(Tl, tmp1, Dl, n);
+    // sum, UDT
+    for (size_t e = 0; e < nn; ++e) Tl[e] = Tl[e] + Tr[e];
+    ref_udt_pivot(Tr, Dl, Tl, o.pivot.data(), o.tempv.data(), n, 0);
+    // B5
+    v_maxinv(Dr, Dr, n);
+    diag_matrix(Ul, Dr, n);
+    ref_rdivp(Ul, Tl, tmp1, o.pivot.data(), n);
+    v_inv(Dl, n);
+    ref_vmul_nd(tmp1, Ul, Dl, n);
+    ref_vmul_nt(Ul, tmp1, Tr, n);
+    v_maxinv(Dl, D, n);
+    ref_vmul_nd(G, Ul, Dl, n);
+    // B6
+    ref_vmul_nt(Tr, G, U, n);
+    ref_vmul_nn(G, Ur, Tr, n);
+}
+
+// calculate_greens_full2!  :529-622 : G(slice1 <- slice2), slice1 <= slice2
+void ut_full2(Oracle& o, int slice1, int slice2)
+{
+    const int n = o.N;
+    const size_t nn = (size_t)n * n;
+    ut_inverse_block(o, slice1, slice2);
+    ut_forward_block(o, slice1);
+    ut_backward_block(o, slice2);
+    double *G = o.ut_greens.data(), *U = o.ut_U.data(), *D = o.ut_D.data(), *T = o.ut_T.data();
+    double *Ul = o.Ul.data(), *Dl = o.Dl.data(), *Tl = o.Tl.data(), *Ur = o.Ur.data(), *Dr = o.Dr.data(), *Tr = o.Tr.data();
+    double* tmp1 = o.tmp1.data();
+    // B1
+    ref_vmul_nt(G, Tl, Tr, n);
+    ref_vmul_dn(tmp1, Dl, G, n);
+    ref_vmul_nd(G, tmp1, Dr, n);
+    // udt
+    ref_udt_pivot(Tr, Dr, G, o.pivot.data(), o.tempv.data(), n, 0);
+    // B2
+    ref_vmul_nn(Tl, Ul, Tr, n);
+    ref_vmul_tn(Ul, U, Tl, n);
+    v_maxinv(Dl, D, n);
+    ref_vmul_dn(U, Dl, Ul, n);
+    v_min(Dl, Dr, n);
+    ref_vmul_nd(Ul, U, Dl, n);
+    // B3
+    ref_vmul_nn(U, T, Ur, n);
+    ref_rdivp(U, G, Ur, o.pivot.data(), n);
+    v_min(Dl, D, n);
+    ref_vmul_dn(Ur, Dl, U, n);
+    v_maxinv(Dl, Dr, n);
+    ref_vmul_nd(Tr, Ur, Dl, n);
+    // sum, udt
+    for (size_t e = 0; e < nn; ++e) Tr[e] = Tr[e] + Ul[e];
+    ref_udt_pivot(Ul, Dl, Tr, o.pivot.data(), o.tempv.data(), n, 0);
+    // B4
+    v_min(Dr, Dr, n);
+    diag_matrix(U, Dr, n);
+    ref_rdivp(U, Tr, Ur, o.pivot.data(), n);
+    v_inv(Dl, n);
+    ref_vmul_nd(Ur, U, Dl, n);
+    ref_vmul_nt(U, Ur, Ul, n);
+    v_min(D, D, n);
+    ref_vmul_nd(Ur, U, D, n);
+    // B6
+    ref_vmul_nn(Tr, Ur, T, n);
+    ref_vmul_nn(G, Tl, Tr, n);
+    for (size_t e = 0; e < nn; ++e) G[e] = -G[e];
+}
+
 } // namespace
 
 extern "C" {
@@ -418,6 +637,21 @@ void orc_calculate_greens_at(void* h, int slice, double* out)
         ref_vmul_nn(o.Tl.data(), o.tmp1.data(), o.tmp2.data(), n);
     }
     calc_greens(o, out);
+}
+
+// calculate_greens(mc, slice1, slice2) (unequal_time_stack.jl:291-305): effective G(slice1 <- slice2) of the
+// current configuration, 0 <= slice <= M; physical != 0 applies _greens! as orc_get_greens does.
+// Clobbers Ul..Tr, tmp1, tmp2, curr_U like the reference (call between sweeps, then rebuild or re-propagate).
+void orc_greens_unequal(void* h, int slice1, int slice2, double* out, int physical)
+{
+    Oracle& o = *(Oracle*)h;
+    ut_build(o);
+    if (slice1 >= slice2) ut_full1(o, slice1, slice2);
+    else ut_full2(o, slice1, slice2);
+    if (!physical) { ref_copy(out, o.ut_greens.data(), o.N); return; }
+    std::vector<double> t((size_t)o.N * o.N);
+    ref_vmul_nn(t.data(), o.ut_greens.data(), o.eT.data(), o.N);
+    ref_vmul_nn(out, o.eTinv.data(), t.data(), o.N);
 }
 
 // ---- bare linear-algebra entry points for the property tests (test/slice_matrices.jl:141-235)

@@ -54,6 +54,7 @@ def lib(native=False):
     L.orc_get_greens.argtypes = [C.c_void_p, _f64p, C.c_int]
     L.orc_get_state.argtypes = [C.c_void_p, _i64p, _f64p]
     L.orc_calculate_greens_at.argtypes = [C.c_void_p, C.c_int, _f64p]
+    L.orc_greens_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _f64p, C.c_int]
     L.orc_vmul.argtypes = [_f64p, _f64p, _f64p, C.c_int, C.c_int]
     L.orc_udt_pivot.argtypes = [_f64p, _f64p, _f64p, _i64p, C.c_int, C.c_int]
     L.orc_rdivp.argtypes = [_f64p, _f64p, _i64p, C.c_int]
@@ -134,6 +135,12 @@ class OracleDQMC:
     def greens_at(self, slice_):
         out = np.empty(self.N * self.N)
         self.L.orc_calculate_greens_at(self.h, slice_, out)
+        return unfmat(out, self.N)
+
+    def greens_unequal(self, slice1, slice2, physical=False):
+        """G(slice1 <- slice2), 0 <= slice <= M (unequal_time_stack.jl:291-305). Clobbers the work matrices."""
+        out = np.empty(self.N * self.N)
+        self.L.orc_greens_unequal(self.h, slice1, slice2, out, 1 if physical else 0)
         return unfmat(out, self.N)
 
     def conf(self):
