@@ -103,6 +103,11 @@ int mcb_dqmc_get_greens(mcb_dqmc* h, double* G, int32_t physical);
 /* calculate_greens(mc, slice) from scratch, stack untouched (stack.jl:422-480);
  * overwrites the handle's current G like the reference does. */
 int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G);
+/* greens(mc, k, l): unequal-time G(k <- l) = <c_i(k dtau) c_j^+(l dtau)> of the current configuration,
+ * 0 <= k, l <= n_slices, through the UnequalTimeStack (src/flavors/DQMC/unequal_time_stack.jl:275-305, 443-622).
+ * physical != 0 applies the same transform as mcb_dqmc_get_greens. Does not disturb the sweep state; the
+ * stacks are rebuilt only if the configuration changed since the last call. Layout [chain][col][row]. */
+int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
 
 int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st);
 int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* per_chain);

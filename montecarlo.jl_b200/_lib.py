@@ -55,6 +55,7 @@ SIGNATURES = {
     "mcb_dqmc_sweep": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32]),
     "mcb_dqmc_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
     "mcb_dqmc_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
+    "mcb_dqmc_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
     "mcb_dqmc_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
     "mcb_dqmc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
     "mcb_dqmc_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, _f64]),

@@ -127,6 +127,7 @@ int mcb_dqmc_set_conf(mcb_dqmc* h, const int8_t* conf)
     MCB_CUDA(cudaStreamSynchronize(h->st));
     h->conf_set = true;
     h->stack_built = false;
+    h->conf_version++;
     return MCB_OK;
 }
 
@@ -200,6 +201,24 @@ int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G)
     ProfBind bind(h);
     API_TRY(engine_calculate_greens_at(h, slice));
     MCB_CUDA(cudaMemcpyAsync(G, h->G, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double* G, int32_t physical)
+{
+    REQUIRE(h && G && slice1 >= 0 && slice1 <= h->M && slice2 >= 0 && slice2 <= h->M, "bad argument");
+    if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
+    API_TRY(engine_greens_unequal(h, slice1, slice2));
+    const double* src = unequal_result(h);
+    if (physical) { // _greens! (DQMC.jl:721-730): e^{+dtau T/2} G e^{-dtau T/2}
+        API_TRY(launch_gemm(base_gemm(h, src, false, h->hop[0], true, h->W[0]), h->st));
+        API_TRY(launch_gemm(base_gemm(h, h->hop[1], true, h->W[0], false, h->W[1]), h->st));
+        src = h->W[1];
+    }
+    MCB_CUDA(cudaMemcpyAsync(G, src, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
     return MCB_OK;
 }

@@ -56,34 +56,6 @@ int set_identity(mcb_dqmc* h, double* U, double* T, double* D)
     return 0;
 }
 
-// exp(+-lambda s) of slice l (1-based) as a Scale; power > 0 -> e^{+lambda s}
-Scale conf_scale(const mcb_dqmc* h, int slice, bool positive)
-{
-    Scale sc;
-    sc.s = h->conf + (size_t)(slice - 1) * h->N;
-    sc.stride_s = (long long)h->M * h->N;
-    sc.ep = positive ? h->eVp[0] : h->eVm[0];
-    sc.em = positive ? h->eVp[1] : h->eVm[1];
-    return sc;
-}
-Scale vec_scale(const double* d, long long stride, bool inv = false)
-{
-    Scale sc;
-    sc.d = d; sc.stride_d = stride; sc.inv = inv ? 1 : 0;
-    return sc;
-}
-
-GemmArgs base_gemm(const mcb_dqmc* h, const double* A, bool sharedA, const double* B, bool sharedB,
-                   double* C)
-{
-    GemmArgs g;
-    g.n = h->N; g.batch = h->C;
-    g.A = A; g.strideA = sharedA ? 0 : (long long)h->nn;
-    g.B = B; g.strideB = sharedB ? 0 : (long long)h->nn;
-    g.C = C; g.strideC = (long long)h->nn;
-    return g;
-}
-
 // multiply_slice_matrix_left!: Y = e^{-dtau T} diag(e^{+lambda s_l}) X   (slice_matrices.jl:42-48)
 int mul_slice_left(mcb_dqmc* h, int slice, const double* X, double* Y, const Scale* col = nullptr)
 {
@@ -194,25 +166,34 @@ int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 // add_slice_sequence_right (stack.jl:296-311) for left == false (daggered, descending slices)
 int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
 {
+    return advance_raw(h, left, h->bufU[src], h->bufD[src], h->bufT[src], h->bufU[dst], h->bufD[dst], h->bufT[dst], lo,
+                       hi);
+}
+
+} // namespace
+
+int advance_raw(mcb_dqmc* h, bool left, const double* Usrc, const double* Dsrc, const double* Tsrc, double* Udst,
+                double* Ddst, double* Tdst, int lo, int hi)
+{
     if (h->use_panel) {
         AdvanceArgs a;
         a.n = h->N; a.batch = h->C;
-        a.Usrc = h->bufU[src]; a.Dsrc = h->bufD[src]; a.Tsrc = h->bufT[src];
-        a.Udst = h->bufU[dst]; a.Ddst = h->bufD[dst]; a.Tdst = h->bufT[dst];
+        a.Usrc = Usrc; a.Dsrc = Dsrc; a.Tsrc = Tsrc;
+        a.Udst = Udst; a.Ddst = Ddst; a.Tdst = Tdst;
         a.eT2 = h->hop[2];
         a.conf = h->conf; a.sConf = (long long)h->M * h->N;
         a.lo = lo; a.hi = hi; a.left = left ? 1 : 0;
         a.ep = h->eVp[0]; a.em = h->eVp[1];
         MCB_TRY(launch_slice_products(a, h->W[0], h->st));
         if (!force_general_udt())
-            return launch_udt_times(h->N, h->C, h->W[0], h->bufU[dst], h->bufD[dst], h->bufT[src], h->bufT[dst],
+            return launch_udt_times(h->N, h->C, h->W[0], Udst, Ddst, Tsrc, Tdst,
                                     h->pivot, h->st);
-        MCB_TRY(launch_udt(h->N, h->C, h->W[0], h->nn, h->bufU[dst], h->nn, h->bufD[dst], h->N, h->W[2], h->nn,
+        MCB_TRY(launch_udt(h->N, h->C, h->W[0], h->nn, Udst, h->nn, Ddst, h->N, h->W[2], h->nn,
                            h->pivot, h->N, 1, h->st));
-        return launch_gemm(base_gemm(h, h->W[2], false, h->bufT[src], false, h->bufT[dst]), h->st);
+        return launch_gemm(base_gemm(h, h->W[2], false, Tsrc, false, Tdst), h->st);
     }
-    const double* cur = h->bufU[src];
-    const Scale dcol = vec_scale(h->bufD[src], h->N);
+    const double* cur = Usrc;
+    const Scale dcol = vec_scale(Dsrc, h->N);
     int pp = 0;
     const int cnt = hi - lo + 1;
     for (int t = 0; t < cnt; ++t) {
@@ -225,11 +206,13 @@ int advance(mcb_dqmc* h, bool left, int src, int dst, int lo, int hi)
         pp ^= 1;
     }
     double* X = const_cast<double*>(cur);
-    MCB_TRY(launch_udt(h->N, h->C, X, h->nn, h->bufU[dst], h->nn, h->bufD[dst], h->N, h->W[2], h->nn,
+    MCB_TRY(launch_udt(h->N, h->C, X, h->nn, Udst, h->nn, Ddst, h->N, h->W[2], h->nn,
                        h->pivot, h->N, 1, h->st));
-    GemmArgs g = base_gemm(h, h->W[2], false, h->bufT[src], false, h->bufT[dst]);
+    GemmArgs g = base_gemm(h, h->W[2], false, Tsrc, false, Tdst);
     return launch_gemm(g, h->st);
 }
+
+namespace {
 
 int record_prop_err(mcb_dqmc* h)
 {
@@ -276,6 +259,7 @@ int engine_alloc(mcb_dqmc* h)
 
 void engine_free(mcb_dqmc* h)
 {
+    unequal_free(h);
     for (int i = 0; i < 4; ++i) cudaFree(h->hop[i]);
     cudaFree(h->conf); cudaFree(h->G); cudaFree(h->Gtmp);
     for (int i = 0; i < 8; ++i) cudaFree(h->W[i]);
@@ -379,6 +363,7 @@ int engine_propagate(mcb_dqmc* h, bool defer_wrap, bool* wrap_pending)
 // update (DQMC.jl:523-538) = propagate + sweep_spatial, general path (any N): separate launches
 int engine_update(mcb_dqmc* h)
 {
+    h->conf_version++;
     MCB_TRY(engine_propagate(h, false, nullptr));
     SweepArgs a;
     a.n = h->N; a.batch = h->C;
@@ -406,6 +391,7 @@ int engine_update(mcb_dqmc* h)
 // same direction (at most safe_mult - 1 of them), up to max_updates.
 int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_point, int64_t* done)
 {
+    h->conf_version++;
     *done = 0;
     if (max_updates <= 0) return 0;
     if (!h->use_panel) {

@@ -50,11 +50,41 @@ struct mcb_dqmc {
     float last_ms = 0.f;
     bool use_panel = false; // chain-resident kernels (panel.cuh) exist for this N
     bool hopping_set = false, conf_set = false, stack_built = false;
+    struct UtStack* ut = nullptr; // unequal-time stacks and work matrices, allocated on first use (unequal.cu)
+    int64_t conf_version = 0;     // bumped whenever the configuration may have changed
 
     int obs_len() const { return 4 + 2 * n_dirs; }
 };
 
 namespace mcb {
+// exp(+-lambda s) of slice l (1-based) as a Scale; power > 0 -> e^{+lambda s}
+inline Scale conf_scale(const mcb_dqmc* h, int slice, bool positive)
+{
+    Scale sc;
+    sc.s = h->conf + (size_t)(slice - 1) * h->N;
+    sc.stride_s = (long long)h->M * h->N;
+    sc.ep = positive ? h->eVp[0] : h->eVm[0];
+    sc.em = positive ? h->eVp[1] : h->eVm[1];
+    return sc;
+}
+inline Scale vec_scale(const double* d, long long stride, bool inv = false)
+{
+    Scale sc;
+    sc.d = d; sc.stride_d = stride; sc.inv = inv ? 1 : 0;
+    return sc;
+}
+
+inline GemmArgs base_gemm(const mcb_dqmc* h, const double* A, bool sharedA, const double* B, bool sharedB,
+                   double* C)
+{
+    GemmArgs g;
+    g.n = h->N; g.batch = h->C;
+    g.A = A; g.strideA = sharedA ? 0 : (long long)h->nn;
+    g.B = B; g.strideB = sharedB ? 0 : (long long)h->nn;
+    g.C = C; g.strideC = (long long)h->nn;
+    return g;
+}
+
 int engine_alloc(mcb_dqmc* h);
 void engine_free(mcb_dqmc* h);
 int engine_build_stack(mcb_dqmc* h);
@@ -64,6 +94,13 @@ int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_p
 int engine_calculate_greens_at(mcb_dqmc* h, int slice);
 int engine_physical_greens(mcb_dqmc* h, double* out_dev);
 int engine_measure(mcb_dqmc* h);
+// unequal-time Green's function G(k <- l) of the current configuration into h->G (unequal.cu)
+int engine_greens_unequal(mcb_dqmc* h, int slice1, int slice2);
+void unequal_free(mcb_dqmc* h);
+double* unequal_result(mcb_dqmc* h);
+// add_slice_sequence_left/right on raw (U, D, T) triples
+int advance_raw(mcb_dqmc* h, bool left, const double* Usrc, const double* Dsrc, const double* Tsrc, double* Udst,
+                double* Ddst, double* Tdst, int lo, int hi);
 // batched calculate_greens on raw device buffers (shared with the linalg entry point)
 int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const double* Tl,
                     const double* Ur, const double* Dr, const double* Tr, double* G, double* const W[6],

@@ -128,6 +128,13 @@ class DQMC:
         _lib.check(self.L.mcb_dqmc_calculate_greens_at(self.h, slice_, buf))
         return self._unbatch(buf)
 
+    def greens_unequal(self, slice1, slice2, physical=True):
+        """greens(mc, k, l) = G(k <- l), 0 <= k, l <= M (unequal_time_stack.jl:275-305); physical=False returns the
+        effective G of calculate_greens(mc, k, l). Leaves the sweep state untouched. Shape (C, N, N)."""
+        buf = np.empty(self.n_chains * self.N * self.N)
+        _lib.check(self.L.mcb_dqmc_greens_unequal(self.h, slice1, slice2, buf, int(physical)))
+        return self._unbatch(buf)
+
     def state(self):
         st = _lib.DqmcState()
         _lib.check(self.L.mcb_dqmc_get_state(self.h, C.byref(st)))

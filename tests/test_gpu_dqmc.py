@@ -339,3 +339,48 @@ def test_config_d_20x20_first_updates_match_oracle():
             assert np.array_equal(conf[c], o.conf()), (cp, c)
         done = cp
     mc.close()
+
+
+# ------------------------------------------------------------------ unequal-time Green's functions
+UNEQUAL_PAIRS = [(0, 0), (3, 3), (7, 2), (6, 5), (10, 4), (2, 7), (4, 5), (0, 3), (5, 10)]
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("L,U,beta,safe_mult", [(4, 1.0, 2.0, 5), (8, 2.0, 2.0, 10), (6, 4.0, 2.0, 4)])
+def test_unequal_time_greens_matches_oracle(L, U, beta, safe_mult, general):
+    """greens(mc, k, l) (unequal_time_stack.jl:291-305, full1 / full2) against the CPU restatement, on the
+    chain-resident kernels (N = 16, 64), the general kernels, and a size without panel kernels (N = 36)."""
+    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, 2, general=general)
+    M = mc.M
+    for k, l in UNEQUAL_PAIRS + [(M, 0), (0, M), (M, M), (M - 1, 1), (1, M - 1)]:
+        G = mc.greens_unequal(k, l, physical=False)
+        for c, o in enumerate(oracles):
+            want = o.greens_unequal(k, l)
+            assert relerr(G[c], want) < RTOL_G, (k, l, c, relerr(G[c], want))
+    Gp = mc.greens_unequal(7, 2, physical=True)
+    assert relerr(Gp[0], oracles[0].greens_unequal(7, 2, physical=True)) < RTOL_G
+    mc.close()
+
+
+def test_unequal_time_properties_and_sweep_state():
+    """test/flavortests_DQMC.jl:103-115 at beta = 15, safe_mult = 5: G(k, k) equals calculate_greens(mc, k),
+    G(t, 0) = -G(t, beta); the call leaves the sweep state alone and follows the configuration after updates."""
+    mc, oracles = _pair(4, 1.0, 15.0, 0.1, 5, 2, seed=11)
+    M = mc.M
+    for s in (0, 1, 5, 6, 75, 149, 150):
+        assert np.abs(mc.greens_at(s) - mc.greens_unequal(s, s, physical=False)).max() < 1e-11, s
+    for s in (0, 1, 37, 100, 149):
+        assert np.abs(mc.greens_unequal(s, 0, physical=False) + mc.greens_unequal(s, M, physical=False)).max() < 1e-11, s
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    mc.update(7)
+    G0, st0 = mc.greens(physical=False), mc.state()
+    Gu = mc.greens_unequal(20, 4, physical=False)
+    assert np.array_equal(G0, mc.greens(physical=False)) and st0 == mc.state()
+    for c, o in enumerate(oracles):
+        o.update(7)
+        assert relerr(Gu[c], o.greens_unequal(20, 4)) < RTOL_G  # stacks rebuilt for the updated field
+    mc.update(3)  # the sweep carries on
+    assert mc.state()["n_updates"] == st0["n_updates"] + 3
+    mc.close()
