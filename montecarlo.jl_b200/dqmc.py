@@ -194,6 +194,27 @@ class DQMC:
         return self.observables()
 
 
+class CombinedGreensIterator:
+    """CombinedGreensIterator(mc) (unequal_time_stack.jl:746-883): yields, for l = 1..M, the physical Green's
+    functions (G(0 <- l), G(l <- 0), G(l <- l)), each of shape (C, N, N), for time-displaced measurements.
+    The reference propagates one slice at a time between stabilised recalculations (and checks the result
+    against greens(mc, l, 0) etc. to 1e-10, test/flavortests_DQMC.jl:143-160); here every l is the stabilised
+    evaluation itself, on stacks that are built once per configuration."""
+
+    def __init__(self, mc, physical=True):
+        self.mc = mc
+        self.physical = physical
+
+    def __len__(self):
+        return self.mc.M
+
+    def __iter__(self):
+        mc = self.mc
+        for l in range(1, mc.M + 1):
+            yield (mc.greens_unequal(0, l, self.physical), mc.greens_unequal(l, 0, self.physical),
+                   mc.greens_unequal(l, l, self.physical))
+
+
 def mean_and_error(per_chain):
     """Mean over chains and its standard error (chains are independent Markov chains)."""
     a = np.asarray(per_chain, dtype=np.float64)

@@ -384,3 +384,17 @@ def test_unequal_time_properties_and_sweep_state():
     mc.update(3)  # the sweep carries on
     assert mc.state()["n_updates"] == st0["n_updates"] + 3
     mc.close()
+
+
+def test_combined_greens_iterator():
+    """test/flavortests_DQMC.jl:143-160: (G0l, Gl0, Gll) of the iterator against the direct evaluations."""
+    mc, oracles = _pair(4, 1.0, 1.0, 0.1, 5, 2)
+    it = mcb.CombinedGreensIterator(mc)
+    assert len(it) == mc.M
+    o = oracles[0]
+    for l, (G0l, Gl0, Gll) in enumerate(it, start=1):
+        assert relerr(G0l[0], o.greens_unequal(0, l, physical=True)) < RTOL_G, l
+        assert relerr(Gl0[0], o.greens_unequal(l, 0, physical=True)) < RTOL_G, l
+        want = mc.hop[1] @ o.greens_at(l) @ mc.hop[0]  # _greens!(calculate_greens(mc, l))
+        assert relerr(Gll[0], want) < RTOL_G, l
+    mc.close()
