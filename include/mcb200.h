@@ -109,6 +109,18 @@ int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G);
  * stacks are rebuilt only if the configuration changed since the last call. Layout [chain][col][row]. */
 int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
 
+/* Recorded configurations in the reference's wire format compress(mc, model, conf) = BitArray(conf .== 1)
+ * (src/models/HubbardModel/HubbardModel.jl:56-59, ConfigRecorder src/configurations.jl:24-43): per chain
+ * mcb_dqmc_conf_chunks(h) = ceil(N*M/64) little-endian 64-bit chunks, bit b = spin i + N*l. */
+int mcb_dqmc_conf_chunks(mcb_dqmc* h);
+int mcb_dqmc_set_conf_bits(mcb_dqmc* h, const uint64_t* chunks);
+int mcb_dqmc_get_conf_bits(mcb_dqmc* h, uint64_t* chunks);
+/* The measurement loop of replay!(mc, configurations) (src/flavors/DQMC/DQMC.jl:649-660): for every recorded
+ * configuration decompress, calculate_greens(mc, 0), measure. n_confs must be a multiple of n_chains (one
+ * configuration per chain and batch); results accumulate in the observables of the handle. The sweep state is
+ * invalid afterwards (build_stack again before update). */
+int mcb_dqmc_replay(mcb_dqmc* h, const uint64_t* chunks, int64_t n_confs);
+
 int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st);
 int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* per_chain);
 

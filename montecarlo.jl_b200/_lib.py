@@ -40,6 +40,7 @@ _f64 = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _i8 = np.ctypeslib.ndpointer(dtype=np.int8, flags="C_CONTIGUOUS")
 _i32 = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _i64 = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+_u64 = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
 
 # name -> (restype, argtypes); every symbol include/mcb200.h declares
 SIGNATURES = {
@@ -56,6 +57,10 @@ SIGNATURES = {
     "mcb_dqmc_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
     "mcb_dqmc_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
     "mcb_dqmc_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
+    "mcb_dqmc_conf_chunks": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_set_conf_bits": (C.c_int, [C.c_void_p, _u64]),
+    "mcb_dqmc_get_conf_bits": (C.c_int, [C.c_void_p, _u64]),
+    "mcb_dqmc_replay": (C.c_int, [C.c_void_p, _u64, C.c_int64]),
     "mcb_dqmc_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
     "mcb_dqmc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
     "mcb_dqmc_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, _f64]),

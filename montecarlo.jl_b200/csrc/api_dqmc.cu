@@ -47,6 +47,30 @@ struct ProfBind {
     explicit ProfBind(mcb_dqmc* h) { set_current_profiler(&h->prof); }
     ~ProfBind() { set_current_profiler(nullptr); }
 };
+
+// compress / decompress (HubbardModel.jl:56-59): a configuration travels as BitArray(conf .== 1), i.e. bit b of
+// 64-bit chunk b >> 6 is spin b = i + N * l (Julia column-major), stored at the same linear index here.
+__global__ void unpack_conf_kernel(int8_t* conf, const unsigned long long* bits, size_t per_chain, size_t chunks,
+                                   size_t total)
+{
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t chain = e / per_chain, b = e % per_chain;
+        conf[e] = ((bits[chain * chunks + (b >> 6)] >> (b & 63)) & 1ull) ? 1 : -1;
+    }
+}
+__global__ void pack_conf_kernel(unsigned long long* bits, const int8_t* conf, size_t per_chain, size_t chunks,
+                                 size_t total_chunks)
+{
+    for (size_t c = blockIdx.x * (size_t)blockDim.x + threadIdx.x; c < total_chunks; c += (size_t)gridDim.x * blockDim.x) {
+        const size_t chain = c / chunks, k = c % chunks;
+        unsigned long long w = 0;
+        for (int j = 0; j < 64; ++j) {
+            const size_t b = k * 64 + j;
+            if (b < per_chain && conf[chain * per_chain + b] == 1) w |= 1ull << j;
+        }
+        bits[c] = w;
+    }
+}
 } // namespace
 
 extern "C" {
@@ -220,6 +244,61 @@ int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double*
     }
     MCB_CUDA(cudaMemcpyAsync(G, src, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_conf_chunks(mcb_dqmc* h) { return h ? (int)(((size_t)h->N * h->M + 63) / 64) : 0; }
+
+static int upload_bits(mcb_dqmc* h, const uint64_t* chunks)
+{
+    const size_t per = (size_t)h->N * h->M, nch = (per + 63) / 64;
+    if (!h->conf_bits) MCB_CUDA(cudaMalloc(&h->conf_bits, (size_t)h->C * nch * sizeof(uint64_t)));
+    MCB_CUDA(cudaMemcpyAsync(h->conf_bits, chunks, (size_t)h->C * nch * sizeof(uint64_t), cudaMemcpyHostToDevice, h->st));
+    unpack_conf_kernel<<<296, 256, 0, h->st>>>(h->conf, (const unsigned long long*)h->conf_bits, per, nch, (size_t)h->C * per);
+    MCB_CUDA(cudaGetLastError());
+    h->conf_set = true;
+    h->stack_built = false;
+    h->conf_version++;
+    return 0;
+}
+
+int mcb_dqmc_set_conf_bits(mcb_dqmc* h, const uint64_t* chunks)
+{
+    REQUIRE(h && chunks, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    API_TRY(upload_bits(h, chunks));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_get_conf_bits(mcb_dqmc* h, uint64_t* chunks)
+{
+    REQUIRE(h && chunks, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    const size_t per = (size_t)h->N * h->M, nch = (per + 63) / 64;
+    if (!h->conf_bits) MCB_CUDA(cudaMalloc(&h->conf_bits, (size_t)h->C * nch * sizeof(uint64_t)));
+    pack_conf_kernel<<<296, 256, 0, h->st>>>((unsigned long long*)h->conf_bits, h->conf, per, nch, (size_t)h->C * nch);
+    MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(cudaMemcpyAsync(chunks, h->conf_bits, (size_t)h->C * nch * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_replay(mcb_dqmc* h, const uint64_t* chunks, int64_t n_confs)
+{
+    REQUIRE(h && chunks && n_confs > 0, "bad argument");
+    REQUIRE(n_confs % h->C == 0, "replay: the number of configurations must be a multiple of n_chains");
+    if (!h->hopping_set) { set_error("set_hopping first"); return MCB_ERR_STATE; }
+    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
+    const size_t nch = ((size_t)h->N * h->M + 63) / 64;
+    for (int64_t b = 0; b < n_confs / h->C; ++b) {
+        API_TRY(upload_bits(h, chunks + (size_t)b * h->C * nch));
+        API_TRY(engine_calculate_greens_at(h, 0));
+        API_TRY(engine_measure(h));
+        MCB_CUDA(cudaStreamSynchronize(h->st)); // the staging buffer is reused by the next batch
+    }
     return MCB_OK;
 }
 

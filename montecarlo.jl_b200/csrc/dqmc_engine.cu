@@ -261,7 +261,7 @@ void engine_free(mcb_dqmc* h)
 {
     unequal_free(h);
     for (int i = 0; i < 4; ++i) cudaFree(h->hop[i]);
-    cudaFree(h->conf); cudaFree(h->G); cudaFree(h->Gtmp);
+    cudaFree(h->conf); cudaFree(h->conf_bits); cudaFree(h->G); cudaFree(h->Gtmp);
     for (int i = 0; i < 8; ++i) cudaFree(h->W[i]);
     for (int i = 0; i < 2; ++i) cudaFree(h->Dw[i]);
     cudaFree(h->pivot); cudaFree(h->Dx);

@@ -24,6 +24,7 @@ struct mcb_dqmc {
     // device memory
     double* hop[4] = {nullptr, nullptr, nullptr, nullptr}; // eT, eTinv, eT2, eTinv2
     int8_t* conf = nullptr;                                 // [C][M][N]
+    uint64_t* conf_bits = nullptr;                          // staging for the bit-packed wire format
     double* G = nullptr;
     double* Gtmp = nullptr;
     double* W[8] = {};

@@ -57,6 +57,7 @@ class DQMC:
         self.model = model
         self.p = DQMCParameters(**kwargs)
         self.n_chains, self.seed, self.chain_offset, self.device = int(n_chains), int(seed), int(chain_offset), int(device)
+        self.general_path = bool(general_path)
         self.N, self.M = len(model.l), self.p.slices
         if self.M % self.p.safe_mult != 0:
             raise ValueError("slices must be a multiple of safe_mult (stack.jl:115)")
@@ -105,6 +106,41 @@ class DQMC:
         buf = np.empty(self.n_chains * self.N * self.M, dtype=np.int8)
         _lib.check(self.L.mcb_dqmc_get_conf(self.h, buf))
         return buf.reshape(self.n_chains, self.M, self.N).transpose(0, 2, 1).copy()
+
+    # -- recorded configurations (ConfigRecorder wire format) ------------------------------------
+    def conf_bits(self):
+        """compress(mc, model, conf) for every chain: (C, ceil(N*M/64)) uint64, bit b = spin i + N*l."""
+        buf = np.empty(self.n_chains * self.L.mcb_dqmc_conf_chunks(self.h), dtype=np.uint64)
+        _lib.check(self.L.mcb_dqmc_get_conf_bits(self.h, buf))
+        return buf.reshape(self.n_chains, -1)
+
+    def set_conf_bits(self, bits):
+        bits = np.ascontiguousarray(bits, dtype=np.uint64)
+        assert bits.shape == (self.n_chains, self.L.mcb_dqmc_conf_chunks(self.h))
+        _lib.check(self.L.mcb_dqmc_set_conf_bits(self.h, bits.reshape(-1)))
+
+    def replay(self, configurations):
+        """The measurement loop of replay!(mc, configurations) (DQMC.jl:649-660): for every recorded configuration
+        decompress, calculate_greens(mc, 0), measure. `configurations`: (n, ceil(N*M/64)) uint64 as produced by
+        compress / conf_bits. One configuration per chain and batch; a remainder smaller than n_chains goes through
+        a handle of that size. Returns the per-configuration-slot observables of the full batches and, if any,
+        of the remainder (their moments combine like chains do, sharding.mean_and_error_from_moments)."""
+        cfg = np.ascontiguousarray(configurations, dtype=np.uint64)
+        n, C_ = cfg.shape[0], self.n_chains
+        self.enable_measurements()
+        out = []
+        full = (n // C_) * C_
+        if full:
+            _lib.check(self.L.mcb_dqmc_replay(self.h, cfg[:full].reshape(-1), full))
+            out.append(self.observables())
+        if n > full:
+            rest = DQMC(self.model, n_chains=n - full, seed=self.seed, beta=self.p.beta, delta_tau=self.p.delta_tau,
+                        safe_mult=self.p.safe_mult, general_path=self.general_path, device=self.device)
+            rest.enable_measurements()
+            _lib.check(rest.L.mcb_dqmc_replay(rest.h, cfg[full:].reshape(-1), n - full))
+            out.append(rest.observables())
+            rest.close()
+        return out
 
     def build_stack(self):
         """init! + build_stack + propagate (DQMC.jl:412-414)."""
@@ -192,6 +228,21 @@ class DQMC:
             self.sweep(sw, self.p.measure_rate)
         self.last_sweep += th + sw
         return self.observables()
+
+
+def compress(conf):
+    """compress(mc, model, conf) = BitArray(conf .== 1) (HubbardModel.jl:56): conf (N, M) of +-1 -> uint64 chunks in
+    Julia's BitArray layout (column-major bit index, 64 bits per chunk, least significant bit first)."""
+    bits = (np.asarray(conf).T.reshape(-1) == 1).astype(np.uint8)  # linear index i + N*l
+    pad = (-len(bits)) % 64
+    packed = np.packbits(np.concatenate([bits, np.zeros(pad, np.uint8)]), bitorder="little")
+    return packed.view("<u8").astype(np.uint64)
+
+
+def decompress(chunks, N, M):
+    """decompress(mc, model, c) = 2c .- 1 (HubbardModel.jl:57-59)."""
+    bits = np.unpackbits(np.ascontiguousarray(chunks, dtype="<u8").view(np.uint8), bitorder="little")[:N * M]
+    return (2 * bits.astype(np.int8) - 1).reshape(M, N).T.copy()
 
 
 class CombinedGreensIterator:

@@ -398,3 +398,44 @@ def test_combined_greens_iterator():
         want = mc.hop[1] @ o.greens_at(l) @ mc.hop[0]  # _greens!(calculate_greens(mc, l))
         assert relerr(Gll[0], want) < RTOL_G, l
     mc.close()
+
+
+def test_replay_of_recorded_configurations():
+    """replay! (DQMC.jl:649-660) over ConfigRecorder data: bit-packed wire format round trip, and the batched
+    measurement loop against one-at-a-time set_conf + calculate_greens(mc, 0) + measure."""
+    model = mcb.HubbardModelAttractive(L=4, U=2.0)
+    kw = dict(beta=1.0, delta_tau=0.1, safe_mult=5)
+    mc = mcb.DQMC(model, n_chains=3, seed=9, **kw)
+    N, M = mc.N, mc.M
+    # wire format: compress == the library's packing == numpy's BitArray layout, decompress inverts it
+    bits = mc.conf_bits()
+    conf = mc.conf()
+    for c in range(3):
+        assert np.array_equal(bits[c], mcb.compress(conf[c]))
+        assert np.array_equal(mcb.decompress(bits[c], N, M), conf[c])
+    flipped = -conf
+    mc.set_conf_bits(np.stack([mcb.compress(flipped[c]) for c in range(3)]))
+    assert np.array_equal(mc.conf(), flipped)
+    # 7 recorded configurations through a 3-chain handle: 2 full batches + a remainder of 1
+    rng = np.random.default_rng(3)
+    confs = rng.choice(np.array([-1, 1], dtype=np.int8), size=(7, N, M))
+    packed = np.stack([mcb.compress(c) for c in confs])
+    res = mc.replay(packed)
+    assert [r["count"] for r in res] == [2, 1]
+    one = mcb.DQMC(model, n_chains=1, seed=9, **kw)
+    one.enable_measurements()
+    per_conf = []
+    for c in confs:
+        one.L.mcb_dqmc_reset_observables(one.h)
+        one.set_conf(c[None])
+        G = one.greens_at(0)
+        o = orc.OracleDQMC(N, M, 5, 0.1, 2.0, one.hop, c)
+        assert relerr(G[0], o.greens_at(0)) < RTOL_G
+        one.measure()
+        per_conf.append(one.observables())
+    for key in ("occupation", "double_occupancy", "e_kin", "e_int"):
+        want_full = np.array([[per_conf[b * 3 + c][key][0] for b in range(2)] for c in range(3)]).mean(axis=1)
+        assert np.allclose(res[0][key], want_full, rtol=1e-10, atol=1e-12), key
+        assert np.allclose(res[1][key], per_conf[6][key], rtol=1e-10, atol=1e-12), key
+    assert np.allclose(res[0]["cdc"][1], np.mean([per_conf[1]["cdc"][0], per_conf[4]["cdc"][0]], axis=0), atol=1e-10)
+    mc.close(); one.close()
