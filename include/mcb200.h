@@ -93,6 +93,11 @@ int mcb_dqmc_build_stack(mcb_dqmc* h);
  * If measure_every > 0 the built-in observables are accumulated after every update that ends at
  * current_slice == 1 && direction == +1 and whose sweep index is a multiple of measure_every
  * (DQMC.jl:429-436). */
+/* resume!(mc) (src/flavors/DQMC/DQMC.jl:517-521, FileIO.jl:38-156): continue a run whose configuration was saved
+ * after `last_sweep` complete sweeps: build_stack + propagate on the uploaded configuration (as run! does after
+ * loading), with the update counter (= random-number counters, measurement schedule) set to last_sweep * 2M.
+ * The checkpoint itself is {conf (mcb_dqmc_get_conf / _get_conf_bits), last_sweep, seed, chain_offset, parameters}. */
+int mcb_dqmc_resume(mcb_dqmc* h, int64_t last_sweep);
 int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every);
 /* n_sweeps * 2M updates (the body of run!'s sweep loop, DQMC.jl:420-438) */
 int mcb_dqmc_sweep(mcb_dqmc* h, int64_t n_sweeps, int32_t measure_every);

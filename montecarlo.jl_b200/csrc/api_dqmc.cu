@@ -177,6 +177,14 @@ int mcb_dqmc_build_stack(mcb_dqmc* h)
     return MCB_OK;
 }
 
+int mcb_dqmc_resume(mcb_dqmc* h, int64_t last_sweep)
+{
+    REQUIRE(h && last_sweep >= 0, "bad argument");
+    API_TRY(mcb_dqmc_build_stack(h));
+    h->n_updates = last_sweep * 2 * (int64_t)h->M; // Philox counters and the sweep index carry on
+    return MCB_OK;
+}
+
 int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every)
 {
     REQUIRE(h && n_updates >= 0, "bad argument");

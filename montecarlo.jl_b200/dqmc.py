@@ -142,6 +142,24 @@ class DQMC:
             rest.close()
         return out
 
+    # -- checkpoint / resume (FileIO.jl:38-156, DQMC.jl:463-477, 517-521) -----------------------
+    def checkpoint(self):
+        """What save(filename, mc) keeps of the Markov chain: the configuration (bit-packed), the number of complete
+        sweeps, and what identifies the random streams. Call between sweeps."""
+        st = self.state()
+        if st["n_updates"] % (2 * self.M) != 0:
+            raise ValueError("checkpoints are taken between sweeps")
+        return dict(conf_bits=self.conf_bits(), last_sweep=st["n_updates"] // (2 * self.M), seed=self.seed,
+                    chain_offset=self.chain_offset, n_chains=self.n_chains)
+
+    def resume(self, ckpt):
+        """resume!(mc): upload the saved configuration, rebuild the stack, continue the counters."""
+        if (ckpt["seed"], ckpt["chain_offset"], ckpt["n_chains"]) != (self.seed, self.chain_offset, self.n_chains):
+            raise ValueError("checkpoint belongs to different chains")
+        self.set_conf_bits(ckpt["conf_bits"])
+        _lib.check(self.L.mcb_dqmc_resume(self.h, int(ckpt["last_sweep"])))
+        self.last_sweep = int(ckpt["last_sweep"])
+
     def build_stack(self):
         """init! + build_stack + propagate (DQMC.jl:412-414)."""
         _lib.check(self.L.mcb_dqmc_build_stack(self.h))

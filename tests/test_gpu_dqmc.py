@@ -439,3 +439,26 @@ def test_replay_of_recorded_configurations():
         assert np.allclose(res[1][key], per_conf[6][key], rtol=1e-10, atol=1e-12), key
     assert np.allclose(res[0]["cdc"][1], np.mean([per_conf[1]["cdc"][0], per_conf[4]["cdc"][0]], axis=0), atol=1e-10)
     mc.close(); one.close()
+
+
+def test_checkpoint_and_resume_continue_the_same_chains():
+    """save / resume! (FileIO.jl:38-156, DQMC.jl:517-521): 2 sweeps + checkpoint + resume in a NEW handle + 2 sweeps
+    gives the chains of 4 uninterrupted sweeps (same random streams; G rebuilt from the stack at the resume)."""
+    a, _ = _pair(4, 2.0, 1.0, 0.1, 5, 3, seed=21)
+    b, _ = _pair(4, 2.0, 1.0, 0.1, 5, 3, seed=21)
+    a.build_stack(); a.sweep(4)
+    b.build_stack(); b.sweep(2)
+    ck = b.checkpoint()
+    assert ck["last_sweep"] == 2
+    b.update(1)
+    with pytest.raises(ValueError):
+        b.checkpoint()
+    b.close()
+    c, _ = _pair(4, 2.0, 1.0, 0.1, 5, 3, seed=21)
+    c.resume(ck)
+    assert c.state()["n_updates"] == 2 * 2 * c.M
+    c.sweep(2)
+    assert a.state() == c.state()
+    assert np.array_equal(a.conf(), c.conf())
+    assert relerr(a.greens(False), c.greens(False)) < 1e-9
+    a.close(); c.close()
