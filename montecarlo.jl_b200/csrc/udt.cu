@@ -224,7 +224,7 @@ int init_udt_kernels()
 {
     MCB_CUDA(cudaFuncSetAttribute(udt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    return 0;
+    return init_udt_cluster_kernels();
 }
 
 int launch_udt(int n, int batch, double* X, long long sX, double* U, long long sU, double* D,
@@ -236,6 +236,10 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
     if (udt_panel_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
         sD == n && sP == n)
         return launch_udt_panel(n, batch, X, U, D, T, pivot, apply_pivot, st);
+    // sizes beyond one SM: a cluster of 8 CTAs per chain holds the matrix in distributed shared memory
+    if (udt_cluster_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
+        sD == n && sP == n)
+        return launch_udt_cluster(n, batch, X, U, D, T, pivot, apply_pivot, st);
     UdtArgs a{n, X, sX, U, sU, D, sD, T, sT, pivot, sP, apply_pivot, 0};
     const size_t hdr = (size_t)(3 * n + 2 + (n + 3) / 2 + 2) * sizeof(double);
     const size_t mat = (size_t)n * n * sizeof(double);

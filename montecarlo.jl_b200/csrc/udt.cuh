@@ -16,6 +16,11 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
                  const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st);
 
 int init_udt_kernels();
+// cluster-per-chain factorisation (udt_cluster.cu): 8 CTAs share one matrix through distributed shared memory
+bool udt_cluster_supported(int n);
+int init_udt_cluster_kernels();
+int launch_udt_cluster(int n, int batch, double* X, double* U, double* D, double* T, int* pivot, int apply_pivot,
+                       cudaStream_t st);
 // testing aid: route every size through udt_kernel / rdivp_kernel
 void set_force_general_udt(bool on);
 bool force_general_udt();

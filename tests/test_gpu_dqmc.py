@@ -53,7 +53,7 @@ def linalg_path(request):
 
 
 @pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
-@pytest.mark.parametrize("n", [4, 16, 32, 64, 100, 144, 200])
+@pytest.mark.parametrize("n", [4, 16, 32, 64, 100, 144, 200, 256, 400])
 @pytest.mark.parametrize("apply_pivot", [1, 0])
 def test_udt_contract(n, apply_pivot, linalg_path):
     rng = np.random.default_rng(100 + n)
