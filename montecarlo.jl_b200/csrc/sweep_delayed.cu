@@ -11,7 +11,17 @@
 // date with ONE product G -= U * Rc (N x K x N) on the FP64 tensor pipe. The Metropolis decisions see
 // exactly the Green's function the immediate updates would give (the arithmetic is re-associated only).
 // One barrier per site: the next site's G_ii is published by the thread that owns its row.
+//
+// Small batches of large matrices (config D: 32 chains, N = 400) leave most SMs idle with one CTA per chain,
+// and the flush is 2/3 of the kernel. There a thread-block CLUSTER of `cls` CTAs serves one chain: every CTA
+// runs the (cheap, sequential) site loop redundantly on its own copy of the block's columns and rows, so
+// no data is exchanged, and the flush tiles are divided among the CTAs; one cluster barrier per block
+// orders the G tiles written by the peers before the next block's loads.
 #include "sweep.cuh"
+#include <cooperative_groups.h>
+#include <stdlib.h>
+
+namespace cg = cooperative_groups;
 
 namespace mcb {
 
@@ -22,6 +32,8 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
     size_t smem;
+    int cls;   // CTAs per chain (thread-block cluster), 1 = plain launch
+    int exp;   // timing experiments (MCB_SWEEP_EXP): 1 = no flush, 2 = no site loop; results invalid
 };
 
 __host__ __device__ inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
@@ -40,6 +52,8 @@ DelayedGeom delayed_geom(int n)
     g.K = K;
     g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
     g.smem = hdr + 3 * (size_t)K * g.ld * sizeof(double);
+    static const int exp_flags = getenv("MCB_SWEEP_EXP") ? atoi(getenv("MCB_SWEEP_EXP")) : 0;
+    g.exp = exp_flags;
     return g;
 }
 
@@ -48,7 +62,9 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
 {
     extern __shared__ __align__(16) double sm[];
     const int n = g.n, ld = g.ld, K = g.K;
-    const int chain = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    const int cls = g.cls;
+    const int chain = blockIdx.x / cls, crank = blockIdx.x % cls, tid = threadIdx.x, T = blockDim.x;
+    cg::cluster_group cluster = cg::this_cluster();
     double* unif = sm;                  // [n]
     double* gnext = unif + n;           // [2] G_ii of the next site (double buffered)
     double* Cc = gnext + 16;            // [K][ld]  column j of the block at Cc + j*ld
@@ -79,7 +95,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     for (int i0 = 0; i0 < n; i0 += K) {
         const int kb = min(K, n - i0);
         const int kb4 = round_up(kb, 4);
-        __syncthreads(); // previous flush done (G up to date, buffers free)
+        // previous flush done (G up to date in every CTA of the chain, buffers free)
+        if (cls > 1 && i0 > 0) cluster.sync(); else __syncthreads();
         // ---- load the block's columns and rows; zero the padding the flush will read
         for (int j = warp; j < kb4; j += nwarps) {
             const double* gcol = Gg + (size_t)(i0 + j) * n;
@@ -93,7 +110,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
         if (tid == 0) gnext[0] = Gg[i0 + (size_t)i0 * n];
-        for (int j = 0; j < kb; ++j) {
+        for (int j = 0; j < ((g.exp & 2) ? 0 : kb); ++j) {
             __syncthreads();
             if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
             const int i = i0 + j;
@@ -153,7 +170,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         __syncthreads();
         // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
         const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
-        for (int tile = warp; tile < tm * tn; tile += nwarps) {
+        for (int tile = warp + nwarps * crank; tile < ((g.exp & 1) ? 0 : tm * tn); tile += nwarps * cls) {
             const int row0 = (tile % tm) * 32, col0 = (tile / tm) * 16;
             // rows / columns past the padded size are clamped: their products are never stored
             const double* ua[4];
@@ -200,18 +217,25 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                     }
         }
     }
-    __syncthreads();
+    if (cls > 1) cluster.sync(); else __syncthreads();
+    // every CTA of the chain checks its share of G; rank 0 owns the chain's outputs
     bool bad = false;
-    for (size_t e = tid; e < (size_t)n * n; e += T) bad |= !isfinite(Gg[e]);
-    for (int i = tid; i < n; i += T) cg[i] = s_out[i];
-    if (__syncthreads_or(bad) && tid == 0) a.nonfinite[chain] += 1;
-    if (tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
+    for (size_t e = tid + (size_t)T * crank; e < (size_t)n * n; e += (size_t)T * cls) bad |= !isfinite(Gg[e]);
+    if (crank == 0)
+        for (int i = tid; i < n; i += T) cg[i] = s_out[i];
+    if (__syncthreads_or(bad) && tid == 0) atomicAdd((unsigned long long*)&a.nonfinite[chain], 1ull);
+    if (crank == 0 && tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
 }
 
 } // namespace
 
+static int g_sms = 0;
+
 int init_sweep_delayed_kernels()
 {
+    int dev = 0;
+    MCB_CUDA(cudaGetDevice(&dev));
+    MCB_CUDA(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
     MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     return 0;
@@ -219,12 +243,31 @@ int init_sweep_delayed_kernels()
 
 int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
 {
-    const DelayedGeom g = delayed_geom(a.n);
+    DelayedGeom g = delayed_geom(a.n);
     if (g.K < 4) { set_error("delayed sweep: matrix too large for one CTA's shared memory"); return -1; }
+    // CTAs per chain: as many as keep the whole batch in one wave of one CTA per SM (clusters of 4 leave a few
+    // SMs of each GPC unused, hence the margin); only where the flush is large enough to be worth dividing
+    static const int force_cls = getenv("MCB_SWEEP_CLS") ? atoi(getenv("MCB_SWEEP_CLS")) : 0;
+    int cls = 1;
+    if (a.n >= 128) {
+        if (a.batch * 4 <= g_sms - 16) cls = 4;
+        else if (a.batch * 2 <= g_sms - 4) cls = 2;
+    }
+    if (force_cls == 1 || force_cls == 2 || force_cls == 4) cls = force_cls;
+    g.cls = cls;
     LaunchScope scope(LC_SWEEP, st, 0.0);
-    if (g.threads <= 512) sweep_delayed_kernel<512><<<a.batch, g.threads, g.smem, st>>>(a, g);
-    else sweep_delayed_kernel<1024><<<a.batch, g.threads, g.smem, st>>>(a, g);
-    MCB_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.batch * cls, 1, 1);
+    cfg.blockDim = dim3(g.threads, 1, 1);
+    cfg.dynamicSmemBytes = g.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cls; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (g.threads <= 512) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512>, a, g));
+    else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024>, a, g));
     return 0;
 }
 
