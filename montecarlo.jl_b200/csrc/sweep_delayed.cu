@@ -7,7 +7,8 @@
 // An accepted flip at site i = i0 + j is the rank-1 update G -= u v' with u = x (e_i - G[:, i]),
 // v = G[i, :], x = gamma / (1 + gamma (1 - G_ii))  (accept_local!, :142-153). It is applied at once
 // only to the columns j' > j of Cc and the rows k > j of Rc (2 K N flop instead of 2 N^2); u is
-// recorded in U[:, j], v stays frozen in Rc[j, :]. After the block the whole matrix is brought up to
+// recorded in place of column j of Cc (no later site reads it; the store is deferred to the next barrier
+// because the current site still does), v stays frozen in Rc[j, :]. After the block the whole matrix is brought up to
 // date with ONE product G -= U * Rc (N x K x N) on the FP64 tensor pipe. The Metropolis decisions see
 // exactly the Green's function the immediate updates would give (the arithmetic is re-associated only).
 // One barrier per site: the next site's G_ii is published by the thread that owns its row.
@@ -45,13 +46,13 @@ DelayedGeom delayed_geom(int n)
     g.np = round_up(n, 8);
     g.ld = g.np + ((20 - g.np % 16) % 16 == 0 ? 16 : (20 - g.np % 16) % 16); // ld % 16 == 4, ld > np
     const size_t hdr = (size_t)(2 * n + 16) * sizeof(double) + 2 * (size_t)round_up(n, 8);
-    int K = (int)((SMEM_LIMIT - 2048 - hdr) / (3 * (size_t)g.ld * sizeof(double)));
+    int K = (int)((SMEM_LIMIT - 2048 - hdr) / (2 * (size_t)g.ld * sizeof(double)));
     K = K / 4 * 4;
     if (K > 32) K = 32;
     if (K > round_up(n, 4)) K = round_up(n, 4);
     g.K = K;
     g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
-    g.smem = hdr + 3 * (size_t)K * g.ld * sizeof(double);
+    g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double);
     static const int exp_flags = getenv("MCB_SWEEP_EXP") ? atoi(getenv("MCB_SWEEP_EXP")) : 0;
     g.exp = exp_flags;
     return g;
@@ -69,8 +70,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     double* gnext = unif + n;           // [2] G_ii of the next site (double buffered)
     double* Cc = gnext + 16;            // [K][ld]  column j of the block at Cc + j*ld
     double* Rc = Cc + (size_t)K * ld;   // [K][ld]  row k of the block at Rc + k*ld
-    double* U = Rc + (size_t)K * ld;    // [K][ld]  recorded u of site j at U + j*ld (zero if rejected)
-    int8_t* s_in = (int8_t*)(U + (size_t)K * ld);
+    double* U = Cc;                     // recorded u of site j replaces column j (zero if rejected)
+    int8_t* s_in = (int8_t*)(Rc + (size_t)K * ld);
     int8_t* s_out = s_in + round_up(n, 8);
     double* Gg = a.G + (size_t)chain * a.sG;
     int8_t* cg = a.conf + (size_t)chain * a.sConf;
@@ -102,7 +103,6 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             const double* gcol = Gg + (size_t)(i0 + j) * n;
             for (int row = lane; row < ld; row += 32) {
                 Cc[j * ld + row] = (j < kb && row < n) ? gcol[row] : 0.0;
-                U[j * ld + row] = 0.0;
             }
         }
         for (int l = warp; l < ld; l += nwarps) {
@@ -110,9 +110,12 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
         if (tid == 0) gnext[0] = Gg[i0 + (size_t)i0 * n];
+        double u_prev = 0.0;   // u of the previous site, stored once nobody reads its column any more
         for (int j = 0; j < ((g.exp & 2) ? 0 : kb); ++j) {
             __syncthreads();
             if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
+            if (j > 0 && worker && grp == 0) U[(j - 1) * ld + e] = u_prev;
+            u_prev = 0.0;
             const int i = i0 + j;
             const double gii = gnext[j & 1];
             const int s = s_in[i];
@@ -128,7 +131,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                 if (worker) {
                     // columns j' > j of the block: element (row e, column j')
                     const double u = x * ((e == i ? 1.0 : 0.0) - cj[e]);
-                    if (grp == 0) U[j * ld + e] = u;
+                    u_prev = u;
                     const int first = j + 1 + grp;
                     double* cp = Cc + first * ld + e;
                     const double* vp = vj + i0 + first;
@@ -167,6 +170,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             }
             if (tid == 0) s_out[i] = (int8_t)(accept ? -s : s);
         }
+        __syncthreads();
+        if (!(g.exp & 2) && worker && grp == 0) U[(kb - 1) * ld + e] = u_prev;
         __syncthreads();
         // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
         const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
