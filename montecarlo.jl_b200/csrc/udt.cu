@@ -3,6 +3,7 @@
 // both: it works through generic pointers.
 #include "udt.cuh"
 #include "stab.cuh"
+#include <stdlib.h>
 
 namespace mcb {
 
@@ -232,6 +233,10 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
                cudaStream_t st)
 {
     if (X == T || X == U || U == T) { set_error("udt: buffers alias"); return -1; }
+    static const bool prefer_smem = getenv("MCB_UDT_SMEM") && atoi(getenv("MCB_UDT_SMEM")) != 0;
+    if (prefer_smem && n <= 200 && udt_cluster_supported(n) && !force_general_udt() && sX == (long long)n * n &&
+        sU == sX && sT == sX && sD == n && sP == n)
+        return launch_udt_cluster(n, batch, X, U, D, T, pivot, apply_pivot, st);
     // sizes beyond the chain-resident path that still fit one SM's registers: register-resident QR
     if (udt_panel_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX &&
         sD == n && sP == n)

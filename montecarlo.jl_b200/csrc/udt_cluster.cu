@@ -27,17 +27,16 @@ namespace mcb {
 
 namespace {
 
-constexpr int CL = 8;          // CTAs per chain (portable cluster size)
+constexpr int CL = 8;          // CTAs per chain for 200 < N (portable cluster size); 1 CTA when the matrix fits one SM
 constexpr int FW = 25;         // warps per CTA, factor kernel
 constexpr int FT = FW * 32;
 constexpr int QW = 8;          // warps per CTA, form-Q kernel (one column pair each)
 constexpr int QT = QW * 32;
-constexpr int QNR = 15;        // 32-row blocks per column held in registers (N <= 480)
 constexpr int KC = 8;          // reflectors per shared-memory chunk
 constexpr int NMAX = 448;       // n*n + 57 n bytes of shared memory per CTA must stay below 227 KB
 
 struct ClusterUdtArgs {
-    int n, nc;                 // nc = n / CL columns per CTA
+    int n, nc, cl;             // cl CTAs per chain, nc = n / cl columns per CTA
     double* X;                 // in: the matrix; out: scaled Householder vectors below, tau on the diagonal
     double* D;
     double* T;
@@ -46,9 +45,9 @@ struct ClusterUdtArgs {
     int exp;                   // timing experiments (MCB_UDT_EXP): phases switched off, results invalid
 };
 
-size_t factor_smem_bytes(int n)
+size_t factor_smem_bytes(int n, int cl)
 {
-    const int nc = n / CL;
+    const int nc = n / cl;
     // A (nc*n) + vbuf (n) + norms (2n) + xrow (2n) + dtab (n) + rinv, tau (nc each) doubles,
     // colpos + colat ints, elim bytes, level-1 pivot candidates
     return (size_t)nc * n * 8 + (size_t)6 * n * 8 + (size_t)2 * nc * 8 + (size_t)2 * n * 4 + (size_t)n + 16 + 3 * 16 * 4 + 16;
@@ -104,8 +103,8 @@ __device__ __forceinline__ void update_block(int r, int lane, int n, int j, cons
 
 template <int K>
 __device__ __forceinline__ void apply_reflector(double* const (&col)[K], const int (&cidx)[K], const double* vb,
-                                                int j, int n, double tj, double rinv, int lane, double* rnorm,
-                                                double* rxrow, int exp)
+                                                int j, int n, double tj, double rinv, int lane, int cl,
+                                                double* rnorm, double* rxrow, int exp)
 {
     const int rb0 = (j + 1) >> 6;   // vb is zero on the rows <= j of this block
     double dot[2 * K], w[K], wj[K], nrm[K];   // even / odd rows accumulate separately (shorter dependency chains)
@@ -140,7 +139,7 @@ __device__ __forceinline__ void apply_reflector(double* const (&col)[K], const i
         nrm[k] = warp_sum(nrm[k]);
         xr[k] = col[k][j + 1];
     }
-    if (lane < CL && !(exp & 16)) {
+    if (lane < cl && !(exp & 16)) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             rnorm[cidx[k]] = nrm[k];
@@ -162,9 +161,9 @@ __global__ void __launch_bounds__(FT, 1) udt_cluster_factor_kernel(ClusterUdtArg
 {
     cg::cluster_group cluster = cg::this_cluster();
     extern __shared__ __align__(16) unsigned char smraw[];
-    const int n = a.n, nc = a.nc;
+    const int n = a.n, nc = a.nc, cl = a.cl;
     const int rank = (int)cluster.block_rank();
-    const int chain = blockIdx.x / CL;
+    const int chain = blockIdx.x / cl;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* A = reinterpret_cast<double*>(smraw);     // my nc columns, column-major, never permuted
     double* vbuf = A + (size_t)nc * n;                // Householder vector of the current step
@@ -184,10 +183,10 @@ __global__ void __launch_bounds__(FT, 1) udt_cluster_factor_kernel(ClusterUdtArg
 
     for (int e = tid; e < nc * n; e += FT) A[e] = Xg[(size_t)c0 * n + e];
     for (int c = tid; c < n; c += FT) { colpos[c] = c; colat[c] = c; elim[c] = 0; }
-    // remote views of the tables: lane r (< CL) writes into CTA r
+    // remote views of the tables: lane r (< cl) writes into CTA r
     double* rnorms = norms;
     double* rxrows = xrow;
-    if (lane < CL) {
+    if (lane < cl) {
         rnorms = cluster.map_shared_rank(norms, lane);
         rxrows = cluster.map_shared_rank(xrow, lane);
     }
@@ -198,7 +197,7 @@ __global__ void __launch_bounds__(FT, 1) udt_cluster_factor_kernel(ClusterUdtArg
         double s = 0.0;
         for (int i = lane; i < n; i += 32) s = fma(col[i], col[i], s);
         s = warp_sum(s);
-        if (lane < CL) { rnorms[c0 + lc] = s; rxrows[c0 + lc] = col[0]; }
+        if (lane < cl) { rnorms[c0 + lc] = s; rxrows[c0 + lc] = col[0]; }
     }
 
     int prev_jm = -1;
@@ -285,11 +284,11 @@ __global__ void __launch_bounds__(FT, 1) udt_cluster_factor_kernel(ClusterUdtArg
                 if (act0 && act1) {
                     double* const cols[2] = {A + (size_t)l0 * n, A + (size_t)l1 * n};
                     const int idx[2] = {g0, g1};
-                    apply_reflector<2>(cols, idx, vbuf, j, n, tj, rinv, lane, rn, rx, a.exp);
+                    apply_reflector<2>(cols, idx, vbuf, j, n, tj, rinv, lane, cl, rn, rx, a.exp);
                 } else if (act0 || act1) {
                     double* const cols[1] = {A + (size_t)(act0 ? l0 : l1) * n};
                     const int idx[1] = {act0 ? g0 : g1};
-                    apply_reflector<1>(cols, idx, vbuf, j, n, tj, rinv, lane, rn, rx, a.exp);
+                    apply_reflector<1>(cols, idx, vbuf, j, n, tj, rinv, lane, cl, rn, rx, a.exp);
                 }
             }
         }
@@ -326,10 +325,9 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
 }
 
-constexpr int QNP = 32 * QNR;   // padded column length of the reflector chunks (rows >= n stay zero)
 
 // reflector k applied to the warp's columns; RB = k / 32 is static so that only blocks r >= RB exist in the code
-template <int RB, bool BOTH>
+template <int QNR, int RB, bool BOTH>
 __device__ __forceinline__ void formq_step(int k, int lane, const double* vk, double (&ua)[QNR], double (&ub)[QNR])
 {
     const double tk = vk[k];
@@ -360,8 +358,10 @@ __device__ __forceinline__ void formq_step(int k, int lane, const double* vk, do
     }
 }
 
+template <int QNR>
 __device__ __forceinline__ void formq_load_chunk(int n, int k0, int tid, double* dst, const double* Xc)
 {
+    constexpr int QNP = 32 * QNR;
     const int half = (n - k0) >> 1;   // 16-byte pieces per column, rows k0..n-1 (k0, n even)
     for (int idx = tid; idx < KC * half; idx += QT) {
         const int col = idx / half, pc = idx - col * half;
@@ -371,21 +371,22 @@ __device__ __forceinline__ void formq_load_chunk(int n, int k0, int tid, double*
 }
 
 // all reflectors k with k / 32 == RB (chunks of KC, next chunk in flight), then the levels below
-template <int RB>
+template <int QNR, int RB>
 __device__ __forceinline__ void formq_levels(int n, int kstart, bool valid, int ca, int cb, int lane, int tid,
                                              double* buf, const double* Xc, int& b, double (&ua)[QNR],
                                              double (&ub)[QNR])
 {
+    constexpr int QNP = 32 * QNR;   // padded column length of the reflector chunks (rows >= n stay zero)
     if (32 * RB <= kstart) {   // CTA-uniform
         for (int k0 = min(kstart, 32 * RB + 32 - KC); k0 >= 32 * RB; k0 -= KC) {
-            if (k0 >= KC) formq_load_chunk(n, k0 - KC, tid, buf + (size_t)(b ^ 1) * KC * QNP, Xc);
+            if (k0 >= KC) formq_load_chunk<QNR>(n, k0 - KC, tid, buf + (size_t)(b ^ 1) * KC * QNP, Xc);
             if (valid) {
                 const double* chunk = buf + (size_t)b * KC * QNP;
                 for (int kk = KC - 1; kk >= 0; --kk) {
                     const int k = k0 + kk;
                     if (k > cb) continue;
-                    if (k <= ca) formq_step<RB, true>(k, lane, chunk + (size_t)kk * QNP, ua, ub);
-                    else formq_step<RB, false>(k, lane, chunk + (size_t)kk * QNP, ua, ub);
+                    if (k <= ca) formq_step<QNR, RB, true>(k, lane, chunk + (size_t)kk * QNP, ua, ub);
+                    else formq_step<QNR, RB, false>(k, lane, chunk + (size_t)kk * QNP, ua, ub);
                 }
             }
             asm volatile("cp.async.wait_all;\n" ::);
@@ -393,11 +394,14 @@ __device__ __forceinline__ void formq_levels(int n, int kstart, bool valid, int 
             b ^= 1;
         }
     }
-    if constexpr (RB > 0) formq_levels<RB - 1>(n, kstart, valid, ca, cb, lane, tid, buf, Xc, b, ua, ub);
+    if constexpr (RB > 0) formq_levels<QNR, RB - 1>(n, kstart, valid, ca, cb, lane, tid, buf, Xc, b, ua, ub);
 }
 
+// QNR = 32-row blocks per column held in registers (n <= 32 QNR)
+template <int QNR>
 __global__ void __launch_bounds__(QT, 2) udt_formq_kernel(int n, const double* __restrict__ X, double* __restrict__ U)
 {
+    constexpr int QNP = 32 * QNR;
     extern __shared__ __align__(16) unsigned char smraw[];
     double* buf = reinterpret_cast<double*>(smraw);   // [2][KC][QNP]
     const int chain = blockIdx.y;
@@ -419,11 +423,11 @@ __global__ void __launch_bounds__(QT, 2) udt_formq_kernel(int n, const double* _
     }
     // first chunk: the one that holds reflector n-1-pair0 (the longest column of this CTA)
     const int kstart = ((n - 1 - pair0) / KC) * KC;
-    formq_load_chunk(n, kstart, tid, buf, Xc);
+    formq_load_chunk<QNR>(n, kstart, tid, buf, Xc);
     asm volatile("cp.async.wait_all;\n" ::);
     __syncthreads();
     int b = 0;
-    formq_levels<QNR - 1>(n, kstart, valid, ca, cb, lane, tid, buf, Xc, b, ua, ub);
+    formq_levels<QNR, QNR - 1>(n, kstart, valid, ca, cb, lane, tid, buf, Xc, b, ua, ub);
     if (valid) {
         double* Uc = U + (size_t)chain * n * n;
 #pragma unroll
@@ -437,34 +441,52 @@ __global__ void __launch_bounds__(QT, 2) udt_formq_kernel(int n, const double* _
     }
 }
 
-bool g_cluster_ok = false;
+int g_max_clusters = 0;   // clusters of CL CTAs the device runs at once (0: shape unavailable)
+bool g_single_ok = false; // the one-CTA shape can be launched
+
+int set_factor_smem(int n, int cl, cudaLaunchConfig_t* cfg, cudaLaunchAttribute* at, int batch, cudaStream_t st)
+{
+    *cfg = cudaLaunchConfig_t{};
+    cfg->gridDim = dim3(batch * cl, 1, 1);
+    cfg->blockDim = dim3(FT, 1, 1);
+    cfg->dynamicSmemBytes = factor_smem_bytes(n, cl);
+    cfg->stream = st;
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg->attrs = at;
+    cfg->numAttrs = 1;
+    return 0;
+}
+
+constexpr int N1MAX = 160;      // one CTA: n*n*8 + tables in 227 KB, and 5 row blocks in form-Q
 
 } // namespace
 
-bool udt_cluster_supported(int n) { return g_cluster_ok && n > 200 && n <= NMAX && n % 8 == 0; }
+bool udt_cluster_supported(int n)
+{
+    if (n % 8 != 0) return false;
+    if (n > 200) return g_max_clusters > 0 && n <= NMAX;
+    // the matrix fits one SM: same kernel with a "cluster" of one CTA (columns in shared memory, 25 warps)
+    return g_single_ok && n > 128 && n <= N1MAX;
+}
 
 int init_udt_cluster_kernels()
 {
     MCB_CUDA(cudaFuncSetAttribute(udt_cluster_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)factor_smem_bytes(NMAX)));
-    MCB_CUDA(cudaFuncSetAttribute(udt_formq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  2 * KC * QNP * (int)sizeof(double)));
-    // can the device co-schedule one cluster of this shape at all?
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(CL, 1, 1);
-    cfg.blockDim = dim3(FT, 1, 1);
-    cfg.dynamicSmemBytes = factor_smem_bytes(NMAX);
+                                  (int)factor_smem_bytes(NMAX, CL)));
+    MCB_CUDA(cudaFuncSetAttribute(udt_formq_kernel<15>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  2 * KC * 32 * 15 * (int)sizeof(double)));
+    MCB_CUDA(cudaFuncSetAttribute(udt_formq_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  2 * KC * 32 * 5 * (int)sizeof(double)));
+    // can the device co-schedule clusters of this shape at all?
+    cudaLaunchConfig_t cfg;
     cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    int nclusters = 0;
-    if (cudaOccupancyMaxActiveClusters(&nclusters, udt_cluster_factor_kernel, &cfg) != cudaSuccess) {
+    set_factor_smem(NMAX, CL, &cfg, at, 1, 0);
+    if (cudaOccupancyMaxActiveClusters(&g_max_clusters, udt_cluster_factor_kernel, &cfg) != cudaSuccess) {
         cudaGetLastError();
-        nclusters = 0;
+        g_max_clusters = 0;
     }
-    g_cluster_ok = nclusters > 0;
+    g_single_ok = factor_smem_bytes(N1MAX, 1) <= (size_t)factor_smem_bytes(NMAX, CL);
     return 0;
 }
 
@@ -473,26 +495,21 @@ int launch_udt_cluster(int n, int batch, double* X, double* U, double* D, double
 {
     if (!udt_cluster_supported(n)) { set_error("udt_cluster: unsupported size"); return -1; }
     static const int exp_flags = getenv("MCB_UDT_EXP") ? atoi(getenv("MCB_UDT_EXP")) : 0;
-    ClusterUdtArgs a{n, n / CL, X, D, T, pivot, apply_pivot, exp_flags};
+    const int cl = n > 200 ? CL : 1;
+    ClusterUdtArgs a{n, n / cl, cl, X, D, T, pivot, apply_pivot, exp_flags};
     const double n3 = (double)n * n * n * batch;
     {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(batch * CL, 1, 1);
-        cfg.blockDim = dim3(FT, 1, 1);
-        cfg.dynamicSmemBytes = factor_smem_bytes(n);
-        cfg.stream = st;
+        cudaLaunchConfig_t cfg;
         cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at;
-        cfg.numAttrs = 1;
+        set_factor_smem(n, cl, &cfg, at, batch, st);
         LaunchScope scope(LC_UDT, st, 4.0 / 3.0 * n3);
         MCB_CUDA(cudaLaunchKernelEx(&cfg, udt_cluster_factor_kernel, a));
     }
     {
         LaunchScope scope(LC_UDT, st, 4.0 / 3.0 * n3);
         const dim3 grid((n / 2 + QW - 1) / QW, batch, 1);
-        udt_formq_kernel<<<grid, QT, 2 * KC * QNP * sizeof(double), st>>>(n, X, U);
+        if (n <= 160) udt_formq_kernel<5><<<grid, QT, 2 * KC * 32 * 5 * sizeof(double), st>>>(n, X, U);
+        else udt_formq_kernel<15><<<grid, QT, 2 * KC * 32 * 15 * sizeof(double), st>>>(n, X, U);
         MCB_CUDA(cudaGetLastError());
     }
     return 0;
