@@ -183,6 +183,31 @@ int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, cons
                                 const double* Tl, const double* Ur, const double* Dr,
                                 const double* Tr, double* G, int32_t device_id);
 
+/* ------------------------------------------------- DQMC{HubbardModelRepulsive} ---- */
+/* SURVEY.md 8(f) rank 4. The reference keeps the two spin sectors as the blocks of BlockDiagonal matrices
+ * (src/models/HubbardModel/HubbardModelRepulsive.jl:72-232, src/linalg/blockdiagonal.jl:156-428); here they are
+ * two batched stacks that share one field and one sweep_spatial launch. Same parameter struct, same call
+ * sequence and error codes as the mcb_dqmc_* functions above; n_sites >= 16.
+ * Green's functions travel as [chain][sector (up, down)][col][row], i.e. the two diagonal blocks of mc.s.greens. */
+typedef struct mcb_dqmc_rep mcb_dqmc_rep;
+int mcb_dqmc_rep_create(const mcb_dqmc_params* p, mcb_dqmc_rep** out);
+int mcb_dqmc_rep_destroy(mcb_dqmc_rep* h);
+/* hopping_matrix = BlockDiagonal(T, copy(T)) (HubbardModelRepulsive.jl:84-100): one block is passed */
+int mcb_dqmc_rep_set_hopping(mcb_dqmc_rep* h, const double* eT_half_minus, const double* eT_half_plus,
+                             const double* eT_minus, const double* eT_plus);
+int mcb_dqmc_rep_set_conf(mcb_dqmc_rep* h, const int8_t* conf);
+int mcb_dqmc_rep_get_conf(mcb_dqmc_rep* h, int8_t* conf);
+int mcb_dqmc_rep_build_stack(mcb_dqmc_rep* h);
+/* n x update(mc, i): propagate on both blocks, then sweep_spatial with propose_local / accept_local! of
+ * HubbardModelRepulsive.jl:126-232 (detratio = R_up R_down, no bosonic factor, one rank-1 update per block) */
+int mcb_dqmc_rep_update(mcb_dqmc_rep* h, int64_t n_updates);
+int mcb_dqmc_rep_sweep(mcb_dqmc_rep* h, int64_t n_sweeps);
+int mcb_dqmc_rep_get_greens(mcb_dqmc_rep* h, double* G, int32_t physical);
+int mcb_dqmc_rep_calculate_greens_at(mcb_dqmc_rep* h, int32_t slice, double* G);
+int mcb_dqmc_rep_get_state(mcb_dqmc_rep* h, mcb_dqmc_state* st);
+int mcb_dqmc_rep_get_stats(mcb_dqmc_rep* h, mcb_dqmc_chain_stats* out);
+double mcb_dqmc_rep_last_elapsed_ms(mcb_dqmc_rep* h);
+
 /* ----------------------------------------------------------------- Ising ---- */
 
 typedef struct mcb_ising mcb_ising;

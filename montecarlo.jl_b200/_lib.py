@@ -73,6 +73,19 @@ SIGNATURES = {
     "mcb_dqmc_profile": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "mcb_dqmc_get_profile": (C.c_int, [C.c_void_p, _i64, _f64, _i64, _f64]),
     "mcb_dqmc_last_elapsed_ms": (C.c_double, [C.c_void_p]),
+    "mcb_dqmc_rep_create": (C.c_int, [C.POINTER(DqmcParams), C.POINTER(C.c_void_p)]),
+    "mcb_dqmc_rep_destroy": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_rep_set_hopping": (C.c_int, [C.c_void_p, _f64, _f64, _f64, _f64]),
+    "mcb_dqmc_rep_set_conf": (C.c_int, [C.c_void_p, _i8]),
+    "mcb_dqmc_rep_get_conf": (C.c_int, [C.c_void_p, _i8]),
+    "mcb_dqmc_rep_build_stack": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_rep_update": (C.c_int, [C.c_void_p, C.c_int64]),
+    "mcb_dqmc_rep_sweep": (C.c_int, [C.c_void_p, C.c_int64]),
+    "mcb_dqmc_rep_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
+    "mcb_dqmc_rep_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
+    "mcb_dqmc_rep_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
+    "mcb_dqmc_rep_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
+    "mcb_dqmc_rep_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_launch_count": (C.c_int64, [C.c_void_p]),
     "mcb_linalg_force_general": (C.c_int, [C.c_int32]),

@@ -1,0 +1,218 @@
+// extern "C" entry points of DQMC{HubbardModelRepulsive} (include/mcb200.h).
+//
+// The reference keeps the two spin sectors as the two blocks of BlockDiagonal matrices
+// (src/models/HubbardModel/HubbardModelRepulsive.jl:72-124, src/linalg/blockdiagonal.jl:156-428): every stack,
+// wrap and UDT operation acts on the blocks independently; the sectors meet only in propose_local
+// (:126-154), where the determinant ratio is the product of the two diagonal 2x2 entries, and accept_local!
+// (:156-232) updates each block with its own rank-1 term. The spin-down block sees exp(-sign(power) lambda s),
+// i.e. it is the attractive model's slice matrix on the NEGATED field. Here a repulsive run therefore is a
+// pair of ordinary engine handles on one stream - `up` on the field s, `dn` on -s - that propagate
+// separately (all stabilisation kernels are reused as they are) and share one sweep_spatial launch
+// (sweep_delayed.cu: a cluster of two CTAs per chain, one per sector).
+#include "dqmc_engine.cuh"
+#include <math.h>
+#include <vector>
+
+using namespace mcb;
+
+struct mcb_dqmc_rep {
+    mcb_dqmc* up = nullptr;
+    mcb_dqmc* dn = nullptr;
+    cudaStream_t dn_stream = nullptr; // the stream dn was created with (unused: dn runs on up's stream)
+    std::vector<int8_t> neg;          // host staging for the negated field
+};
+
+#define API_TRY(expr)                        \
+    do {                                     \
+        const int rc__ = (expr);             \
+        if (rc__ != 0) return rc__;          \
+    } while (0)
+#define REQUIRE(cond, msg)                   \
+    do {                                     \
+        if (!(cond)) { set_error(msg); return MCB_ERR_ARG; } \
+    } while (0)
+
+namespace {
+struct ProfBind {
+    explicit ProfBind(mcb_dqmc* h) { set_current_profiler(&h->prof); }
+    ~ProfBind() { set_current_profiler(nullptr); }
+};
+
+// update (DQMC.jl:523-538) of the pair: propagate both sectors, one joint sweep_spatial
+int rep_update(mcb_dqmc_rep* r)
+{
+    mcb_dqmc* u = r->up;
+    mcb_dqmc* d = r->dn;
+    u->conf_version++; d->conf_version++;
+    API_TRY(engine_propagate(u, false, nullptr));
+    API_TRY(engine_propagate(d, false, nullptr));
+    SweepArgs a;
+    a.n = u->N; a.batch = u->C;
+    a.G = u->G; a.G2 = d->G; a.sG = (long long)u->nn;
+    a.conf = u->conf + (size_t)(u->current_slice - 1) * u->N;
+    a.conf2 = d->conf + (size_t)(d->current_slice - 1) * d->N;
+    a.sConf = (long long)u->M * u->N;
+    // Delta = exp(-+2 alpha s) - 1 (HubbardModelRepulsive.jl:136-140); no bosonic factor in the weight
+    const double dEp = -2.0 * u->lambda * 1.0, dEm = -2.0 * u->lambda * -1.0;
+    a.gamma_p = exp(dEp) - 1.0; a.efac_p = 1.0;
+    a.gamma_m = exp(dEm) - 1.0; a.efac_m = 1.0;
+    a.key0 = seed_key0(u->p.seed);
+    a.chain_offset = u->p.chain_offset;
+    a.sweep = (uint32_t)(u->n_updates / (2 * (int64_t)u->M));
+    a.visit = (uint32_t)(u->n_updates % (2 * (int64_t)u->M));
+    a.acc = u->acc; a.prop = u->prop; a.nonfinite = u->nonfinite;
+    API_TRY(launch_sweep_delayed(a, u->st));
+    u->n_updates += 1;
+    d->n_updates += 1;
+    return 0;
+}
+} // namespace
+
+extern "C" {
+
+int mcb_dqmc_rep_create(const mcb_dqmc_params* p, mcb_dqmc_rep** out)
+{
+    REQUIRE(p && out, "null argument");
+    REQUIRE(p->n_sites >= 16, "HubbardModelRepulsive needs at least 16 sites (the joint sweep is the delayed-update kernel)");
+    mcb_dqmc_rep* r = new mcb_dqmc_rep();
+    int rc = mcb_dqmc_create(p, &r->up);
+    if (rc == MCB_OK) rc = mcb_dqmc_create(p, &r->dn);
+    if (rc != MCB_OK) {
+        if (r->up) mcb_dqmc_destroy(r->up);
+        delete r;
+        return rc;
+    }
+    // one stream for the pair: the joint sweep needs both propagations
+    r->dn_stream = r->dn->st;
+    r->dn->st = r->up->st;
+    r->neg.resize((size_t)p->n_chains * p->n_slices * p->n_sites);
+    *out = r;
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_destroy(mcb_dqmc_rep* r)
+{
+    if (!r) return MCB_OK;
+    cudaSetDevice(r->up->p.device_id);
+    cudaStreamSynchronize(r->up->st);
+    r->dn->st = r->dn_stream;
+    mcb_dqmc_destroy(r->dn);
+    mcb_dqmc_destroy(r->up);
+    delete r;
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_set_hopping(mcb_dqmc_rep* r, const double* eT_half_minus, const double* eT_half_plus,
+                             const double* eT_minus, const double* eT_plus)
+{
+    REQUIRE(r, "null handle");
+    // hopping_matrix returns BlockDiagonal(T, copy(T)) (HubbardModelRepulsive.jl:84-100): same block twice
+    API_TRY(mcb_dqmc_set_hopping(r->up, eT_half_minus, eT_half_plus, eT_minus, eT_plus));
+    return mcb_dqmc_set_hopping(r->dn, eT_half_minus, eT_half_plus, eT_minus, eT_plus);
+}
+
+int mcb_dqmc_rep_set_conf(mcb_dqmc_rep* r, const int8_t* conf)
+{
+    REQUIRE(r && conf, "null argument");
+    for (size_t e = 0; e < r->neg.size(); ++e) r->neg[e] = (int8_t)-conf[e];
+    API_TRY(mcb_dqmc_set_conf(r->up, conf));
+    return mcb_dqmc_set_conf(r->dn, r->neg.data());
+}
+
+int mcb_dqmc_rep_get_conf(mcb_dqmc_rep* r, int8_t* conf)
+{
+    REQUIRE(r && conf, "null argument");
+    return mcb_dqmc_get_conf(r->up, conf);
+}
+
+int mcb_dqmc_rep_build_stack(mcb_dqmc_rep* r)
+{
+    REQUIRE(r, "null handle");
+    API_TRY(mcb_dqmc_build_stack(r->up));
+    return mcb_dqmc_build_stack(r->dn);
+}
+
+int mcb_dqmc_rep_update(mcb_dqmc_rep* r, int64_t n_updates)
+{
+    REQUIRE(r && n_updates >= 0, "bad argument");
+    mcb_dqmc* u = r->up;
+    if (!u->stack_built || !r->dn->stack_built) { set_error("build_stack first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    ProfBind bind(u);
+    MCB_CUDA(cudaEventRecord(u->ev0, u->st));
+    for (int64_t k = 0; k < n_updates; ++k) API_TRY(rep_update(r));
+    MCB_CUDA(cudaEventRecord(u->ev1, u->st));
+    MCB_CUDA(cudaStreamSynchronize(u->st));
+    MCB_CUDA(cudaEventElapsedTime(&u->last_ms, u->ev0, u->ev1));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_sweep(mcb_dqmc_rep* r, int64_t n_sweeps)
+{
+    REQUIRE(r && n_sweeps >= 0, "bad argument");
+    return mcb_dqmc_rep_update(r, n_sweeps * 2 * (int64_t)r->up->M);
+}
+
+int mcb_dqmc_rep_get_greens(mcb_dqmc_rep* r, double* G, int32_t physical)
+{
+    REQUIRE(r && G, "null argument");
+    mcb_dqmc* hs[2] = {r->up, r->dn};
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    const size_t nn = r->up->nn;
+    for (int f = 0; f < 2; ++f) {
+        mcb_dqmc* h = hs[f];
+        const double* src = h->G;
+        if (physical) { API_TRY(engine_physical_greens(h, h->W[1])); src = h->W[1]; }
+        // [chain][sector][col][row]: the two diagonal blocks of the reference's BlockDiagonal G
+        MCB_CUDA(cudaMemcpy2DAsync(G + f * nn, 2 * nn * sizeof(double), src, nn * sizeof(double), nn * sizeof(double),
+                                   h->C, cudaMemcpyDeviceToHost, h->st));
+    }
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_calculate_greens_at(mcb_dqmc_rep* r, int32_t slice, double* G)
+{
+    REQUIRE(r && G, "null argument");
+    mcb_dqmc* hs[2] = {r->up, r->dn};
+    const size_t nn = r->up->nn;
+    REQUIRE(slice >= 0 && slice <= r->up->M, "bad slice");
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    for (int f = 0; f < 2; ++f) {
+        mcb_dqmc* h = hs[f];
+        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+        API_TRY(engine_calculate_greens_at(h, slice));
+        MCB_CUDA(cudaMemcpy2DAsync(G + f * nn, 2 * nn * sizeof(double), h->G, nn * sizeof(double), nn * sizeof(double),
+                                   h->C, cudaMemcpyDeviceToHost, h->st));
+    }
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_get_state(mcb_dqmc_rep* r, mcb_dqmc_state* st)
+{
+    REQUIRE(r, "null handle");
+    return mcb_dqmc_get_state(r->up, st);
+}
+
+int mcb_dqmc_rep_get_stats(mcb_dqmc_rep* r, mcb_dqmc_chain_stats* out)
+{
+    REQUIRE(r && out, "null argument");
+    mcb_dqmc* u = r->up;
+    API_TRY(mcb_dqmc_get_stats(u, out));
+    // propagation error and non-finite flags: the worse of the two sectors
+    std::vector<mcb_dqmc_chain_stats> d(u->C);
+    API_TRY(mcb_dqmc_get_stats(r->dn, d.data()));
+    for (int c = 0; c < u->C; ++c) {
+        if (d[c].max_propagation_error > out[c].max_propagation_error)
+            out[c].max_propagation_error = d[c].max_propagation_error;
+        out[c].n_nonfinite += d[c].n_nonfinite;
+    }
+    return MCB_OK;
+}
+
+double mcb_dqmc_rep_last_elapsed_ms(mcb_dqmc_rep* r) { return r ? r->up->last_ms : 0.0; }
+
+} // extern "C"

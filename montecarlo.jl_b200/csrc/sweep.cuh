@@ -15,6 +15,11 @@ struct SweepArgs {
     long long* acc = nullptr;   // [batch]
     long long* prop = nullptr;  // [batch]
     long long* nonfinite = nullptr; // [batch]
+    // HubbardModelRepulsive (HubbardModelRepulsive.jl:126-232): two spin sectors share the field with opposite
+    // sign. The second sector is kept as an attractive-like chain on the negated field (G2, conf2 = -conf);
+    // the two sectors only meet in the acceptance probability p = R_up * R_down (no bosonic factor).
+    double* G2 = nullptr;
+    int8_t* conf2 = nullptr;
 };
 
 int launch_sweep_spatial(const SweepArgs& a, cudaStream_t st);

@@ -18,6 +18,12 @@
 // runs the (cheap, sequential) site loop redundantly on its own copy of the block's columns and rows, so
 // no data is exchanged, and the flush tiles are divided among the CTAs; one cluster barrier per block
 // orders the G tiles written by the peers before the next block's loads.
+//
+// HubbardModelRepulsive: a cluster of two CTAs per chain, one per spin sector (a.G / a.G2 on the fields
+// a.conf / a.conf2 = -a.conf). Each CTA publishes the next site's G_ii to its partner through distributed
+// shared memory, the per-site barrier becomes a cluster barrier, and both take the same decision from
+// p = R_own * R_partner (propose_local, HubbardModelRepulsive.jl:126-154; G is block diagonal, so the 2x2
+// determinant is the product of the diagonal entries).
 #include "sweep.cuh"
 #include <cooperative_groups.h>
 #include <stdlib.h>
@@ -34,6 +40,7 @@ struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
     size_t smem;
     int cls;   // CTAs per chain (thread-block cluster), 1 = plain launch
+    int two;   // 1: the two CTAs of a cluster are the two spin sectors of the repulsive model (cls == 2)
     int exp;   // timing experiments (MCB_SWEEP_EXP): 1 = no flush, 2 = no site loop; results invalid
 };
 
@@ -73,8 +80,12 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     double* U = Cc;                     // recorded u of site j replaces column j (zero if rejected)
     int8_t* s_in = (int8_t*)(Rc + (size_t)K * ld);
     int8_t* s_out = s_in + round_up(n, 8);
-    double* Gg = a.G + (size_t)chain * a.sG;
-    int8_t* cg = a.conf + (size_t)chain * a.sConf;
+    const bool two = g.two != 0;
+    const int fcls = two ? 1 : cls, frank = two ? 0 : crank;   // division of the flush / checks among the CTAs
+    double* Gg = ((two && crank) ? a.G2 : a.G) + (size_t)chain * a.sG;
+    int8_t* cg = ((two && crank) ? a.conf2 : a.conf) + (size_t)chain * a.sConf;
+    double* gpeer = gnext + 2;          // [2] the partner sector's G_ii (written by the partner)
+    double* gpeer_remote = two ? cluster.map_shared_rank(gpeer, crank ^ 1) : gpeer;
 
     for (int i = tid; i < n; i += T) {
         s_in[i] = cg[i];
@@ -97,7 +108,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         const int kb = min(K, n - i0);
         const int kb4 = round_up(kb, 4);
         // previous flush done (G up to date in every CTA of the chain, buffers free)
-        if (cls > 1 && i0 > 0) cluster.sync(); else __syncthreads();
+        // (two sectors: also before the first block, the partner must be running before its shared memory is written)
+        if (cls > 1 && (i0 > 0 || two)) cluster.sync(); else __syncthreads();
         // ---- load the block's columns and rows; zero the padding the flush will read
         for (int j = warp; j < kb4; j += nwarps) {
             const double* gcol = Gg + (size_t)(i0 + j) * n;
@@ -109,10 +121,14 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             const double* gcol = Gg + (size_t)l * n + i0;
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
-        if (tid == 0) gnext[0] = Gg[i0 + (size_t)i0 * n];
+        if (tid == 0) {
+            const double g0 = Gg[i0 + (size_t)i0 * n];
+            gnext[0] = g0;
+            if (two) gpeer_remote[0] = g0;
+        }
         double u_prev = 0.0;   // u of the previous site, stored once nobody reads its column any more
         for (int j = 0; j < ((g.exp & 2) ? 0 : kb); ++j) {
-            __syncthreads();
+            if (two) cluster.sync(); else __syncthreads();
             if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
             if (j > 0 && worker && grp == 0) U[(j - 1) * ld + e] = u_prev;
             u_prev = 0.0;
@@ -122,7 +138,11 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
             const double efac = s > 0 ? a.efac_p : a.efac_m;
             const double rt = 1.0 + gamma * (1.0 - gii);
-            const double p = efac * (rt * rt);
+            double p = efac * (rt * rt);
+            if (two) { // the partner sits on the negated field
+                const double rp = 1.0 + (s > 0 ? a.gamma_m : a.gamma_p) * (1.0 - gpeer[j & 1]);
+                p = rt * rp;
+            }
             const bool accept = (p > 1.0 || unif[i] < p); // uniform over the CTA
             const double* cj = Cc + j * ld;
             const double* vj = Rc + j * ld;
@@ -138,6 +158,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                     if (grp == 0 && e == i + 1 && first < kb) {
                         const double cnew = *cp - u * *vp;
                         gnext[(j + 1) & 1] = cnew;
+                        if (two) gpeer_remote[(j + 1) & 1] = cnew;
                     }
                     // (operands are fetched four iterations at a time: the compiler cannot prove that
                     // the stores do not alias the next loads)
@@ -166,7 +187,11 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                 }
                 ++nacc;
             } else if (j + 1 < kb) {
-                if (tid == 0) gnext[(j + 1) & 1] = Cc[(j + 1) * ld + i + 1];
+                if (tid == 0) {
+                    const double gn = Cc[(j + 1) * ld + i + 1];
+                    gnext[(j + 1) & 1] = gn;
+                    if (two) gpeer_remote[(j + 1) & 1] = gn;
+                }
             }
             if (tid == 0) s_out[i] = (int8_t)(accept ? -s : s);
         }
@@ -175,7 +200,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         __syncthreads();
         // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
         const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
-        for (int tile = warp + nwarps * crank; tile < ((g.exp & 1) ? 0 : tm * tn); tile += nwarps * cls) {
+        for (int tile = warp + nwarps * frank; tile < ((g.exp & 1) ? 0 : tm * tn); tile += nwarps * fcls) {
             const int row0 = (tile % tm) * 32, col0 = (tile / tm) * 16;
             // rows / columns past the padded size are clamped: their products are never stored
             const double* ua[4];
@@ -225,8 +250,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     if (cls > 1) cluster.sync(); else __syncthreads();
     // every CTA of the chain checks its share of G; rank 0 owns the chain's outputs
     bool bad = false;
-    for (size_t e = tid + (size_t)T * crank; e < (size_t)n * n; e += (size_t)T * cls) bad |= !isfinite(Gg[e]);
-    if (crank == 0)
+    for (size_t e = tid + (size_t)T * frank; e < (size_t)n * n; e += (size_t)T * fcls) bad |= !isfinite(Gg[e]);
+    if (crank == 0 || two)
         for (int i = tid; i < n; i += T) cg[i] = s_out[i];
     if (__syncthreads_or(bad) && tid == 0) atomicAdd((unsigned long long*)&a.nonfinite[chain], 1ull);
     if (crank == 0 && tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
@@ -259,6 +284,11 @@ int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
         else if (a.batch * 2 <= g_sms - 4) cls = 2;
     }
     if (force_cls == 1 || force_cls == 2 || force_cls == 4) cls = force_cls;
+    g.two = a.G2 != nullptr ? 1 : 0;
+    if (g.two) {
+        if (!a.conf2) { set_error("delayed sweep: second sector without its field"); return -1; }
+        cls = 2;
+    }
     g.cls = cls;
     LaunchScope scope(LC_SWEEP, st, 0.0);
     cudaLaunchConfig_t cfg = {};

@@ -8,7 +8,7 @@ import math
 import numpy as np
 
 from . import _lib
-from .models import HubbardModelAttractive
+from .models import HubbardModelAttractive, HubbardModelRepulsive
 
 
 class DQMCParameters:
@@ -48,6 +48,11 @@ class DQMC:
     """`DQMC(model; beta, ...)` for a batch of `n_chains` chains (global ids chain_offset + c).
 
     conf has shape (n_chains, N, M): conf[c] is the reference's HubbardConf (HubbardModel.jl:4).
+
+    With a HubbardModelRepulsive the Green's functions have shape (n_chains, 2, N, N): the spin-up and spin-down
+    diagonal blocks of the reference's BlockDiagonal mc.s.greens. That model runs the sweep (build_stack, update,
+    sweep, greens, greens_at, conf, state, stats); measurements, unequal-time G, replay and checkpoints are the
+    attractive model's.
     """
 
     def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, general_path=False,
@@ -55,6 +60,8 @@ class DQMC:
         if not isinstance(model, HubbardModelAttractive):
             raise TypeError("the B200 engine implements DQMC{HubbardModelAttractive, CheckerboardFalse}")
         self.model = model
+        self.rep = isinstance(model, HubbardModelRepulsive)
+        self._pfx = "mcb_dqmc_rep_" if self.rep else "mcb_dqmc_"
         self.p = DQMCParameters(**kwargs)
         self.n_chains, self.seed, self.chain_offset, self.device = int(n_chains), int(seed), int(chain_offset), int(device)
         self.general_path = bool(general_path)
@@ -66,9 +73,9 @@ class DQMC:
                               self.seed, self.chain_offset, self.device,
                               int(self.p.check_propagation_error), int(general_path))
         self.h = C.c_void_p()
-        _lib.check(self.L.mcb_dqmc_create(C.byref(prm), C.byref(self.h)))
+        _lib.check(self._f("create")(C.byref(prm), C.byref(self.h)))
         self.hop = model.hopping_exponentials(self.p.delta_tau)
-        _lib.check(self.L.mcb_dqmc_set_hopping(self.h, *[self._fm(a) for a in self.hop]))
+        _lib.check(self._f("set_hopping")(self.h, *[self._fm(a) for a in self.hop]))
         if conf is None:
             conf = np.stack([model.rand_conf(self.M, self.seed, self.chain_offset + c)
                              for c in range(self.n_chains)])
@@ -76,17 +83,25 @@ class DQMC:
         self.last_sweep = 0
         self._tables = False
 
+    def _f(self, name, attractive_only=False):
+        """The C-ABI entry point `name` of this model's handle type."""
+        if attractive_only and self.rep:
+            raise NotImplementedError(f"{name}: not available for HubbardModelRepulsive (SURVEY.md 8f rank 4 covers the sweep)")
+        return getattr(self.L, self._pfx + name)
+
     # -- layout helpers: numpy [i, j] (row-major view of Julia semantics) <-> column-major buffers
     @staticmethod
     def _fm(a):
         return np.ascontiguousarray(np.asarray(a, dtype=np.float64).T).reshape(-1)
 
     def _unbatch(self, buf):
+        if buf.size == 2 * self.n_chains * self.N * self.N:  # two sectors per chain
+            return buf.reshape(self.n_chains, 2, self.N, self.N).transpose(0, 1, 3, 2).copy()
         return buf.reshape(self.n_chains, self.N, self.N).transpose(0, 2, 1).copy()
 
     def close(self):
         if getattr(self, "h", None) is not None and self.h.value:
-            self.L.mcb_dqmc_destroy(self.h)
+            self._f("destroy")(self.h)
             self.h = C.c_void_p()
 
     def __del__(self):
@@ -100,24 +115,24 @@ class DQMC:
         if conf.shape != (self.n_chains, self.N, self.M):
             raise ValueError(f"conf must have shape {(self.n_chains, self.N, self.M)}")
         buf = np.ascontiguousarray(conf.transpose(0, 2, 1)).reshape(-1)
-        _lib.check(self.L.mcb_dqmc_set_conf(self.h, buf))
+        _lib.check(self._f("set_conf")(self.h, buf))
 
     def conf(self):
         buf = np.empty(self.n_chains * self.N * self.M, dtype=np.int8)
-        _lib.check(self.L.mcb_dqmc_get_conf(self.h, buf))
+        _lib.check(self._f("get_conf")(self.h, buf))
         return buf.reshape(self.n_chains, self.M, self.N).transpose(0, 2, 1).copy()
 
     # -- recorded configurations (ConfigRecorder wire format) ------------------------------------
     def conf_bits(self):
         """compress(mc, model, conf) for every chain: (C, ceil(N*M/64)) uint64, bit b = spin i + N*l."""
-        buf = np.empty(self.n_chains * self.L.mcb_dqmc_conf_chunks(self.h), dtype=np.uint64)
-        _lib.check(self.L.mcb_dqmc_get_conf_bits(self.h, buf))
+        buf = np.empty(self.n_chains * self._f("conf_chunks", True)(self.h), dtype=np.uint64)
+        _lib.check(self._f("get_conf_bits", True)(self.h, buf))
         return buf.reshape(self.n_chains, -1)
 
     def set_conf_bits(self, bits):
         bits = np.ascontiguousarray(bits, dtype=np.uint64)
-        assert bits.shape == (self.n_chains, self.L.mcb_dqmc_conf_chunks(self.h))
-        _lib.check(self.L.mcb_dqmc_set_conf_bits(self.h, bits.reshape(-1)))
+        assert bits.shape == (self.n_chains, self._f("conf_chunks", True)(self.h))
+        _lib.check(self._f("set_conf_bits", True)(self.h, bits.reshape(-1)))
 
     def replay(self, configurations):
         """The measurement loop of replay!(mc, configurations) (DQMC.jl:649-660): for every recorded configuration
@@ -131,7 +146,7 @@ class DQMC:
         out = []
         full = (n // C_) * C_
         if full:
-            _lib.check(self.L.mcb_dqmc_replay(self.h, cfg[:full].reshape(-1), full))
+            _lib.check(self._f("replay", True)(self.h, cfg[:full].reshape(-1), full))
             out.append(self.observables())
         if n > full:
             rest = DQMC(self.model, n_chains=n - full, seed=self.seed, beta=self.p.beta, delta_tau=self.p.delta_tau,
@@ -157,47 +172,52 @@ class DQMC:
         if (ckpt["seed"], ckpt["chain_offset"], ckpt["n_chains"]) != (self.seed, self.chain_offset, self.n_chains):
             raise ValueError("checkpoint belongs to different chains")
         self.set_conf_bits(ckpt["conf_bits"])
-        _lib.check(self.L.mcb_dqmc_resume(self.h, int(ckpt["last_sweep"])))
+        _lib.check(self._f("resume", True)(self.h, int(ckpt["last_sweep"])))
         self.last_sweep = int(ckpt["last_sweep"])
 
     def build_stack(self):
         """init! + build_stack + propagate (DQMC.jl:412-414)."""
-        _lib.check(self.L.mcb_dqmc_build_stack(self.h))
+        _lib.check(self._f("build_stack")(self.h))
 
     def update(self, n=1, measure_every=0):
-        _lib.check(self.L.mcb_dqmc_update(self.h, n, measure_every))
+        if self.rep:
+            if measure_every:
+                raise NotImplementedError("built-in measurements are the attractive model's")
+            _lib.check(self.L.mcb_dqmc_rep_update(self.h, n))
+        else:
+            _lib.check(self.L.mcb_dqmc_update(self.h, n, measure_every))
 
     def sweep(self, n=1, measure_every=0):
-        _lib.check(self.L.mcb_dqmc_sweep(self.h, n, measure_every))
+        self.update(n * 2 * self.M, measure_every)
 
     def greens(self, physical=True):
         """greens(mc) (DQMC.jl:711-730); physical=False returns mc.s.greens. Shape (C, N, N)."""
-        buf = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self.L.mcb_dqmc_get_greens(self.h, buf, int(physical)))
+        buf = np.empty(self.n_chains * self.model.flv * self.N * self.N)
+        _lib.check(self._f("get_greens")(self.h, buf, int(physical)))
         return self._unbatch(buf)
 
     def greens_at(self, slice_):
         """calculate_greens(mc, slice) (stack.jl:422-480). Shape (C, N, N)."""
-        buf = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self.L.mcb_dqmc_calculate_greens_at(self.h, slice_, buf))
+        buf = np.empty(self.n_chains * self.model.flv * self.N * self.N)
+        _lib.check(self._f("calculate_greens_at")(self.h, slice_, buf))
         return self._unbatch(buf)
 
     def greens_unequal(self, slice1, slice2, physical=True):
         """greens(mc, k, l) = G(k <- l), 0 <= k, l <= M (unequal_time_stack.jl:275-305); physical=False returns the
         effective G of calculate_greens(mc, k, l). Leaves the sweep state untouched. Shape (C, N, N)."""
         buf = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self.L.mcb_dqmc_greens_unequal(self.h, slice1, slice2, buf, int(physical)))
+        _lib.check(self._f("greens_unequal", True)(self.h, slice1, slice2, buf, int(physical)))
         return self._unbatch(buf)
 
     def state(self):
         st = _lib.DqmcState()
-        _lib.check(self.L.mcb_dqmc_get_state(self.h, C.byref(st)))
+        _lib.check(self._f("get_state")(self.h, C.byref(st)))
         return dict(current_slice=st.current_slice, direction=st.direction, n_updates=st.n_updates,
                     n_measurements=st.n_measurements)
 
     def stats(self):
         arr = (_lib.DqmcChainStats * self.n_chains)()
-        _lib.check(self.L.mcb_dqmc_get_stats(self.h, arr))
+        _lib.check(self._f("get_stats")(self.h, arr))
         return dict(prop_local=np.array([a.prop_local for a in arr]),
                     acc_local=np.array([a.acc_local for a in arr]),
                     max_propagation_error=np.array([a.max_propagation_error for a in arr]),
@@ -211,21 +231,21 @@ class DQMC:
             self.n_dirs = len(dirs)
             # dir_of[src, trg] -> buffer index src + trg*N
             tab = np.ascontiguousarray(dir_of.T.astype(np.int32)).reshape(-1)
-            _lib.check(self.L.mcb_dqmc_set_measurement_tables(self.h, tab, self.n_dirs,
+            _lib.check(self._f("set_measurement_tables", True)(self.h, tab, self.n_dirs,
                                                               self._fm(self.model.hopping_matrix())))
             self._tables = True
 
     def measure(self):
-        _lib.check(self.L.mcb_dqmc_measure(self.h))
+        _lib.check(self._f("measure", True)(self.h))
 
     def observables(self):
         """Per-chain means over measurements. Returns dict of arrays with leading chain axis."""
-        n = self.L.mcb_dqmc_observable_len(self.h)
+        n = self._f("observable_len", True)(self.h)
         buf = np.empty(self.n_chains * n)
         cnt = C.c_int64()
-        _lib.check(self.L.mcb_dqmc_get_observables(self.h, buf, C.byref(cnt)))
+        _lib.check(self._f("get_observables", True)(self.h, buf, C.byref(cnt)))
         gs = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self.L.mcb_dqmc_get_greens_sum(self.h, gs))
+        _lib.check(self._f("get_greens_sum", True)(self.h, gs))
         k = max(cnt.value, 1)
         rec = buf.reshape(self.n_chains, n) / k
         nd = self.n_dirs

@@ -1,6 +1,7 @@
 """Model definitions (host side) mirroring the reference's model plug-ins.
 
 HubbardModelAttractive : src/models/HubbardModel/HubbardModelAttractive.jl:27-40, :78-110
+HubbardModelRepulsive  : src/models/HubbardModel/HubbardModelRepulsive.jl:27-124
 IsingModel             : src/models/Ising/IsingModel.jl:1-60
 Only what the engine needs as *inputs* lives here: the hopping matrix, its
 exponentials, lambda, and random initial configurations.
@@ -56,6 +57,16 @@ class HubbardModelAttractive:
         N = len(self.l)
         bits = philox.random_bits(N * nslices, seed, chain, domain=0xC0DF1E1D)
         return (2 * bits.astype(np.int8) - 1).reshape(nslices, N).T.copy()
+
+
+class HubbardModelRepulsive(HubbardModelAttractive):
+    """HubbardModelRepulsive (HubbardModelRepulsive.jl:27-70): two flavors. The hopping matrix of the reference is
+    BlockDiagonal(T, copy(T)) (:84-100) with the T of the attractive model; the engine is handed the one block.
+    The interaction exponential is exp(+-sign(power) lambda s) for spin up / down (:112-124)."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.flv = 2
 
 
 class IsingModel:

@@ -284,6 +284,50 @@ void sweep_spatial(Oracle& o)
     }
 }
 
+// DQMC{HubbardModelRepulsive}: sweep_spatial (DQMC.jl:546-582) with propose_local / accept_local! of
+// src/models/HubbardModel/HubbardModelRepulsive.jl:126-232. The reference holds G as BlockDiagonal(G_up, G_down)
+// (blockdiagonal.jl); here the spin-down block is the Oracle `dn`, which lives on the NEGATED field because
+// interaction_matrix_exp! gives it exp(-sign(power) lambda s) (:112-124). With G block diagonal the off-diagonal
+// entries R[1,2], R[2,1] vanish: detratio = R[1,1] R[2,2]; there is no bosonic factor (:151-153); accept_local!
+// subtracts IGR[:, b] G_b[i, :] from block b with IGR[:, b] = (e_i - G_b[:, i]) Delta_b / R[b, b].
+void sweep_spatial_repulsive(Oracle& up, Oracle& dn)
+{
+    const int n = up.N;
+    const int slice = up.current_slice;
+    int8_t* cu = up.conf.data() + (size_t)(slice - 1) * n;
+    int8_t* cd = dn.conf.data() + (size_t)(slice - 1) * n;
+    double* G[2] = {up.greens.data(), dn.greens.data()};
+    const uint32_t sweep = (uint32_t)(up.update_count / (uint64_t)(2 * up.M));
+    const uint32_t visit = (uint32_t)(up.update_count % (uint64_t)(2 * up.M));
+    std::vector<double> IG(n), Gr(n);
+    for (int i = 0; i < n; ++i) {
+        const double dE = -2.0 * up.lambda * cu[i];          // Delta E_Boson of :136
+        const double delta[2] = {exp(dE) - 1.0, exp(-dE) - 1.0};
+        const double r[2] = {1.0 + delta[0] * (1.0 - G[0][IDX(i, i, n)]), 1.0 + delta[1] * (1.0 - G[1][IDX(i, i, n)])};
+        const double detratio = r[0] * r[1];
+        up.prop_local += 1;
+        const double p = detratio;                            // exp(-0.0) * detratio
+        const double u = next_uniform(up, sweep, visit, (uint32_t)i);
+        if (p > 1.0 || u < p) {
+            for (int b = 0; b < 2; ++b) {
+                double* Gb = G[b];
+                for (int j = 0; j < n; ++j) { IG[j] = -Gb[IDX(j, i, n)]; Gr[j] = Gb[IDX(i, j, n)]; }
+                IG[i] += 1.0;
+                const double x = delta[b] / r[b];
+                for (int l = 0; l < n; ++l) {
+                    const double xv = x * Gr[l];
+                    double* g = Gb + IDX(0, l, n);
+#pragma omp simd
+                    for (int k = 0; k < n; ++k) g[k] -= IG[k] * xv;
+                }
+            }
+            cu[i] = (int8_t)-cu[i];
+            cd[i] = (int8_t)-cd[i];
+            up.acc_local += 1;
+        }
+    }
+}
+
 // DQMC.jl:523-538
 void update(Oracle& o)
 {
@@ -576,6 +620,20 @@ void orc_update(void* h, int64_t n)
     for (int64_t i = 0; i < n; ++i) update(o);
 }
 void orc_sweep(void* h, int64_t n) { orc_update(h, n * 2 * ((Oracle*)h)->M); }
+// update (DQMC.jl:523-538) of a repulsive chain held as (up on s, dn on -s): propagate acts on the blocks
+// independently (blockdiagonal.jl:156-428), sweep_spatial is joint
+void orc_update_repulsive(void* hup, void* hdn, int64_t n)
+{
+    Oracle& up = *(Oracle*)hup;
+    Oracle& dn = *(Oracle*)hdn;
+    for (int64_t i = 0; i < n; ++i) {
+        propagate(up);
+        propagate(dn);
+        sweep_spatial_repulsive(up, dn);
+        up.update_count += 1;
+        dn.update_count += 1;
+    }
+}
 void orc_propagate_only(void* h) { propagate(*(Oracle*)h); }
 
 // physical != 0 applies _greens! (DQMC.jl:721-730): e^{+dtau T/2} G e^{-dtau T/2}

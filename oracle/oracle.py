@@ -64,6 +64,7 @@ def lib(native=False):
     L.orc_uniform.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
     L.orc_philox.argtypes = [_u32p, _u32p, _u32p]
     L.orc_sweep_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int]
+    L.orc_update_repulsive.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
     # Ising
     L.ising_energy_cubic.restype = C.c_double
     L.ising_energy_cubic.argtypes = [_i64p, C.c_int, C.c_int]
@@ -85,6 +86,43 @@ def lib(native=False):
     L.ising_random_spins.argtypes = [_i8p, C.c_int, C.c_uint64, C.c_uint32]
     _LIBS[key] = L
     return L
+
+
+class OracleDQMCRepulsive:
+    """One Markov chain of DQMC{HubbardModelRepulsive, CheckerboardFalse} on the CPU: the two diagonal blocks of
+    the reference's BlockDiagonal matrices as two sectors, `up` on the field s and `dn` on -s
+    (HubbardModelRepulsive.jl:112-124), with the joint sweep_spatial of dqmc_oracle.cpp."""
+
+    def __init__(self, N, M, safe_mult, dtau, U, hop, conf, seed=123, chain=0, check_propagation=False):
+        conf = np.asarray(conf, dtype=np.int8)
+        self.up = OracleDQMC(N, M, safe_mult, dtau, U, hop, conf, seed, chain, check_propagation)
+        self.dn = OracleDQMC(N, M, safe_mult, dtau, U, hop, -conf, seed, chain, check_propagation)
+        self.N, self.M = N, M
+
+    def build_stack(self):
+        self.up.build_stack()
+        self.dn.build_stack()
+
+    def update(self, n=1):
+        self.up.L.orc_update_repulsive(self.up.h, self.dn.h, n)
+
+    def sweep(self, n=1):
+        self.update(n * 2 * self.M)
+
+    def greens(self, physical=False):
+        """(2, N, N): spin-up and spin-down block."""
+        return np.stack([self.up.greens(physical), self.dn.greens(physical)])
+
+    def greens_at(self, slice_):
+        return np.stack([self.up.greens_at(slice_), self.dn.greens_at(slice_)])
+
+    def conf(self):
+        c = self.up.conf()
+        assert np.array_equal(c, -self.dn.conf())
+        return c
+
+    def state(self):
+        return self.up.state()
 
 
 def fmat(a):

@@ -1,0 +1,106 @@
+"""GPU parity of DQMC{HubbardModelRepulsive} through the C ABI (mcb_dqmc_rep_*): same hopping
+exponentials, HS field and Philox stream as the CPU oracle -> after every update() of a sweep both blocks of the
+Green's function agree to 1e-10 relative max-norm and the fields are identical."""
+import numpy as np
+import pytest
+
+import montecarlo_jl_b200 as mcb
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL_G = 1e-10
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / np.abs(b).max()
+
+
+def _pair(L, U, beta, dtau, safe_mult, n_chains, seed=77, general=False, chain_offset=0):
+    model = mcb.HubbardModelRepulsive(L=L, U=U)
+    mc = mcb.DQMC(model, n_chains=n_chains, seed=seed, chain_offset=chain_offset, beta=beta, delta_tau=dtau,
+                  safe_mult=safe_mult, general_path=general)
+    conf0 = mc.conf()
+    oracles = [orc.OracleDQMCRepulsive(L * L, mc.M, safe_mult, dtau, U, mc.hop, conf0[c], seed=seed,
+                                       chain=chain_offset + c) for c in range(n_chains)]
+    return mc, oracles
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("L,U,beta,safe_mult,chains", [(4, 2.0, 1.0, 5, 3), (4, 4.0, 2.0, 10, 2), (6, 4.0, 1.0, 5, 2)])
+def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains, general):
+    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, chains, general=general)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    G = mc.greens(physical=False)
+    assert G.shape == (chains, 2, L * L, L * L)
+    for c, o in enumerate(oracles):
+        assert relerr(G[c], o.greens()) < RTOL_G
+    for u in range(2 * mc.M + 3):
+        mc.update(1)
+        G = mc.greens(physical=False)
+        st = mc.state()
+        conf = mc.conf()
+        for c, o in enumerate(oracles):
+            o.update(1)
+            so = o.state()
+            assert (st["current_slice"], st["direction"]) == (so["current_slice"], so["direction"])
+            assert relerr(G[c, 0], o.greens()[0]) < RTOL_G, (u, c, "up")
+            assert relerr(G[c, 1], o.greens()[1]) < RTOL_G, (u, c, "down")
+            assert np.array_equal(conf[c], o.conf()), (u, c)
+    stats = mc.stats()
+    for c, o in enumerate(oracles):
+        so = o.state()
+        assert stats["acc_local"][c] == so["acc_local"] and stats["prop_local"][c] == so["prop_local"]
+        assert stats["n_nonfinite"][c] == 0
+    Gp = mc.greens(physical=True)
+    for c, o in enumerate(oracles):
+        assert relerr(Gp[c], o.greens(physical=True)) < RTOL_G
+    mc.close()
+
+
+def test_8x8_beta4_partial_sweep_and_from_scratch_greens():
+    """N = 64 at U = 4: a stretch of updates across a stabilisation point, then calculate_greens(mc, slice) of both
+    blocks against the oracle."""
+    mc, oracles = _pair(8, 4.0, 4.0, 0.1, 10, 2)
+    mc.build_stack()
+    for o in oracles:
+        o.build_stack()
+    mc.update(23)
+    G = mc.greens(physical=False)
+    conf = mc.conf()
+    for c, o in enumerate(oracles):
+        o.update(23)
+        assert relerr(G[c], o.greens()) < RTOL_G
+        assert np.array_equal(conf[c], o.conf())
+    for s in (0, 7, 40):
+        Gs = mc.greens_at(s)
+        for c, o in enumerate(oracles):
+            assert relerr(Gs[c], o.greens_at(s)) < 1e-9
+    mc.close()
+
+
+def test_batched_updates_equal_single_updates_and_chain_ids_are_global():
+    a, _ = _pair(4, 4.0, 1.0, 0.1, 5, 4)
+    b, _ = _pair(4, 4.0, 1.0, 0.1, 5, 2, chain_offset=2)
+    a.build_stack(); b.build_stack()
+    a.update(13)
+    for _ in range(13):
+        b.update(1)
+    assert np.array_equal(a.conf()[2:], b.conf())
+    assert np.abs(a.greens(False)[2:] - b.greens(False)).max() < 1e-12
+    a.close(); b.close()
+
+
+def test_attractive_only_entry_points_are_refused():
+    mc, _ = _pair(4, 2.0, 1.0, 0.1, 5, 1)
+    with pytest.raises(NotImplementedError):
+        mc.greens_unequal(0, 1)
+    with pytest.raises(NotImplementedError):
+        mc.update(1, measure_every=1)
+    mc.close()
+
+
+def test_small_lattices_are_refused():
+    with pytest.raises(mcb.McbError):
+        mcb.DQMC(mcb.HubbardModelRepulsive(L=2, U=1.0), n_chains=1, beta=1.0, safe_mult=5)
