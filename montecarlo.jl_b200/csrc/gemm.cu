@@ -1,5 +1,6 @@
-// Batched FP64 DMMA GEMM, square tile T x T x 16 with T in {48, 64, 80} chosen so that it divides the
-// matrix size (12x12 lattice -> 48, 8x8 -> 64, 20x20 -> 80; no padded tiles), 4 warps (2x2) of
+// Batched FP64 DMMA GEMM, square tile T x T x BK with T in {48, 64, 80} chosen so that it divides the
+// matrix size (12x12 lattice -> 48, 8x8 -> 64, 20x20 -> 80; no padded tiles; BK = 16, or 8 for T = 80 so that
+// three CTAs fit the register file of an SM: 253 -> 200 us per batched 400^3 product), 4 warps (2x2) of
 // T/2 x T/2, register-staged double buffering (global loads of tile k+1 are in flight while tile k
 // is multiplied).
 #include "gemm.cuh"
@@ -8,12 +9,14 @@ namespace mcb {
 
 namespace {
 
-constexpr int BK = 16;
 constexpr int THREADS = 128;
-constexpr int LDK = BK + 4;  // [x][k] layout
 
 template <int T>
 struct Tile {
+    // K depth of a shared-memory tile: 8 for the 80-wide tile (its 100 accumulator registers leave room for
+    // 3 CTAs per SM only with half the staging registers), 16 otherwise
+    static constexpr int BK = T >= 80 ? 8 : 16;
+    static constexpr int LDK = BK + 4;  // [x][k] layout
     static constexpr int LDX = T + 4;  // [k][x] layout: conflict-free fragment reads need ld % 16 == 4
     static constexpr int PER_THREAD = T * BK / THREADS;
     static constexpr int SMEM_TILE = (T * LDK > BK * LDX) ? T * LDK : BK * LDX;
@@ -26,7 +29,7 @@ template <int T, bool XC>
 __device__ __forceinline__ void load_tile(double (&r)[Tile<T>::PER_THREAD], const double* __restrict__ P, int n,
                                           int x0, int k0, int tid)
 {
-    constexpr int BM = T;
+    constexpr int BM = T, BK = Tile<T>::BK;
 #pragma unroll
     for (int e = 0; e < Tile<T>::PER_THREAD; ++e) {
         const int idx = tid + e * THREADS;
@@ -44,7 +47,7 @@ template <int T, bool XC, bool SCALE>
 __device__ __forceinline__ void store_tile(const double (&r)[Tile<T>::PER_THREAD], double* S, int tid,
                                            const Scale& mid, int chain, int k0, int n)
 {
-    constexpr int BM = T, LDX = Tile<T>::LDX;
+    constexpr int BM = T, LDX = Tile<T>::LDX, BK = Tile<T>::BK, LDK = Tile<T>::LDK;
 #pragma unroll
     for (int e = 0; e < Tile<T>::PER_THREAD; ++e) {
         const int idx = tid + e * THREADS;
@@ -60,13 +63,13 @@ __device__ __forceinline__ void store_tile(const double (&r)[Tile<T>::PER_THREAD
 template <int T, bool XC>
 __device__ __forceinline__ double frag(const double* S, int x, int k)
 {
-    return XC ? S[k * Tile<T>::LDX + x] : S[x * LDK + k];
+    return XC ? S[k * Tile<T>::LDX + x] : S[x * Tile<T>::LDK + k];
 }
 
 template <int T, bool TA, bool TB>
 __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
 {
-    constexpr int BM = T, BN = T, WT = Tile<T>::WT, PER_THREAD = Tile<T>::PER_THREAD;
+    constexpr int BM = T, BN = T, WT = Tile<T>::WT, PER_THREAD = Tile<T>::PER_THREAD, BK = Tile<T>::BK;
     extern __shared__ __align__(16) double gemm_smem[];
     double (*As)[Tile<T>::SMEM_TILE] = reinterpret_cast<double (*)[Tile<T>::SMEM_TILE]>(gemm_smem);
     double (*Bs)[Tile<T>::SMEM_TILE] = As + 2;
