@@ -55,6 +55,8 @@ DelayedGeom delayed_geom(int n)
     const size_t hdr = (size_t)(2 * n + 16) * sizeof(double) + 2 * (size_t)round_up(n, 8);
     int K = (int)((SMEM_LIMIT - 2048 - hdr) / (2 * (size_t)g.ld * sizeof(double)));
     K = K / 4 * 4;
+    static const int kcap = getenv("MCB_SWEEP_K") ? atoi(getenv("MCB_SWEEP_K")) : 32;
+    if (K > kcap) K = kcap;
     if (K > 32) K = 32;
     if (K > round_up(n, 4)) K = round_up(n, 4);
     g.K = K;
