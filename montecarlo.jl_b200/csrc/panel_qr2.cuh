@@ -57,10 +57,15 @@ __device__ __forceinline__ void r2s2(const double (&A)[Geo2<N>::MT][CW][2], doub
 //    search compares (hi, lo, key) words on the integer pipe and reduces over the warp with REDUX;
 //  * the pivot column stays untouched in registers; -nu and 1/(x_j + nu) are kept per step
 //    (qs.D / qs.Dinv, overwritten by make_d later) and applied once after the last step.
-template <int N, int CW = 2>
-__device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSmem<N>& qs, const Lane2& t)
+// EARLY (large N, F != nullptr): a pivot column is scaled the moment it is eliminated and every block of 8 rows goes
+// to the shared-memory matrix F as soon as its 8 steps are over, so that its registers are free for the rest of
+// the factorisation (at N = 144 the 144 matrix registers per thread do not fit next to the working set).
+template <int N, int CW = 2, bool EARLY = false>
+__device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSmem<N>& qs, const Lane2& t,
+                                          double* F = nullptr)
 {
     constexpr int MT = Geo2<N, CW>::MT, NW = Geo2<N, CW>::NW, NT = Geo2<N, CW>::NT, KC = 2 * CW;
+    constexpr int LDF = Geo2<N, CW>::LD;
     int curpos[KC];
     bool done[KC];
     double nrm[KC];
@@ -135,9 +140,13 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSme
             const int pj = gkey & 0xffff, jm = gkey >> 16;
             const double* x = qs.cand[buf][pj / (8 * CW)];
             const double xlow = t.r > rj ? x[8 * mj + t.r] : 0.0;
-            double xm[MT];
+            // (large N: the vector is read again in the update loop instead of being held in MT registers)
+            constexpr bool RELOAD = N > 64;
+            double xm[RELOAD ? 1 : MT];
+            if (!RELOAD) {
 #pragma unroll
-            for (int m = mj + 1; m < MT; ++m) xm[m] = x[8 * m + t.r];
+                for (int m = mj + 1; m < MT; ++m) xm[m] = x[8 * m + t.r];
+            }
             const double xj = x[j];
             const bool live = maxval > 0.0;
             const double rs = live ? fast_rsqrt(maxval) : 0.0;
@@ -151,12 +160,15 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSme
 #pragma unroll
             for (int k = 0; k < KC; ++k) dot[k] = xd * A[mj][k >> 1][k & 1];
 #pragma unroll
-            for (int m = mj + 1; m < MT; ++m)
+            for (int m = mj + 1; m < MT; ++m) {
+                const double xv = RELOAD ? x[8 * m + t.r] : xm[RELOAD ? 0 : m];
 #pragma unroll
-                for (int k = 0; k < KC; ++k) dot[k] += xm[m] * A[m][k >> 1][k & 1];
+                for (int k = 0; k < KC; ++k) dot[k] += xv * A[m][k >> 1][k & 1];
+            }
 #pragma unroll
             for (int k = 0; k < KC; ++k) dot[k] = col_sum(dot[k]);
             // ---- reflectorApply! (UDT.jl:32-50) + fresh trailing norms
+            if (RELOAD) asm volatile("" ::: "memory");
             double s[KC], nn[KC];
 #pragma unroll
             for (int k = 0; k < KC; ++k) {
@@ -166,12 +178,14 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSme
                 nn[k] = t.r > rj ? A[mj][k >> 1][k & 1] * A[mj][k >> 1][k & 1] : 0.0;
             }
 #pragma unroll
-            for (int m = mj + 1; m < MT; ++m)
+            for (int m = mj + 1; m < MT; ++m) {
+                const double xv = RELOAD ? x[8 * m + t.r] : xm[RELOAD ? 0 : m];
 #pragma unroll
                 for (int k = 0; k < KC; ++k) {
-                    A[m][k >> 1][k & 1] -= s[k] * xm[m];
+                    A[m][k >> 1][k & 1] -= s[k] * xv;
                     nn[k] += A[m][k >> 1][k & 1] * A[m][k >> 1][k & 1];
                 }
+            }
 #pragma unroll
             for (int k = 0; k < KC; ++k) nrm[k] = col_sum(nn[k]);
 #pragma unroll
@@ -185,9 +199,25 @@ __device__ __forceinline__ void qr_pivot2(double (&A)[Geo2<N>::MT][CW][2], QrSme
                 qs.tau[j] = tj; qs.piv[j] = pj; qs.pos[pj] = j;
                 qs.D[j] = -nu; qs.Dinv[j] = inv;
             }
+            if (EARLY && pj / (8 * CW) == t.w) {   // my warp owns the pivot column: -nu on row j, vector below
+#pragma unroll
+                for (int k = 0; k < KC; ++k) {
+                    const bool is_piv = (t.col0 + 8 * (k >> 1) + (k & 1) == pj);
+                    const double a = A[mj][k >> 1][k & 1];
+                    A[mj][k >> 1][k & 1] = !is_piv ? a : (t.r < rj ? a : (t.r == rj ? -nu : a * inv));
+#pragma unroll
+                    for (int m = mj + 1; m < MT; ++m) A[m][k >> 1][k & 1] *= is_piv ? inv : 1.0;
+                }
+            }
+        }
+        if (EARLY) {   // rows 8 mj .. 8 mj + 7 are final
+#pragma unroll
+            for (int k = 0; k < KC; ++k)
+                F[(8 * mj + t.r) + (size_t)(t.col0 + 8 * (k >> 1) + (k & 1)) * LDF] = A[mj][k >> 1][k & 1];
         }
     }
     bar2(NT);
+    if (EARLY) return;
     // every column keeps R above its position, -nu on it and the Householder vector below
 #pragma unroll
     for (int k = 0; k < KC; ++k) {

@@ -161,8 +161,14 @@ udt2_kernel(UdtFused a)
                 for (int k = 0; k < KC; ++k) A[m][k >> 1][k & 1] *= r;
             }
         }
-        qr_pivot2<N, CW>(A, sm.qs, t);
-        r2s2<N, CW>(A, sm.F, t);
+        if (N > 64) {
+            // (the product prologue staged PB in F: everybody is done with it before the first rows arrive)
+            if (!a.X) __syncthreads();
+            qr_pivot2<N, CW, true>(A, sm.qs, t, sm.F);
+        } else {
+            qr_pivot2<N, CW>(A, sm.qs, t);
+            r2s2<N, CW>(A, sm.F, t);
+        }
     }
     __syncthreads();
     for (int i = tid; i < N; i += NT) {
