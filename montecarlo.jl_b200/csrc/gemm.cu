@@ -4,6 +4,7 @@
 // T/2 x T/2, register-staged double buffering (global loads of tile k+1 are in flight while tile k
 // is multiplied).
 #include "gemm.cuh"
+#include <stdlib.h>
 
 namespace mcb {
 
@@ -151,6 +152,149 @@ __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// One CTA per chain, the whole NN x NN product in the registers of 12 warps (6 x 2 warps of 24 x 72,
+// 3 x 9 DMMA tiles each): for 128 chains of N = 144 (config C) the tiled kernel above spends half its time in
+// the prologue / epilogue of 1152 short-lived CTAs; here every SM streams one matrix product from start to end.
+// K depth 8 per shared-memory stage, register-staged double buffering as above.
+template <int NN>
+struct Full {
+    static constexpr int THREADS = 384, BK = 8;
+    static constexpr int WM = NN / 6, WN = NN / 2;       // warp tile
+    static constexpr int IT = WM / 8, JT = WN / 8;       // DMMA tiles per warp
+    static constexpr int LDX = NN + 4, LDK = BK + 4;     // [k][x] and [x][k] layouts (conflict-free fragment reads)
+    static constexpr int PER_THREAD = NN * BK / THREADS;
+    static constexpr int SMEM_TILE = (NN * LDK > BK * LDX) ? NN * LDK : BK * LDX;
+    static_assert(NN % 48 == 0 && (NN * BK) % THREADS == 0 && LDX % 16 == 4, "unsupported size");
+};
+
+template <int NN, bool XC>
+__device__ __forceinline__ void full_load(double (&r)[Full<NN>::PER_THREAD], const double* __restrict__ P, int k0, int tid)
+{
+    constexpr int BK = Full<NN>::BK;
+#pragma unroll
+    for (int e = 0; e < Full<NN>::PER_THREAD; ++e) {
+        const int idx = tid + e * Full<NN>::THREADS;
+        int x, k;
+        if (XC) { x = idx % NN; k = idx / NN; }
+        else { k = idx % BK; x = idx / BK; }
+        r[e] = XC ? P[(size_t)x + (size_t)(k0 + k) * NN] : P[(size_t)(k0 + k) + (size_t)x * NN];
+    }
+}
+
+template <int NN, bool XC, bool SCALE>
+__device__ __forceinline__ void full_store(const double (&r)[Full<NN>::PER_THREAD], double* S, int tid, const Scale& mid,
+                                           int chain, int k0)
+{
+    constexpr int BK = Full<NN>::BK;
+#pragma unroll
+    for (int e = 0; e < Full<NN>::PER_THREAD; ++e) {
+        const int idx = tid + e * Full<NN>::THREADS;
+        int x, k;
+        if (XC) { x = idx % NN; k = idx / NN; }
+        else { k = idx % BK; x = idx / BK; }
+        double v = r[e];
+        if (SCALE) v *= mid.at(chain, k0 + k);
+        if (XC) S[k * Full<NN>::LDX + x] = v; else S[x * Full<NN>::LDK + k] = v;
+    }
+}
+
+template <int NN, bool TA, bool TB>
+__global__ void __launch_bounds__(Full<NN>::THREADS, 1) gemm_full_kernel(GemmArgs g)
+{
+    using F = Full<NN>;
+    constexpr int BK = F::BK, IT = F::IT, JT = F::JT;
+    extern __shared__ __align__(16) double gemm_smem[];
+    double (*As)[F::SMEM_TILE] = reinterpret_cast<double (*)[F::SMEM_TILE]>(gemm_smem);
+    double (*Bs)[F::SMEM_TILE] = As + 2;
+    const int chain = blockIdx.x;
+    const double* A = g.A + (size_t)chain * g.strideA;
+    const double* B = g.B + (size_t)chain * g.strideB;
+    double* C = g.C + (size_t)chain * g.strideC;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = (warp % 6) * F::WM, wn = (warp / 6) * F::WN;
+    const int r = lane >> 2, q = lane & 3;
+    const bool has_mid = g.mid.active();
+
+    double acc[IT][JT][2];
+#pragma unroll
+    for (int i = 0; i < IT; ++i)
+#pragma unroll
+        for (int j = 0; j < JT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    double ra[F::PER_THREAD], rb[F::PER_THREAD];
+    constexpr int nk = NN / BK;
+    full_load<NN, !TA>(ra, A, 0, tid);
+    full_load<NN, TB>(rb, B, 0, tid);
+    if (has_mid) full_store<NN, !TA, true>(ra, As[0], tid, g.mid, chain, 0);
+    else full_store<NN, !TA, false>(ra, As[0], tid, g.mid, chain, 0);
+    full_store<NN, TB, false>(rb, Bs[0], tid, g.mid, chain, 0);
+    __syncthreads();
+    for (int kt = 0; kt < nk; ++kt) {
+        const int cur = kt & 1;
+        if (kt + 1 < nk) {
+            full_load<NN, !TA>(ra, A, (kt + 1) * BK, tid);
+            full_load<NN, TB>(rb, B, (kt + 1) * BK, tid);
+        }
+        const double* as = As[cur];
+        const double* bs = Bs[cur];
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 4) {
+            double a[IT], b[JT];
+#pragma unroll
+            for (int i = 0; i < IT; ++i) {
+                const int x = wm + i * 8 + r, k = kk + q;
+                a[i] = !TA ? as[k * F::LDX + x] : as[x * F::LDK + k];
+            }
+#pragma unroll
+            for (int j = 0; j < JT; ++j) {
+                const int x = wn + j * 8 + r, k = kk + q;
+                b[j] = TB ? bs[k * F::LDX + x] : bs[x * F::LDK + k];
+            }
+#pragma unroll
+            for (int i = 0; i < IT; ++i)
+#pragma unroll
+                for (int j = 0; j < JT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        if (kt + 1 < nk) {
+            const int nxt = cur ^ 1;
+            if (has_mid) full_store<NN, !TA, true>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK);
+            else full_store<NN, !TA, false>(ra, As[nxt], tid, g.mid, chain, (kt + 1) * BK);
+            full_store<NN, TB, false>(rb, Bs[nxt], tid, g.mid, chain, (kt + 1) * BK);
+        }
+        __syncthreads();
+    }
+    const bool has_row = g.row.active(), has_col = g.col.active();
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+        const int gm = wm + i * 8 + r;
+        const double rs = has_row ? g.row.at(chain, gm) : 1.0;
+#pragma unroll
+        for (int j = 0; j < JT; ++j)
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int gn = wn + j * 8 + 2 * q + c;
+                double v = acc[i][j][c];
+                if (has_row) v *= rs;
+                if (has_col) v *= g.col.at(chain, gn);
+                if (g.add && gm == gn) v += g.add[(size_t)chain * g.stride_add + gm];
+                C[(size_t)gm + (size_t)gn * NN] = v;
+            }
+    }
+}
+
+template <int NN>
+int launch_gemm_full(const GemmArgs& g, cudaStream_t st)
+{
+    constexpr size_t smem = 4 * Full<NN>::SMEM_TILE * sizeof(double);
+    if (!g.transA && !g.transB) gemm_full_kernel<NN, false, false><<<g.batch, Full<NN>::THREADS, smem, st>>>(g);
+    else if (!g.transA && g.transB) gemm_full_kernel<NN, false, true><<<g.batch, Full<NN>::THREADS, smem, st>>>(g);
+    else if (g.transA && !g.transB) gemm_full_kernel<NN, true, false><<<g.batch, Full<NN>::THREADS, smem, st>>>(g);
+    else gemm_full_kernel<NN, true, true><<<g.batch, Full<NN>::THREADS, smem, st>>>(g);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 template <int T>
 int launch_gemm_t(const GemmArgs& g, cudaStream_t st)
 {
@@ -178,8 +322,20 @@ int set_gemm_attrs()
 
 } // namespace
 
+static int g_sms = 148;
+
 int init_gemm_kernels()
 {
+    {
+        int dev = 0;
+        MCB_CUDA(cudaGetDevice(&dev));
+        MCB_CUDA(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
+        constexpr int smem = 4 * Full<144>::SMEM_TILE * (int)sizeof(double);
+        MCB_CUDA(cudaFuncSetAttribute(gemm_full_kernel<144, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MCB_CUDA(cudaFuncSetAttribute(gemm_full_kernel<144, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MCB_CUDA(cudaFuncSetAttribute(gemm_full_kernel<144, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MCB_CUDA(cudaFuncSetAttribute(gemm_full_kernel<144, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    }
     if (set_gemm_attrs<48>() || set_gemm_attrs<64>() || set_gemm_attrs<80>()) return -2;
     return 0;
 }
@@ -189,6 +345,9 @@ int launch_gemm(const GemmArgs& g, cudaStream_t st)
     if (g.n <= 0 || g.batch <= 0) return 0;
     if (g.C == g.A || g.C == g.B) { set_error("gemm: output aliases an input"); return -1; }
     LaunchScope scope(LC_GEMM, st, 2.0 * g.n * (double)g.n * g.n * g.batch);
+    // a batch that fills the device with one CTA per matrix: the whole product stays in one CTA's registers
+    static const int full_on = getenv("MCB_GEMM_FULL") ? atoi(getenv("MCB_GEMM_FULL")) : 1;
+    if (g.n == 144 && full_on && g.batch >= g_sms / 2) return launch_gemm_full<144>(g, st);
     // the tile that wastes the least padded work
     auto padded = [&](int t) { const int k = (g.n + t - 1) / t * t; return (long long)k * k; };
     int best = 64;

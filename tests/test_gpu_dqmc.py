@@ -43,6 +43,20 @@ def test_vmul_modes(n):
             assert relerr(_uncm(out, b, n)[k], orc.vmul(A[k], B[k], mode)) < 1e-13
 
 
+def test_vmul_whole_matrix_kernel_n144():
+    """Batches that fill the device at N = 144 take the one-CTA-per-matrix GEMM (gemm_full_kernel): all transpose
+    modes against numpy and the oracle's loop nests."""
+    n, b = 144, 96
+    rng = np.random.default_rng(5)
+    A, B = rng.standard_normal((b, n, n)), rng.standard_normal((b, n, n))
+    L = _lib.lib()
+    for mode, want in ((0, A @ B), (1, A @ B.transpose(0, 2, 1)), (2, A.transpose(0, 2, 1) @ B)):
+        out = np.empty(b * n * n)
+        _lib.check(L.mcb_linalg_vmul(n, b, _cm(A), _cm(B), out, mode, 0))
+        assert relerr(_uncm(out, b, n), want) < 1e-13
+        assert relerr(_uncm(out, b, n)[7], orc.vmul(A[7], B[7], mode)) < 1e-13
+
+
 @pytest.fixture
 def linalg_path(request):
     """general=True forces the any-N kernels where a chain-resident kernel exists (N = 16, 32, 64)."""
