@@ -206,6 +206,13 @@ int mcb_dqmc_rep_get_greens(mcb_dqmc_rep* h, double* G, int32_t physical);
 int mcb_dqmc_rep_calculate_greens_at(mcb_dqmc_rep* h, int32_t slice, double* G);
 int mcb_dqmc_rep_get_state(mcb_dqmc_rep* h, mcb_dqmc_state* st);
 int mcb_dqmc_rep_get_stats(mcb_dqmc_rep* h, mcb_dqmc_chain_stats* out);
+/* greens(mc, k, l), the recorded-configuration wire format and resume!(mc) for the two-block handle: as the
+ * mcb_dqmc_* functions of the same names (the spin-down stack sees the complemented bits) */
+int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
+int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* h);
+int mcb_dqmc_rep_get_conf_bits(mcb_dqmc_rep* h, uint64_t* chunks);
+int mcb_dqmc_rep_set_conf_bits(mcb_dqmc_rep* h, const uint64_t* chunks);
+int mcb_dqmc_rep_resume(mcb_dqmc_rep* h, int64_t last_sweep);
 double mcb_dqmc_rep_last_elapsed_ms(mcb_dqmc_rep* h);
 
 /* ----------------------------------------------------------------- Ising ---- */

@@ -85,6 +85,11 @@ SIGNATURES = {
     "mcb_dqmc_rep_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
     "mcb_dqmc_rep_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
     "mcb_dqmc_rep_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
+    "mcb_dqmc_rep_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
+    "mcb_dqmc_rep_conf_chunks": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_rep_get_conf_bits": (C.c_int, [C.c_void_p, _u64]),
+    "mcb_dqmc_rep_set_conf_bits": (C.c_int, [C.c_void_p, _u64]),
+    "mcb_dqmc_rep_resume": (C.c_int, [C.c_void_p, C.c_int64]),
     "mcb_dqmc_rep_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_launch_count": (C.c_int64, [C.c_void_p]),

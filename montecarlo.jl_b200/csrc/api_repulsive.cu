@@ -213,6 +213,60 @@ int mcb_dqmc_rep_get_stats(mcb_dqmc_rep* r, mcb_dqmc_chain_stats* out)
     return MCB_OK;
 }
 
+// greens(mc, k, l) = G(k <- l) of both blocks (unequal_time_stack.jl:275-305 on BlockDiagonal matrices)
+int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* r, int32_t slice1, int32_t slice2, double* G, int32_t physical)
+{
+    REQUIRE(r && G, "null argument");
+    mcb_dqmc* hs[2] = {r->up, r->dn};
+    const size_t nn = r->up->nn;
+    REQUIRE(slice1 >= 0 && slice1 <= r->up->M && slice2 >= 0 && slice2 <= r->up->M, "bad slice");
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    for (int f = 0; f < 2; ++f) {
+        mcb_dqmc* h = hs[f];
+        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+        API_TRY(engine_greens_unequal(h, slice1, slice2));
+        const double* src = unequal_result(h);
+        if (physical) { // _greens! (DQMC.jl:721-730): e^{+dtau T/2} G e^{-dtau T/2}
+            API_TRY(launch_gemm(base_gemm(h, src, false, h->hop[0], true, h->W[0]), h->st));
+            API_TRY(launch_gemm(base_gemm(h, h->hop[1], true, h->W[0], false, h->W[1]), h->st));
+            src = h->W[1];
+        }
+        MCB_CUDA(cudaMemcpy2DAsync(G + f * nn, 2 * nn * sizeof(double), src, nn * sizeof(double), nn * sizeof(double),
+                                   h->C, cudaMemcpyDeviceToHost, h->st));
+    }
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+// compress / decompress (HubbardModel.jl:56-59): the field travels as BitArray(conf .== 1); the spin-down stack
+// lives on the negated field, i.e. on the complemented bits
+int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* r) { return r ? mcb_dqmc_conf_chunks(r->up) : 0; }
+
+int mcb_dqmc_rep_get_conf_bits(mcb_dqmc_rep* r, uint64_t* chunks)
+{
+    REQUIRE(r && chunks, "null argument");
+    return mcb_dqmc_get_conf_bits(r->up, chunks);
+}
+
+int mcb_dqmc_rep_set_conf_bits(mcb_dqmc_rep* r, const uint64_t* chunks)
+{
+    REQUIRE(r && chunks, "null argument");
+    const size_t n = (size_t)r->up->C * mcb_dqmc_conf_chunks(r->up);
+    std::vector<uint64_t> inv(n);
+    for (size_t e = 0; e < n; ++e) inv[e] = ~chunks[e];
+    API_TRY(mcb_dqmc_set_conf_bits(r->up, chunks));
+    return mcb_dqmc_set_conf_bits(r->dn, inv.data());
+}
+
+// resume!(mc) (DQMC.jl:517-521): rebuild both stacks on the uploaded field, continue the counters
+int mcb_dqmc_rep_resume(mcb_dqmc_rep* r, int64_t last_sweep)
+{
+    REQUIRE(r && last_sweep >= 0, "bad argument");
+    API_TRY(mcb_dqmc_resume(r->up, last_sweep));
+    return mcb_dqmc_resume(r->dn, last_sweep);
+}
+
 double mcb_dqmc_rep_last_elapsed_ms(mcb_dqmc_rep* r) { return r ? r->up->last_ms : 0.0; }
 
 } // extern "C"

@@ -51,8 +51,8 @@ class DQMC:
 
     With a HubbardModelRepulsive the Green's functions have shape (n_chains, 2, N, N): the spin-up and spin-down
     diagonal blocks of the reference's BlockDiagonal mc.s.greens. That model runs the sweep (build_stack, update,
-    sweep, greens, greens_at, conf, state, stats); measurements, unequal-time G, replay and checkpoints are the
-    attractive model's.
+    sweep, greens, greens_at, greens_unequal, conf, conf_bits, checkpoint / resume, state, stats); the built-in
+    measurements and replay are the attractive model's.
     """
 
     def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, general_path=False,
@@ -125,14 +125,14 @@ class DQMC:
     # -- recorded configurations (ConfigRecorder wire format) ------------------------------------
     def conf_bits(self):
         """compress(mc, model, conf) for every chain: (C, ceil(N*M/64)) uint64, bit b = spin i + N*l."""
-        buf = np.empty(self.n_chains * self._f("conf_chunks", True)(self.h), dtype=np.uint64)
-        _lib.check(self._f("get_conf_bits", True)(self.h, buf))
+        buf = np.empty(self.n_chains * self._f("conf_chunks")(self.h), dtype=np.uint64)
+        _lib.check(self._f("get_conf_bits")(self.h, buf))
         return buf.reshape(self.n_chains, -1)
 
     def set_conf_bits(self, bits):
         bits = np.ascontiguousarray(bits, dtype=np.uint64)
-        assert bits.shape == (self.n_chains, self._f("conf_chunks", True)(self.h))
-        _lib.check(self._f("set_conf_bits", True)(self.h, bits.reshape(-1)))
+        assert bits.shape == (self.n_chains, self._f("conf_chunks")(self.h))
+        _lib.check(self._f("set_conf_bits")(self.h, bits.reshape(-1)))
 
     def replay(self, configurations):
         """The measurement loop of replay!(mc, configurations) (DQMC.jl:649-660): for every recorded configuration
@@ -172,7 +172,7 @@ class DQMC:
         if (ckpt["seed"], ckpt["chain_offset"], ckpt["n_chains"]) != (self.seed, self.chain_offset, self.n_chains):
             raise ValueError("checkpoint belongs to different chains")
         self.set_conf_bits(ckpt["conf_bits"])
-        _lib.check(self._f("resume", True)(self.h, int(ckpt["last_sweep"])))
+        _lib.check(self._f("resume")(self.h, int(ckpt["last_sweep"])))
         self.last_sweep = int(ckpt["last_sweep"])
 
     def build_stack(self):
@@ -205,8 +205,8 @@ class DQMC:
     def greens_unequal(self, slice1, slice2, physical=True):
         """greens(mc, k, l) = G(k <- l), 0 <= k, l <= M (unequal_time_stack.jl:275-305); physical=False returns the
         effective G of calculate_greens(mc, k, l). Leaves the sweep state untouched. Shape (C, N, N)."""
-        buf = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self._f("greens_unequal", True)(self.h, slice1, slice2, buf, int(physical)))
+        buf = np.empty(self.n_chains * self.model.flv * self.N * self.N)
+        _lib.check(self._f("greens_unequal")(self.h, slice1, slice2, buf, int(physical)))
         return self._unbatch(buf)
 
     def state(self):
