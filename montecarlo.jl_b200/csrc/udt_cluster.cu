@@ -101,6 +101,29 @@ __device__ __forceinline__ void update_block(int r, int lane, int n, int j, cons
     default: CALL(6);                         \
     }
 
+// sums over the warp of K per-lane values, result in every lane. Two values share one butterfly: after the first
+// exchange the lower half-warp carries the first sum and the upper half the second (7 instead of 10 shuffles;
+// the shuffle / shared-memory pipe is what bounds this kernel).
+template <int K>
+__device__ __forceinline__ void warp_sums(double (&a)[K], int lane)
+{
+    if (K == 2) {
+        const unsigned F = 0xffffffffu;
+        const bool hi = lane & 16;
+        double k = hi ? a[K - 1] : a[0];
+        k += __shfl_xor_sync(F, hi ? a[0] : a[K - 1], 16);
+        k += __shfl_xor_sync(F, k, 8);
+        k += __shfl_xor_sync(F, k, 4);
+        k += __shfl_xor_sync(F, k, 2);
+        k += __shfl_xor_sync(F, k, 1);
+        a[0] = __shfl_sync(F, k, 0);
+        a[K - 1] = __shfl_sync(F, k, 16);
+    } else {
+#pragma unroll
+        for (int i = 0; i < K; ++i) a[i] = warp_sum(a[i]);
+    }
+}
+
 template <int K>
 __device__ __forceinline__ void apply_reflector(double* const (&col)[K], const int (&cidx)[K], const double* vb,
                                                 int j, int n, double tj, double rinv, int lane, int cl,
@@ -115,10 +138,14 @@ __device__ __forceinline__ void apply_reflector(double* const (&col)[K], const i
     MCB_BLOCKS_FROM(rb0, MCB_DOT)
     }
 #undef MCB_DOT
+    double dsum[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) dsum[k] = dot[k] + dot[K + k];
+    warp_sums<K>(dsum, lane);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         // vb holds the RAW pivot column: v = rinv * vb, so v.c = rinv * (vb.c) and c -= v w = vb (rinv w)
-        const double d = warp_sum(dot[k] + dot[K + k]);
+        const double d = dsum[k];
         wj[k] = tj * fma(rinv, d, col[k][j]);
         w[k] = rinv * wj[k];
         nrm[k] = 0.0;
@@ -134,11 +161,9 @@ __device__ __forceinline__ void apply_reflector(double* const (&col)[K], const i
         for (int k = 0; k < K; ++k) col[k][j] -= wj[k];
     }
     double xr[K];
+    warp_sums<K>(nrm, lane);
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-        nrm[k] = warp_sum(nrm[k]);
-        xr[k] = col[k][j + 1];
-    }
+    for (int k = 0; k < K; ++k) xr[k] = col[k][j + 1];
     if (lane < cl && !(exp & 16)) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
