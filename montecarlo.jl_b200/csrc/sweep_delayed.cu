@@ -11,7 +11,8 @@
 // because the current site still does), v stays frozen in Rc[j, :]. After the block the whole matrix is brought up to
 // date with ONE product G -= U * Rc (N x K x N) on the FP64 tensor pipe. The Metropolis decisions see
 // exactly the Green's function the immediate updates would give (the arithmetic is re-associated only).
-// One barrier per site: the next site's G_ii is published by the thread that owns its row.
+// One barrier per site: the next site's G_ii is published by the thread that owns its row. (For N > 256 the sites
+// of a block are decided on its diagonal block first and the vectors follow from recurrences, see decide_block.)
 //
 // Small batches of large matrices (config D: 32 chains, N = 400) leave most SMs idle with one CTA per chain,
 // and the flush is 2/3 of the kernel. There a thread-block CLUSTER of `cls` CTAs serves one chain: every CTA
@@ -35,6 +36,7 @@ namespace mcb {
 namespace {
 
 constexpr int SMEM_LIMIT = 227 * 1024;
+constexpr size_t TABLE_BYTES = (32 * 33 + 32) * sizeof(double) + 16;   // DD, xs of the block-wise decisions
 
 struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
@@ -53,7 +55,7 @@ DelayedGeom delayed_geom(int n)
     g.np = round_up(n, 8);
     g.ld = g.np + ((20 - g.np % 16) % 16 == 0 ? 16 : (20 - g.np % 16) % 16); // ld % 16 == 4, ld > np
     const size_t hdr = (size_t)(2 * n + 16) * sizeof(double) + 2 * (size_t)round_up(n, 8);
-    int K = (int)((SMEM_LIMIT - 2048 - hdr) / (2 * (size_t)g.ld * sizeof(double)));
+    int K = (int)((SMEM_LIMIT - 2048 - hdr - TABLE_BYTES) / (2 * (size_t)g.ld * sizeof(double)));
     K = K / 4 * 4;
     // block size: 24 measured best at N = 144 (196 against 204 us per slice with 32) and at N = 400 (1092 / 1124)
     static const int kcap = getenv("MCB_SWEEP_K") ? atoi(getenv("MCB_SWEEP_K")) : 24;
@@ -62,10 +64,109 @@ DelayedGeom delayed_geom(int n)
     if (K > round_up(n, 4)) K = round_up(n, 4);
     g.K = K;
     g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
-    g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double);
+    g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double) + TABLE_BYTES;
     static const int exp_flags = getenv("MCB_SWEEP_EXP") ? atoi(getenv("MCB_SWEEP_EXP")) : 0;
     g.exp = exp_flags;
     return g;
+}
+
+// ---- the sites of a block without a block-wide barrier per site (one spin sector) -------------------
+// The decisions of a block only need its K x K diagonal block D = G[i0.., i0..]. Four warps work on a copy DD in
+// shared memory (thread = row a, every fourth column) and walk through the sites - G_ii, Metropolis decision,
+// rank-1 update of the trailing part of DD, one named barrier of 128 threads - like a right-looking elimination:
+// after site j neither row j nor column j of DD is touched again, so at the end DD holds, for every site, the row
+// of D at the moment the site was visited (upper triangle) and its column (lower triangle, then scaled by x_j),
+// next to x_j itself (0 if rejected). The full vectors follow from two triangular recurrences that need no
+// decisions and no barriers, one element of a column / of a row per thread:
+//   u_j   = x_j (e_i - [Cc_j - sum_{j'<j} u_j' DD[j'][j]])                     (column role, u_j replaces Cc_j)
+//   row_j = Rc_j + sum_{j'<j} (x_j' DD[j][j']) row_j'                            (row role, frozen rows in Rc)
+// which is what the site-by-site updates of the columns j' > j and rows k > j add up to.
+constexpr int DLD = 33;        // row stride of DD (conflict-free column access)
+constexpr int DEC_THREADS = 128;
+
+__device__ __forceinline__ void dec_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc, int ld, int i0, int kb,
+                                            const int8_t* s_in, int8_t* s_out, const double* unif, double* DD,
+                                            double* xs, int tid)
+{
+    const int ra = tid & 31, cg0 = tid >> 5;   // my row, my first column; columns cg0, cg0 + 4, ...
+    double* myrow = DD + ra * DLD;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int b = cg0 + 4 * q;
+        myrow[b] = (ra < kb && b < kb) ? Cc[b * ld + i0 + ra] : 0.0;
+    }
+    dec_bar();
+    int nacc = 0;
+    for (int j = 0; j < kb; ++j) {
+        const int i = i0 + j;
+        const double* rowj = DD + j * DLD;
+        const double gii = rowj[j];
+        const int s = s_in[i];
+        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+        const double efac = s > 0 ? a.efac_p : a.efac_m;
+        const double rt = 1.0 + gamma * (1.0 - gii);
+        const double x = gamma * fast_rcp(rt);          // speculative: only used if accepted
+        const double p = efac * (rt * rt);
+        const bool accept = (p > 1.0 || unif[i] < p);    // uniform over the four warps
+        if (accept) {
+            if (ra > j && ra < kb) {
+                const double mu = x * myrow[j];           // -u of row ra: u = x (e_i - G[:, i])
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int b = cg0 + 4 * q;
+                    if (b > j && b < kb) myrow[b] = fma(mu, rowj[b], myrow[b]);
+                }
+            }
+            ++nacc;
+        }
+        if (tid == 0) { xs[j] = accept ? x : 0.0; s_out[i] = (int8_t)(accept ? -s : s); }
+        dec_bar();
+    }
+    // lower triangle: column j' of the block scaled by x_j' for the row recurrence
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int b = cg0 + 4 * q;
+        if (b < ra && ra < kb) myrow[b] *= xs[b];
+    }
+    return nacc;
+}
+
+__device__ __forceinline__ void column_recurrence(double* Cc, int ld, int i0, int kb, const double* DD, const double* xs, int e)
+{
+    for (int j = 0; j < kb; ++j) {
+        double c0 = Cc[j * ld + e], c1 = 0.0, c2 = 0.0, c3 = 0.0;
+        const double* dj = DD + j;
+        const double* up = Cc + e;
+        int jp = 0;
+        for (; jp + 4 <= j; jp += 4) {
+            c0 = fma(-up[jp * ld], dj[jp * DLD], c0);
+            c1 = fma(-up[(jp + 1) * ld], dj[(jp + 1) * DLD], c1);
+            c2 = fma(-up[(jp + 2) * ld], dj[(jp + 2) * DLD], c2);
+            c3 = fma(-up[(jp + 3) * ld], dj[(jp + 3) * DLD], c3);
+        }
+        for (; jp < j; ++jp) c0 = fma(-up[jp * ld], dj[jp * DLD], c0);
+        Cc[j * ld + e] = xs[j] * ((e == i0 + j ? 1.0 : 0.0) - ((c0 + c1) + (c2 + c3)));
+    }
+}
+
+__device__ __forceinline__ void row_recurrence(double* Rc, int ld, int kb, const double* DD, int e)
+{
+    for (int j = 0; j < kb; ++j) {
+        double r0 = Rc[j * ld + e], r1 = 0.0, r2 = 0.0, r3 = 0.0;
+        const double* dj = DD + j * DLD;
+        const double* rp = Rc + e;
+        int jp = 0;
+        for (; jp + 4 <= j; jp += 4) {
+            r0 = fma(dj[jp], rp[jp * ld], r0);
+            r1 = fma(dj[jp + 1], rp[(jp + 1) * ld], r1);
+            r2 = fma(dj[jp + 2], rp[(jp + 2) * ld], r2);
+            r3 = fma(dj[jp + 3], rp[(jp + 3) * ld], r3);
+        }
+        for (; jp < j; ++jp) r0 = fma(dj[jp], rp[jp * ld], r0);
+        Rc[j * ld + e] = (r0 + r1) + (r2 + r3);
+    }
 }
 
 template <int MAXT>
@@ -83,6 +184,8 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     double* U = Cc;                     // recorded u of site j replaces column j (zero if rejected)
     int8_t* s_in = (int8_t*)(Rc + (size_t)K * ld);
     int8_t* s_out = s_in + round_up(n, 8);
+    double* DD = reinterpret_cast<double*>(s_out + round_up(n, 8));   // [32][DLD] diagonal block of the decisions
+    double* xs = DD + 32 * DLD;                                        // [32] x_j, 0 for rejected sites
     const bool two = g.two != 0;
     const int fcls = two ? 1 : cls, frank = two ? 0 : crank;   // division of the flush / checks among the CTAs
     double* Gg = ((two && crank) ? a.G2 : a.G) + (size_t)chain * a.sG;
@@ -95,6 +198,10 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
     }
     int nacc = 0;
+    // block-wise decisions: measured faster where the per-site barrier spans 32 warps (N = 400: 953 against 1092 us per
+    // slice), slower with 16 warps (N = 144: 224 against 210 us: the recurrences run on 10 warps only); MCB_SWEEP_EXP
+    // bit 16 forces the site-by-site loop, bit 32 the block-wise scheme
+    const bool blockwise = !two && !(g.exp & 16) && (T > 512 || (g.exp & 32));
     const int nv = round_up(n, 32);                 // threads per group (whole warps)
     // groups of nv threads that share the per-site work; more groups shorten the loops but every
     // extra warp repeats the fixed per-site instructions, so two groups at most
@@ -124,83 +231,104 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             const double* gcol = Gg + (size_t)l * n + i0;
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
-        if (tid == 0) {
-            const double g0 = Gg[i0 + (size_t)i0 * n];
-            gnext[0] = g0;
-            if (two) gpeer_remote[0] = g0;
-        }
-        double u_prev = 0.0;   // u of the previous site, stored once nobody reads its column any more
-        for (int j = 0; j < ((g.exp & 2) ? 0 : kb); ++j) {
-            if (two) cluster.sync(); else __syncthreads();
-            if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
-            if (j > 0 && worker && grp == 0) U[(j - 1) * ld + e] = u_prev;
-            u_prev = 0.0;
-            const int i = i0 + j;
-            const double gii = gnext[j & 1];
-            const int s = s_in[i];
-            const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
-            const double efac = s > 0 ? a.efac_p : a.efac_m;
-            const double rt = 1.0 + gamma * (1.0 - gii);
-            double p = efac * (rt * rt);
-            if (two) { // the partner sits on the negated field
-                const double rp = 1.0 + (s > 0 ? a.gamma_m : a.gamma_p) * (1.0 - gpeer[j & 1]);
-                p = rt * rp;
-            }
-            const bool accept = (p > 1.0 || unif[i] < p); // uniform over the CTA
-            const double* cj = Cc + j * ld;
-            const double* vj = Rc + j * ld;
-            if (accept) {
-                const double x = gamma * fast_rcp(rt);
-                if (worker) {
-                    // columns j' > j of the block: element (row e, column j')
-                    const double u = x * ((e == i ? 1.0 : 0.0) - cj[e]);
-                    u_prev = u;
-                    const int first = j + 1 + grp;
-                    double* cp = Cc + first * ld + e;
-                    const double* vp = vj + i0 + first;
-                    if (grp == 0 && e == i + 1 && first < kb) {
-                        const double cnew = *cp - u * *vp;
-                        gnext[(j + 1) & 1] = cnew;
-                        if (two) gpeer_remote[(j + 1) & 1] = cnew;
+        if (blockwise) {
+            // ---- decisions on the diagonal block by four warps, then the vector recurrences
+            __syncthreads();
+            if (!(g.exp & 2)) {
+                if (tid < DEC_THREADS) nacc += decide_block(a, Cc, ld, i0, (g.exp & 8) ? 1 : kb, s_in, s_out, unif, DD, xs, tid);
+                __syncthreads();
+                if (g.exp & 4) {
+                } else if (2 * nv <= T) {
+                    if (tid < nv) { if (tid < n) column_recurrence(Cc, ld, i0, kb, DD, xs, tid); }
+                    else if (tid < 2 * nv) { if (tid - nv < n) row_recurrence(Rc, ld, kb, DD, tid - nv); }
+                } else {
+                    for (int ee = tid; ee < n; ee += T) {
+                        column_recurrence(Cc, ld, i0, kb, DD, xs, ee);
+                        row_recurrence(Rc, ld, kb, DD, ee);
                     }
-                    // (operands are fetched four iterations at a time: the compiler cannot prove that
-                    // the stores do not alias the next loads)
-                    const double xv = x * vj[e];
-                    double* rp = Rc + first * ld + e;
-                    const double* up = cj + i0 + first;
-                    for (int jp = first; jp < kb; jp += 4 * ngrp) {
-                        double c[4], v[4], rr[4], uu[4];
-#pragma unroll
-                        for (int z = 0; z < 4; ++z) {
-                            const bool ok = jp + z * ngrp < kb;
-                            c[z] = ok ? cp[z * gstep] : 0.0;
-                            v[z] = ok ? vp[z * ngrp] : 0.0;
-                            rr[z] = ok ? rp[z * gstep] : 0.0;
-                            uu[z] = ok ? up[z * ngrp] : 0.0;
+                }
+            }
+            __syncthreads();
+        } else {
+            // ---- site by site (two spin sectors: the partner's G_ii arrives through distributed shared memory)
+            if (tid == 0) {
+                const double g0 = Gg[i0 + (size_t)i0 * n];
+                gnext[0] = g0;
+                if (two) gpeer_remote[0] = g0;
+            }
+            double u_prev = 0.0;   // u of the previous site, stored once nobody reads its column any more
+            for (int j = 0; j < ((g.exp & 2) ? 0 : kb); ++j) {
+                if (two) cluster.sync(); else __syncthreads();
+                if (tid >= ngrp * nv) continue; // warps without per-site work only keep the barrier count
+                if (j > 0 && worker && grp == 0) U[(j - 1) * ld + e] = u_prev;
+                u_prev = 0.0;
+                const int i = i0 + j;
+                const double gii = gnext[j & 1];
+                const int s = s_in[i];
+                const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+                const double efac = s > 0 ? a.efac_p : a.efac_m;
+                const double rt = 1.0 + gamma * (1.0 - gii);
+                double p = efac * (rt * rt);
+                if (two) { // the partner sits on the negated field
+                    const double rp = 1.0 + (s > 0 ? a.gamma_m : a.gamma_p) * (1.0 - gpeer[j & 1]);
+                    p = rt * rp;
+                }
+                const bool accept = (p > 1.0 || unif[i] < p); // uniform over the CTA
+                const double* cj = Cc + j * ld;
+                const double* vj = Rc + j * ld;
+                if (accept) {
+                    const double x = gamma * fast_rcp(rt);
+                    if (worker) {
+                        // columns j' > j of the block: element (row e, column j')
+                        const double u = x * ((e == i ? 1.0 : 0.0) - cj[e]);
+                        u_prev = u;
+                        const int first = j + 1 + grp;
+                        double* cp = Cc + first * ld + e;
+                        const double* vp = vj + i0 + first;
+                        if (grp == 0 && e == i + 1 && first < kb) {
+                            const double cnew = *cp - u * *vp;
+                            gnext[(j + 1) & 1] = cnew;
+                            if (two) gpeer_remote[(j + 1) & 1] = cnew;
                         }
-#pragma unroll
-                        for (int z = 0; z < 4; ++z) {
-                            if (jp + z * ngrp < kb) {
-                                cp[z * gstep] = c[z] - u * v[z];    // columns j' > j: element (row e, column j')
-                                rp[z * gstep] = rr[z] + uu[z] * xv; // rows k > j: element (row k, column e), u_k = -x G[i0+k, i]
+                        // (operands are fetched four iterations at a time: the compiler cannot prove that
+                        // the stores do not alias the next loads)
+                        const double xv = x * vj[e];
+                        double* rp = Rc + first * ld + e;
+                        const double* up = cj + i0 + first;
+                        for (int jp = first; jp < kb; jp += 4 * ngrp) {
+                            double c[4], v[4], rr[4], uu[4];
+    #pragma unroll
+                            for (int z = 0; z < 4; ++z) {
+                                const bool ok = jp + z * ngrp < kb;
+                                c[z] = ok ? cp[z * gstep] : 0.0;
+                                v[z] = ok ? vp[z * ngrp] : 0.0;
+                                rr[z] = ok ? rp[z * gstep] : 0.0;
+                                uu[z] = ok ? up[z * ngrp] : 0.0;
                             }
+    #pragma unroll
+                            for (int z = 0; z < 4; ++z) {
+                                if (jp + z * ngrp < kb) {
+                                    cp[z * gstep] = c[z] - u * v[z];    // columns j' > j: element (row e, column j')
+                                    rp[z * gstep] = rr[z] + uu[z] * xv; // rows k > j: element (row k, column e), u_k = -x G[i0+k, i]
+                                }
+                            }
+                            cp += 4 * gstep; vp += 4 * ngrp; rp += 4 * gstep; up += 4 * ngrp;
                         }
-                        cp += 4 * gstep; vp += 4 * ngrp; rp += 4 * gstep; up += 4 * ngrp;
+                    }
+                    ++nacc;
+                } else if (j + 1 < kb) {
+                    if (tid == 0) {
+                        const double gn = Cc[(j + 1) * ld + i + 1];
+                        gnext[(j + 1) & 1] = gn;
+                        if (two) gpeer_remote[(j + 1) & 1] = gn;
                     }
                 }
-                ++nacc;
-            } else if (j + 1 < kb) {
-                if (tid == 0) {
-                    const double gn = Cc[(j + 1) * ld + i + 1];
-                    gnext[(j + 1) & 1] = gn;
-                    if (two) gpeer_remote[(j + 1) & 1] = gn;
-                }
+                if (tid == 0) s_out[i] = (int8_t)(accept ? -s : s);
             }
-            if (tid == 0) s_out[i] = (int8_t)(accept ? -s : s);
+            __syncthreads();
+            if (!(g.exp & 2) && worker && grp == 0) U[(kb - 1) * ld + e] = u_prev;
+            __syncthreads();
         }
-        __syncthreads();
-        if (!(g.exp & 2) && worker && grp == 0) U[(kb - 1) * ld + e] = u_prev;
-        __syncthreads();
         // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
         const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
         for (int tile = warp + nwarps * frank; tile < ((g.exp & 1) ? 0 : tm * tn); tile += nwarps * fcls) {

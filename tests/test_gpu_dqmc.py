@@ -355,6 +355,23 @@ def test_config_d_20x20_first_updates_match_oracle():
     mc.close()
 
 
+def test_blockwise_sweep_scheme_on_small_lattices():
+    """The block-wise decision scheme of the delayed sweep (decide_block + triangular recurrences, sweep_delayed.cu)
+    is the default only for N > 256 (config D test above). MCB_SWEEP_EXP=32 forces it for every size: the
+    every-update parity tests of the general path (4x4, 8x8 full sweep) and config C must hold with it too. The switch
+    is read once per process, hence the child process."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, MCB_SWEEP_EXP="32")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_dqmc.py"), "-m", "gpu", "-q",
+                        "-x", "-k", "(every_update and True) or (config_a and True) or config_c"],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout and "no tests ran" not in r.stdout
+
+
 # ------------------------------------------------------------------ unequal-time Green's functions (SURVEY §8f rank 2)
 UNEQUAL_PAIRS = [(0, 0), (3, 3), (7, 2), (6, 5), (10, 4), (2, 7), (4, 5), (0, 3), (5, 10)]
 
