@@ -169,7 +169,8 @@ __device__ __forceinline__ void row_recurrence(double* Rc, int ld, int kb, const
     }
 }
 
-template <int MAXT>
+// BW: block-wise decisions (one spin sector only); the site-by-site loop otherwise
+template <int MAXT, bool BW>
 __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, DelayedGeom g)
 {
     extern __shared__ __align__(16) double sm[];
@@ -198,10 +199,9 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
     }
     int nacc = 0;
-    // block-wise decisions: measured faster where the per-site barrier spans 32 warps (N = 400: 953 against 1092 us per
-    // slice), slower with 16 warps (N = 144: 224 against 210 us: the recurrences run on 10 warps only); MCB_SWEEP_EXP
-    // bit 16 forces the site-by-site loop, bit 32 the block-wise scheme
-    const bool blockwise = !two && !(g.exp & 16) && (T > 512 || (g.exp & 32));
+    // (the host picks BW: measured faster where the per-site barrier spans 32 warps - N = 400: 953 against 1092 us per
+    // slice -, slower with 16 warps - N = 144: 224 against 210 us, the recurrences run on 10 warps only)
+    constexpr bool blockwise = BW;
     const int nv = round_up(n, 32);                 // threads per group (whole warps)
     // groups of nv threads that share the per-site work; more groups shorten the loops but every
     // extra warp repeats the fixed per-site instructions, so two groups at most
@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             const double* gcol = Gg + (size_t)l * n + i0;
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
-        if (blockwise) {
+        if constexpr (blockwise) {
             // ---- decisions on the diagonal block by four warps, then the vector recurrences
             __syncthreads();
             if (!(g.exp & 2)) {
@@ -397,8 +397,10 @@ int init_sweep_delayed_kernels()
     int dev = 0;
     MCB_CUDA(cudaGetDevice(&dev));
     MCB_CUDA(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
-    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<512, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<1024, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    MCB_CUDA(cudaFuncSetAttribute(sweep_delayed_kernel<1024, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     return 0;
 }
 
@@ -432,8 +434,16 @@ int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
     at[0].val.clusterDim.x = cls; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    if (g.threads <= 512) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512>, a, g));
-    else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024>, a, g));
+    // block-wise decisions for one spin sector and N > 256; MCB_SWEEP_EXP bit 16 forces the site-by-site loop,
+    // bit 32 the block-wise scheme for every size
+    const bool bw = !g.two && !(g.exp & 16) && (g.threads > 512 || (g.exp & 32));
+    if (g.threads <= 512) {
+        if (bw) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512, true>, a, g));
+        else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512, false>, a, g));
+    } else {
+        if (bw) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024, true>, a, g));
+        else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024, false>, a, g));
+    }
     return 0;
 }
 
