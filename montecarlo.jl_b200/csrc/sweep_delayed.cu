@@ -11,7 +11,7 @@
 // because the current site still does), v stays frozen in Rc[j, :]. After the block the whole matrix is brought up to
 // date with ONE product G -= U * Rc (N x K x N) on the FP64 tensor pipe. The Metropolis decisions see
 // exactly the Green's function the immediate updates would give (the arithmetic is re-associated only).
-// One barrier per site: the next site's G_ii is published by the thread that owns its row. (For N > 256 the sites
+// One barrier per site: the next site's G_ii is published by the thread that owns its row. (For N > 64 the sites
 // of a block are decided on its diagonal block first and the vectors follow from recurrences, see decide_block.)
 //
 // Small batches of large matrices (config D: 32 chains, N = 400) leave most SMs idle with one CTA per chain,
@@ -133,39 +133,50 @@ __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc
     return nacc;
 }
 
+// Both recurrences run in sub-blocks of 8 sites: the contributions of all earlier sub-blocks are plain sums with
+// eight independent accumulators (one load of the earlier vector element per eight FMAs), only the 8 x 8 triangle
+// inside the sub-block is a dependent chain.
 __device__ __forceinline__ void column_recurrence(double* Cc, int ld, int i0, int kb, const double* DD, const double* xs, int e)
 {
-    for (int j = 0; j < kb; ++j) {
-        double c0 = Cc[j * ld + e], c1 = 0.0, c2 = 0.0, c3 = 0.0;
-        const double* dj = DD + j;
-        const double* up = Cc + e;
-        int jp = 0;
-        for (; jp + 4 <= j; jp += 4) {
-            c0 = fma(-up[jp * ld], dj[jp * DLD], c0);
-            c1 = fma(-up[(jp + 1) * ld], dj[(jp + 1) * DLD], c1);
-            c2 = fma(-up[(jp + 2) * ld], dj[(jp + 2) * DLD], c2);
-            c3 = fma(-up[(jp + 3) * ld], dj[(jp + 3) * DLD], c3);
+    for (int j0 = 0; j0 < kb; j0 += 8) {
+        double c[8], u[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) c[q] = (j0 + q < kb) ? Cc[(j0 + q) * ld + e] : 0.0;
+        for (int jp = 0; jp < j0; ++jp) {
+            const double up = Cc[jp * ld + e];          // u_jp, final
+            const double* d = DD + jp * DLD + j0;        // row jp of the block at the moment of site jp
+#pragma unroll
+            for (int q = 0; q < 8; ++q) c[q] = fma(-up, d[q], c[q]);
         }
-        for (; jp < j; ++jp) c0 = fma(-up[jp * ld], dj[jp * DLD], c0);
-        Cc[j * ld + e] = xs[j] * ((e == i0 + j ? 1.0 : 0.0) - ((c0 + c1) + (c2 + c3)));
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            double cc = c[q];
+#pragma unroll
+            for (int p = 0; p < q; ++p) cc = fma(-u[p], DD[(j0 + p) * DLD + j0 + q], cc);
+            u[q] = (j0 + q < kb) ? xs[j0 + q] * ((e == i0 + j0 + q ? 1.0 : 0.0) - cc) : 0.0;
+            if (j0 + q < kb) Cc[(j0 + q) * ld + e] = u[q];
+        }
     }
 }
 
 __device__ __forceinline__ void row_recurrence(double* Rc, int ld, int kb, const double* DD, int e)
 {
-    for (int j = 0; j < kb; ++j) {
-        double r0 = Rc[j * ld + e], r1 = 0.0, r2 = 0.0, r3 = 0.0;
-        const double* dj = DD + j * DLD;
-        const double* rp = Rc + e;
-        int jp = 0;
-        for (; jp + 4 <= j; jp += 4) {
-            r0 = fma(dj[jp], rp[jp * ld], r0);
-            r1 = fma(dj[jp + 1], rp[(jp + 1) * ld], r1);
-            r2 = fma(dj[jp + 2], rp[(jp + 2) * ld], r2);
-            r3 = fma(dj[jp + 3], rp[(jp + 3) * ld], r3);
+    for (int j0 = 0; j0 < kb; j0 += 8) {
+        double r[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) r[q] = (j0 + q < kb) ? Rc[(j0 + q) * ld + e] : 0.0;
+        for (int jp = 0; jp < j0; ++jp) {
+            const double rp = Rc[jp * ld + e];           // row_jp, final
+            const double* d = DD + j0 * DLD + jp;         // x_jp times column jp of the block at the moment of site jp
+#pragma unroll
+            for (int q = 0; q < 8; ++q) r[q] = fma(d[q * DLD], rp, r[q]);
         }
-        for (; jp < j; ++jp) r0 = fma(dj[jp], rp[jp * ld], r0);
-        Rc[j * ld + e] = (r0 + r1) + (r2 + r3);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+#pragma unroll
+            for (int p = 0; p < q; ++p) r[q] = fma(DD[(j0 + q) * DLD + j0 + p], r[p], r[q]);
+            if (j0 + q < kb) Rc[(j0 + q) * ld + e] = r[q];
+        }
     }
 }
 
@@ -199,8 +210,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
     }
     int nacc = 0;
-    // (the host picks BW: measured faster where the per-site barrier spans 32 warps - N = 400: 953 against 1092 us per
-    // slice -, slower with 16 warps - N = 144: 224 against 210 us, the recurrences run on 10 warps only)
+    // (the host picks BW, see launch_sweep_delayed)
     constexpr bool blockwise = BW;
     const int nv = round_up(n, 32);                 // threads per group (whole warps)
     // groups of nv threads that share the per-site work; more groups shorten the loops but every
@@ -434,9 +444,9 @@ int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
     at[0].val.clusterDim.x = cls; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    // block-wise decisions for one spin sector and N > 256; MCB_SWEEP_EXP bit 16 forces the site-by-site loop,
-    // bit 32 the block-wise scheme for every size
-    const bool bw = !g.two && !(g.exp & 16) && (g.threads > 512 || (g.exp & 32));
+    // block-wise decisions for one spin sector and N > 64 (measured per slice: N = 144 182 against 203 us, N = 400 794
+    // against 1092 us); MCB_SWEEP_EXP bit 16 forces the site-by-site loop, bit 32 the block-wise scheme for every size
+    const bool bw = !g.two && !(g.exp & 16) && (g.threads >= 512 || (g.exp & 32));
     if (g.threads <= 512) {
         if (bw) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512, true>, a, g));
         else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<512, false>, a, g));

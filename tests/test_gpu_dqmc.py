@@ -357,7 +357,7 @@ def test_config_d_20x20_first_updates_match_oracle():
 
 def test_blockwise_sweep_scheme_on_small_lattices():
     """The block-wise decision scheme of the delayed sweep (decide_block + triangular recurrences, sweep_delayed.cu)
-    is the default only for N > 256 (config D test above). MCB_SWEEP_EXP=32 forces it for every size: the
+    is the default for N > 64 (config C and D tests above). MCB_SWEEP_EXP=32 forces it for every size: the
     every-update parity tests of the general path (4x4, 8x8 full sweep) and config C must hold with it too. The switch
     is read once per process, hence the child process."""
     import os
