@@ -42,6 +42,7 @@ struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
     size_t smem;
     int cls;   // CTAs per chain (thread-block cluster), 1 = plain launch
+    int ndw;   // warps of the block-wise decision phase (4 or 8: 8 / 4 columns of the diagonal block per thread)
     int two;   // 1: the two CTAs of a cluster are the two spin sectors of the repulsive model (cls == 2)
     int exp;   // timing experiments (MCB_SWEEP_EXP): 1 = no flush, 2 = no site loop; results invalid
 };
@@ -67,13 +68,18 @@ DelayedGeom delayed_geom(int n)
     g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double) + TABLE_BYTES;
     static const int exp_flags = getenv("MCB_SWEEP_EXP") ? atoi(getenv("MCB_SWEEP_EXP")) : 0;
     g.exp = exp_flags;
+    // measured per slice: N = 144 (512 threads) 170 us with 8 decision warps against 181 with 4; N = 400 (1024 threads,
+    // 64 registers) 839 against 790
+    static const int dw = getenv("MCB_SWEEP_DW") ? atoi(getenv("MCB_SWEEP_DW")) : 0;
+    g.ndw = (g.threads >= 256 && g.threads <= 512) ? 8 : 4;
+    if ((dw == 4 || dw == 8) && g.threads >= 256) g.ndw = dw;
     return g;
 }
 
 // ---- the sites of a block without a block-wide barrier per site (one spin sector) -------------------
-// The decisions of a block only need its K x K diagonal block D = G[i0.., i0..]. Four warps work on a copy DD in
-// shared memory (thread = row a, every fourth column) and walk through the sites - G_ii, Metropolis decision,
-// rank-1 update of the trailing part of DD, one named barrier of 128 threads - like a right-looking elimination:
+// The decisions of a block only need its K x K diagonal block D = G[i0.., i0..]. Four or eight warps work on a copy DD in
+// shared memory (thread = row a, every fourth / eighth column) and walk through the sites - G_ii, Metropolis decision,
+// rank-1 update of the trailing part of DD, one named barrier of these warps - like a right-looking elimination:
 // after site j neither row j nor column j of DD is touched again, so at the end DD holds, for every site, the row
 // of D at the moment the site was visited (upper triangle) and its column (lower triangle, then scaled by x_j),
 // next to x_j itself (0 if rejected). The full vectors follow from two triangular recurrences that need no
@@ -82,22 +88,21 @@ DelayedGeom delayed_geom(int n)
 //   row_j = Rc_j + sum_{j'<j} (x_j' DD[j][j']) row_j'                            (row role, frozen rows in Rc)
 // which is what the site-by-site updates of the columns j' > j and rows k > j add up to.
 constexpr int DLD = 33;        // row stride of DD (conflict-free column access)
-constexpr int DEC_THREADS = 128;
-
-__device__ __forceinline__ void dec_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void dec_bar(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
 
 __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc, int ld, int i0, int kb,
                                             const int8_t* s_in, int8_t* s_out, const double* unif, double* DD,
-                                            double* xs, int tid)
+                                            double* xs, int tid, int ndw)
 {
-    const int ra = tid & 31, cg0 = tid >> 5;   // my row, my first column; columns cg0, cg0 + 4, ...
+    const int ra = tid & 31, cg0 = tid >> 5;   // my row, my first column; columns cg0, cg0 + ndw, ... (ndw warps)
+    const int nth = 32 * ndw;
     double* myrow = DD + ra * DLD;
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-        const int b = cg0 + 4 * q;
-        myrow[b] = (ra < kb && b < kb) ? Cc[b * ld + i0 + ra] : 0.0;
+        const int b = cg0 + ndw * q;
+        if (b < 32) myrow[b] = (ra < kb && b < kb) ? Cc[b * ld + i0 + ra] : 0.0;
     }
-    dec_bar();
+    dec_bar(nth);
     int nacc = 0;
     for (int j = 0; j < kb; ++j) {
         const int i = i0 + j;
@@ -109,25 +114,25 @@ __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc
         const double rt = 1.0 + gamma * (1.0 - gii);
         const double x = gamma * fast_rcp(rt);          // speculative: only used if accepted
         const double p = efac * (rt * rt);
-        const bool accept = (p > 1.0 || unif[i] < p);    // uniform over the four warps
+        const bool accept = (p > 1.0 || unif[i] < p);    // uniform over the deciding warps
         if (accept) {
             if (ra > j && ra < kb) {
                 const double mu = x * myrow[j];           // -u of row ra: u = x (e_i - G[:, i])
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
-                    const int b = cg0 + 4 * q;
+                    const int b = cg0 + ndw * q;
                     if (b > j && b < kb) myrow[b] = fma(mu, rowj[b], myrow[b]);
                 }
             }
             ++nacc;
         }
         if (tid == 0) { xs[j] = accept ? x : 0.0; s_out[i] = (int8_t)(accept ? -s : s); }
-        dec_bar();
+        dec_bar(nth);
     }
     // lower triangle: column j' of the block scaled by x_j' for the row recurrence
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-        const int b = cg0 + 4 * q;
+        const int b = cg0 + ndw * q;
         if (b < ra && ra < kb) myrow[b] *= xs[b];
     }
     return nacc;
@@ -242,10 +247,10 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             for (int k = lane; k < kb4; k += 32) Rc[k * ld + l] = (k < kb && l < n) ? gcol[k] : 0.0;
         }
         if constexpr (blockwise) {
-            // ---- decisions on the diagonal block by four warps, then the vector recurrences
+            // ---- decisions on the diagonal block by a few warps, then the vector recurrences
             __syncthreads();
             if (!(g.exp & 2)) {
-                if (tid < DEC_THREADS) nacc += decide_block(a, Cc, ld, i0, (g.exp & 8) ? 1 : kb, s_in, s_out, unif, DD, xs, tid);
+                if (tid < 32 * g.ndw) nacc += decide_block(a, Cc, ld, i0, (g.exp & 8) ? 1 : kb, s_in, s_out, unif, DD, xs, tid, g.ndw);
                 __syncthreads();
                 if (g.exp & 4) {
                 } else if (2 * nv <= T) {
