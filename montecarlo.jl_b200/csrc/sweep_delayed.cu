@@ -88,21 +88,22 @@ DelayedGeom delayed_geom(int n)
 //   row_j = Rc_j + sum_{j'<j} (x_j' DD[j][j']) row_j'                            (row role, frozen rows in Rc)
 // which is what the site-by-site updates of the columns j' > j and rows k > j add up to.
 constexpr int DLD = 33;        // row stride of DD (conflict-free column access)
-__device__ __forceinline__ void dec_bar(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
+template <int NTH>
+__device__ __forceinline__ void dec_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NTH) : "memory"); }
 
+template <int ndw>   // deciding warps
 __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc, int ld, int i0, int kb,
                                             const int8_t* s_in, int8_t* s_out, const double* unif, double* DD,
-                                            double* xs, int tid, int ndw)
+                                            double* xs, int tid)
 {
     const int ra = tid & 31, cg0 = tid >> 5;   // my row, my first column; columns cg0, cg0 + ndw, ... (ndw warps)
-    const int nth = 32 * ndw;
     double* myrow = DD + ra * DLD;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < 32 / ndw; ++q) {
         const int b = cg0 + ndw * q;
         if (b < 32) myrow[b] = (ra < kb && b < kb) ? Cc[b * ld + i0 + ra] : 0.0;
     }
-    dec_bar(nth);
+    dec_bar<32 * ndw>();
     int nacc = 0;
     for (int j = 0; j < kb; ++j) {
         const int i = i0 + j;
@@ -119,7 +120,7 @@ __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc
             if (ra > j && ra < kb) {
                 const double mu = x * myrow[j];           // -u of row ra: u = x (e_i - G[:, i])
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
+                for (int q = 0; q < 32 / ndw; ++q) {
                     const int b = cg0 + ndw * q;
                     if (b > j && b < kb) myrow[b] = fma(mu, rowj[b], myrow[b]);
                 }
@@ -127,11 +128,11 @@ __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc
             ++nacc;
         }
         if (tid == 0) { xs[j] = accept ? x : 0.0; s_out[i] = (int8_t)(accept ? -s : s); }
-        dec_bar(nth);
+        dec_bar<32 * ndw>();
     }
     // lower triangle: column j' of the block scaled by x_j' for the row recurrence
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < 32 / ndw; ++q) {
         const int b = cg0 + ndw * q;
         if (b < ra && ra < kb) myrow[b] *= xs[b];
     }
@@ -250,7 +251,9 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             // ---- decisions on the diagonal block by a few warps, then the vector recurrences
             __syncthreads();
             if (!(g.exp & 2)) {
-                if (tid < 32 * g.ndw) nacc += decide_block(a, Cc, ld, i0, (g.exp & 8) ? 1 : kb, s_in, s_out, unif, DD, xs, tid, g.ndw);
+                const int kdec = (g.exp & 8) ? 1 : kb;
+                if (g.ndw == 8) { if (tid < 256) nacc += decide_block<8>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid); }
+                else if (tid < 128) nacc += decide_block<4>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid);
                 __syncthreads();
                 if (g.exp & 4) {
                 } else if (2 * nv <= T) {
