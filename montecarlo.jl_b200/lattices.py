@@ -36,48 +36,47 @@ class SquareLattice:
         y = np.arange(self.sites) // self.L + 1
         return np.stack([x, y], axis=1).astype(np.float64)
 
-    def pair_direction_table(self, eps=1e-6):
-        """dir_of[src, trg] -> direction index, ordered like EachSitePairByDistance.
+    def direction_targets(self, eps=1e-6):
+        """trg_of[dir, src] = the target of the one pair (src, trg) that EachSitePairByDistance files under
+        direction `dir` for source `src` (a periodic Bravais lattice has exactly one; -1 would mean none), and the
+        displacement vectors in the iterator's order.
 
-        Restates lattice_iterators.jl:153-189: the displacement pos(src) - pos(trg) is
-        wrapped to the shortest periodic image (ties broken by the angle-weighted
-        `directed_norm`), unique displacements are numbered in order of first
-        appearance and then sorted by directed_norm.
-        """
-        L = self.L
+        Restates lattice_iterators.jl:153-189 array-wise: the displacement pos(src) - pos(trg) is moved to the
+        periodic image the reference picks (scan of the 9 box shifts, replace when `directed_norm` is smaller by
+        more than eps), unique displacements are numbered in order of first appearance (src-major scan) and then
+        stably sorted by `directed_norm` = |d| + eps * angle(d, e_x). Inside a direction the reference lists the
+        pairs by ascending src, which is the second index here; the first K rows are also the (dir, trg) lists
+        EachLocalQuadByDistance{K} builds per source (lattice_iterators.jl:268-274)."""
+        L, N = self.L, self.sites
         pos = self.positions()
         shifts = [np.zeros(2)]
-        for v in (np.array([L, 0.0]), np.array([0.0, L])):
+        for v in (np.array([float(L), 0.0]), np.array([0.0, float(L)])):
             shifts = [e - v for e in shifts] + shifts + [e + v for e in shifts]
 
-        def dnorm(v):
-            l = float(np.hypot(v[0], v[1]))
-            if l > eps:
-                ang = np.arccos(v[0] / l)
-                if v[1] < 0:
-                    ang = 2 * np.pi - ang
-                return l + eps * ang
-            return l
+        def dnorm(d):
+            l = np.hypot(d[..., 0], d[..., 1])
+            safe = np.where(l > eps, l, 1.0)
+            ang = np.arccos(np.clip(d[..., 0] / safe, -1.0, 1.0))
+            ang = np.where(d[..., 1] < 0, 2 * np.pi - ang, ang)
+            return np.where(l > eps, l + eps * ang, l)
 
-        dirs = []
-        dir_of = np.zeros((self.sites, self.sites), dtype=np.int32)
-        for o in range(self.sites):
-            for t in range(self.sites):
-                d = pos[o] - pos[t] + shifts[0]
-                for v in shifts[1:]:
-                    nd = pos[o] - pos[t] + v
-                    if dnorm(nd) + eps < dnorm(d):
-                        d = nd
-                idx = None
-                for k, e in enumerate(dirs):
-                    if np.allclose(e, d, atol=eps, rtol=0):
-                        idx = k
-                        break
-                if idx is None:
-                    dirs.append(d.copy())
-                    idx = len(dirs) - 1
-                dir_of[o, t] = idx
-        order = np.argsort([dnorm(d) for d in dirs], kind="stable")
-        rank = np.empty(len(dirs), dtype=np.int32)
-        rank[order] = np.arange(len(dirs), dtype=np.int32)
-        return rank[dir_of], np.array(dirs)[order]
+        base = pos[:, None, :] - pos[None, :, :]          # [src, trg]
+        d = base + shifts[0]
+        for v in shifts[1:]:
+            nd = base + v
+            take = dnorm(nd) + eps < dnorm(d)
+            d = np.where(take[..., None], nd, d)
+        key = np.rint(d).astype(np.int64)
+        code = (key[..., 0] + 4 * L) * (8 * L) + (key[..., 1] + 4 * L)
+        flat = code.reshape(-1)                             # src-major scan = order of first appearance
+        uniq, first = np.unique(flat, return_index=True)
+        appearance = uniq[np.argsort(first, kind="stable")]
+        dirs = np.stack([appearance // (8 * L) - 4 * L, appearance % (8 * L) - 4 * L], axis=1).astype(np.float64)
+        order = np.argsort(dnorm(dirs), kind="stable")
+        dirs = dirs[order]
+        rank_of_code = {int(c): r for r, c in enumerate(appearance[order])}
+        trg_of = np.full((len(dirs), N), -1, dtype=np.int32)
+        for src in range(N):
+            for trg in range(N):
+                trg_of[rank_of_code[int(code[src, trg])], src] = trg
+        return trg_of, dirs

@@ -17,6 +17,7 @@ _f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _i8p = np.ctypeslib.ndpointer(dtype=np.int8, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 _u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 
 
 def build(native=False, force=False):
@@ -24,7 +25,8 @@ def build(native=False, force=False):
     out = "liboracle_native.so" if native else "liboracle.so"
     path = os.path.join(_HERE, out)
     srcs = [os.path.join(_HERE, f) for f in
-            ("dqmc_oracle.cpp", "ising_oracle.cpp", "linalg_ref.h", "philox_ref.h")]
+            ("dqmc_oracle.cpp", "ising_oracle.cpp", "measure_oracle.cpp", "linalg_ref.h", "philox_ref.h",
+             "measure_ref.h")]
     stale = (not os.path.exists(path)) or any(
         os.path.getmtime(s) > os.path.getmtime(path) for s in srcs)
     if stale or force:
@@ -65,6 +67,15 @@ def lib(native=False):
     L.orc_philox.argtypes = [_u32p, _u32p, _u32p]
     L.orc_sweep_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int]
     L.orc_update_repulsive.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+    # measurements (measure_oracle.cpp)
+    L.orc_meas_pairs.argtypes = [_f64p, C.c_int, C.c_int, C.c_int, _i32p, C.c_int64, _f64p, C.c_int]
+    L.orc_meas_quads.argtypes = [_f64p, C.c_int, C.c_int, _i32p, C.c_int64, _f64p, C.c_int]
+    L.orc_meas_sites.argtypes = [_f64p, C.c_int, C.c_int, C.c_int, _f64p]
+    L.orc_meas_o5.argtypes = [_f64p, C.c_int, _f64p, C.c_double, _f64p]
+    L.orc_run_measured.restype = C.c_int64
+    L.orc_run_measured.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int64,
+                                   C.c_int, _i32p, C.c_int64, C.c_int, _i32p, C.c_int64, C.c_int, _f64p,
+                                   C.c_double] + [C.c_void_p] * 7
     # Ising
     L.ising_energy_cubic.restype = C.c_double
     L.ising_energy_cubic.argtypes = [_i64p, C.c_int, C.c_int]
@@ -244,3 +255,74 @@ def calculate_greens_udt(Ul, Dl, Tl, Ur, Dr, Tr):
     lib().orc_calculate_greens_udt(fmat(Ul), np.array(Dl, dtype=np.float64), fmat(Tl), fmat(Ur),
                                    np.array(Dr, dtype=np.float64), fmat(Tr), g, n)
     return unfmat(g, n)
+
+
+# ---------------------------------------------------------------- measurements (measure_oracle.cpp)
+class MeasurementTables:
+    """The lattice iterators of a periodic L x L square lattice as the tuple lists the reference iterates
+    (oracle/lattice_iterators.py): EachSitePairByDistance and EachLocalQuadByDistance{K}."""
+
+    def __init__(self, L, K=5):
+        from . import lattice_iterators as li
+        self.L, self.N, self.K = L, L * L, K
+        self.pairs, self.directions = li.each_site_pair_by_distance(L)
+        self.n_dirs = len(self.pairs)
+        self.trip = np.ascontiguousarray(li.pair_triplets(self.pairs))
+        self.implied = li.each_local_quad_by_distance(self.pairs, self.N, K)
+        self.quint = np.ascontiguousarray(li.quad_quintuplets(self.implied, K))
+        self.n_pc = self.n_dirs * K * K
+
+
+def measure(G, tables, flavors=1, T=None, U=0.0):
+    """All equal-time measurements of one physical Green's function G ((fN, fN) numpy, Julia semantics G[i, j]).
+    Returns a dict in the reference's output layouts: occupation (fN), cdc / sdc_x / sdc_y / sdc_z (n_dirs),
+    pc (n_dirs, K, K), mx / my / mz (N), and for one flavor the O5 scalars."""
+    L_ = lib()
+    N, nd, K = tables.N, tables.n_dirs, tables.K
+    g = fmat(G)
+    out = {}
+    o = np.empty(flavors * N)
+    L_.orc_meas_sites(g, N, flavors, 0, o)
+    out["occupation"] = o.copy()
+    for k, name in ((1, "mx"), (2, "my"), (3, "mz")):
+        o = np.empty(N)
+        L_.orc_meas_sites(g, N, flavors, k, o)
+        out[name] = o.copy()
+    for k, name in enumerate(("cdc", "sdc_x", "sdc_y", "sdc_z")):
+        o = np.empty(nd)
+        L_.orc_meas_pairs(g, N, flavors, k, tables.trip, len(tables.trip), o, nd)
+        out[name] = o
+    o = np.empty(tables.n_pc)
+    L_.orc_meas_quads(g, N, flavors, tables.quint, len(tables.quint), o, tables.n_pc)
+    out["pc"] = o.reshape(K, K, nd).transpose(2, 1, 0).copy()  # column-major (n_dirs, K, K)
+    if flavors == 1 and T is not None:
+        o = np.empty(4)
+        L_.orc_meas_o5(g, N, fmat(T), U, o)
+        out.update(n=o[0], double_occupancy=o[1], e_kin=o[2], e_int=o[3])
+    return out
+
+
+def run_measured(chain, tables, thermalization, sweeps, measure_rate=10, T=None, U=0.0, first=1):
+    """run!(mc) after build_stack (DQMC.jl:420-438) on an OracleDQMC or OracleDQMCRepulsive chain: sweeps
+    first .. thermalization + sweeps with the reference's measurement schedule. Returns the means over
+    measurements in the layouts of measure() plus G and the count."""
+    rep = isinstance(chain, OracleDQMCRepulsive)
+    hup, hdn = (chain.up.h, chain.dn.h) if rep else (chain.h, None)
+    N, M, nd, K = chain.N, chain.M, tables.n_dirs, tables.K
+    f = 2 if rep else 1
+    acc = dict(G=np.zeros((f * N) ** 2), occupation=np.zeros(f * N), cdc=np.zeros(nd), sdc=np.zeros(3 * nd),
+               pc=np.zeros(tables.n_pc), mz=np.zeros(N), o5=np.zeros(4))
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+    Tm = fmat(T) if T is not None else np.zeros(N * N)
+    cnt = lib().orc_run_measured(hup, hdn, N, M, first, thermalization + sweeps, thermalization, measure_rate,
+                                 tables.trip, len(tables.trip), nd, tables.quint, len(tables.quint), tables.n_pc,
+                                 Tm, U, ptr(acc["G"]), ptr(acc["occupation"]), ptr(acc["cdc"]), ptr(acc["sdc"]),
+                                 ptr(acc["pc"]), ptr(acc["mz"]), ptr(acc["o5"]) if (T is not None and not rep) else None)
+    k = max(cnt, 1)
+    out = dict(count=cnt, G=unfmat(acc["G"], f * N) / k, occupation=acc["occupation"] / k, cdc=acc["cdc"] / k,
+               sdc_x=acc["sdc"][:nd] / k, sdc_y=acc["sdc"][nd:2 * nd] / k, sdc_z=acc["sdc"][2 * nd:] / k,
+               pc=acc["pc"].reshape(K, K, nd).transpose(2, 1, 0) / k, mz=acc["mz"] / k)
+    if T is not None and not rep:
+        out.update(n=acc["o5"][0] / k, double_occupancy=acc["o5"][1] / k, e_kin=acc["o5"][2] / k,
+                   e_int=acc["o5"][3] / k)
+    return out
