@@ -129,18 +129,26 @@ int mcb_dqmc_replay(mcb_dqmc* h, const uint64_t* chunks, int64_t n_confs);
 int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st);
 int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* per_chain);
 
-/* Observables (measurement kernels; src/flavors/DQMC/measurements/measurements.jl:31-44,
- * src/models/HubbardModel/HubbardModelAttractive.jl:221-245).
- * dir_of_pair: N*N int32, dir_of_pair[src + trg*N] = direction index of EachSitePairByDistance
- * (lattice_iterators.jl:131-221), n_dirs directions; hop: N x N hopping matrix T (for E_kin). */
-int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* dir_of_pair, int32_t n_dirs,
+/* Observables: the reference's equal-time measurement kernels over its lattice iterators
+ * (greens_kernel, occupation_kernel src/flavors/DQMC/measurements/measurements.jl:31-44; cdc / sdc / pc overloads
+ * src/models/HubbardModel/HubbardModelAttractive.jl:221-245; apply! / finish! src/flavors/DQMC/measurements/generic.jl:279-347;
+ * SURVEY.md 8a O1-O5, 8f rank 1).
+ * trg_of: n_dirs * N int32, trg_of[dir*N + src] = target site (0-based) of the pair (src, trg) that
+ * EachSitePairByDistance files under direction `dir` (src/lattices/lattice_iterators.jl:131-221), -1 if src has none;
+ * K: EachLocalQuadByDistance{K} (lattice_iterators.jl:258-355) pairs every source with its targets in the first K
+ * directions (0 <= K <= n_dirs; 5 = on-site + 4 nearest neighbours on the square lattice, measurements.jl:197-201);
+ * hop: N x N hopping matrix T (kinetic energy). */
+int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* trg_of, int32_t n_dirs, int32_t K,
                                     const double* hop);
 /* accumulate the observables of the current G now (what apply!(groups) does, generic.jl:194-243) */
 int mcb_dqmc_measure(mcb_dqmc* h);
 int mcb_dqmc_reset_observables(mcb_dqmc* h);
-/* Length of one chain's scalar observable record, and the record itself: per chain the SUM over
- * measurements of [occupation n = 2(1-G_ii) avg over sites, double occupancy, E_kin/N, E_int/N,
- * cdc[0..n_dirs), swave_pairing[0..n_dirs)] followed by the count. */
+/* Length of one chain's observable record, and the records: per chain the SUM over measurements of
+ *   [ n = mean_i 2(1-G_ii), double occupancy mean_i (1-G_ii)^2, E_kin/N, E_int/N          
+ *   | cdc[n_dirs] | sdc_x[n_dirs] (= sdc_y) | sdc_z[n_dirs]                                (outputs of EachSitePairByDistance, /N)
+ *   | pc[n_dirs*K*K], column-major (dir12, dir1, dir2) like the reference's output array   (EachLocalQuadByDistance{K}, /N)
+ *   | occupation[N] = 1 - G_ii ]                                                           (EachSiteAndFlavor)
+ * followed by the number of measurements. Sums are formed in a fixed order: repeated runs agree bit for bit. */
 int32_t mcb_dqmc_observable_len(mcb_dqmc* h);
 int mcb_dqmc_get_observables(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t* count);
 /* per chain SUM over measurements of G_phys, [chain][col][row] */
@@ -187,7 +195,7 @@ int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, cons
 /* SURVEY.md 8(f) rank 4. The reference keeps the two spin sectors as the blocks of BlockDiagonal matrices
  * (src/models/HubbardModel/HubbardModelRepulsive.jl:72-232, src/linalg/blockdiagonal.jl:156-428); here they are
  * two batched stacks that share one field and one sweep_spatial launch. Same parameter struct, same call
- * sequence and error codes as the mcb_dqmc_* functions above; n_sites >= 16.
+ * sequence and error codes as the mcb_dqmc_* functions above.
  * Green's functions travel as [chain][sector (up, down)][col][row], i.e. the two diagonal blocks of mc.s.greens. */
 typedef struct mcb_dqmc_rep mcb_dqmc_rep;
 int mcb_dqmc_rep_create(const mcb_dqmc_params* p, mcb_dqmc_rep** out);
@@ -200,8 +208,8 @@ int mcb_dqmc_rep_get_conf(mcb_dqmc_rep* h, int8_t* conf);
 int mcb_dqmc_rep_build_stack(mcb_dqmc_rep* h);
 /* n x update(mc, i): propagate on both blocks, then sweep_spatial with propose_local / accept_local! of
  * HubbardModelRepulsive.jl:126-232 (detratio = R_up R_down, no bosonic factor, one rank-1 update per block) */
-int mcb_dqmc_rep_update(mcb_dqmc_rep* h, int64_t n_updates);
-int mcb_dqmc_rep_sweep(mcb_dqmc_rep* h, int64_t n_sweeps);
+int mcb_dqmc_rep_update(mcb_dqmc_rep* h, int64_t n_updates, int32_t measure_every);
+int mcb_dqmc_rep_sweep(mcb_dqmc_rep* h, int64_t n_sweeps, int32_t measure_every);
 int mcb_dqmc_rep_get_greens(mcb_dqmc_rep* h, double* G, int32_t physical);
 int mcb_dqmc_rep_calculate_greens_at(mcb_dqmc_rep* h, int32_t slice, double* G);
 int mcb_dqmc_rep_get_state(mcb_dqmc_rep* h, mcb_dqmc_state* st);
@@ -214,6 +222,20 @@ int mcb_dqmc_rep_get_conf_bits(mcb_dqmc_rep* h, uint64_t* chunks);
 int mcb_dqmc_rep_set_conf_bits(mcb_dqmc_rep* h, const uint64_t* chunks);
 int mcb_dqmc_rep_resume(mcb_dqmc_rep* h, int64_t last_sweep);
 double mcb_dqmc_rep_last_elapsed_ms(mcb_dqmc_rep* h);
+/* Observables of the two-flavor model: the general kernels of src/flavors/DQMC/measurements/measurements.jl:41-207
+ * (occupation, cdc, mz, sdc_x/y/z, pc) on the BlockDiagonal G (its off-diagonal blocks vanish, so mx = my = 0 and
+ * sdc_y = sdc_x). Tables as for mcb_dqmc_set_measurement_tables. Record per chain:
+ *   [ n, double occupancy <n_up n_dn>, E_kin/N, E_int/N | cdc[n_dirs] | sdc_x[n_dirs] | sdc_z[n_dirs]
+ *   | pc[n_dirs*K*K] | occupation[2N] (EachSiteAndFlavor: up sites, then down sites) | mz[N] ]
+ * mcb_dqmc_rep_get_greens_sum: [chain][sector][col][row]. replay: as mcb_dqmc_replay. */
+int mcb_dqmc_rep_set_measurement_tables(mcb_dqmc_rep* h, const int32_t* trg_of, int32_t n_dirs, int32_t K,
+                                        const double* hop);
+int mcb_dqmc_rep_measure(mcb_dqmc_rep* h);
+int mcb_dqmc_rep_reset_observables(mcb_dqmc_rep* h);
+int32_t mcb_dqmc_rep_observable_len(mcb_dqmc_rep* h);
+int mcb_dqmc_rep_get_observables(mcb_dqmc_rep* h, double* sums, int64_t* count);
+int mcb_dqmc_rep_get_greens_sum(mcb_dqmc_rep* h, double* Gsum);
+int mcb_dqmc_rep_replay(mcb_dqmc_rep* h, const uint64_t* chunks, int64_t n_confs);
 
 /* ----------------------------------------------------------------- Ising ---- */
 

@@ -64,7 +64,7 @@ SIGNATURES = {
     "mcb_dqmc_replay": (C.c_int, [C.c_void_p, _u64, C.c_int64]),
     "mcb_dqmc_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
     "mcb_dqmc_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
-    "mcb_dqmc_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, _f64]),
+    "mcb_dqmc_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, C.c_int32, _f64]),
     "mcb_dqmc_measure": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_reset_observables": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_observable_len": (C.c_int32, [C.c_void_p]),
@@ -79,8 +79,8 @@ SIGNATURES = {
     "mcb_dqmc_rep_set_conf": (C.c_int, [C.c_void_p, _i8]),
     "mcb_dqmc_rep_get_conf": (C.c_int, [C.c_void_p, _i8]),
     "mcb_dqmc_rep_build_stack": (C.c_int, [C.c_void_p]),
-    "mcb_dqmc_rep_update": (C.c_int, [C.c_void_p, C.c_int64]),
-    "mcb_dqmc_rep_sweep": (C.c_int, [C.c_void_p, C.c_int64]),
+    "mcb_dqmc_rep_update": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32]),
+    "mcb_dqmc_rep_sweep": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32]),
     "mcb_dqmc_rep_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
     "mcb_dqmc_rep_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
     "mcb_dqmc_rep_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
@@ -91,6 +91,13 @@ SIGNATURES = {
     "mcb_dqmc_rep_set_conf_bits": (C.c_int, [C.c_void_p, _u64]),
     "mcb_dqmc_rep_resume": (C.c_int, [C.c_void_p, C.c_int64]),
     "mcb_dqmc_rep_last_elapsed_ms": (C.c_double, [C.c_void_p]),
+    "mcb_dqmc_rep_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, C.c_int32, _f64]),
+    "mcb_dqmc_rep_measure": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_rep_reset_observables": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_rep_observable_len": (C.c_int32, [C.c_void_p]),
+    "mcb_dqmc_rep_get_observables": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
+    "mcb_dqmc_rep_get_greens_sum": (C.c_int, [C.c_void_p, _f64]),
+    "mcb_dqmc_rep_replay": (C.c_int, [C.c_void_p, _u64, C.c_int64]),
     "mcb_ising_last_elapsed_ms": (C.c_double, [C.c_void_p]),
     "mcb_ising_launch_count": (C.c_int64, [C.c_void_p]),
     "mcb_linalg_force_general": (C.c_int, [C.c_int32]),

@@ -297,7 +297,7 @@ int mcb_dqmc_replay(mcb_dqmc* h, const uint64_t* chunks, int64_t n_confs)
     REQUIRE(h && chunks && n_confs > 0, "bad argument");
     REQUIRE(n_confs % h->C == 0, "replay: the number of configurations must be a multiple of n_chains");
     if (!h->hopping_set) { set_error("set_hopping first"); return MCB_ERR_STATE; }
-    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
     ProfBind bind(h);
     const size_t nch = ((size_t)h->N * h->M + 63) / 64;
@@ -316,7 +316,7 @@ int mcb_dqmc_get_state(mcb_dqmc* h, mcb_dqmc_state* st)
     st->current_slice = h->current_slice;
     st->direction = h->direction;
     st->n_updates = h->n_updates;
-    st->n_measurements = h->n_meas;
+    st->n_measurements = h->ms.n_meas;
     return MCB_OK;
 }
 
@@ -341,34 +341,20 @@ int mcb_dqmc_get_stats(mcb_dqmc* h, mcb_dqmc_chain_stats* out)
     return MCB_OK;
 }
 
-int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* dir_of_pair, int32_t n_dirs, const double* hop)
+int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* trg_of, int32_t n_dirs, int32_t K, const double* hop)
 {
-    REQUIRE(h && dir_of_pair && hop && n_dirs > 0, "bad argument");
+    REQUIRE(h && trg_of && hop && n_dirs > 0 && K >= 0 && K <= n_dirs, "bad argument");
     MCB_CUDA(cudaSetDevice(h->p.device_id));
-    for (size_t e = 0; e < h->nn; ++e) REQUIRE(dir_of_pair[e] >= 0 && dir_of_pair[e] < n_dirs, "direction out of range");
-    cudaFree(h->dir_of_pair); cudaFree(h->hopT); cudaFree(h->obs); cudaFree(h->Gsum);
-    h->dir_of_pair = nullptr; h->hopT = nullptr; h->obs = nullptr; h->Gsum = nullptr;
-    h->n_dirs = n_dirs;
-    MCB_CUDA(cudaMalloc(&h->dir_of_pair, h->nn * sizeof(int32_t)));
-    MCB_CUDA(cudaMalloc(&h->hopT, h->nn * sizeof(double)));
-    MCB_CUDA(cudaMalloc(&h->obs, (size_t)h->C * h->obs_len() * sizeof(double)));
-    MCB_CUDA(cudaMalloc(&h->Gsum, h->mat * sizeof(double)));
-    MCB_CUDA(cudaMemcpyAsync(h->dir_of_pair, dir_of_pair, h->nn * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
-    MCB_CUDA(cudaMemcpyAsync(h->hopT, hop, h->nn * sizeof(double), cudaMemcpyHostToDevice, h->st));
-    MCB_CUDA(cudaStreamSynchronize(h->st));
-    return mcb_dqmc_reset_observables(h);
+    for (size_t e = 0; e < (size_t)n_dirs * h->N; ++e) REQUIRE(trg_of[e] >= -1 && trg_of[e] < h->N, "target site out of range");
+    return measure_setup(h->ms, h->N, h->C, 1, trg_of, n_dirs, K, hop, -h->p.U, h->st);
 }
 
 int mcb_dqmc_reset_observables(mcb_dqmc* h)
 {
     REQUIRE(h, "null handle");
-    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
-    MCB_CUDA(cudaMemsetAsync(h->obs, 0, (size_t)h->C * h->obs_len() * sizeof(double), h->st));
-    MCB_CUDA(cudaMemsetAsync(h->Gsum, 0, h->mat * sizeof(double), h->st));
-    MCB_CUDA(cudaStreamSynchronize(h->st));
-    h->n_meas = 0;
-    return MCB_OK;
+    return measure_reset(h->ms, h->st);
 }
 
 int mcb_dqmc_measure(mcb_dqmc* h)
@@ -408,25 +394,25 @@ int mcb_dqmc_get_profile(mcb_dqmc* h, int64_t* launches, double* ms, int64_t* ti
 
 double mcb_dqmc_last_elapsed_ms(mcb_dqmc* h) { return h ? (double)h->last_ms : -1.0; }
 
-int32_t mcb_dqmc_observable_len(mcb_dqmc* h) { return h ? h->obs_len() : 0; }
+int32_t mcb_dqmc_observable_len(mcb_dqmc* h) { return h ? h->ms.obs_len() : 0; }
 
 int mcb_dqmc_get_observables(mcb_dqmc* h, double* sums, int64_t* count)
 {
     REQUIRE(h && sums && count, "null argument");
-    if (!h->obs) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
-    MCB_CUDA(cudaMemcpyAsync(sums, h->obs, (size_t)h->C * h->obs_len() * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaMemcpyAsync(sums, h->ms.obs, (size_t)h->C * h->ms.obs_len() * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
-    *count = h->n_meas;
+    *count = h->ms.n_meas;
     return MCB_OK;
 }
 
 int mcb_dqmc_get_greens_sum(mcb_dqmc* h, double* Gsum)
 {
     REQUIRE(h && Gsum, "null argument");
-    if (!h->Gsum) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(h->p.device_id));
-    MCB_CUDA(cudaMemcpyAsync(Gsum, h->Gsum, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaMemcpyAsync(Gsum, h->ms.Gsum, h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
     return MCB_OK;
 }

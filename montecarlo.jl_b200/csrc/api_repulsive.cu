@@ -61,7 +61,9 @@ int rep_update(mcb_dqmc_rep* r)
     a.sweep = (uint32_t)(u->n_updates / (2 * (int64_t)u->M));
     a.visit = (uint32_t)(u->n_updates % (2 * (int64_t)u->M));
     a.acc = u->acc; a.prop = u->prop; a.nonfinite = u->nonfinite;
-    API_TRY(launch_sweep_delayed(a, u->st));
+    // N < 16: immediate rank-1 updates in shared memory (sweep.cu); otherwise the delayed-update cluster kernel
+    if (u->N < 16) API_TRY(launch_sweep_spatial(a, u->st));
+    else API_TRY(launch_sweep_delayed(a, u->st));
     u->n_updates += 1;
     d->n_updates += 1;
     return 0;
@@ -73,7 +75,6 @@ extern "C" {
 int mcb_dqmc_rep_create(const mcb_dqmc_params* p, mcb_dqmc_rep** out)
 {
     REQUIRE(p && out, "null argument");
-    REQUIRE(p->n_sites >= 16, "HubbardModelRepulsive needs at least 16 sites (the joint sweep is the delayed-update kernel)");
     mcb_dqmc_rep* r = new mcb_dqmc_rep();
     int rc = mcb_dqmc_create(p, &r->up);
     if (rc == MCB_OK) rc = mcb_dqmc_create(p, &r->dn);
@@ -132,25 +133,115 @@ int mcb_dqmc_rep_build_stack(mcb_dqmc_rep* r)
     return mcb_dqmc_build_stack(r->dn);
 }
 
-int mcb_dqmc_rep_update(mcb_dqmc_rep* r, int64_t n_updates)
+// apply!(::Greens, ...) for the two-block handle: physical G of both sectors, one measurement launch
+static int rep_measure(mcb_dqmc_rep* r)
+{
+    mcb_dqmc* u = r->up;
+    mcb_dqmc* d = r->dn;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    API_TRY(engine_physical_greens(u, u->W[1]));
+    API_TRY(engine_physical_greens(d, d->W[1]));
+    return measure_accumulate(u->ms, u->W[1], d->W[1], u->st);
+}
+
+int mcb_dqmc_rep_update(mcb_dqmc_rep* r, int64_t n_updates, int32_t measure_every)
 {
     REQUIRE(r && n_updates >= 0, "bad argument");
     mcb_dqmc* u = r->up;
     if (!u->stack_built || !r->dn->stack_built) { set_error("build_stack first"); return MCB_ERR_STATE; }
+    if (measure_every > 0 && !u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     MCB_CUDA(cudaSetDevice(u->p.device_id));
     ProfBind bind(u);
     MCB_CUDA(cudaEventRecord(u->ev0, u->st));
-    for (int64_t k = 0; k < n_updates; ++k) API_TRY(rep_update(r));
+    for (int64_t k = 0; k < n_updates; ++k) {
+        API_TRY(rep_update(r));
+        if (measure_every > 0 && u->current_slice == 1 && u->direction == 1) { // DQMC.jl:429-436
+            const int64_t sweep = (u->n_updates - 1) / (2 * (int64_t)u->M) + 1;
+            if (sweep % measure_every == 0) API_TRY(rep_measure(r));
+        }
+    }
     MCB_CUDA(cudaEventRecord(u->ev1, u->st));
     MCB_CUDA(cudaStreamSynchronize(u->st));
     MCB_CUDA(cudaEventElapsedTime(&u->last_ms, u->ev0, u->ev1));
     return MCB_OK;
 }
 
-int mcb_dqmc_rep_sweep(mcb_dqmc_rep* r, int64_t n_sweeps)
+int mcb_dqmc_rep_sweep(mcb_dqmc_rep* r, int64_t n_sweeps, int32_t measure_every)
 {
     REQUIRE(r && n_sweeps >= 0, "bad argument");
-    return mcb_dqmc_rep_update(r, n_sweeps * 2 * (int64_t)r->up->M);
+    return mcb_dqmc_rep_update(r, n_sweeps * 2 * (int64_t)r->up->M, measure_every);
+}
+
+int mcb_dqmc_rep_set_measurement_tables(mcb_dqmc_rep* r, const int32_t* trg_of, int32_t n_dirs, int32_t K, const double* hop)
+{
+    REQUIRE(r && trg_of && hop && n_dirs > 0 && K >= 0 && K <= n_dirs, "bad argument");
+    mcb_dqmc* u = r->up;
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    for (size_t e = 0; e < (size_t)n_dirs * u->N; ++e) REQUIRE(trg_of[e] >= -1 && trg_of[e] < u->N, "target site out of range");
+    return measure_setup(u->ms, u->N, u->C, 2, trg_of, n_dirs, K, hop, +u->p.U, u->st);
+}
+
+int mcb_dqmc_rep_measure(mcb_dqmc_rep* r)
+{
+    REQUIRE(r, "null handle");
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    API_TRY(rep_measure(r));
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_reset_observables(mcb_dqmc_rep* r)
+{
+    REQUIRE(r, "null handle");
+    if (!r->up->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    return measure_reset(r->up->ms, r->up->st);
+}
+
+int32_t mcb_dqmc_rep_observable_len(mcb_dqmc_rep* r) { return r ? r->up->ms.obs_len() : 0; }
+
+int mcb_dqmc_rep_get_observables(mcb_dqmc_rep* r, double* sums, int64_t* count)
+{
+    REQUIRE(r && sums && count, "null argument");
+    mcb_dqmc* u = r->up;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(sums, u->ms.obs, (size_t)u->C * u->ms.obs_len() * sizeof(double), cudaMemcpyDeviceToHost, u->st));
+    MCB_CUDA(cudaStreamSynchronize(u->st));
+    *count = u->ms.n_meas;
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_get_greens_sum(mcb_dqmc_rep* r, double* Gsum)
+{
+    REQUIRE(r && Gsum, "null argument");
+    mcb_dqmc* u = r->up;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(Gsum, u->ms.Gsum, 2 * u->mat * sizeof(double), cudaMemcpyDeviceToHost, u->st));
+    MCB_CUDA(cudaStreamSynchronize(u->st));
+    return MCB_OK;
+}
+
+// replay!(mc, configurations) measurement loop (DQMC.jl:649-660) on both blocks
+int mcb_dqmc_rep_replay(mcb_dqmc_rep* r, const uint64_t* chunks, int64_t n_confs)
+{
+    REQUIRE(r && chunks && n_confs > 0, "bad argument");
+    mcb_dqmc* u = r->up;
+    REQUIRE(n_confs % u->C == 0, "replay: the number of configurations must be a multiple of n_chains");
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    const size_t nch = (size_t)mcb_dqmc_conf_chunks(u);
+    for (int64_t b = 0; b < n_confs / u->C; ++b) {
+        API_TRY(mcb_dqmc_rep_set_conf_bits(r, chunks + (size_t)b * u->C * nch));
+        MCB_CUDA(cudaSetDevice(u->p.device_id));
+        ProfBind bind(u);
+        API_TRY(engine_calculate_greens_at(u, 0));
+        API_TRY(engine_calculate_greens_at(r->dn, 0));
+        API_TRY(rep_measure(r));
+        MCB_CUDA(cudaStreamSynchronize(u->st));
+    }
+    return MCB_OK;
 }
 
 int mcb_dqmc_rep_get_greens(mcb_dqmc_rep* r, double* G, int32_t physical)

@@ -269,7 +269,7 @@ void engine_free(mcb_dqmc* h)
     for (auto p : h->bufT) cudaFree(p);
     for (auto p : h->bufD) cudaFree(p);
     cudaFree(h->acc); cudaFree(h->prop); cudaFree(h->nonfinite); cudaFree(h->prop_err);
-    cudaFree(h->dir_of_pair); cudaFree(h->hopT); cudaFree(h->obs); cudaFree(h->Gsum);
+    measure_free(h->ms);
 }
 
 // ------------------------------------------------------------------ stack schedule
@@ -502,75 +502,13 @@ int engine_physical_greens(mcb_dqmc* h, double* out)
 }
 
 // ------------------------------------------------------------------ measurements
-namespace {
-
-// One CTA per chain. G = physical Green's function of the chain.
-//   occupation_kernel  1 - G_ii                  measurements.jl:41-44   (both spins: n_i = 2(1-G_ii))
-//   cdc_kernel         4(1-G_ii)(1-G_jj) + 2(delta_ji - G_ji) G_ij, i = src, j = trg
-//                                                HubbardModelAttractive.jl:221-224, summed per
-//                                                direction and divided by N (generic.jl:283-286, 331-336)
-//   pc_kernel          G[src1,src2] G[trg1,trg2] with on-site pairs = G_ij^2 (s-wave plane)
-//                                                HubbardModelAttractive.jl:243-245
-//   double occupancy (1-G_ii)^2, E_kin, E_int    SURVEY.md §8a O5 (no reference kernel)
-__global__ void measure_kernel(const double* G, const int32_t* dir_of_pair, const double* hopT, int n,
-                               int n_dirs, double U, double* obs, double* Gsum)
-{
-    extern __shared__ double bins[]; // [2*n_dirs] + 4
-    const int chain = blockIdx.x, tid = threadIdx.x;
-    const size_t nn = (size_t)n * n;
-    const double* g = G + (size_t)chain * nn;
-    double* gs = Gsum + (size_t)chain * nn;
-    for (int i = tid; i < 2 * n_dirs + 4; i += blockDim.x) bins[i] = 0.0;
-    __syncthreads();
-    double* cdc = bins + 4;
-    double* pc = bins + 4 + n_dirs;
-    double ekin = 0.0;
-    for (size_t e = tid; e < nn; e += blockDim.x) {
-        const int i = (int)(e % n), j = (int)(e / n); // e = i + j*n : G[i,j], src = i, trg = j
-        const double gij = g[e];
-        const double gji = g[j + (size_t)i * n];
-        const double gii = g[i + (size_t)i * n], gjj = g[j + (size_t)j * n];
-        gs[e] += gij;
-        const double dji = (i == j) ? 1.0 : 0.0;
-        const int d = dir_of_pair[e];
-        atomicAdd(&cdc[d], 4.0 * (1.0 - gii) * (1.0 - gjj) + 2.0 * (dji - gji) * gij);
-        atomicAdd(&pc[d], gij * gij);
-        ekin += hopT[e] * (dji - gji);
-    }
-    double occ = 0.0, docc = 0.0;
-    for (int i = tid; i < n; i += blockDim.x) {
-        const double ni = 1.0 - g[i + (size_t)i * n];
-        occ += 2.0 * ni;
-        docc += ni * ni;
-    }
-    occ = warp_sum(occ); docc = warp_sum(docc); ekin = warp_sum(ekin);
-    if ((tid & 31) == 0) { atomicAdd(&bins[0], occ); atomicAdd(&bins[1], docc); atomicAdd(&bins[2], ekin); }
-    __syncthreads();
-    const double invN = 1.0 / n;
-    double* o = obs + (size_t)chain * (4 + 2 * n_dirs);
-    if (tid == 0) {
-        const double occ_t = bins[0], docc_t = bins[1];
-        o[0] += occ_t * invN;
-        o[1] += docc_t * invN;
-        o[2] += 2.0 * bins[2] * invN;
-        o[3] += -U * (docc_t - 0.5 * occ_t + 0.25 * n) * invN;
-    }
-    for (int d = tid; d < 2 * n_dirs; d += blockDim.x) o[4 + d] += bins[4 + d] * invN;
-}
-
-} // namespace
-
+// apply!(::Greens, ...) (measurements/generic.jl:207-215): G = greens!(mc), then every measurement of the group
 int engine_measure(mcb_dqmc* h)
 {
-    if (!h->dir_of_pair) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (h->ms.flavors != 1) { set_error("two-flavor tables on a one-flavor handle"); return MCB_ERR_STATE; }
     MCB_TRY(engine_physical_greens(h, h->W[1]));
-    const size_t smem = (size_t)(2 * h->n_dirs + 4) * sizeof(double);
-    LaunchScope scope(LC_MEASURE, h->st, 0.0);
-    measure_kernel<<<h->C, 256, smem, h->st>>>(h->W[1], h->dir_of_pair, h->hopT, h->N, h->n_dirs, h->p.U,
-                                               h->obs, h->Gsum);
-    MCB_CUDA(cudaGetLastError());
-    h->n_meas += 1;
-    return 0;
+    return measure_accumulate(h->ms, h->W[1], h->W[1], h->st);
 }
 
 } // namespace mcb

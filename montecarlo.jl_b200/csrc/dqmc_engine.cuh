@@ -9,6 +9,7 @@
 #include "segment.cuh"
 #include "stab.cuh"
 #include "udt.cuh"
+#include "measure.cuh"
 #include <vector>
 
 struct mcb_dqmc {
@@ -36,13 +37,8 @@ struct mcb_dqmc {
     int spare = 0;
     long long *acc = nullptr, *prop = nullptr, *nonfinite = nullptr;
     double* prop_err = nullptr; // [C]
-    // measurement
-    int32_t* dir_of_pair = nullptr;
-    double* hopT = nullptr;
-    int n_dirs = 0;
-    double* obs = nullptr;  // [C][obs_len]
-    double* Gsum = nullptr; // [C][N*N]
-    int64_t n_meas = 0;
+    // measurement tables and accumulators (measure.cu)
+    mcb::MeasureState ms;
     // schedule state
     int current_slice = 0, direction = 1;
     int64_t n_updates = 0;
@@ -53,8 +49,6 @@ struct mcb_dqmc {
     bool hopping_set = false, conf_set = false, stack_built = false;
     struct UtStack* ut = nullptr; // unequal-time stacks and work matrices, allocated on first use (unequal.cu)
     int64_t conf_version = 0;     // bumped whenever the configuration may have changed
-
-    int obs_len() const { return 4 + 2 * n_dirs; }
 };
 
 namespace mcb {

@@ -15,17 +15,19 @@ __global__ void sweep_kernel(SweepArgs a, int in_smem)
     extern __shared__ double sm[];
     const int n = a.n, chain = blockIdx.x, tid = threadIdx.x;
     const size_t nn = (size_t)n * n;
+    const int nb = a.G2 ? 2 : 1; // HubbardModelRepulsive: second sector on the negated field (sweep.cuh)
     double* u = sm;
     double* v = u + n;
     double* unif = v + n;
     int8_t* sconf = (int8_t*)(unif + n);
     double* Gs = unif + n + (n + 7) / 8;
-    double* Gg = a.G + (size_t)chain * a.sG;
-    double* G = in_smem ? Gs : Gg;
+    double* Gg[2] = {a.G + (size_t)chain * a.sG, a.G2 ? a.G2 + (size_t)chain * a.sG : nullptr};
+    double* G[2] = {in_smem ? Gs : Gg[0], in_smem ? Gs + nn : Gg[1]};
     int8_t* cg = a.conf + (size_t)chain * a.sConf;
 
     if (in_smem)
-        for (size_t e = tid; e < nn; e += blockDim.x) G[e] = Gg[e];
+        for (int b = 0; b < nb; ++b)
+            for (size_t e = tid; e < nn; e += blockDim.x) G[b][e] = Gg[b][e];
     for (int i = tid; i < n; i += blockDim.x) {
         sconf[i] = cg[i];
         unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
@@ -34,24 +36,29 @@ __global__ void sweep_kernel(SweepArgs a, int in_smem)
 
     int nacc = 0;
     for (int i = 0; i < n; ++i) {
-        const double gii = G[i + (size_t)i * n];
         const int s = sconf[i];
-        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
+        // sector 0 sees the field s, sector 1 (if any) the field -s
+        const double gam[2] = {s > 0 ? a.gamma_p : a.gamma_m, s > 0 ? a.gamma_m : a.gamma_p};
         const double efac = s > 0 ? a.efac_p : a.efac_m;
-        const double r = 1.0 + gamma * (1.0 - gii);
-        const double p = efac * (r * r);
+        const double r0 = 1.0 + gam[0] * (1.0 - G[0][i + (size_t)i * n]);
+        const double r1 = nb == 2 ? 1.0 + gam[1] * (1.0 - G[1][i + (size_t)i * n]) : r0;
+        const double p = efac * (r0 * r1);
         if (p > 1.0 || unif[i] < p) { // uniform over the CTA: every thread sees the same G_ii
-            for (int k = tid; k < n; k += blockDim.x) {
-                double uk = -G[k + (size_t)i * n];
-                if (k == i) uk += 1.0;
-                u[k] = uk;
-                v[k] = G[i + (size_t)k * n];
-            }
-            __syncthreads();
-            const double x = gamma / (1.0 + gamma * u[i]);
-            for (size_t e = tid; e < nn; e += blockDim.x) {
-                const int k = (int)(e % n), l = (int)(e / n);
-                G[e] -= u[k] * (x * v[l]);
+            for (int b = 0; b < nb; ++b) {
+                double* Gb = G[b];
+                for (int k = tid; k < n; k += blockDim.x) {
+                    double uk = -Gb[k + (size_t)i * n];
+                    if (k == i) uk += 1.0;
+                    u[k] = uk;
+                    v[k] = Gb[i + (size_t)k * n];
+                }
+                __syncthreads();
+                const double x = gam[b] / (1.0 + gam[b] * u[i]);
+                for (size_t e = tid; e < nn; e += blockDim.x) {
+                    const int k = (int)(e % n), l = (int)(e / n);
+                    Gb[e] -= u[k] * (x * v[l]);
+                }
+                __syncthreads();
             }
             if (tid == 0) sconf[i] = (int8_t)-s;
             ++nacc;
@@ -60,9 +67,13 @@ __global__ void sweep_kernel(SweepArgs a, int in_smem)
     }
     bool bad = false;
     if (in_smem) {
-        for (size_t e = tid; e < nn; e += blockDim.x) { const double g = G[e]; Gg[e] = g; bad |= !isfinite(g); }
+        for (int b = 0; b < nb; ++b)
+            for (size_t e = tid; e < nn; e += blockDim.x) { const double g = G[b][e]; Gg[b][e] = g; bad |= !isfinite(g); }
     }
-    for (int i = tid; i < n; i += blockDim.x) cg[i] = sconf[i];
+    for (int i = tid; i < n; i += blockDim.x) {
+        cg[i] = sconf[i];
+        if (nb == 2) a.conf2[(size_t)chain * a.sConf + i] = (int8_t)-sconf[i];
+    }
     if (__syncthreads_or(bad) && tid == 0) a.nonfinite[chain] += 1;
     if (tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
 }
@@ -79,7 +90,7 @@ int launch_sweep_spatial(const SweepArgs& a, cudaStream_t st)
 {
     const int n = a.n;
     const size_t hdr = (size_t)(3 * n + (n + 7) / 8) * sizeof(double);
-    const size_t mat = (size_t)n * n * sizeof(double);
+    const size_t mat = (size_t)n * n * sizeof(double) * (a.G2 ? 2 : 1);
     const int in_smem = hdr + mat <= (size_t)SMEM_LIMIT;
     const int threads = n <= 32 ? 128 : (n <= 96 ? 256 : (n <= 200 ? 512 : 1024));
     LaunchScope scope(LC_SWEEP, st, 0.0);

@@ -51,8 +51,8 @@ class DQMC:
 
     With a HubbardModelRepulsive the Green's functions have shape (n_chains, 2, N, N): the spin-up and spin-down
     diagonal blocks of the reference's BlockDiagonal mc.s.greens. That model runs the sweep (build_stack, update,
-    sweep, greens, greens_at, greens_unequal, conf, conf_bits, checkpoint / resume, state, stats); the built-in
-    measurements and replay are the attractive model's.
+    sweep, greens, greens_at, greens_unequal, conf, conf_bits, checkpoint / resume, state, stats) and the
+    two-flavor measurement kernels (measurements.jl:41-207) incl. replay.
     """
 
     def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, conf=None, general_path=False,
@@ -83,10 +83,8 @@ class DQMC:
         self.last_sweep = 0
         self._tables = False
 
-    def _f(self, name, attractive_only=False):
+    def _f(self, name):
         """The C-ABI entry point `name` of this model's handle type."""
-        if attractive_only and self.rep:
-            raise NotImplementedError(f"{name}: not available for HubbardModelRepulsive (SURVEY.md 8f rank 4 covers the sweep)")
         return getattr(self.L, self._pfx + name)
 
     # -- layout helpers: numpy [i, j] (row-major view of Julia semantics) <-> column-major buffers
@@ -146,13 +144,13 @@ class DQMC:
         out = []
         full = (n // C_) * C_
         if full:
-            _lib.check(self._f("replay", True)(self.h, cfg[:full].reshape(-1), full))
+            _lib.check(self._f("replay")(self.h, cfg[:full].reshape(-1), full))
             out.append(self.observables())
         if n > full:
             rest = DQMC(self.model, n_chains=n - full, seed=self.seed, beta=self.p.beta, delta_tau=self.p.delta_tau,
                         safe_mult=self.p.safe_mult, general_path=self.general_path, device=self.device)
-            rest.enable_measurements()
-            _lib.check(rest.L.mcb_dqmc_replay(rest.h, cfg[full:].reshape(-1), n - full))
+            rest.enable_measurements(self.K)
+            _lib.check(rest._f("replay")(rest.h, cfg[full:].reshape(-1), n - full))
             out.append(rest.observables())
             rest.close()
         return out
@@ -180,12 +178,9 @@ class DQMC:
         _lib.check(self._f("build_stack")(self.h))
 
     def update(self, n=1, measure_every=0):
-        if self.rep:
-            if measure_every:
-                raise NotImplementedError("built-in measurements are the attractive model's")
-            _lib.check(self.L.mcb_dqmc_rep_update(self.h, n))
-        else:
-            _lib.check(self.L.mcb_dqmc_update(self.h, n, measure_every))
+        if measure_every:
+            self.enable_measurements()
+        _lib.check(self._f("update")(self.h, n, measure_every))
 
     def sweep(self, n=1, measure_every=0):
         self.update(n * 2 * self.M, measure_every)
@@ -224,35 +219,70 @@ class DQMC:
                     n_nonfinite=np.array([a.n_nonfinite for a in arr]))
 
     # -- measurements ---------------------------------------------------------------------
-    def enable_measurements(self):
-        if not self._tables:
-            dir_of, dirs = self.model.l.pair_direction_table()
-            self.directions = dirs
-            self.n_dirs = len(dirs)
-            # dir_of[src, trg] -> buffer index src + trg*N
-            tab = np.ascontiguousarray(dir_of.T.astype(np.int32)).reshape(-1)
-            _lib.check(self._f("set_measurement_tables", True)(self.h, tab, self.n_dirs,
-                                                              self._fm(self.model.hopping_matrix())))
-            self._tables = True
+    def enable_measurements(self, K=None):
+        """Upload the lattice-iterator tables: EachSitePairByDistance and EachLocalQuadByDistance{K}
+        (lattice_iterators.jl:131-355). K defaults to 1 + number of nearest-neighbour directions like
+        pairing(...) does (measurements.jl:197-201), capped by the number of directions of a tiny lattice."""
+        if self._tables and (K is None or K == self.K):
+            return
+        trg_of, dirs = self.model.l.direction_targets()
+        self.directions = dirs
+        self.n_dirs = len(dirs)
+        if K is None:
+            K = min(5, self.n_dirs)
+        self.K = int(K)
+        tab = np.ascontiguousarray(trg_of.astype(np.int32)).reshape(-1)
+        _lib.check(self._f("set_measurement_tables")(self.h, tab, self.n_dirs, self.K,
+                                                     self._fm(self.model.hopping_matrix())))
+        self._tables = True
 
     def measure(self):
-        _lib.check(self._f("measure", True)(self.h))
+        self.enable_measurements()
+        _lib.check(self._f("measure")(self.h))
+
+    def reset_observables(self):
+        _lib.check(self._f("reset_observables")(self.h))
 
     def observables(self):
-        """Per-chain means over measurements. Returns dict of arrays with leading chain axis."""
-        n = self._f("observable_len", True)(self.h)
+        """Per-chain means over measurements, in the reference's output layouts (leading chain axis):
+        G (C, N, N) [(C, 2, N, N) for two flavors], occupation (C, flv*N), cdc / sdc_x / sdc_y / sdc_z (C, n_dirs),
+        pc (C, n_dirs, K, K), swave_pairing = pc[:, :, 0, 0], and the scalars n, double_occupancy, e_kin, e_int,
+        energy; two flavors add mz (C, N)."""
+        n = self._f("observable_len")(self.h)
         buf = np.empty(self.n_chains * n)
         cnt = C.c_int64()
-        _lib.check(self._f("get_observables", True)(self.h, buf, C.byref(cnt)))
-        gs = np.empty(self.n_chains * self.N * self.N)
-        _lib.check(self._f("get_greens_sum", True)(self.h, gs))
+        _lib.check(self._f("get_observables")(self.h, buf, C.byref(cnt)))
+        gs = np.empty(self.n_chains * self.model.flv * self.N * self.N)
+        _lib.check(self._f("get_greens_sum")(self.h, gs))
         k = max(cnt.value, 1)
         rec = buf.reshape(self.n_chains, n) / k
-        nd = self.n_dirs
-        return dict(count=cnt.value, occupation=rec[:, 0], double_occupancy=rec[:, 1],
-                    e_kin=rec[:, 2], e_int=rec[:, 3], energy=rec[:, 2] + rec[:, 3],
-                    cdc=rec[:, 4:4 + nd], swave_pairing=rec[:, 4 + nd:4 + 2 * nd],
-                    G=self._unbatch(gs) / k)
+        nd, K, N, f = self.n_dirs, self.K, self.N, self.model.flv
+        o_pc = 4 + 3 * nd
+        o_occ = o_pc + nd * K * K
+        pc = rec[:, o_pc:o_occ].reshape(self.n_chains, K, K, nd).transpose(0, 3, 2, 1)  # column-major (nd, K, K)
+        out = dict(count=cnt.value, n=rec[:, 0], occupation_mean=rec[:, 0], double_occupancy=rec[:, 1],
+                   e_kin=rec[:, 2], e_int=rec[:, 3], energy=rec[:, 2] + rec[:, 3],
+                   cdc=rec[:, 4:4 + nd], sdc_x=rec[:, 4 + nd:4 + 2 * nd], sdc_y=rec[:, 4 + nd:4 + 2 * nd],
+                   sdc_z=rec[:, 4 + 2 * nd:4 + 3 * nd], pc=pc, swave_pairing=pc[:, :, 0, 0],
+                   occupation=rec[:, o_occ:o_occ + f * N], G=self._unbatch(gs) / k)
+        if f == 2:
+            out["mz"] = rec[:, o_occ + 2 * N:o_occ + 3 * N]
+        return out
+
+    @staticmethod
+    def observable_shapes(model, K=None):
+        """Trailing shapes (without the chain axis) of everything observables() returns as an array; lets a rank
+        without chains take part in the reduction with correctly shaped zero moments."""
+        N, f = len(model.l), model.flv
+        nd = N  # a periodic Bravais lattice has one direction per site
+        K = min(5, nd) if K is None else K
+        g = (f, N, N) if f == 2 else (N, N)
+        shapes = dict(n=(), occupation_mean=(), double_occupancy=(), e_kin=(), e_int=(), energy=(), cdc=(nd,),
+                      sdc_x=(nd,), sdc_y=(nd,), sdc_z=(nd,), pc=(nd, K, K), swave_pairing=(nd,),
+                      occupation=(f * N,), G=g)
+        if f == 2:
+            shapes["mz"] = (N,)
+        return shapes
 
     def run(self, thermalization=None, sweeps=None):
         """run!(mc) (DQMC.jl:369-515): thermalise, then sweep with measurements every measure_rate."""

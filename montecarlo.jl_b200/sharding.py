@@ -38,7 +38,7 @@ def local_moments(per_chain):
     for key, val in per_chain.items():
         a = np.asarray(val, dtype=np.float64)
         if a.ndim == 0:
-            continue
+            continue  # not per chain (e.g. the measurement count)
         n = a.shape[0] if n is None else n
         if a.shape[0] != n:
             raise ValueError(f"observable {key!r} has {a.shape[0]} chains, expected {n}")
@@ -99,15 +99,20 @@ class ShardedDQMC:
         self.offset, self.count = shard(total_chains, self.rank, self.world)
         self.total_chains, self.group = total_chains, group
         self.mc = None
+        self.model = model
         if self.count > 0:
             self.mc = DQMC(model, n_chains=self.count, seed=seed, chain_offset=self.offset,
                            device=self.local_rank, **kwargs)
 
     def run(self, thermalization=None, sweeps=None):
-        per_chain = {}
         if self.mc is not None:
             obs = self.mc.run(thermalization, sweeps)
             per_chain = {k: v for k, v in obs.items() if k != "count"}
+        else:
+            # a rank without chains (total_chains < world_size) sends zero moments of the SAME layout; an
+            # all_reduce with mismatched payload sizes would hang or corrupt
+            from .dqmc import DQMC
+            per_chain = {k: np.zeros((0,) + shp) for k, shp in DQMC.observable_shapes(self.model).items()}
         device = None
         try:
             import torch

@@ -26,7 +26,8 @@ def _pair(L, U, beta, dtau, safe_mult, n_chains, seed=77, general=False, chain_o
 
 
 @pytest.mark.parametrize("general", [False, True])
-@pytest.mark.parametrize("L,U,beta,safe_mult,chains", [(4, 2.0, 1.0, 5, 3), (4, 4.0, 2.0, 10, 2), (6, 4.0, 1.0, 5, 2)])
+@pytest.mark.parametrize("L,U,beta,safe_mult,chains", [(2, 1.0, 1.0, 5, 3), (4, 2.0, 1.0, 5, 3), (4, 4.0, 2.0, 10, 2),
+                                                  (6, 4.0, 1.0, 5, 2)])
 def test_every_update_of_a_sweep_matches_oracle(L, U, beta, safe_mult, chains, general):
     mc, oracles = _pair(L, U, beta, 0.1, safe_mult, chains, general=general)
     mc.build_stack()

@@ -72,10 +72,11 @@ def test_square_lattice_tables():
     assert mcb.HubbardModelAttractive(L=2).hopping_matrix()[0, 1] == -2.0
     eTm, eTp, eT2m, eT2p = m.hopping_exponentials(0.1)
     assert np.allclose(eTm @ eTp, np.eye(16)) and np.allclose(eT2m @ eT2p, np.eye(16))
-    dir_of, dirs = l.pair_direction_table()
-    assert dir_of.shape == (16, 16) and len(dirs) == 16
-    assert np.all(np.bincount(dir_of.reshape(-1)) == 16)
-    assert np.all(np.diag(dir_of) == 0) and np.allclose(dirs[0], 0)
+    trg_of, dirs = l.direction_targets()
+    assert trg_of.shape == (16, 16) and len(dirs) == 16
+    assert all(sorted(row) == list(range(16)) for row in trg_of.tolist())   # one target per (direction, source)
+    assert np.array_equal(trg_of[0], np.arange(16)) and np.allclose(dirs[0], 0)
+    assert np.array_equal(trg_of[1], l.neighs[2])   # direction (1, 0) = pos[src] - pos[trg]: trg is the "down" neighbour
     nrm = np.hypot(dirs[:, 0], dirs[:, 1])
     assert np.all(np.diff(nrm) >= -1e-9)
 

@@ -89,3 +89,62 @@ def test_error_bars_are_standard_errors_over_chains():
     assert n == 64
     assert np.allclose(res["x"][0], x.mean(0))
     assert np.allclose(res["x"][1], x.std(0, ddof=1) / 8.0)
+
+
+class _FakeDQMC:
+    """Stands in for the CUDA-backed DQMC inside the CPU workers: observables are functions of the global chain id,
+    in the real layout (DQMC.observable_shapes)."""
+    observable_shapes = staticmethod(mcb.DQMC.observable_shapes)
+
+    def __init__(self, model, n_chains=1, seed=123, chain_offset=0, device=0, **kw):
+        self.model, self.n, self.off = model, n_chains, chain_offset
+
+    def run(self, thermalization=None, sweeps=None):
+        ids = np.arange(self.off, self.off + self.n, dtype=np.float64)
+        out = dict(count=3)
+        for k, shp in self.observable_shapes(self.model).items():
+            out[k] = (1.0 + ids).reshape((-1,) + (1,) * len(shp)) * np.ones((self.n,) + shp)
+        return out
+
+    def close(self):
+        pass
+
+
+def _sharded_worker(rank, world, port, total, q):
+    import torch.distributed as dist
+    from montecarlo_jl_b200 import dqmc as dqmc_mod
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        dqmc_mod.DQMC = _FakeDQMC
+        sh = sharding.ShardedDQMC(mcb.HubbardModelAttractive(L=2, U=1.0), total, beta=1.0)
+        res, n = sh.run(0, 1)
+        q.put((rank, sh.count, n, {k: (np.array(v[0]), np.array(v[1])) for k, v in res.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("total", [1, 3])
+def test_sharded_run_with_an_empty_or_ragged_shard(total):
+    """total_chains < world_size leaves a rank without chains: it must join the all-reduce with a payload of the
+    same layout (mismatched sizes hang or corrupt)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sharded_worker, args=(r, 2, port, total, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = sorted([q.get(timeout=120) for _ in procs], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert [o[1] for o in out] == [total - total // 2, total // 2]
+    ids = 1.0 + np.arange(total)
+    for _, _, n, res in out:
+        assert n == total
+        assert set(res) == set(mcb.DQMC.observable_shapes(mcb.HubbardModelAttractive(L=2, U=1.0)))
+        for k, (mean, err) in res.items():
+            assert np.allclose(mean, ids.mean()) and mean.shape == mcb.DQMC.observable_shapes(
+                mcb.HubbardModelAttractive(L=2, U=1.0))[k]
