@@ -133,7 +133,7 @@ int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, cons
     int* piv = d.alloc<int>(vcnt); CHECK_ALLOC(piv);
     for (int i = 0; i < 4; ++i) MCB_CUDA(cudaMemcpy(m[i], hm[i], cnt * sizeof(double), cudaMemcpyHostToDevice));
     for (int i = 0; i < 2; ++i) MCB_CUDA(cudaMemcpy(v[i], hv[i], vcnt * sizeof(double), cudaMemcpyHostToDevice));
-    L_TRY(calc_greens_raw(n, batch, m[0], v[0], m[1], m[2], v[1], m[3], m[4], W, Dw, piv, 0));
+    L_TRY(calc_greens_raw(n, batch, m[0], v[0], m[1], m[2], v[1], m[3], m[4], W, Dw, piv, 0, !force_general_udt()));
     MCB_CUDA(cudaDeviceSynchronize());
     MCB_CUDA(cudaMemcpy(G, m[4], cnt * sizeof(double), cudaMemcpyDeviceToHost));
     return MCB_OK;

@@ -8,6 +8,19 @@
 
 namespace mcb {
 
+// Switches that turn phases of a kernel off for timing runs (results invalid) are read from the environment only
+// in -DMCB_EXPERIMENTS builds (profiles/); the shipped library ignores them.
+inline int experiment_flags(const char* name)
+{
+#ifdef MCB_EXPERIMENTS
+    const char* e = getenv(name);
+    return e ? atoi(e) : 0;
+#else
+    (void)name;
+    return 0;
+#endif
+}
+
 void set_error(const std::string& msg);
 
 #define MCB_CUDA(call)                                                                          \

@@ -105,7 +105,7 @@ int wrap_greens(mcb_dqmc* h, double* Gx, double* Gt, int curr_slice, int directi
 // calculate_greens_AVX! (stack.jl:337-393) without clobbering its inputs.
 int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const double* Tl,
                     const double* Ur, const double* Dr, const double* Tr, double* G, double* const W[6],
-                    double* const Dw[2], int* pivot, cudaStream_t st)
+                    double* const Dw[2], int* pivot, cudaStream_t st, bool resident)
 {
     const long long nn = (long long)n * n;
     auto gemm = [&](const double* A, bool ta, const double* B, bool tb, double* C) {
@@ -116,7 +116,7 @@ int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const 
         g.C = C; g.strideC = nn;
         return g;
     };
-    if (stab_supported(n) && !force_general_udt()) {
+    if (resident && stab_supported(n)) {
         // one CTA per chain: the scaled product inside the first factorisation, everything between and
         // after the factorisations in the two glue kernels (stab.cuh)
         MCB_TRY(launch_udt_of_product(n, batch, Tl, Tr, Dl, Dr, W[1], Dw[0], W[2], pivot, st));
@@ -159,7 +159,7 @@ namespace {
 int calc_greens(mcb_dqmc* h, int physL, int physR, double* out)
 {
     return calc_greens_raw(h->N, h->C, h->bufU[physL], h->bufD[physL], h->bufT[physL], h->bufU[physR],
-                           h->bufD[physR], h->bufT[physR], out, h->W, h->Dw, h->pivot, h->st);
+                           h->bufD[physR], h->bufT[physR], out, h->W, h->Dw, h->pivot, h->st, h->use_panel);
 }
 
 // add_slice_sequence_left (stack.jl:272-287): phys buffer `dst` <- udt(B_hi ... B_lo * U_src D_src) , T_dst = T T_src
@@ -490,7 +490,7 @@ int engine_calculate_greens_at(mcb_dqmc* h, int slice)
     MCB_TRY(scratch_side(h, false, slice + 1, h->M, h->bufU[sp], h->bufD[sp], h->bufT[sp]));
     MCB_TRY(scratch_side(h, true, 1, slice, h->Gtmp, leftD, h->W[6]));
     return calc_greens_raw(h->N, h->C, h->Gtmp, leftD, h->W[6], h->bufU[sp], h->bufD[sp], h->bufT[sp],
-                           h->G, h->W, h->Dw, h->pivot, h->st);
+                           h->G, h->W, h->Dw, h->pivot, h->st, h->use_panel);
 }
 
 // _greens! (DQMC.jl:721-730): out = e^{+dtau T/2} (G e^{-dtau T/2})

@@ -96,8 +96,9 @@ double* unequal_result(mcb_dqmc* h);
 // add_slice_sequence_left/right on raw (U, D, T) triples
 int advance_raw(mcb_dqmc* h, bool left, const double* Usrc, const double* Dsrc, const double* Tsrc, double* Udst,
                 double* Ddst, double* Tdst, int lo, int hi);
-// batched calculate_greens on raw device buffers (shared with the linalg entry point)
+// batched calculate_greens on raw device buffers (shared with the linalg entry point); resident: use the
+// chain-resident kernels of stab.cuh where they exist for n (the handle's use_panel / the linalg force flag)
 int calc_greens_raw(int n, int batch, const double* Ul, const double* Dl, const double* Tl,
                     const double* Ur, const double* Dr, const double* Tr, double* G, double* const W[6],
-                    double* const Dw[2], int* pivot, cudaStream_t st);
+                    double* const Dw[2], int* pivot, cudaStream_t st, bool resident);
 } // namespace mcb

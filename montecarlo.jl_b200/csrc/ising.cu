@@ -191,6 +191,7 @@ int mcb_ising_create(int32_t L, double beta, int32_t n_replicas, uint64_t seed, 
     if (!out || L < 2 || (L & 1) || n_replicas <= 0) { set_error("L must be even and >= 2, replicas > 0"); return MCB_ERR_ARG; }
     if (L / 2 > 64 && (L / 2) % 64 != 0) { set_error("L/2 must be <= 64 or a multiple of 64"); return MCB_ERR_ARG; }
     if (n_replicas > 65535) { set_error("at most 65535 replicas per handle"); return MCB_ERR_ARG; }
+    if (!(beta >= 0.0) || !isfinite(beta)) { set_error("beta must be finite and >= 0"); return MCB_ERR_ARG; }
     const int rc = check_device(device_id);
     if (rc) return rc;
     mcb_ising* h = new mcb_ising();
@@ -199,8 +200,9 @@ int mcb_ising_create(int32_t L, double beta, int32_t n_replicas, uint64_t seed, 
     h->W = (L / 2 + 63) / 64;
     h->nbits = (L / 2 >= 64) ? 64 : L / 2;
     // thresholds in double on the host, compared as integers on the device (bit-exact by construction)
-    h->thr4 = (uint32_t)floor(exp(-4.0 * beta) * 4294967296.0);
-    h->thr8 = (uint32_t)floor(exp(-8.0 * beta) * 4294967296.0);
+    // (saturated: at beta = 0 the product is 2^32, which does not fit; r < 2^32 - 1 then accepts all but one word)
+    h->thr4 = (uint32_t)fmin(floor(exp(-4.0 * beta) * 4294967296.0), 4294967295.0);
+    h->thr8 = (uint32_t)fmin(floor(exp(-8.0 * beta) * 4294967296.0), 4294967295.0);
     MCB_CUDA(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
     MCB_CUDA(cudaMalloc(&h->planes, (size_t)h->R * 2 * h->L * h->W * sizeof(uint64_t)));
     MCB_CUDA(cudaMalloc(&h->spins_dev, (size_t)h->R * h->L * h->L));

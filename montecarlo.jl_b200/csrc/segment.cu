@@ -357,7 +357,9 @@ __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArg
             if (a.phase_sync) __syncthreads();
         }
         // ---- sweep_spatial of `slice`
-        if (!wrapping) chain_sync(bar_id, TPC);
+        // the wrap's last product reads all of cs.X as its A operand and site_block<0> overwrites columns 0..15 of
+        // it: without the CTA barrier above the chain needs its own (also orders s_in / unif when nothing wrapped)
+        if (!wrapping || !a.phase_sync) chain_sync(bar_id, TPC);
         site_block<N, 0>(acc, cs, a, t, bar_id, nacc);
         chain_sync(bar_id, TPC);
         for (int i = t.ctid; i < N; i += TPC) cg[(size_t)(slice - 1) * N + i] = cs.s_out[i];

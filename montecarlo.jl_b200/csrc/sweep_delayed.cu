@@ -66,7 +66,7 @@ DelayedGeom delayed_geom(int n)
     g.K = K;
     g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
     g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double) + TABLE_BYTES;
-    static const int exp_flags = getenv("MCB_SWEEP_EXP") ? atoi(getenv("MCB_SWEEP_EXP")) : 0;
+    static const int exp_flags = experiment_flags("MCB_SWEEP_EXP");
     g.exp = exp_flags;
     // measured per slice: N = 144 (512 threads) 170 us with 8 decision warps against 181 with 4; N = 400 (1024 threads,
     // 64 registers) 839 against 790

@@ -519,7 +519,7 @@ int launch_udt_cluster(int n, int batch, double* X, double* U, double* D, double
                        cudaStream_t st)
 {
     if (!udt_cluster_supported(n)) { set_error("udt_cluster: unsupported size"); return -1; }
-    static const int exp_flags = getenv("MCB_UDT_EXP") ? atoi(getenv("MCB_UDT_EXP")) : 0;
+    static const int exp_flags = experiment_flags("MCB_UDT_EXP");
     const int cl = n > 200 ? CL : 1;
     ClusterUdtArgs a{n, n / cl, cl, X, D, T, pivot, apply_pivot, exp_flags};
     const double n3 = (double)n * n * n * batch;

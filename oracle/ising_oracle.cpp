@@ -71,8 +71,9 @@ double ising_delta_e_square(const int64_t* conf, int L, int64_t site)
 // Integer acceptance thresholds, computed once on the host in double precision.
 void ising_thresholds(double beta, uint32_t* thr4, uint32_t* thr8)
 {
-    *thr4 = (uint32_t)floor(exp(-4.0 * beta) * 4294967296.0);
-    *thr8 = (uint32_t)floor(exp(-8.0 * beta) * 4294967296.0);
+    // saturated so that beta = 0 (product 2^32) stays representable; beta < 0 is rejected by the callers
+    *thr4 = (uint32_t)fmin(floor(exp(-4.0 * beta) * 4294967296.0), 4294967295.0);
+    *thr8 = (uint32_t)fmin(floor(exp(-8.0 * beta) * 4294967296.0), 4294967295.0);
 }
 
 static inline int words_per_row(int L) { return (L / 2 + 63) / 64; }
