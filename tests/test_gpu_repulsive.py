@@ -93,12 +93,42 @@ def test_batched_updates_equal_single_updates_and_chain_ids_are_global():
     a.close(); b.close()
 
 
-def test_attractive_only_entry_points_are_refused():
-    mc, _ = _pair(4, 2.0, 1.0, 0.1, 5, 1)
-    with pytest.raises(NotImplementedError):
-        mc.measure()
-    with pytest.raises(NotImplementedError):
-        mc.update(1, measure_every=1)
+def test_replay_and_run_schedule_of_the_two_block_handle():
+    """replay! (DQMC.jl:649-660) and the measurement schedule of run! for HubbardModelRepulsive: the batched replay of
+    recorded fields equals measuring the from-scratch G of each field, which the oracle's general kernels reproduce."""
+    model = mcb.HubbardModelRepulsive(L=4, U=2.0)
+    kw = dict(beta=1.0, delta_tau=0.1, safe_mult=5)
+    mc = mcb.DQMC(model, n_chains=2, seed=4, **kw)
+    rng = np.random.default_rng(8)
+    confs = rng.choice(np.array([-1, 1], dtype=np.int8), size=(4, 16, 10))
+    res = mc.replay(np.stack([mcb.compress(c) for c in confs]))
+    assert [r["count"] for r in res] == [2]
+    tables = orc.MeasurementTables(4, 5)
+    for c in range(2):
+        want = []
+        for conf in (confs[c], confs[2 + c]):
+            o = orc.OracleDQMCRepulsive(16, 10, 5, 0.1, 2.0, mc.hop, conf)
+            g = [mc.hop[1] @ gb @ mc.hop[0] for gb in o.greens_at(0)]
+            G2 = np.zeros((32, 32))
+            G2[:16, :16], G2[16:, 16:] = g
+            want.append(orc.measure(G2, tables, flavors=2))
+        for k in ("cdc", "sdc_x", "sdc_z", "pc", "mz", "occupation"):
+            assert np.abs(res[0][k][c] - np.mean([w[k] for w in want], axis=0)).max() < 1e-9, (k, c)
+    mc.close()
+    # run!: measurements every 2nd sweep after 2 thermalisation sweeps
+    mc = mcb.DQMC(model, n_chains=2, seed=4, thermalization=2, sweeps=6, measure_rate=2, **kw)
+    conf0 = mc.conf()
+    obs = mc.run()
+    for c in range(2):
+        o = orc.OracleDQMCRepulsive(16, 10, 5, 0.1, 2.0, mc.hop, conf0[c], seed=4, chain=c)
+        o.build_stack()
+        want = orc.run_measured(o, tables, thermalization=2, sweeps=6, measure_rate=2)
+        assert want["count"] == obs["count"] == 3
+        G2 = np.zeros((32, 32))
+        G2[:16, :16], G2[16:, 16:] = obs["G"][c]
+        assert np.abs(G2 - want["G"]).max() < 1e-9
+        for k in ("cdc", "sdc_x", "sdc_z", "pc", "mz"):
+            assert np.abs(obs[k][c] - want[k]).max() < 1e-9, (k, c)
     mc.close()
 
 
@@ -141,8 +171,3 @@ def test_checkpoint_and_resume_continue_the_same_chains():
     # the resumed stack is rebuilt from scratch: agreement to stabilisation accuracy, not bitwise
     assert np.abs(second.greens(False) - full.greens(False)).max() < 1e-8
     full.close(); second.close()
-
-
-def test_small_lattices_are_refused():
-    with pytest.raises(mcb.McbError):
-        mcb.DQMC(mcb.HubbardModelRepulsive(L=2, U=1.0), n_chains=1, beta=1.0, safe_mult=5)
