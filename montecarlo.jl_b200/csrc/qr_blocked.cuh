@@ -1,0 +1,244 @@
+// Device-side building blocks of the blocked Householder QR (udt_blocked.cu):
+//   panel_steps   NB unpivoted Householder steps on a register-held panel, one block barrier per step
+//   panel_gram    S = V'V of the finished panel on the tensor pipe
+//   panel_tfactor T of H_1 .. H_NB = I - V T V' from S and tau
+//   apply_strip   C <- (I - V op(T) V') C for an 8-column strip held in registers, three DMMA products
+// Layout conventions are documented at each function; NB = 16 throughout.
+#pragma once
+#include "common.cuh"
+
+namespace mcb {
+namespace qrb {
+
+constexpr int NB = 16;       // panel width
+constexpr int TLD = NB + 8;  // leading dimension of k-contiguous operands: 16-byte loads at (l/4) * TLD + 2 * (l%4)
+                             // are bank-conflict free when TLD % 16 == 8
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Panel layout: NW warps; for each of its row tiles t = warp + NW * u (8 rows of the active part) a thread owns row
+// l/4 and the four columns 4 * (l%4) + {0..3}: x[u][cc].
+//
+// Step k (reflector! and reflectorApply!, src/linalg/UDT.jl:32-50, 133-148): with a = current panel,
+//   s_c = sum_{i>k} a_ik a_ic  (c >= k; c = k gives the squared norm below the diagonal),
+//   normu = sqrt(a_kk^2 + s_k), nu = copysign(normu, a_kk), xi1 = a_kk + nu, tau = xi1 / nu, R_kk = -nu,
+//   v = [1; a_{k+1:,k} / xi1],  w_c = a_kc + s_c / xi1,  a_c -= tau w_c v.
+// The s_c of all columns travel in ONE reduction: 3 shuffle levels inside a warp, per-warp partials through shared
+// memory, one barrier. part: [2][NW][NB], rowk: [2][NB] doubles of shared memory; taus: [NB]; Dout: D + j (global).
+template <int NW, int TPW>
+__device__ __forceinline__ void panel_steps(double (&x)[TPW][4], int mt, int warp, int lane, double* part, double* rowk,
+                                            double* taus, double* Dout)
+{
+    const int q = lane & 3, rl = lane >> 2;
+    const int i0 = 8 * warp + rl; // row of tile u = 0; tiles u >= 1 start at row 8 * NW >= NB: always below the diagonal
+    static_assert(8 * NW >= NB, "tile 0 of every warp must cover the rows on and above the panel's diagonal");
+#pragma unroll
+    for (int k = 0; k < NB; ++k) {
+        const int buf = k & 1;
+        double ak[TPW];
+#pragma unroll
+        for (int u = 0; u < TPW; ++u) ak[u] = __shfl_sync(0xffffffffu, x[u][k & 3], (lane & ~3) | (k >> 2));
+        double p[4], p2[4];
+        {
+            const double a0 = i0 > k ? ak[0] : 0.0;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) { p[cc] = a0 * x[0][cc]; p2[cc] = 0.0; }
+        }
+#pragma unroll
+        for (int u = 1; u < TPW; ++u) {
+            if (warp + NW * u < mt) {
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) {
+                    if (u & 1) p2[cc] = fma(ak[u], x[u][cc], p2[cc]);
+                    else p[cc] = fma(ak[u], x[u][cc], p[cc]);
+                }
+            }
+        }
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            p[cc] += p2[cc];
+            p[cc] += __shfl_xor_sync(0xffffffffu, p[cc], 4);
+            p[cc] += __shfl_xor_sync(0xffffffffu, p[cc], 8);
+            p[cc] += __shfl_xor_sync(0xffffffffu, p[cc], 16);
+        }
+        if (rl == 0) {
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) part[(buf * NW + warp) * NB + 4 * q + cc] = p[cc];
+        }
+        if (warp == (k >> 3) && rl == (k & 7)) { // the owner of row k publishes it
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) rowk[buf * NB + 4 * q + cc] = x[0][cc];
+        }
+        __syncthreads();
+        double s = 0.0;
+        if (lane < NB) {
+            double s2 = 0.0;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                if (w & 1) s2 += part[(buf * NW + w) * NB + lane];
+                else s += part[(buf * NW + w) * NB + lane];
+            }
+            s += s2;
+        }
+        const double sk = __shfl_sync(0xffffffffu, s, k);
+        const double akk = rowk[buf * NB + k];
+        const double normu2 = fma(akk, akk, sk);
+        const bool live = normu2 != 0.0;
+        double nu = 0.0, rxi = 0.0, tau = 0.0;
+        if (live) {
+            const double rn = fast_rsqrt(normu2);
+            nu = copysign(normu2 * rn, akk);
+            const double xi1 = akk + nu;
+            rxi = fast_rcp(xi1);
+            tau = xi1 * copysign(rn, akk);
+        }
+        if (warp == 0 && lane == 0) { taus[k] = tau; Dout[k] = fabs(nu); }
+        double f[4], g[4], m1[4];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            const int c = 4 * q + cc;
+            const double sc = __shfl_sync(0xffffffffu, s, c);
+            const double wc = fma(sc, rxi, rowk[buf * NB + c]);     // v' a_c
+            f[cc] = c > k ? tau * wc : 0.0;
+            g[cc] = f[cc] * rxi;
+            m1[cc] = (c == k && live) ? rxi : 1.0;
+        }
+        // tile 0 holds the rows on and above the diagonal of this step
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            const int c = 4 * q + cc;
+            const double old = x[0][cc];
+            const double below = fma(-g[cc], ak[0], old * m1[cc]);
+            const double onrow = (c == k && live) ? -nu : old - f[cc];
+            x[0][cc] = i0 > k ? below : (i0 == k ? onrow : old);
+        }
+#pragma unroll
+        for (int u = 1; u < TPW; ++u)
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) x[u][cc] = fma(-g[cc], ak[u], x[u][cc] * m1[cc]);
+    }
+}
+
+// S = V'V (NB x NB, only the strict upper part is used) of the panel stored column-major in P (column c at
+// P + c * ldp, active rows start at P[.. + row0], ldp % 16 == 8, row0 even), V = unit lower trapezoid: the caller has
+// patched the top NB x NB block (ones on the diagonal, zeros above). Warps 0 .. GW-1 split the row tiles; their
+// partial tiles are summed in fixed order through Sred [GW][NB*NB]. Result in Ssm[c * NB + k]. Two barriers inside.
+// DMMA with the k index standing for row pairs: one 16-byte load feeds the A operand of row tile c and the B operand
+// of column tile k.
+template <int GW>
+__device__ __forceinline__ void panel_gram(const double* P, int ldp, int row0, int mt, int warp, int lane, int nthreads,
+                                           int tid, double* Sred, double* Ssm)
+{
+    const int q = lane & 3, rl = lane >> 2;
+    if (warp < GW) {
+        double acc[2][2][2] = {};
+        for (int t = warp; t < mt; t += GW) {
+            double2 a[2];
+#pragma unroll
+            for (int ct = 0; ct < 2; ++ct)
+                a[ct] = *reinterpret_cast<const double2*>(P + (size_t)(ct * 8 + rl) * ldp + row0 + 8 * t + 2 * q);
+#pragma unroll
+            for (int ct = 0; ct < 2; ++ct)
+#pragma unroll
+                for (int kt = 0; kt < 2; ++kt) {
+                    dmma884(acc[ct][kt][0], acc[ct][kt][1], a[ct].x, a[kt].x);
+                    dmma884(acc[ct][kt][0], acc[ct][kt][1], a[ct].y, a[kt].y);
+                }
+        }
+#pragma unroll
+        for (int ct = 0; ct < 2; ++ct)
+#pragma unroll
+            for (int kt = 0; kt < 2; ++kt)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                    Sred[(size_t)warp * NB * NB + (ct * 8 + rl) * NB + kt * 8 + 2 * q + e] = acc[ct][kt][e];
+    }
+    __syncthreads();
+    for (int e = tid; e < NB * NB; e += nthreads) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < GW; ++w) s += Sred[(size_t)w * NB * NB + e];
+        Ssm[e] = s;
+    }
+    __syncthreads();
+}
+
+// T of H_1 .. H_NB = I - V T V' (dlarft, forward / columnwise): T_kk = tau_k, T[0:k, k] = -tau_k T[0:k, 0:k] S[0:k, k].
+// Row i lives in lane i of the calling warp (lanes >= NB idle). Tout: column-major NB x NB, Tout[i + k * NB].
+__device__ __forceinline__ void panel_tfactor(const double* Ssm, const double* taus, int lane, double* Tout)
+{
+    if (lane >= NB) return;
+    double Trow[NB];
+#pragma unroll
+    for (int k = 0; k < NB; ++k) {
+        double acc = 0.0;
+#pragma unroll
+        for (int mm = 0; mm < k; ++mm) {
+            const double sv = Ssm[mm * NB + k];
+            if (mm >= lane) acc = fma(Trow[mm], sv, acc);
+        }
+        const double tk = taus[k];
+        Trow[k] = lane < k ? -tk * acc : (lane == k ? tk : 0.0);
+    }
+#pragma unroll
+    for (int k = 0; k < NB; ++k) Tout[lane + k * NB] = Trow[k];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// C <- (I - V op(T) V') C on an 8-column strip held in registers: c[t] = C[rows 8t + 2q + {0,1}][column l/4] for the mt
+// active row tiles, i.e. the DMMA accumulator layout of the TRANSPOSED tile, which is also a valid A-operand layout if
+// k slot q of two consecutive DMMA steps stands for rows 2q and 2q+1. Operands in shared memory:
+//   Vs [NB][ldv]   V[r][k] at k * ldv + r      (ldv % 16 == 8)
+//   Vt [m][TLD]    V[r][k] at r * TLD + k
+//   Ts [NB][TLD]   op(T)[k][k2] at k2 * TLD + k   (op(T) = T' for Q' C, T for Q C; the caller fills it)
+// Returns the squared norm of the rows >= 8 * t_norm of the thread's column (partial: sum over the 4 lanes of a column).
+template <int RT>
+__device__ __forceinline__ double apply_strip(double (&c)[RT][2], int mt, int t_norm, const double* Vs, int ldv,
+                                              const double* Vt, const double* Ts, int lane)
+{
+    const int q = lane & 3, rl = lane >> 2;
+    double w[2][2];
+    {
+        double wh[2][2][2] = {}; // even / odd row tiles: four independent DMMA chains
+#pragma unroll
+        for (int t = 0; t < RT; ++t) {
+            if (t < mt) {
+#pragma unroll
+                for (int kt = 0; kt < 2; ++kt) {
+                    const double2 b = *reinterpret_cast<const double2*>(Vs + (size_t)(kt * 8 + rl) * ldv + 8 * t + 2 * q);
+                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][0], b.x);
+                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][1], b.y);
+                }
+            }
+        }
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) { w[kt][0] = wh[0][kt][0] + wh[1][kt][0]; w[kt][1] = wh[0][kt][1] + wh[1][kt][1]; }
+    }
+    double y[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+    for (int ko = 0; ko < 2; ++ko)
+#pragma unroll
+        for (int ki = 0; ki < 2; ++ki) {
+            const double2 b = *reinterpret_cast<const double2*>(Ts + (size_t)(ko * 8 + rl) * TLD + ki * 8 + 2 * q);
+            dmma884(y[ko][0], y[ko][1], w[ki][0], b.x);
+            dmma884(y[ko][0], y[ko][1], w[ki][1], b.y);
+        }
+#pragma unroll
+    for (int ko = 0; ko < 2; ++ko) { y[ko][0] = -y[ko][0]; y[ko][1] = -y[ko][1]; }
+    double nrm = 0.0;
+#pragma unroll
+    for (int t = 0; t < RT; ++t) {
+        if (t < mt) {
+#pragma unroll
+            for (int kt = 0; kt < 2; ++kt) {
+                const double2 b = *reinterpret_cast<const double2*>(Vt + (size_t)(8 * t + rl) * TLD + kt * 8 + 2 * q);
+                dmma884(c[t][0], c[t][1], y[kt][0], b.x);
+                dmma884(c[t][0], c[t][1], y[kt][1], b.y);
+            }
+            if (t >= t_norm) nrm += c[t][0] * c[t][0] + c[t][1] * c[t][1];
+        }
+    }
+    return nrm;
+}
+
+} // namespace qrb
+} // namespace mcb

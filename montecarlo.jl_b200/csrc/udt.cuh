@@ -21,6 +21,11 @@ bool udt_cluster_supported(int n);
 int init_udt_cluster_kernels();
 int launch_udt_cluster(int n, int batch, double* X, double* U, double* D, double* T, int* pivot, int apply_pivot,
                        cudaStream_t st);
+// blocked panel-pivoted QR on the tensor pipe (udt_blocked.cu): n % 16 == 0, 128 <= n <= 400
+bool udt_blocked_supported(int n);
+int init_udt_blocked_kernels();
+int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
+                       long long sP, int apply_pivot, cudaStream_t st);
 // testing aid: route every size through udt_kernel / rdivp_kernel
 void set_force_general_udt(bool on);
 bool force_general_udt();

@@ -1,0 +1,364 @@
+// Blocked, panel-pivoted Householder QR with compact-WY block reflectors on the FP64 tensor pipe (DMMA):
+// udt_AVX_pivot! (src/linalg/UDT.jl:192-306) for N % 16 == 0, 128 <= N <= 400 (configs C / D: N = 144, 400).
+//
+// The reference pivots column by column: every step applies one reflector to the whole trailing matrix (BLAS-2) and
+// re-measures all trailing norms; on a GPU that is a chain of N dependent, barrier-separated steps. Here the matrix is
+// factored in panels of NB = 16 columns:
+//   1. qrb_panel_kernel   (one CTA per chain) the exact squared norms of the trailing columns are known from the
+//      previous update; the NB largest form the next panel, sorted by decreasing norm, and are moved to positions
+//      j .. j+NB-1 (the displaced columns fill the holes; all column traffic is TMA bulk copies). The panel is factored
+//      by unpivoted Householder steps with the reference's reflector! convention, all warps of the CTA on registers,
+//      ONE block barrier per step (qr_blocked.cuh). Output: V (unit lower trapezoid) and R in place, tau, D = |R_kk|,
+//      and the NB x NB triangular factor T of  H_1 .. H_NB = I - V T V'  (Gram matrix V'V on the tensor pipe).
+//   2. qrb_apply_kernel   (grid = column blocks x chains) every warp keeps an 8-column strip of the trailing matrix in
+//      registers and applies  A <- A - V T' (V' A)  as three DMMA products; the strip itself serves as the tensor
+//      operand of V' A (the k index of a DMMA product may be permuted freely as long as both operands agree, so the
+//      accumulator layout of one product is the A-operand layout of the next). The squared norms of the updated
+//      columns below the panel come out of the same registers, in a fixed order.
+//   3. the same apply kernel, reflectors in reverse order, forms the explicit Q from the identity (UDT.jl:250-266).
+//   4. qrb_emit_kernel    T = D^-1 R P' or the "dirty" D^-1 R + pivot (UDT.jl:283-306).
+// Pivot order differs from the reference's (panel-wise instead of step-wise selection); U D T = X, the grading of D
+// and the accuracy of the Green's functions built from it do not (profiles/experiments/panel_pivot_qr.py: 4e-12 /
+// 8e-13 relative to the step-wise CPU restatement at configs C / D, the same distance LAPACK's dgeqp3 has).
+#include "udt.cuh"
+#include "prof.cuh"
+#include "qr_blocked.cuh"
+#include "tma.cuh"
+
+namespace mcb {
+
+namespace {
+
+using qrb::NB;
+using qrb::TLD;
+
+struct QrbArgs {
+    int n = 0, j = 0;
+    double* A = nullptr;     // [batch][n*n] the matrix being factored (V below, R above the diagonal afterwards)
+    double* D = nullptr; long long sD = 0;
+    double* norms = nullptr; // [batch][n] squared norms of rows >= j of the columns at positions >= j
+    int* perm = nullptr;     // [batch][n] original column index of the column at each position
+    double* Tfac = nullptr;  // [batch][n/NB][NB*NB] block-reflector factors, column-major
+};
+
+// ---------------------------------------------------------------------------------------------- panel
+template <int NW>
+size_t panel_smem(int n)
+{
+    const size_t ldp = n + 8; // ldp % 16 == 8 for n % 16 == 0
+    return (2 * NB * ldp + NB * NB /*Ptop*/ + n /*nrm*/ + 2 * NW * NB + 2 * NB + NB * NB /*Ssm*/ +
+            (size_t)NW * NB * NB /*Sred*/ + NB /*taus*/ + 2 /*mbarrier*/) * sizeof(double) + (4 * NB + 4) * sizeof(int);
+}
+
+template <int NW, int TPW>
+__global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
+{
+    extern __shared__ __align__(16) double sm[];
+    const int n = a.n, j = a.j, chain = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int T = NW * 32;
+    const int ldp = n + 8;
+    double* P = sm;                              // [NB][ldp] the panel, all n rows
+    double* Dsp = P + (size_t)NB * ldp;          // [NB][ldp] staging of the displaced columns
+    double* Ptop = Dsp + (size_t)NB * ldp;       // [NB][NB] raw top block of the factored panel
+    double* nrm = Ptop + NB * NB;                // [n]
+    double* part = nrm + n;                      // [2][NW][NB]
+    double* rowk = part + 2 * NW * NB;           // [2][NB]
+    double* Ssm = rowk + 2 * NB;                 // [NB][NB]
+    double* Sred = Ssm + NB * NB;                // [NW][NB*NB]
+    double* taus = Sred + (size_t)NW * NB * NB;  // [NB]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(taus + NB);
+    int* sel = reinterpret_cast<int*>(mbar + 2); // [NB] selected positions, [NB] displaced, [NB] holes, [NB] perm staging
+    int* disp = sel + NB;
+    int* hole = disp + NB;
+    int* pstage = hole + NB;
+    int* ndisp = pstage + NB;
+    double* A = a.A + (size_t)chain * n * n;
+    const double* gn = a.norms + (size_t)chain * n;
+    int* perm = a.perm + (size_t)chain * n;
+    const int m = n - j, mt = m / 8;
+
+    if (tid == 0) mbar_init(mbar, 1);
+    // ---- squared norms of the trailing columns (rows >= j): exact, from the previous update; computed here at j = 0
+    if (j == 0) {
+        for (int c = warp; c < n; c += NW) {
+            const double* col = A + (size_t)c * n;
+            double s = 0.0;
+#pragma unroll 8
+            for (int i = lane; i < n; i += 32) { const double v = __ldcg(col + i); s = fma(v, v, s); }
+            s = warp_sum(s);
+            if (lane == 0) nrm[c] = (s == s) ? s : INFINITY; // NaN columns sort first: the ranking needs a total order
+        }
+        for (int c = tid; c < n; c += T) perm[c] = c;
+    } else {
+        for (int c = j + tid; c < n; c += T) { const double s = __ldcg(gn + c); nrm[c] = (s == s) ? s : INFINITY; }
+    }
+    if (tid < NB) sel[tid] = -1;
+    __syncthreads();
+    // ---- the NB largest, by decreasing norm (ties: lower position first)
+    for (int c = j + tid; c < n; c += T) {
+        const double v = nrm[c];
+        int rank = 0;
+        for (int o = j; o < n; ++o) {
+            const double w = nrm[o];
+            rank += (w > v || (w == v && o < c)) ? 1 : 0;
+        }
+        if (rank < NB) sel[rank] = c;
+    }
+    __syncthreads();
+    // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
+    if (tid < NB) pstage[tid] = perm[sel[tid]];
+    if (tid == 0) {
+        int nd = 0, nh = 0;
+        for (int p = j; p < j + NB; ++p) {
+            bool chosen = false;
+            for (int s = 0; s < NB; ++s) chosen |= (sel[s] == p);
+            if (!chosen) disp[nd++] = p;
+        }
+        for (int s = 0; s < NB; ++s)                   // holes: selected positions beyond the panel (as many as displaced)
+            if (sel[s] >= j + NB) hole[nh++] = sel[s];
+        *ndisp = nd;
+        const uint32_t colbytes = (uint32_t)n * sizeof(double);
+        mbar_expect_tx(mbar, (uint32_t)(NB + nd) * colbytes);
+        for (int s = 0; s < NB; ++s) bulk_g2s(P + (size_t)s * ldp, A + (size_t)sel[s] * n, colbytes, mbar);
+        for (int d = 0; d < nd; ++d) bulk_g2s(Dsp + (size_t)d * ldp, A + (size_t)disp[d] * n, colbytes, mbar);
+    }
+    __syncthreads();
+    const int nd = *ndisp;
+    int moved = -1;
+    if (tid < nd) moved = perm[disp[tid]];
+    mbar_wait(mbar, 0);
+    __syncthreads();   // every thread has read its perm entries; the staged columns are complete
+    if (tid < nd) perm[hole[tid]] = moved;
+    if (tid < NB) perm[j + tid] = pstage[tid];
+    if (tid == 0 && nd > 0) {
+        for (int d = 0; d < nd; ++d) bulk_s2g(A + (size_t)hole[d] * n, Dsp + (size_t)d * ldp, (uint32_t)n * sizeof(double));
+        bulk_commit();
+    }
+    // ---- panel into registers, NB Householder steps
+    double x[TPW][4];
+    const int q = lane & 3, rl = lane >> 2;
+#pragma unroll
+    for (int u = 0; u < TPW; ++u) {
+        const int t = warp + NW * u;
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] : 0.0;
+    }
+    qrb::panel_steps<NW, TPW>(x, mt, warp, lane, part, rowk, taus, a.D + (size_t)chain * a.sD + j);
+    // ---- V back to P; the raw top block is kept aside while P carries the unit lower trapezoid for V'V
+#pragma unroll
+    for (int u = 0; u < TPW; ++u) {
+        const int t = warp + NW * u;
+        if (t < mt) {
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] = x[u][cc];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < NB * NB; e += T) {
+        const int c = e / NB, r = e % NB;
+        const double v = P[(size_t)c * ldp + j + r];
+        Ptop[e] = v;
+        P[(size_t)c * ldp + j + r] = r > c ? v : (r == c ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    qrb::panel_gram<NW>(P, ldp, j, mt, warp, lane, T, tid, Sred, Ssm);
+    if (warp == 0) qrb::panel_tfactor(Ssm, taus, lane, a.Tfac + ((size_t)chain * (n / NB) + j / NB) * NB * NB);
+    for (int e = tid; e < NB * NB; e += T) P[(size_t)(e / NB) * ldp + j + e % NB] = Ptop[e];
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+        for (int s = 0; s < NB; ++s) bulk_s2g(A + (size_t)(j + s) * n, P + (size_t)s * ldp, (uint32_t)n * sizeof(double));
+        bulk_commit();
+        bulk_wait_all();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- apply
+// C <- (I - V op(T) V') C for the columns [c_lo, n) of C, rows >= j; V = unit lower trapezoid stored in A[j:, j:j+NB].
+//   mode 0 (factorisation): op(T) = T', C = A itself (trailing columns), epilogue = squared norms of rows >= j + NB
+//   mode 1 (form Q):        op(T) = T,  C = Q
+// One warp per 8-column strip (qrb::apply_strip); V arrives by TMA bulk copies while the strip is loaded.
+struct ApplyArgs {
+    int n = 0, j = 0, c_lo = 0, mode = 0;
+    const double* A = nullptr; // reflectors
+    const double* Tfac = nullptr;
+    double* Cm = nullptr;      // [batch][n*n]
+    double* norms = nullptr;
+};
+
+template <int RT, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32) qrb_apply_kernel(ApplyArgs a)
+{
+    extern __shared__ __align__(16) double sm[];
+    const int n = a.n, j = a.j, chain = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int m = n - j, mt = m / 8;
+    const int ldv = m + ((8 - (m & 15)) & 15);       // ldv % 16 == 8
+    double* Vs = sm;                                  // [NB][ldv]   V[r][k] at k * ldv + r
+    double* Vt = Vs + (size_t)NB * ldv;               // [m][TLD]    V[r][k] at r * TLD + k
+    double* Ts = Vt + (size_t)m * TLD;                // [NB][TLD]   op(T)[k][k2] at k2 * TLD + k
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Ts + (size_t)NB * TLD);
+    const double* A = a.A + (size_t)chain * n * n;
+    if (tid == 0) {
+        mbar_init(mbar, 1);
+        const uint32_t colbytes = (uint32_t)m * sizeof(double);
+        mbar_expect_tx(mbar, NB * colbytes);
+        for (int k = 0; k < NB; ++k) bulk_g2s(Vs + (size_t)k * ldv, A + (size_t)(j + k) * n + j, colbytes, mbar);
+    }
+    {
+        const double* Tg = a.Tfac + ((size_t)chain * (n / NB) + j / NB) * NB * NB;
+        for (int e = tid; e < NB * NB; e += NWARPS * 32) {
+            const int k = e % NB, k2 = e / NB; // Tg[k + k2 * NB] = T[k][k2]
+            const double v = __ldcg(Tg + e);
+            if (a.mode == 0) Ts[k2 * TLD + k] = v;   // Y' = W' T
+            else Ts[k * TLD + k2] = v;               // Y' = W' T'
+        }
+    }
+    const int c0 = a.c_lo + 8 * (blockIdx.x * NWARPS + warp);
+    const bool active = c0 < n;
+    const int q = lane & 3, rl = lane >> 2;
+    double* Ccol = a.Cm + (size_t)chain * n * n + (size_t)(active ? c0 + rl : 0) * n + j + 2 * q;
+    double c[RT][2];
+#pragma unroll
+    for (int t = 0; t < RT; ++t) {
+        if (active && t < mt) {
+            const double2 v = __ldcg(reinterpret_cast<const double2*>(Ccol + 8 * t));
+            c[t][0] = v.x; c[t][1] = v.y;
+        } else { c[t][0] = 0.0; c[t][1] = 0.0; }
+    }
+    __syncthreads();          // the barrier is initialised for everybody
+    mbar_wait(mbar, 0);
+    // unit lower trapezoid: the top NB x NB block still carries R on and above its diagonal
+    for (int e = tid; e < NB * NB; e += NWARPS * 32) {
+        const int k = e / NB, r = e % NB;
+        if (r <= k) Vs[(size_t)k * ldv + r] = (r == k) ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    for (int e = tid; e < (NB / 2) * m; e += NWARPS * 32) {
+        const int kp = e / m, r = e - kp * m;   // two k at a time: 16-byte stores
+        *reinterpret_cast<double2*>(Vt + (size_t)r * TLD + 2 * kp) =
+            make_double2(Vs[(size_t)(2 * kp) * ldv + r], Vs[(size_t)(2 * kp + 1) * ldv + r]);
+    }
+    __syncthreads();
+    if (!active) return;
+    double nrm = qrb::apply_strip<RT>(c, mt, NB / 8, Vs, ldv, Vt, Ts, lane);
+#pragma unroll
+    for (int t = 0; t < RT; ++t)
+        if (t < mt) *reinterpret_cast<double2*>(Ccol + 8 * t) = make_double2(c[t][0], c[t][1]);
+    if (a.mode == 0) {
+        nrm += __shfl_xor_sync(0xffffffffu, nrm, 1);
+        nrm += __shfl_xor_sync(0xffffffffu, nrm, 2);
+        if (q == 0) a.norms[(size_t)chain * n + c0 + rl] = nrm;
+    }
+}
+
+__global__ void qrb_identity_kernel(double* U, int n)
+{
+    double* u = U + (size_t)blockIdx.y * n * n;
+    for (size_t e = blockIdx.x * blockDim.x + threadIdx.x; e < (size_t)n * n; e += (size_t)gridDim.x * blockDim.x)
+        u[e] = (e % n == e / n) ? 1.0 : 0.0;
+}
+
+// T = D^-1 R P' (apply_pivot) or D^-1 R in position order with a zero lower triangle; pivot = perm
+__global__ void qrb_emit_kernel(const double* A, const double* D, long long sD, const int* perm, double* T, int* pivot,
+                                long long sP, int n, int apply_pivot)
+{
+    const int chain = blockIdx.y;
+    const double* a = A + (size_t)chain * n * n;
+    const double* d = D + (size_t)chain * sD;
+    const int* pm = perm + (size_t)chain * n;
+    double* t = T + (size_t)chain * n * n;
+    for (int pos = blockIdx.x; pos < n; pos += gridDim.x) {
+        const int dst = apply_pivot ? pm[pos] : pos;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) t[i + (size_t)dst * n] = (i <= pos) ? a[i + (size_t)pos * n] / d[i] : 0.0;
+        if (threadIdx.x == 0) pivot[(size_t)chain * sP + pos] = pm[pos];
+    }
+}
+
+size_t apply_smem(int n, int j)
+{
+    const int m = n - j;
+    const int ldv = m + ((8 - (m & 15)) & 15);
+    return ((size_t)NB * ldv + (size_t)m * TLD + (size_t)NB * TLD + 2) * sizeof(double);
+}
+
+template <int RT, int NWARPS>
+int launch_apply(const ApplyArgs& a, int batch, cudaStream_t st)
+{
+    const int strips = (a.n - a.c_lo) / 8;
+    if (strips <= 0) return 0;
+    dim3 grid((strips + NWARPS - 1) / NWARPS, batch);
+    qrb_apply_kernel<RT, NWARPS><<<grid, NWARPS * 32, apply_smem(a.n, a.j), st>>>(a);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+constexpr int AW = 8; // warps (strips) per CTA of the apply kernel
+
+// The whole factorisation on caller-provided scratch: norms [batch][n] doubles, perm [batch][n] ints,
+// Tfac [batch][n/NB][NB*NB] doubles. Launches only; no allocation.
+int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
+                           long long sP, int apply_pivot, double* norms, int* perm, double* Tfac, cudaStream_t st)
+{
+    const int npan = n / NB;
+    const bool small = n <= 192;
+    QrbArgs a;
+    a.n = n; a.A = X; a.D = D; a.sD = sD; a.norms = norms; a.perm = perm; a.Tfac = Tfac;
+    ApplyArgs ap;
+    ap.n = n; ap.A = X; ap.Tfac = Tfac; ap.norms = norms;
+    for (int p = 0; p < npan; ++p) {
+        a.j = p * NB;
+        if (small) qrb_panel_kernel<4, 6><<<batch, 128, panel_smem<4>(n), st>>>(a);
+        else qrb_panel_kernel<8, 7><<<batch, 256, panel_smem<8>(n), st>>>(a);
+        MCB_CUDA(cudaGetLastError());
+        ap.j = a.j; ap.c_lo = a.j + NB; ap.mode = 0; ap.Cm = X;
+        if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
+        else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
+    }
+    // explicit Q: the block reflectors in reverse order on the identity; panel p leaves columns < p*NB alone
+    qrb_identity_kernel<<<dim3(8, batch), 256, 0, st>>>(U, n);
+    MCB_CUDA(cudaGetLastError());
+    ap.mode = 1; ap.Cm = U;
+    for (int p = npan - 1; p >= 0; --p) {
+        ap.j = p * NB; ap.c_lo = p * NB;
+        if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
+        else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
+    }
+    qrb_emit_kernel<<<dim3(n < 64 ? n : 64, batch), 128, 0, st>>>(X, D, sD, perm, T, pivot, sP, n, apply_pivot);
+    MCB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace
+
+bool udt_blocked_supported(int n) { return n % NB == 0 && n >= 128 && n <= 400; }
+
+int init_udt_blocked_kernels()
+{
+    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<4, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<4>(192)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<8, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<8>(400)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<24, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(192, 0)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<50, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(400, 0)));
+    return 0;
+}
+
+// same contract as launch_udt (udt.cuh); X is the workspace the factorisation happens in
+int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
+                       long long sP, int apply_pivot, cudaStream_t st)
+{
+    const int npan = n / NB;
+    double* norms = nullptr; int* perm = nullptr; double* Tfac = nullptr;
+    MCB_CUDA(cudaMallocAsync(&norms, (size_t)batch * n * sizeof(double), st));
+    MCB_CUDA(cudaMallocAsync(&perm, (size_t)batch * n * sizeof(int), st));
+    MCB_CUDA(cudaMallocAsync(&Tfac, (size_t)batch * npan * NB * NB * sizeof(double), st));
+    int rc;
+    {
+        LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
+        rc = udt_blocked_on_scratch(n, batch, X, U, D, sD, T, pivot, sP, apply_pivot, norms, perm, Tfac, st);
+    }
+    MCB_CUDA(cudaFreeAsync(norms, st));
+    MCB_CUDA(cudaFreeAsync(perm, st));
+    MCB_CUDA(cudaFreeAsync(Tfac, st));
+    return rc;
+}
+
+} // namespace mcb

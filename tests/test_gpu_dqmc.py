@@ -90,9 +90,20 @@ def test_udt_contract(n, apply_pivot, linalg_path):
             P[np.arange(n), piv[k]] = 1.0
             assert np.abs(U[k] @ np.diag(D[k]) @ np.triu(T[k]) @ P - X[k]).max() < 1e-12 * scale * n
         Uo, Do, To, po = orc.udt_pivot(X[k], bool(apply_pivot))
-        assert np.allclose(D[k], Do, rtol=1e-9)
+        assert sorted(piv[k]) == list(range(n))
         if np.array_equal(po, piv[k]):
+            assert np.allclose(D[k], Do, rtol=1e-9)
             assert np.abs(U[k] - Uo).max() < 1e-9
+        else:
+            # panel-pivoted kernels (n % 16 == 0, n >= 128, csrc/udt_blocked.cu) choose 16 columns at a time:
+            # the factorisation is a different one, with the same determinant and the same scale separation
+            assert not linalg_path and n % 16 == 0 and n >= 128
+            assert np.isclose(np.log(D[k]).sum(), np.log(Do).sum(), rtol=1e-9, atol=1e-9)
+            Tt = np.triu(T[k]) if not apply_pivot else T[k]
+            assert np.abs(Tt).max() < 8.0                      # strict pivoting bounds |T_ij| by 1
+            assert np.linalg.cond(Tt) < 50 * np.linalg.cond(np.triu(To) if not apply_pivot else To)
+            lead = D[k].reshape(-1, 16)[:, 0]                  # the largest column of every panel: non-increasing
+            assert np.all(np.diff(lead) <= 1e-9 * lead[0])
 
 
 @pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
