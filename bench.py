@@ -124,11 +124,28 @@ def dist_env():
             int(os.environ.get("WORLD_SIZE", 1)))
 
 
-def traffic_for(kernel):
+def traffic_for(workload, kernel):
+    """DRAM bytes per launch from an ncu --set full capture of THIS workload's kernel shape, else None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
-        return json.load(open(p)).get(kernel)
+        return json.load(open(p)).get(workload, {}).get(kernel)
     return None
+
+
+def config_for(name, w, world):
+    """The `config` object of the JSON line. A function of the workload and the GPU count only, so that the
+    reference arm and ours print the same keys and values (the driver compares them)."""
+    if w["kind"] == "ising":
+        return {"workload": name, "L": w["L"], "beta": w["beta"], "replicas_per_gpu": w["replicas"],
+                "total_replicas": world * w["replicas"], "sweeps_per_step": 10,
+                "l2_policy": "planes (2 MiB/replica) are L2-resident by design; HBM figure is algorithmic"}
+    N, M, C_ = w["L"] ** 2, int(round(w["beta"] / w["dtau"])), w["chains"]
+    big = C_ * N * N * 8 * (2 * (M // w["safe_mult"] + 2) + 11) > 126e6
+    return {"workload": name, "lattice": f"{w['L']}x{w['L']}", "U": w["U"], "beta": w["beta"],
+            "delta_tau": w["dtau"], "slices": M, "safe_mult": w["safe_mult"], "chains_per_gpu": C_,
+            "total_chains": world * C_,
+            "l2_policy": "working set (stack + work matrices) exceeds L2" if big else
+                         "working set fits L2: state is device-resident by design, no flush"}
 
 
 # --------------------------------------------------------------------------- CPU baseline (oracle)
@@ -194,7 +211,7 @@ def run_reference(args, w, rank):
         line = dict(impl="reference", metric="Ising spin-flip attempts/ns", value=b["value"], unit=b["unit"],
                     n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=None,
                     higher_is_better=True, scaling="weak", vs_baseline=None, dtype="u64 bit-planes",
-                    data="synthetic", config={"workload": args.workload},
+                    data="synthetic", config=config_for(args.workload, w, args.gpus),
                     cpu_baseline={k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
                     e2e=dict(value=b["value"], unit=b["unit"], h2d_bytes_per_step=0, d2h_bytes_per_step=0))
         print(json.dumps(line))
@@ -213,26 +230,28 @@ def run_reference(args, w, rank):
                              chain=c, native=native) for c in range(threads)]
     for c in chains:
         c.build_stack()
-    # bound the run: a step = one sweep of `threads` chains (one per core); cap total steps by time
+    # A step = `upd` update() calls of `threads` chains (one per core): a full sweep (2M updates) where that takes
+    # a few seconds at most, else a bounded part of one; chain-sweeps are counted in proportion. Exactly W warm-up
+    # steps and K timed steps as asked.
     t0 = time.perf_counter()
-    orc.sweep_many(chains, 1, threads)
-    one = time.perf_counter() - t0
-    warm = max(0, min(args.warmup - 1, int(20.0 / one)))
-    if warm:
-        orc.sweep_many(chains, warm, threads)
-    steps = max(1, min(args.steps, int(90.0 / one)))
+    orc.update_many(chains, 2, threads)
+    t_upd = (time.perf_counter() - t0) / 2
+    budget = 120.0 / max(1, args.steps + args.warmup)            # seconds per step
+    upd = int(max(1, min(2 * M, budget / max(t_upd, 1e-6))))
+    for _ in range(args.warmup):
+        orc.update_many(chains, upd, threads)
     t0 = time.perf_counter()
-    orc.sweep_many(chains, steps, threads)
+    for _ in range(args.steps):
+        orc.update_many(chains, upd, threads)
     dt = time.perf_counter() - t0
-    value = threads * steps / dt
-    sample = (f"each step = one full sweep of {threads} chains (one per host core, the reference is single-threaded "
-              f"per chain); {steps} of the requested {args.steps} steps timed to bound the run; C++ restatement of "
+    value = threads * args.steps * (upd / (2.0 * M)) / dt
+    sample = (f"each step = {upd} of the {2 * M} update() calls of a sweep, for {threads} chains (one per host core; "
+              f"the reference is single-threaded per chain), chain-sweeps counted in proportion; C++ restatement of "
               f"MonteCarlo.jl ({'-march=native' if native else 'x86-64-v3'}), not Julia")
     line = dict(impl="reference", metric="DQMC chain-sweeps/sec", value=value, unit="chain-sweeps/s",
-                n_gpus=args.gpus, steps=steps, warmup=warm + 1, ms_per_step=dt / steps * 1e3,
+                n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=dt / args.steps * 1e3,
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
-                config={"workload": args.workload, "lattice": f"{w['L']}x{w['L']}", "U": w["U"], "beta": w["beta"],
-                        "delta_tau": w["dtau"], "safe_mult": w["safe_mult"], "chains_per_step": threads},
+                config=config_for(args.workload, w, args.gpus),
                 cpu_baseline=dict(value=value, unit="chain-sweeps/s", cores=threads, kind="port", sample=sample),
                 e2e=dict(value=value, unit="chain-sweeps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line))
@@ -339,12 +358,7 @@ def run_dqmc(args, w, rank, local_rank, world):
         "metric": "DQMC chain-sweeps/sec", "value": value, "unit": "chain-sweeps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "lattice": f"{w['L']}x{w['L']}", "U": w["U"], "beta": w["beta"],
-                   "delta_tau": w["dtau"], "slices": M, "safe_mult": w["safe_mult"], "chains_per_gpu": C_,
-                   "total_chains": world * C_, "acceptance": acc,
-                   "l2_policy": "working set (stack + work matrices) exceeds L2" if
-                   C_ * N * N * 8 * (2 * (M // w["safe_mult"] + 2) + 11) > 126e6 else
-                   "working set fits L2: state is device-resident by design, no flush"},
+        "config": config_for(args.workload, w, world), "acceptance": acc,
         "gpu_launches": gpu_launches,
         "e2e": {"value": e2e_value, "unit": "chain-sweeps/s", "h2d_bytes_per_step": int(conf_np.nbytes),
                 "d2h_bytes_per_step": int(conf_np.nbytes + g_np.nbytes), "steps": e2e_steps,
@@ -358,26 +372,42 @@ def run_dqmc(args, w, rank, local_rank, world):
         "wall_s_timed_region": wall,
     }
     k = shares[top]
-    if top in ("gemm", "udt", "rdivp", "fused", "advance", "greens"):
-        line["roofline"] = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": fp64_peak,
-                            "unit": "TFLOP/s", "frac": (k["tflops"] or 0.0) / fp64_peak,
-                            "traffic": traffic_for(top), "avg_launch_us": k["avg_us"], "share_of_step": k["share"],
-                            "peak_source": "FP64 DGEMM measured in this run (MEASURED_PEAKS.json has no FP64 entry)"}
-    else:
-        # sweep_spatial: per accepted flip the reference moves 16 N^2 bytes
-        byts = 8.0 * acc_flop
-        gbs = byts / (pms[_lib.LAUNCH_CLASSES.index(top)] * 1e-3) / 1e9
-        line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-                            "frac": gbs / hbm_peak, "traffic": traffic_for(top), "avg_launch_us": k["avg_us"],
-                            "share_of_step": k["share"], "peak_source": hbm_src}
-    # the one collective of the path: all-reduce of per-chain moments over the ranks (NCCL when
-    # world > 1). Not timed: it happens once per run, after the sweeps.
+    # every DQMC launch class is FP64 contraction work (wrap / stack products, QR, the delayed-update flush
+    # G -= U * Rc of sweep_spatial: 2 N^2 flop per accepted flip): tensor (DMMA) roofline. The site loop inside
+    # sweep_spatial is latency-bound; its fraction of the tensor peak says how far the kernel is from pipe-bound.
+    line["roofline"] = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": fp64_peak,
+                        "unit": "TFLOP/s", "frac": (k["tflops"] or 0.0) / fp64_peak,
+                        "traffic": traffic_for(args.workload, top), "avg_launch_us": k["avg_us"],
+                        "share_of_step": k["share"],
+                        "peak_source": "FP64 DGEMM measured in this run (MEASURED_PEAKS.json has no FP64 entry)"}
+    # the one collective of the path: all-reduce of the observable moments (sum x, sum x^2 of <G>,
+    # occupation, CDC, SDC, pairing, energies per chain, plus the count) over the ranks, once per run after the sweeps.
+    # Outside the timed region of `value`; its own time is reported here (NCCL when world > 1).
     from montecarlo_jl_b200 import sharding
+    mc.enable_measurements()
+    mc.measure()
+    per_chain = {k2: v for k2, v in mc.observables().items() if k2 != "count"}
     rate = (st1["acc_local"] - st0["acc_local"]) / np.maximum(1, st1["prop_local"] - st0["prop_local"])
-    red, n_red = sharding.reduce_observables({"acceptance": rate}, device=dev)
-    line["observable_reduction"] = {"chains": n_red, "acceptance_mean": float(red["acceptance"][0]),
+    per_chain["acceptance"] = rate
+    mom, _ = sharding.local_moments(per_chain)
+    payload = int(sum(v.size for v in mom.values()) + 1) * 8
+    barrier()
+    t0 = time.perf_counter()
+    red, n_red = sharding.reduce_observables(per_chain, device=dev)
+    barrier()
+    red_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    line["observable_reduction"] = {"chains": n_red, "payload_bytes": payload, "ms": red_ms,
+                                    "acceptance_mean": float(red["acceptance"][0]),
                                     "acceptance_stderr": float(red["acceptance"][1]),
+                                    "occupation_mean": float(red["n"][0]),
                                     "collective": "nccl all_reduce(sum) of moments" if world > 1 else "none (1 rank)"}
+    # the other BASELINE.json configs, so that the driver's records (N = 1, 2, 4, 8) carry them too
+    if args.workload == "dqmc_A512" and not args.no_extra_configs:
+        line["configs"] = {
+            "dqmc_C128": quick_dqmc("dqmc_C128", rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps=3),
+            "dqmc_D32": quick_dqmc("dqmc_D32", rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps=2),
+            "ising64": quick_ising("ising64", rank, local_rank, world, max_over_ranks, barrier, steps=5),
+        }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         b = cpu_dqmc_baseline(w)
         line["cpu_baseline"] = {k2: b[k2] for k2 in ("value", "unit", "cores", "kind", "sample")}
@@ -387,6 +417,71 @@ def run_dqmc(args, w, rank, local_rank, world):
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------- the other BASELINE configs, short runs
+def quick_dqmc(name, rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps, warmup=3):
+    """Short device-timed run of another DQMC workload for the `configs` object of the default line: same
+    timing rules as the main number (W >= 3 warm-up sweeps, CUDA events on the library's stream, max over ranks)."""
+    import montecarlo_jl_b200 as mcb
+    from montecarlo_jl_b200 import _lib
+    w = WORKLOADS[name]
+    C_ = w["chains"]
+    model = mcb.HubbardModelAttractive(L=w["L"], U=w["U"])
+    mc = mcb.DQMC(model, n_chains=C_, seed=SEED, chain_offset=rank * C_, device=local_rank, beta=w["beta"],
+                  delta_tau=w["dtau"], safe_mult=w["safe_mult"], check_propagation_error=False)
+    L, N, M = mc.L, mc.N, mc.M
+    mc.build_stack()
+    mc.sweep(warmup)
+    st0 = mc.stats()
+    barrier()
+    mc.sweep(steps)
+    ms = max_over_ranks(L.mcb_dqmc_last_elapsed_ms(mc.h))
+    barrier()
+    st1 = mc.stats()
+    acc = float((st1["acc_local"] - st0["acc_local"]).sum()) / max(1.0, float((st1["prop_local"] - st0["prop_local"]).sum()))
+    value = world * C_ * steps / (ms * 1e-3)
+    nl = len(_lib.LAUNCH_CLASSES)
+    launches = np.zeros(nl, dtype=np.int64); pms = np.zeros(nl); timed = np.zeros(nl, dtype=np.int64); flops = np.zeros(nl)
+    _lib.check(L.mcb_dqmc_profile(mc.h, 1, 1))
+    st2 = mc.stats()
+    mc.sweep(1)
+    st3 = mc.stats()
+    _lib.check(L.mcb_dqmc_get_profile(mc.h, launches, pms, timed, flops))
+    _lib.check(L.mcb_dqmc_profile(mc.h, 0, 1))
+    acc_flop = 2.0 * N * N * float((st3["acc_local"] - st2["acc_local"]).sum())
+    kern = {}
+    for i, cls in enumerate(_lib.LAUNCH_CLASSES):
+        if timed[i] and pms[i] > 0:
+            f = flops[i] + (acc_flop if cls in ("sweep_spatial", "fused") else 0.0)
+            kern[cls] = dict(ms_per_step=float(pms[i]), share=float(pms[i] / pms.sum()), launches_per_step=int(launches[i]),
+                             tflops=f / (pms[i] * 1e-3) / 1e12, frac=f / (pms[i] * 1e-3) / 1e12 / fp64_peak)
+    top = max(kern, key=lambda c: kern[c]["share"])
+    F_sweep = M * float(N) ** 3 * (12.0 + 4.0 * acc + 40.0 / w["safe_mult"])
+    mc.close()
+    return {"metric": "DQMC chain-sweeps/sec", "value": value, "unit": "chain-sweeps/s", "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "config": config_for(name, w, world), "acceptance": acc,
+            "whole_sweep_frac": F_sweep * value / 1e12 / fp64_peak / world, "dominant_kernel": top, "kernels": kern}
+
+
+def quick_ising(name, rank, local_rank, world, max_over_ranks, barrier, steps, warmup=3):
+    import montecarlo_jl_b200 as mcb
+    w = WORKLOADS[name]
+    R, Ls = w["replicas"], w["L"]
+    sim = mcb.MC(mcb.IsingModel(Ls), beta=w["beta"], n_replicas=R, seed=SEED, replica_offset=rank * R, device=local_rank)
+    for _ in range(warmup):
+        sim.sweep(10)
+    barrier()
+    sim.sweep(steps * 10)
+    ms = max_over_ranks(sim.L.mcb_ising_last_elapsed_ms(sim.h))
+    barrier()
+    sim.close()
+    flips = float(world) * R * Ls * Ls * steps * 10
+    hbm_peak, _ = measured_peaks()
+    gbs = flips / world * (3.0 / 8.0) / (ms * 1e-3) / 1e9
+    return {"metric": "Ising spin-flip attempts/ns", "value": flips / (ms * 1e-3) / 1e9, "unit": "spin-flip attempts/ns",
+            "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "config": config_for(name, w, world),
+            "dominant_kernel": "ising_halfsweep_kernel", "hbm_frac_algorithmic": gbs / hbm_peak}
 
 
 # --------------------------------------------------------------------------- our arm: Ising
@@ -451,15 +546,13 @@ def run_ising(args, w, rank, local_rank, world):
     line = {"metric": "Ising spin-flip attempts/ns", "value": value, "unit": "spin-flip attempts/ns", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64 bit-planes", "data": "synthetic",
-            "config": {"workload": args.workload, "L": Ls, "beta": w["beta"], "replicas_per_gpu": R,
-                       "sweeps_per_step": sweeps_per_step,
-                       "l2_policy": "planes (2 MiB/replica) are L2-resident by design; HBM figure is algorithmic"},
+            "config": config_for(args.workload, w, world),
             "gpu_launches": gpu_launches,
             "e2e": {"value": world * R * Ls * Ls * e2e_steps * sweeps_per_step / dt / 1e9, "unit": "spin-flip attempts/ns",
                     "h2d_bytes_per_step": int(hnp.nbytes), "d2h_bytes_per_step": int(hnp.nbytes + 16 * R)},
             "clocks": clk.summary(),
             "roofline": {"kernel": "ising_halfsweep_kernel", "bound": "hbm", "achieved": gbs, "peak": hbm_peak,
-                         "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": traffic_for("ising"),
+                         "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": traffic_for(args.workload, "ising"),
                          "peak_source": hbm_src,
                          "avg_launch_us": 1e3 * ms / max(1, gpu_launches)}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -481,6 +574,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="dqmc_A512", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-configs", action="store_true",
+                    help="skip the short runs of the other BASELINE configs that the default line carries in `configs`")
     args = ap.parse_args()
     rank, local_rank, world = dist_env()
     w = WORKLOADS[args.workload]

@@ -777,3 +777,16 @@ extern "C" void orc_sweep_many(void** handles, int n_handles, int64_t n_sweeps, 
         });
     for (auto& th : pool) th.join();
 }
+
+// Same, in units of update() calls: lets bench.py's reference arm time a bounded part of a sweep per step on the
+// large lattices (a full 20 x 20, beta = 16 chain-sweep takes tens of seconds on one core).
+extern "C" void orc_update_many(void** handles, int n_handles, int64_t n_updates, int n_threads)
+{
+    if (n_threads < 1) n_threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < n_threads; ++t)
+        pool.emplace_back([=]() {
+            for (int i = t; i < n_handles; i += n_threads) orc_update(handles[i], n_updates);
+        });
+    for (auto& th : pool) th.join();
+}

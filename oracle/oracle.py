@@ -66,6 +66,7 @@ def lib(native=False):
     L.orc_uniform.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
     L.orc_philox.argtypes = [_u32p, _u32p, _u32p]
     L.orc_sweep_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int]
+    L.orc_update_many.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int64, C.c_int]
     L.orc_update_repulsive.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
     # measurements (measure_oracle.cpp)
     L.orc_meas_pairs.argtypes = [_f64p, C.c_int, C.c_int, C.c_int, _i32p, C.c_int64, _f64p, C.c_int]
@@ -220,6 +221,11 @@ class OracleDQMC:
 def sweep_many(chains, n_sweeps, n_threads):
     arr = (C.c_void_p * len(chains))(*[c.h for c in chains])
     chains[0].L.orc_sweep_many(arr, len(chains), n_sweeps, n_threads)
+
+
+def update_many(chains, n_updates, n_threads):
+    arr = (C.c_void_p * len(chains))(*[c.h for c in chains])
+    chains[0].L.orc_update_many(arr, len(chains), n_updates, n_threads)
 
 
 def vmul(A, B, mode):
