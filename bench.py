@@ -526,19 +526,20 @@ def run_ising(args, w, rank, local_rank, world):
     gpu_launches = int(L.mcb_ising_launch_count(sim.h) - l0)
     flips = float(world) * R * Ls * Ls * args.steps * sweeps_per_step
     value = flips / (ms * 1e-3) / 1e9
-    # e2e: spins up, sweeps, spins + (E, M) down
-    host = torch.empty(R * Ls * Ls, dtype=torch.int8).pin_memory()
-    hnp = host.numpy()
-    _lib.check(L.mcb_ising_get_spins(sim.h, hnp))
+    # e2e: spins up, sweeps, spins + (E, M) down, in the bit-packed wire format (1 bit per spin over PCIe)
+    nch = L.mcb_ising_spin_chunks(sim.h)
+    host = torch.empty(R * nch, dtype=torch.int64).pin_memory()
+    hnp = host.numpy().view(np.uint64)
+    _lib.check(L.mcb_ising_get_spins_bits(sim.h, hnp))
     E = np.empty(R, dtype=np.int64); Msum = np.empty(R, dtype=np.int64)
     e2e_steps = max(3, min(args.steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        _lib.check(L.mcb_ising_set_spins(sim.h, hnp))
+        _lib.check(L.mcb_ising_set_spins_bits(sim.h, hnp))
         _lib.check(L.mcb_ising_sweep(sim.h, sweeps_per_step))
         _lib.check(L.mcb_ising_measure(sim.h, E, Msum))
-        _lib.check(L.mcb_ising_get_spins(sim.h, hnp))
+        _lib.check(L.mcb_ising_get_spins_bits(sim.h, hnp))
     barrier()
     dt = max_over_ranks(time.perf_counter() - t0)
     hbm_peak, hbm_src = measured_peaks()

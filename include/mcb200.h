@@ -249,6 +249,13 @@ int mcb_ising_destroy(mcb_ising* h);
 /* mc.conf (IsingModel.jl:3-5): int8 +-1, layout [replica][y][x] (site index x + y*L) */
 int mcb_ising_set_spins(mcb_ising* h, const int8_t* spins);
 int mcb_ising_get_spins(mcb_ising* h, int8_t* spins);
+/* The same configuration in the recorder's wire format compress = BitArray(conf .== 1) (the scheme of
+ * src/models/HubbardModel/HubbardModel.jl:56-59 and ConfigRecorder src/configurations.jl:24-43 applied to IsingConf): per
+ * replica mcb_ising_spin_chunks(h) = ceil(L*L/64) little-endian 64-bit chunks, bit s = site x + y*L. 1 bit per spin
+ * over PCIe instead of 8. */
+int mcb_ising_spin_chunks(mcb_ising* h);
+int mcb_ising_set_spins_bits(mcb_ising* h, const uint64_t* chunks);
+int mcb_ising_get_spins_bits(mcb_ising* h, uint64_t* chunks);
 /* n x sweep(mc) (MC.jl:316-332) */
 int mcb_ising_sweep(mcb_ising* h, int64_t n_sweeps);
 /* energy(mc, m, conf) (IsingModel.jl:177-185) and sum(conf) (Ising/measurements.jl:72-78) */

@@ -111,6 +111,9 @@ SIGNATURES = {
     "mcb_ising_destroy": (C.c_int, [C.c_void_p]),
     "mcb_ising_set_spins": (C.c_int, [C.c_void_p, _i8]),
     "mcb_ising_get_spins": (C.c_int, [C.c_void_p, _i8]),
+    "mcb_ising_spin_chunks": (C.c_int, [C.c_void_p]),
+    "mcb_ising_set_spins_bits": (C.c_int, [C.c_void_p, _u64]),
+    "mcb_ising_get_spins_bits": (C.c_int, [C.c_void_p, _u64]),
     "mcb_ising_sweep": (C.c_int, [C.c_void_p, C.c_int64]),
     "mcb_ising_measure": (C.c_int, [C.c_void_p, _i64, _i64]),
     "mcb_ising_sweep_count": (C.c_int64, [C.c_void_p]),

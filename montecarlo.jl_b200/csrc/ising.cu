@@ -136,6 +136,47 @@ __global__ void ising_unpack_kernel(int8_t* spins, const uint64_t* planes, Ising
     }
 }
 
+// Spins in the recorder's wire format, BitArray(conf .== 1): per replica ceil(L*L/64) little-endian 64-bit chunks,
+// bit s = site x + y*L. One thread per chunk (not a hot path: one pass over L*L bits per call).
+__global__ void ising_planes_to_bits_kernel(uint64_t* bits, const uint64_t* planes, IsingGeom g, int chunks)
+{
+    const size_t total = (size_t)g.R * chunks, sites = (size_t)g.L * g.L;
+    const size_t words_per_plane = (size_t)g.L * g.W;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int rep = (int)(idx / chunks);
+        const size_t s0 = (idx % chunks) * 64;
+        uint64_t out = 0;
+        for (int b = 0; b < 64 && s0 + b < sites; ++b) {
+            const size_t site = s0 + b;
+            const int x = (int)(site % g.L), y = (int)(site / g.L);
+            const int colour = (x + y) & 1, xh = x >> 1;
+            const uint64_t word = planes[((size_t)rep * 2 + colour) * words_per_plane + (size_t)y * g.W + (xh >> 6)];
+            out |= ((word >> (xh & 63)) & 1ull) << b;
+        }
+        bits[idx] = out;
+    }
+}
+
+__global__ void ising_bits_to_planes_kernel(const uint64_t* bits, uint64_t* planes, IsingGeom g, int chunks)
+{
+    const size_t words_per_plane = (size_t)g.L * g.W;
+    const size_t total = (size_t)g.R * 2 * words_per_plane;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int rep = (int)(idx / (2 * words_per_plane));
+        const size_t rem2 = idx % (2 * words_per_plane);
+        const int colour = (int)(rem2 / words_per_plane);
+        const size_t rem = rem2 % words_per_plane;
+        const int y = (int)(rem / g.W), w = (int)(rem % g.W);
+        const uint64_t* src = bits + (size_t)rep * chunks;
+        uint64_t word = 0;
+        for (int b = 0; b < g.nbits; ++b) {
+            const size_t site = (size_t)(2 * (64 * w + b) + ((y + colour) & 1)) + (size_t)y * g.L;
+            word |= ((src[site >> 6] >> (site & 63)) & 1ull) << b;
+        }
+        planes[idx] = word;
+    }
+}
+
 // red[rep][0] += #aligned (site, up) + #aligned (site, right) bonds ; red[rep][1] += #up spins
 __global__ void ising_measure_kernel(const uint64_t* planes, IsingGeom g, unsigned long long* red)
 {
@@ -244,6 +285,35 @@ int mcb_ising_get_spins(mcb_ising* h, int8_t* spins)
     ising_unpack_kernel<<<1184, 256, 0, h->st>>>(h->spins_dev, h->planes, geom(h));
     MCB_CUDA(cudaGetLastError());
     MCB_CUDA(cudaMemcpyAsync(spins, h->spins_dev, (size_t)h->R * h->L * h->L, cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_ising_spin_chunks(mcb_ising* h) { return h ? (int)(((size_t)h->L * h->L + 63) / 64) : 0; }
+
+int mcb_ising_set_spins_bits(mcb_ising* h, const uint64_t* chunks)
+{
+    if (!h || !chunks) { set_error("null argument"); return MCB_ERR_ARG; }
+    MCB_CUDA(cudaSetDevice(h->device));
+    const int nch = mcb_ising_spin_chunks(h);
+    uint64_t* dev = reinterpret_cast<uint64_t*>(h->spins_dev);   // R*L*L bytes >= R*nch*8
+    MCB_CUDA(cudaMemcpyAsync(dev, chunks, (size_t)h->R * nch * sizeof(uint64_t), cudaMemcpyHostToDevice, h->st));
+    ising_bits_to_planes_kernel<<<592, 256, 0, h->st>>>(dev, h->planes, geom(h), nch);
+    MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    h->spins_set = true;
+    return MCB_OK;
+}
+
+int mcb_ising_get_spins_bits(mcb_ising* h, uint64_t* chunks)
+{
+    if (!h || !chunks) { set_error("null argument"); return MCB_ERR_ARG; }
+    MCB_CUDA(cudaSetDevice(h->device));
+    const int nch = mcb_ising_spin_chunks(h);
+    uint64_t* dev = reinterpret_cast<uint64_t*>(h->spins_dev);
+    ising_planes_to_bits_kernel<<<592, 256, 0, h->st>>>(dev, h->planes, geom(h), nch);
+    MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(cudaMemcpyAsync(chunks, dev, (size_t)h->R * nch * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->st));
     MCB_CUDA(cudaStreamSynchronize(h->st));
     return MCB_OK;
 }

@@ -15,6 +15,55 @@ constexpr int TLD = NB + 8;  // leading dimension of k-contiguous operands: 16-b
                              // are bank-conflict free when TLD % 16 == 8
 
 // ---------------------------------------------------------------------------------------------------------------------
+// The NB largest of nrm[j .. n) (squared norms: non-negative, NaN already mapped to +inf), by decreasing value, ties
+// to the lower position: sel[0 .. NB). NB rounds of a block-wide argmax on order-preserving integer keys (the bit
+// pattern of a non-negative double is monotone), one barrier per round; wkey [2][NWARPS], wpos [2][NWARPS] are
+// double-buffered by round parity. Every thread holds CPT candidates (position j + tid + u * NWARPS * 32).
+// Requires n - j >= NB. Ends with a barrier: sel is visible to the block.
+template <int NWARPS, int CPT>
+__device__ __forceinline__ void select_largest(const double* nrm, int j, int n, int tid, unsigned long long* wkey,
+                                               int* wpos, int* sel)
+{
+    const int lane = tid & 31, warp = tid >> 5;
+    unsigned long long key[CPT];
+#pragma unroll
+    for (int u = 0; u < CPT; ++u) {
+        const int c = j + tid + u * NWARPS * 32;
+        key[u] = c < n ? (unsigned long long)__double_as_longlong(nrm[c]) + 1ull : 0ull;   // 0 = no candidate
+    }
+    for (int r = 0; r < NB; ++r) {
+        unsigned long long bk = 0ull;
+        int bp = 0x7fffffff;
+#pragma unroll
+        for (int u = 0; u < CPT; ++u) {   // ascending positions: strict > keeps the lower position on ties
+            if (key[u] > bk) { bk = key[u]; bp = j + tid + u * NWARPS * 32; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bk, o);
+            const int op = __shfl_xor_sync(0xffffffffu, bp, o);
+            if (ok > bk || (ok == bk && op < bp)) { bk = ok; bp = op; }
+        }
+        const int buf = r & 1;
+        if (lane == 0) { wkey[buf * NWARPS + warp] = bk; wpos[buf * NWARPS + warp] = bp; }
+        __syncthreads();
+        bk = wkey[buf * NWARPS];
+        bp = wpos[buf * NWARPS];
+#pragma unroll
+        for (int w = 1; w < NWARPS; ++w) {
+            const unsigned long long ok = wkey[buf * NWARPS + w];
+            const int op = wpos[buf * NWARPS + w];
+            if (ok > bk || (ok == bk && op < bp)) { bk = ok; bp = op; }
+        }
+#pragma unroll
+        for (int u = 0; u < CPT; ++u)
+            if (bp == j + tid + u * NWARPS * 32) key[u] = 0ull;   // the winner leaves the pool
+        if (tid == 0) sel[r] = bp;
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // Panel layout: NW warps; for each of its row tiles t = warp + NW * u (8 rows of the active part) a thread owns row
 // l/4 and the four columns 4 * (l%4) + {0..3}: x[u][cc].
 //
@@ -233,6 +282,104 @@ __device__ __forceinline__ double apply_strip(double (&c)[RT][2], int mt, int t_
                 const double2 b = *reinterpret_cast<const double2*>(Vt + (size_t)(8 * t + rl) * TLD + kt * 8 + 2 * q);
                 dmma884(c[t][0], c[t][1], y[kt][0], b.x);
                 dmma884(c[t][0], c[t][1], y[kt][1], b.y);
+            }
+            if (t >= t_norm) nrm += c[t][0] * c[t][0] + c[t][1] * c[t][1];
+        }
+    }
+    return nrm;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Variants for the shared-memory-resident factorisation (udt_resident.cu). The reflector block lives ONCE in shared
+// memory, column-major with absolute row indices, V[r][k] at vs_index(k, r, ld): the row is XOR-ed with 8 for the
+// columns k with bit 1 set. That makes both access patterns of apply_strip conflict-free on one copy (ld % 16 == 8):
+//   first product  (16-byte loads: column kt*8 + l/4, row pair 8t + 2q)            8 lanes -> 8 distinct 16-byte slots
+//   third product  ( 8-byte loads: columns kt*8 + 2q (+1), row 8t + l/4)           2 lanes per bank pair = 2 wavefronts
+// Rows come in aligned groups of 16 (the active part starts at a multiple of 16 and has an even number of row tiles).
+__device__ __forceinline__ int vs_index(int k, int r, int ld) { return k * ld + (r ^ ((k & 2) << 2)); }
+
+// panel_gram on the swizzled buffer: the panel's active rows are row0 .. row0 + 8 mt - 1 (absolute).
+template <int GW>
+__device__ __forceinline__ void panel_gram_sw(const double* Vs, int ld, int row0, int mt, int warp, int lane, int nthreads,
+                                              int tid, double* Sred, double* Ssm)
+{
+    const int q = lane & 3, rl = lane >> 2;
+    if (warp < GW) {
+        double acc[2][2][2] = {};
+        for (int t = warp; t < mt; t += GW) {
+            double2 a[2];
+#pragma unroll
+            for (int ct = 0; ct < 2; ++ct)
+                a[ct] = *reinterpret_cast<const double2*>(Vs + vs_index(ct * 8 + rl, row0 + 8 * t + 2 * q, ld));
+#pragma unroll
+            for (int ct = 0; ct < 2; ++ct)
+#pragma unroll
+                for (int kt = 0; kt < 2; ++kt) {
+                    dmma884(acc[ct][kt][0], acc[ct][kt][1], a[ct].x, a[kt].x);
+                    dmma884(acc[ct][kt][0], acc[ct][kt][1], a[ct].y, a[kt].y);
+                }
+        }
+#pragma unroll
+        for (int ct = 0; ct < 2; ++ct)
+#pragma unroll
+            for (int kt = 0; kt < 2; ++kt)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                    Sred[(size_t)warp * NB * NB + (ct * 8 + rl) * NB + kt * 8 + 2 * q + e] = acc[ct][kt][e];
+    }
+    __syncthreads();
+    for (int e = tid; e < NB * NB; e += nthreads) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < GW; ++w) s += Sred[(size_t)w * NB * NB + e];
+        Ssm[e] = s;
+    }
+    __syncthreads();
+}
+
+// apply_strip on the swizzled buffer; the strip's tiles are rows row0 + 8t .. of its 8 columns.
+template <int RT>
+__device__ __forceinline__ double apply_strip_sw(double (&c)[RT][2], int mt, int t_norm, const double* Vs, int ld, int row0,
+                                                 const double* Ts, int lane)
+{
+    const int q = lane & 3, rl = lane >> 2;
+    double w[2][2];
+    {
+        double wh[2][2][2] = {};
+#pragma unroll
+        for (int t = 0; t < RT; ++t) {
+            if (t < mt) {
+#pragma unroll
+                for (int kt = 0; kt < 2; ++kt) {
+                    const double2 b = *reinterpret_cast<const double2*>(Vs + vs_index(kt * 8 + rl, row0 + 8 * t + 2 * q, ld));
+                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][0], b.x);
+                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][1], b.y);
+                }
+            }
+        }
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) { w[kt][0] = wh[0][kt][0] + wh[1][kt][0]; w[kt][1] = wh[0][kt][1] + wh[1][kt][1]; }
+    }
+    double y[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+    for (int ko = 0; ko < 2; ++ko)
+#pragma unroll
+        for (int ki = 0; ki < 2; ++ki) {
+            const double2 b = *reinterpret_cast<const double2*>(Ts + (size_t)(ko * 8 + rl) * TLD + ki * 8 + 2 * q);
+            dmma884(y[ko][0], y[ko][1], w[ki][0], b.x);
+            dmma884(y[ko][0], y[ko][1], w[ki][1], b.y);
+        }
+#pragma unroll
+    for (int ko = 0; ko < 2; ++ko) { y[ko][0] = -y[ko][0]; y[ko][1] = -y[ko][1]; }
+    double nrm = 0.0;
+#pragma unroll
+    for (int t = 0; t < RT; ++t) {
+        if (t < mt) {
+#pragma unroll
+            for (int kt = 0; kt < 2; ++kt) {
+                const int k0 = kt * 8 + 2 * q, r = (row0 + 8 * t + rl) ^ ((q & 1) << 3); // same swizzle for k0 and k0 + 1
+                dmma884(c[t][0], c[t][1], y[kt][0], Vs[k0 * ld + r]);
+                dmma884(c[t][0], c[t][1], y[kt][1], Vs[(k0 + 1) * ld + r]);
             }
             if (t >= t_norm) nrm += c[t][0] * c[t][0] + c[t][1] * c[t][1];
         }

@@ -226,6 +226,7 @@ int init_udt_kernels()
     MCB_CUDA(cudaFuncSetAttribute(udt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     MCB_CUDA(cudaFuncSetAttribute(rdivp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     if (init_udt_blocked_kernels()) return -2;
+    if (init_udt_resident_kernels()) return -2;
     return init_udt_cluster_kernels();
 }
 
@@ -237,6 +238,11 @@ int launch_udt(int n, int batch, double* X, long long sX, double* U, long long s
     // blocked panel-pivoted QR with DMMA trailing updates (udt_blocked.cu); MCB_UDT_BLOCKED=0 restores the
     // step-by-step kernels below for comparisons
     static const bool blocked_on = !(getenv("MCB_UDT_BLOCKED") && atoi(getenv("MCB_UDT_BLOCKED")) == 0);
+    // MCB_UDT_RESIDENT=0: the multi-kernel blocked path also where the matrix fits one SM's shared memory
+    static const bool resident_on = !(getenv("MCB_UDT_RESIDENT") && atoi(getenv("MCB_UDT_RESIDENT")) == 0);
+    if (blocked_on && resident_on && udt_resident_supported(n) && !force_general_udt() && sX == (long long)n * n &&
+        sU == sX && sT == sX)
+        return launch_udt_resident(n, batch, X, U, D, sD, T, pivot, sP, apply_pivot, st);
     if (blocked_on && udt_blocked_supported(n) && !force_general_udt() && sX == (long long)n * n && sU == sX && sT == sX)
         return launch_udt_blocked(n, batch, X, U, D, sD, T, pivot, sP, apply_pivot, st);
     static const bool prefer_smem = getenv("MCB_UDT_SMEM") && atoi(getenv("MCB_UDT_SMEM")) != 0;

@@ -26,6 +26,11 @@ bool udt_blocked_supported(int n);
 int init_udt_blocked_kernels();
 int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
                        long long sP, int apply_pivot, cudaStream_t st);
+// the same factorisation as one shared-memory-resident kernel per chain (udt_resident.cu): n = 128, 144
+bool udt_resident_supported(int n);
+int init_udt_resident_kernels();
+int launch_udt_resident(int n, int batch, const double* X, double* U, double* D, long long sD, double* T, int* pivot,
+                        long long sP, int apply_pivot, cudaStream_t st);
 // testing aid: route every size through udt_kernel / rdivp_kernel
 void set_force_general_udt(bool on);
 bool force_general_udt();

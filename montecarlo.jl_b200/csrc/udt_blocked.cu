@@ -92,19 +92,10 @@ __global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
     } else {
         for (int c = j + tid; c < n; c += T) { const double s = __ldcg(gn + c); nrm[c] = (s == s) ? s : INFINITY; }
     }
-    if (tid < NB) sel[tid] = -1;
     __syncthreads();
-    // ---- the NB largest, by decreasing norm (ties: lower position first)
-    for (int c = j + tid; c < n; c += T) {
-        const double v = nrm[c];
-        int rank = 0;
-        for (int o = j; o < n; ++o) {
-            const double w = nrm[o];
-            rank += (w > v || (w == v && o < c)) ? 1 : 0;
-        }
-        if (rank < NB) sel[rank] = c;
-    }
-    __syncthreads();
+    // ---- the NB largest, by decreasing norm (ties: lower position first); `part` is free until the Householder steps
+    qrb::select_largest<NW, (400 + NW * 32 - 1) / (NW * 32)>(nrm, j, n, tid, reinterpret_cast<unsigned long long*>(part),
+                                                              reinterpret_cast<int*>(part + 2 * NW), sel);
     // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
     if (tid < NB) pstage[tid] = perm[sel[tid]];
     if (tid == 0) {
@@ -362,3 +353,4 @@ int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long l
 }
 
 } // namespace mcb
+

@@ -55,6 +55,19 @@ class MC:
         _lib.check(self.L.mcb_ising_get_spins(self.h, buf))
         return buf.reshape(self.R, self.Ls, self.Ls).transpose(0, 2, 1).copy()
 
+    def conf_bits(self):
+        """The configurations in the recorder's wire format BitArray(conf .== 1): (R, ceil(L*L/64)) uint64, bit s of a
+        replica = site x + y*L (Julia's column-major linear index), least significant bit first."""
+        buf = np.empty(self.R * self.L.mcb_ising_spin_chunks(self.h), dtype=np.uint64)
+        _lib.check(self.L.mcb_ising_get_spins_bits(self.h, buf))
+        return buf.reshape(self.R, -1)
+
+    def set_conf_bits(self, bits):
+        bits = np.ascontiguousarray(bits, dtype=np.uint64)
+        if bits.shape != (self.R, self.L.mcb_ising_spin_chunks(self.h)):
+            raise ValueError("bits must have shape (replicas, ceil(L*L/64))")
+        _lib.check(self.L.mcb_ising_set_spins_bits(self.h, bits.reshape(-1)))
+
     def sweep(self, n=1):
         _lib.check(self.L.mcb_ising_sweep(self.h, n))
 
