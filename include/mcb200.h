@@ -185,6 +185,19 @@ int mcb_linalg_udt(int32_t n, int32_t batch, const double* X, double* U, double*
 /* rdivp!(A, T, O, pivot): A <- A[:,pivot] * triu(T)^-1 (src/linalg/general.jl:138-166) */
 int mcb_linalg_rdivp(int32_t n, int32_t batch, double* A, const double* T, const int32_t* pivot,
                      int32_t device_id);
+/* Allocation-free variant of mcb_linalg_udt. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). Unlike every other entry point it takes DEVICE pointers (the caller owns all buffers):
+ * X_dev [batch][n*n] input, used as workspace and overwritten; U_dev, T_dev [batch][n*n]; D_dev [batch][n];
+ * pivot_dev [batch][n] 0-based int32. `stream` is a cudaStream_t (NULL = default stream); the call only enqueues
+ * kernels and returns without synchronising. It runs the blocked panel-pivoted factorisation (csrc/udt_blocked.cu),
+ * same contract as mcb_linalg_udt: U D T = X, pivot order panel-wise.
+ * Limits: n a multiple of 16 with 128 <= n <= 400, batch <= 8; anything larger returns MCB_ERR_ARG. The scratch
+ * (448 000 bytes) is a static device array that every GPU that loads the library holds until exit; all calls share
+ * it, so calls that overlap on the GPU (two streams, two host threads) race. After the first call per device (which
+ * sets kernel attributes and looks up the array's address) it performs no cudaMalloc, cudaFree or other allocation. */
+int mcb_linalg_udt_noalloc(int32_t n, int32_t batch, double* X_dev, double* U_dev, double* D_dev, double* T_dev,
+                           int32_t* pivot_dev, int32_t apply_pivot, int32_t device_id, void* stream);
 /* calculate_greens_AVX!(Ul,Dl,Tl,Ur,Dr,Tr,G) (src/flavors/DQMC/stack.jl:337-393); inputs are NOT
  * clobbered here */
 int mcb_linalg_calculate_greens(int32_t n, int32_t batch, const double* Ul, const double* Dl,

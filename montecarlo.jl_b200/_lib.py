@@ -104,6 +104,8 @@ SIGNATURES = {
     "mcb_linalg_vmul": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, C.c_int32, C.c_int32]),
     "mcb_linalg_udt": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _f64, _f64, _i32, C.c_int32,
                                  C.c_int32]),
+    "mcb_linalg_udt_noalloc": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "mcb_linalg_rdivp": (C.c_int, [C.c_int32, C.c_int32, _f64, _f64, _i32, C.c_int32]),
     "mcb_linalg_calculate_greens": (C.c_int, [C.c_int32, C.c_int32] + [_f64] * 7 + [C.c_int32]),
     "mcb_ising_create": (C.c_int, [C.c_int32, C.c_double, C.c_int32, C.c_uint64, C.c_uint32,

@@ -354,3 +354,78 @@ int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long l
 
 } // namespace mcb
 
+// ---------------------------------------------------------------------------------------------- allocation-free entry
+// mcb_linalg_udt_noalloc (include/mcb200.h): the blocked factorisation above for callers that may not call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it). No counterpart in the reference.
+// The scratch the factorisation needs (trailing column norms, the column permutation
+// and the NB x NB block-reflector factors) lives in a file-scope device array of fixed size: n <= 400, batch <= 8.
+// Every GPU that loads the library holds these 448 000 bytes until the process exits. All calls share the array, so
+// two calls that overlap on the GPU (different streams, or different host threads) race; calls on one stream are fine.
+// Nothing in it has to start at zero: every element that is read was written earlier in the same call.
+#include "../../include/mcb200.h"
+#include <mutex>
+
+namespace mcb {
+namespace {
+
+constexpr int NOALLOC_MAX_N = 400, NOALLOC_MAX_BATCH = 8;
+constexpr size_t NA_NORMS_BYTES = (size_t)NOALLOC_MAX_BATCH * NOALLOC_MAX_N * sizeof(double);                     //  25 600
+constexpr size_t NA_TFAC_BYTES = (size_t)NOALLOC_MAX_BATCH * (NOALLOC_MAX_N / NB) * NB * NB * sizeof(double);     // 409 600
+constexpr size_t NA_PERM_BYTES = (size_t)NOALLOC_MAX_BATCH * NOALLOC_MAX_N * sizeof(int);                         //  12 800
+static __device__ __align__(256) unsigned char qrb_static_scratch[NA_NORMS_BYTES + NA_TFAC_BYTES + NA_PERM_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_na_mutex;
+unsigned char* g_na_scratch[NA_MAX_DEVICES] = {}; // device address of qrb_static_scratch per device (it is a
+                                                  // host-side stand-in in host code, not an address)
+
+// once per device, with that device current: kernel attributes and the device address of the scratch array
+int noalloc_setup(int dev, unsigned char** out)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        set_error("no CUDA device: libmcb200 has no CPU fallback");
+        return MCB_ERR_CUDA;
+    }
+    if (dev < 0 || dev >= count || dev >= NA_MAX_DEVICES) { set_error("bad device id"); return MCB_ERR_ARG; }
+    MCB_CUDA(cudaSetDevice(dev));
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    if (!g_na_scratch[dev]) {
+        if (init_udt_blocked_kernels() != 0) return MCB_ERR_CUDA;
+        unsigned char* p = nullptr;
+        MCB_CUDA(cudaGetSymbolAddress((void**)&p, qrb_static_scratch));
+        if (!p) { set_error("cudaGetSymbolAddress returned a null address"); return MCB_ERR_CUDA; }
+        g_na_scratch[dev] = p;
+    }
+    *out = g_na_scratch[dev];
+    return 0;
+}
+
+} // namespace
+} // namespace mcb
+
+extern "C" int mcb_linalg_udt_noalloc(int32_t n, int32_t batch, double* X_dev, double* U_dev, double* D_dev,
+                                      double* T_dev, int32_t* pivot_dev, int32_t apply_pivot, int32_t device_id,
+                                      void* stream)
+{
+    using namespace mcb;
+    if (!X_dev || !U_dev || !D_dev || !T_dev || !pivot_dev || n <= 0 || batch <= 0) { set_error("bad argument"); return MCB_ERR_ARG; }
+    if (!udt_blocked_supported(n) || n > NOALLOC_MAX_N) {
+        set_error("mcb_linalg_udt_noalloc: n must be a multiple of 16 with 128 <= n <= 400");
+        return MCB_ERR_ARG;
+    }
+    if (batch > NOALLOC_MAX_BATCH) {
+        set_error("mcb_linalg_udt_noalloc: batch exceeds the static scratch (at most 8 matrices per call)");
+        return MCB_ERR_ARG;
+    }
+    if (X_dev == U_dev || X_dev == T_dev || U_dev == T_dev) { set_error("udt: buffers alias"); return MCB_ERR_ARG; }
+    unsigned char* base = nullptr;
+    const int rc = noalloc_setup(device_id, &base);
+    if (rc != 0) return rc;
+    double* norms = reinterpret_cast<double*>(base);
+    double* Tfac = reinterpret_cast<double*>(base + NA_NORMS_BYTES);
+    int* perm = reinterpret_cast<int*>(base + NA_NORMS_BYTES + NA_TFAC_BYTES);
+    // launches only: no cudaMalloc / cudaFree / event creation, no synchronisation (the caller owns the stream)
+    return udt_blocked_on_scratch(n, batch, X_dev, U_dev, D_dev, n, T_dev, pivot_dev, n, apply_pivot, norms, perm, Tfac,
+                                  (cudaStream_t)stream);
+}
