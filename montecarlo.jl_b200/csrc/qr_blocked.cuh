@@ -63,6 +63,36 @@ __device__ __forceinline__ void select_largest(const double* nrm, int j, int n, 
     __syncthreads();
 }
 
+// The same selection by ranking (rank of a column = number of columns that precede it in the order above), the
+// comparisons of a column split over NT / 128 groups of threads and combined with integer atomics (exact, hence
+// order-independent). For m = n - j <= 256 candidates and NT = 512 threads: 4 groups, m / 4 comparisons per thread.
+// rankbuf: [m] ints of shared memory. Starts and ends with a barrier.
+template <int NT>
+__device__ __forceinline__ void select_by_rank(const double* nrm, int j, int n, int tid, int* rankbuf, int* sel)
+{
+    constexpr int G = NT / 128;
+    const int m = n - j, grp = tid >> 7, t = tid & 127;
+    for (int e = tid; e < m; e += NT) rankbuf[e] = 0;
+    __syncthreads();
+    const int mq = (m + G - 1) / G, o0 = j + grp * mq, o1 = min(n, o0 + mq);
+    for (int c = j + t; c < n; c += 128) {
+        const double v = nrm[c];
+        int rank = 0;
+#pragma unroll 4
+        for (int o = o0; o < o1; ++o) {
+            const double w = nrm[o];
+            rank += (w > v || (w == v && o < c)) ? 1 : 0;
+        }
+        if (rank) atomicAdd(&rankbuf[c - j], rank);
+    }
+    __syncthreads();
+    for (int e = tid; e < m; e += NT) {
+        const int r = rankbuf[e];
+        if (r < NB) sel[r] = j + e;
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // Panel layout: NW warps; for each of its row tiles t = warp + NW * u (8 rows of the active part) a thread owns row
 // l/4 and the four columns 4 * (l%4) + {0..3}: x[u][cc].
@@ -73,7 +103,16 @@ __device__ __forceinline__ void select_largest(const double* nrm, int j, int n, 
 //   v = [1; a_{k+1:,k} / xi1],  w_c = a_kc + s_c / xi1,  a_c -= tau w_c v.
 // The s_c of all columns travel in ONE reduction: 3 shuffle levels inside a warp, per-warp partials through shared
 // memory, one barrier. part: [2][NW][NB], rowk: [2][NB] doubles of shared memory; taus: [NB]; Dout: D + j (global).
-template <int NW, int TPW>
+// BAR_ID == 0: the NW warps are the whole CTA (__syncthreads); otherwise they are warps 0 .. NW-1 of a larger CTA
+// and meet at the named barrier BAR_ID.
+template <int NW, int BAR_ID>
+__device__ __forceinline__ void panel_barrier()
+{
+    if constexpr (BAR_ID == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"n"(BAR_ID), "n"(NW * 32) : "memory");
+}
+
+template <int NW, int TPW, int BAR_ID = 0>
 __device__ __forceinline__ void panel_steps(double (&x)[TPW][4], int mt, int warp, int lane, double* part, double* rowk,
                                             double* taus, double* Dout)
 {
@@ -117,7 +156,7 @@ __device__ __forceinline__ void panel_steps(double (&x)[TPW][4], int mt, int war
 #pragma unroll
             for (int cc = 0; cc < 4; ++cc) rowk[buf * NB + 4 * q + cc] = x[0][cc];
         }
-        __syncthreads();
+        panel_barrier<NW, BAR_ID>();
         double s = 0.0;
         if (lane < NB) {
             double s2 = 0.0;

@@ -24,11 +24,20 @@ using qrb::NB;
 using qrb::TLD;
 using qrb::vs_index;
 
+#ifdef UDTR_TIMING
+__device__ long long udtr_clk[64];
+#define UDTR_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) udtr_clk[i] = clock64(); } while (0)
+#else
+#define UDTR_T(i) do { } while (0)
+#endif
+
 constexpr int RW = 16;              // warps per CTA
 constexpr int RTH = RW * 32;
 constexpr int RMAXN = 144;
 constexpr int RRT = RMAXN / 8;      // row tiles of a strip
-constexpr int RTPW = (RRT + RW - 1) / RW;
+constexpr int PW = 4;               // warps that run the Householder steps of a panel (the others wait: more warps
+                                    // only add redundant per-step work, 1900 against 900 cycles per step)
+constexpr int RTPW = (RRT + PW - 1) / PW;
 constexpr int RGW = 4;              // warps of the Gram product
 
 struct ResArgs {
@@ -75,14 +84,15 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
     double* Tfac = a.Tfac + (size_t)chain * (n / NB) * NB * NB;
 
     // ---- load
+    UDTR_T(0);
     if (tid == 0) {
         mbar_init(mbar, 1);
-        const uint32_t colbytes = (uint32_t)n * sizeof(double);
-        mbar_expect_tx(mbar, (uint32_t)n * colbytes);
-        for (int c = 0; c < n; ++c) bulk_g2s(A + (size_t)c * ld, Xg + (size_t)c * n, colbytes, mbar);
+        mbar_expect_tx(mbar, (uint32_t)n * (uint32_t)n * sizeof(double));
     }
     for (int c = tid; c < n; c += RTH) perm[c] = c;
     __syncthreads();
+    // one column per thread: the copies are issued in parallel (the barrier counts bytes, whoever issues them)
+    if (tid < n) bulk_g2s(A + (size_t)tid * ld, Xg + (size_t)tid * n, (uint32_t)n * sizeof(double), mbar);
     mbar_wait(mbar, 0);
     for (int c = warp; c < n; c += RW) {
         const double* col = A + (size_t)c * ld;
@@ -93,12 +103,14 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
     }
 
     const int npan = n / NB;
+    UDTR_T(1);
     for (int p = 0; p < npan; ++p) {
         const int j = p * NB, m = n - j, mt = m / 8;
         __syncthreads();
+        if (p == 1) UDTR_T(10);
         // ---- the NB largest remaining columns, by decreasing norm (ties: lower position first)
-        qrb::select_largest<RW, 1>(nrm, j, n, tid, reinterpret_cast<unsigned long long*>(part),
-                                   reinterpret_cast<int*>(part + 2 * RW), sel);
+        qrb::select_by_rank<RTH>(nrm, j, n, tid, reinterpret_cast<int*>(part), sel);
+        if (p == 1) UDTR_T(11);
         // ---- gather the selected columns (all rows: rows < j carry R of earlier panels) into the reflector buffer
         int ps = 0;
         if (tid < NB) ps = perm[sel[tid]];
@@ -131,23 +143,29 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
         __syncthreads();
         if (tid < nd) perm[hole[tid]] = moved;
         if (tid < NB) perm[j + tid] = ps;
-        // ---- the panel in registers, NB Householder steps
-        double x[RTPW][4];
+        if (p == 1) UDTR_T(12);
+        // ---- the panel in registers of PW warps, NB Householder steps (named barrier of these warps per step)
+        __syncthreads();   // `part` was the selection's scratch
+        if (p == 1) UDTR_T(12);
+        if (warp < PW) {
+            double x[RTPW][4];
 #pragma unroll
-        for (int u = 0; u < RTPW; ++u) {
-            const int t = warp + RW * u;
+            for (int u = 0; u < RTPW; ++u) {
+                const int t = warp + PW * u;
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] : 0.0;
-        }
-        qrb::panel_steps<RW, RTPW>(x, mt, warp, lane, part, rowk, taus, dvec + j);
+                for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] : 0.0;
+            }
+            qrb::panel_steps<PW, RTPW, 1>(x, mt, warp, lane, part, rowk, taus, dvec + j);
 #pragma unroll
-        for (int u = 0; u < RTPW; ++u) {
-            const int t = warp + RW * u;
-            if (t < mt) {
+            for (int u = 0; u < RTPW; ++u) {
+                const int t = warp + PW * u;
+                if (t < mt) {
 #pragma unroll
-                for (int cc = 0; cc < 4; ++cc) Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] = x[u][cc];
+                    for (int cc = 0; cc < 4; ++cc) Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] = x[u][cc];
+                }
             }
         }
+        if (p == 1) UDTR_T(13);
         __syncthreads();
         // ---- R and V into the matrix; the buffer keeps the unit lower trapezoid
         {
@@ -161,6 +179,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
             if (r <= k) Vs[vs_index(k, j + r, ld)] = (r == k) ? 1.0 : 0.0;
         }
         __syncthreads();
+        if (p == 1) UDTR_T(14);
         qrb::panel_gram_sw<RGW>(Vs, ld, j, mt, warp, lane, RTH, tid, Sred, Ssm);
         if (warp == 0) qrb::panel_tfactor(Ssm, taus, lane, Sred);   // Sred[0 .. 255] is free again: T, column-major
         __syncthreads();
@@ -171,6 +190,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
             Tfac[(size_t)p * NB * NB + e] = v;
         }
         __syncthreads();
+        if (p == 1) UDTR_T(15);
         // ---- trailing update: A[j:, j+NB:] <- (I - V T' V') A[j:, j+NB:], one 8-column strip per warp and round
         for (int strip = warp; strip < (m - NB) / 8; strip += RW) {
             const int c0 = j + NB + 8 * strip;
@@ -191,8 +211,10 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
             s += __shfl_xor_sync(0xffffffffu, s, 2);
             if (q == 0) nrm[c0 + rl] = (s == s) ? s : INFINITY;
         }
+        if (p == 1) { __syncthreads(); UDTR_T(16); }
     }
     __syncthreads();
+    UDTR_T(2);
     // ---- emit T = D^-1 R P' (apply_pivot) or D^-1 R in position order with a zero lower triangle; pivot; D
     {
         double* Tg = a.T + (size_t)chain * n * n;
@@ -207,6 +229,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
         }
     }
     __syncthreads();
+    UDTR_T(3);
     // ---- form Q in place: Q = H_1 ... H_P I, block reflectors in reverse order
     for (int p = npan - 1; p >= 0; --p) {
         const int j = p * NB, m = n - j, mt = m / 8;
@@ -247,15 +270,17 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
         }
         __syncthreads();
     }
+    UDTR_T(4);
     // ---- U leaves by bulk copies
     fence_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (tid < n) {   // one column per thread, every issuing thread waits for its own bulk group
         double* Ug = a.U + (size_t)chain * n * n;
-        for (int c = 0; c < n; ++c) bulk_s2g(Ug + (size_t)c * n, A + (size_t)c * ld, (uint32_t)n * sizeof(double));
+        bulk_s2g(Ug + (size_t)tid * n, A + (size_t)tid * ld, (uint32_t)n * sizeof(double));
         bulk_commit();
         bulk_wait_all();
     }
+    UDTR_T(5);
 }
 
 } // namespace
@@ -280,6 +305,16 @@ int launch_udt_resident(int n, int batch, const double* X, double* U, double* D,
         udt_resident_kernel<<<batch, RTH, resident_smem(n), st>>>(a);
     }
     MCB_CUDA(cudaGetLastError());
+#ifdef UDTR_TIMING
+    {
+        long long h[64];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(h, udtr_clk, sizeof(h));
+        fprintf(stderr, "udt_resident cycles: load+norms %lld | all panels %lld | emit %lld | form Q %lld | store %lld || panel 1: select %lld gather+move %lld steps %lld writeback+patch %lld gram+T %lld apply %lld\n",
+                h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[4], h[11] - h[10], h[12] - h[11], h[13] - h[12],
+                h[14] - h[13], h[15] - h[14], h[16] - h[15]);
+    }
+#endif
     MCB_CUDA(cudaFreeAsync(a.Tfac, st));
     return 0;
 }
