@@ -337,6 +337,7 @@ int init_gemm_kernels()
         MCB_CUDA(cudaFuncSetAttribute(gemm_full_kernel<144, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     }
     if (set_gemm_attrs<48>() || set_gemm_attrs<64>() || set_gemm_attrs<80>()) return -2;
+    if (init_gemm_tma_kernels()) return -2;
     return 0;
 }
 
@@ -347,6 +348,12 @@ int launch_gemm(const GemmArgs& g, cudaStream_t st)
     LaunchScope scope(LC_GEMM, st, 2.0 * g.n * (double)g.n * g.n * g.batch);
     // a batch that fills the device with one CTA per matrix: the whole product stays in one CTA's registers
     static const int full_on = getenv("MCB_GEMM_FULL") ? atoi(getenv("MCB_GEMM_FULL")) : 1;
+    // TMA-staged tiles where a tile divides the matrix (MCB_GEMM_TMA=0: the register-staged kernels below)
+    static const int tma_on = getenv("MCB_GEMM_TMA") ? atoi(getenv("MCB_GEMM_TMA")) : 1;
+    static const int full_first = getenv("MCB_GEMM_FULL_FIRST") ? atoi(getenv("MCB_GEMM_FULL_FIRST")) : 0;
+    // (only where both tiles are contiguous along their long side, i.e. A B'; MCB_GEMM_TMA=2 forces every product)
+    const bool tma_wins = !g.transA && g.transB && g.n >= 144 && !(g.n == 144 && g.batch >= g_sms / 2);
+    if (tma_on && gemm_tma_supported(g) && (tma_wins || tma_on == 2) && !full_first) return launch_gemm_tma(g, st);
     if (g.n == 144 && full_on && g.batch >= g_sms / 2) return launch_gemm_full<144>(g, st);
     // the tile that wastes the least padded work
     auto padded = [&](int t) { const int k = (g.n + t - 1) / t * t; return (long long)k * k; };

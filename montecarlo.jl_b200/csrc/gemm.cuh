@@ -24,5 +24,9 @@ struct GemmArgs {
 
 int launch_gemm(const GemmArgs& g, cudaStream_t st);
 int init_gemm_kernels();
+// the same product with TMA-staged tiles (gemm_tma.cu) for sizes a 48 / 64 / 80 tile divides
+bool gemm_tma_supported(const GemmArgs& g);
+int launch_gemm_tma(const GemmArgs& g, cudaStream_t st);
+int init_gemm_tma_kernels();
 
 } // namespace mcb

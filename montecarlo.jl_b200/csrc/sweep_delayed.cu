@@ -38,6 +38,13 @@ namespace {
 constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr size_t TABLE_BYTES = (32 * 33 + 32) * sizeof(double) + 16;   // DD, xs of the block-wise decisions
 
+#ifdef SWD_TIMING
+__device__ long long swd_clk[32];
+#define SWD_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) swd_clk[i] = clock64(); } while (0)
+#else
+#define SWD_T(i) do { } while (0)
+#endif
+
 struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
     size_t smem;
@@ -216,6 +223,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         unif[i] = dqmc_uniform(a.key0, a.chain_offset + (uint32_t)chain, a.sweep, a.visit, (uint32_t)i);
     }
     int nacc = 0;
+    SWD_T(0);
     // (the host picks BW, see launch_sweep_delayed)
     constexpr bool blockwise = BW;
     const int nv = round_up(n, 32);                 // threads per group (whole warps)
@@ -236,6 +244,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         // previous flush done (G up to date in every CTA of the chain, buffers free)
         // (two sectors: also before the first block, the partner must be running before its shared memory is written)
         if (cls > 1 && (i0 > 0 || two)) cluster.sync(); else __syncthreads();
+        if (i0 == K) SWD_T(1);
         // ---- load the block's columns and rows; zero the padding the flush will read
         for (int j = warp; j < kb4; j += nwarps) {
             const double* gcol = Gg + (size_t)(i0 + j) * n;
@@ -250,11 +259,13 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         if constexpr (blockwise) {
             // ---- decisions on the diagonal block by a few warps, then the vector recurrences
             __syncthreads();
+            if (i0 == K) SWD_T(2);
             if (!(g.exp & 2)) {
                 const int kdec = (g.exp & 8) ? 1 : kb;
                 if (g.ndw == 8) { if (tid < 256) nacc += decide_block<8>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid); }
                 else if (tid < 128) nacc += decide_block<4>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid);
                 __syncthreads();
+                if (i0 == K) SWD_T(3);
                 if (g.exp & 4) {
                 } else if (2 * nv <= T) {
                     if (tid < nv) { if (tid < n) column_recurrence(Cc, ld, i0, kb, DD, xs, tid); }
@@ -347,6 +358,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             if (!(g.exp & 2) && worker && grp == 0) U[(kb - 1) * ld + e] = u_prev;
             __syncthreads();
         }
+        if (i0 == K) SWD_T(4);
         // ---- flush: G -= U * Rc on the FP64 tensor pipe. Warp tile 32 x 16 (4 x 2 DMMA tiles).
         const int tm = (g.np + 31) / 32, tn = (g.np + 15) / 16;
         for (int tile = warp + nwarps * frank; tile < ((g.exp & 1) ? 0 : tm * tn); tile += nwarps * fcls) {
@@ -395,8 +407,10 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                         if (row < n && col < n) Gg[row + (size_t)col * n] = gold[x][y][cc] - c[x][y][cc];
                     }
         }
+        if (i0 == K) { __syncthreads(); SWD_T(5); }
     }
     if (cls > 1) cluster.sync(); else __syncthreads();
+    SWD_T(6);
     // every CTA of the chain checks its share of G; rank 0 owns the chain's outputs
     bool bad = false;
     for (size_t e = tid + (size_t)T * frank; e < (size_t)n * n; e += (size_t)T * fcls) bad |= !isfinite(Gg[e]);
@@ -404,6 +418,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         for (int i = tid; i < n; i += T) cg[i] = s_out[i];
     if (__syncthreads_or(bad) && tid == 0) atomicAdd((unsigned long long*)&a.nonfinite[chain], 1ull);
     if (crank == 0 && tid == 0) { a.acc[chain] += nacc; a.prop[chain] += n; }
+    SWD_T(7);
 }
 
 } // namespace
@@ -462,6 +477,18 @@ int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
         if (bw) MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024, true>, a, g));
         else MCB_CUDA(cudaLaunchKernelEx(&cfg, sweep_delayed_kernel<1024, false>, a, g));
     }
+#ifdef SWD_TIMING
+    {
+        static int shown = 0;
+        if (shown++ < 3) {
+            long long h[32];
+            cudaStreamSynchronize(st);
+            cudaMemcpyFromSymbol(h, swd_clk, sizeof(h));
+            fprintf(stderr, "sweep_delayed n=%d K=%d cls=%d cycles: whole loop %lld | tail %lld || block 1: load %lld decide %lld recurrences %lld flush %lld\n",
+                    a.n, g.K, g.cls, h[6] - h[0], h[7] - h[6], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[4]);
+        }
+    }
+#endif
     return 0;
 }
 

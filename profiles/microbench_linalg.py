@@ -17,6 +17,15 @@ L = _lib.lib()
 if len(sys.argv) > 4:
     L.mcb_linalg_force_general(1)
 rng = np.random.default_rng(0)
+if op == "vmul":   # batched n x n products, all three transpose modes (kernel times under ncu)
+    A = rng.standard_normal(b * n * n)
+    Bm = rng.standard_normal(b * n * n)
+    Cm = np.empty(b * n * n)
+    for _ in range(3):
+        for mode in (0, 1, 2):
+            _lib.check(L.mcb_linalg_vmul(n, b, A, Bm, Cm, mode, 0))
+    print("done", op, n, b)
+    sys.exit(0)
 X = rng.standard_normal((b, n, n)) @ np.diag(np.logspace(0, -8, n))
 buf = np.ascontiguousarray(X.transpose(0, 2, 1)).reshape(-1)
 U, T = np.empty(b * n * n), np.empty(b * n * n)
