@@ -49,7 +49,6 @@ struct DelayedGeom {
     int n, np, ld, K, threads; // np = n rounded up to 8, ld = np + 4 (ld % 16 == 4 keeps DMMA fragment loads conflict-free)
     size_t smem;
     int cls;   // CTAs per chain (thread-block cluster), 1 = plain launch
-    int ndw;   // warps of the block-wise decision phase (4 or 8: 8 / 4 columns of the diagonal block per thread)
     int two;   // 1: the two CTAs of a cluster are the two spin sectors of the repulsive model (cls == 2)
     int exp;   // timing experiments (MCB_SWEEP_EXP): 1 = no flush, 2 = no site loop; results invalid
 };
@@ -68,18 +67,18 @@ DelayedGeom delayed_geom(int n)
     // block size: 24 measured best at N = 144 (196 against 204 us per slice with 32) and at N = 400 (1092 / 1124)
     static const int kcap = getenv("MCB_SWEEP_K") ? atoi(getenv("MCB_SWEEP_K")) : 24;
     if (K > kcap) K = kcap;
-    if (K > 32) K = 32;
+    if (K > 24) K = 24;   // the deciding warp keeps a row of the diagonal block in 24 registers (KMAX)
     if (K > round_up(n, 4)) K = round_up(n, 4);
     g.K = K;
-    g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : (n <= 256 ? 512 : 1024));
+    // 512 threads (128 registers each) for every N > 64: no spills in the deciding warp and the old tile values
+    // prefetched in the flush outweigh the sequential column / row recurrences at N = 400 (1.35 M against 1.49 M
+    // cycles per slice); MCB_SWEEP_THREADS=1024 restores the 64-register variant for comparisons
+    static const int thr = getenv("MCB_SWEEP_THREADS") ? atoi(getenv("MCB_SWEEP_THREADS")) : 0;
+    g.threads = n <= 32 ? 128 : (n <= 64 ? 256 : 512);
+    if (thr == 1024 && n > 256) g.threads = 1024;
     g.smem = hdr + 2 * (size_t)K * g.ld * sizeof(double) + TABLE_BYTES;
     static const int exp_flags = experiment_flags("MCB_SWEEP_EXP");
     g.exp = exp_flags;
-    // measured per slice: N = 144 (512 threads) 170 us with 8 decision warps against 181 with 4; N = 400 (1024 threads,
-    // 64 registers) 839 against 790
-    static const int dw = getenv("MCB_SWEEP_DW") ? atoi(getenv("MCB_SWEEP_DW")) : 0;
-    g.ndw = (g.threads >= 256 && g.threads <= 512) ? 8 : 4;
-    if ((dw == 4 || dw == 8) && g.threads >= 256) g.ndw = dw;
     return g;
 }
 
@@ -95,55 +94,73 @@ DelayedGeom delayed_geom(int n)
 //   row_j = Rc_j + sum_{j'<j} (x_j' DD[j][j']) row_j'                            (row role, frozen rows in Rc)
 // which is what the site-by-site updates of the columns j' > j and rows k > j add up to.
 constexpr int DLD = 33;        // row stride of DD (conflict-free column access)
-template <int NTH>
-__device__ __forceinline__ void dec_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NTH) : "memory"); }
 
-template <int ndw>   // deciding warps
+// One warp, the diagonal block in registers: lane a holds row a (KMAX entries), the pivot row travels by shuffles,
+// no shared-memory round trip and no barrier per site (the 8-warp shared-memory version took 670 cycles per site,
+// most of it the named barrier and the LDS -> FMA -> STS chain). Same operations in the same order, hence the same bits.
+constexpr int KMAX = 24;   // block size cap (delayed_geom): 24 entries of a row in registers
+
+struct DecideCtx {
+    double gamma_p, gamma_m, efac_p, efac_m;
+    int s_mine;        // lane j carries the field and the uniform of site j
+    double u_mine;
+    int kb, i0, lane, nacc;
+    double* xs;
+    int8_t* s_out;
+};
+
+// site J of the block (compile-time recursion keeps every register index static). The phase is bound by the
+// shuffle pipe (2 SHFL per entry of the pivot row: 12.3 k cycles per block of 24 at N = 144); starting the next
+// site's reciprocal chain under the rest of this site's update was measured and is no faster (14.4 k).
+template <int J>
+__device__ __forceinline__ void decide_site(double (&reg)[KMAX], DecideCtx& c)
+{
+    if constexpr (J < KMAX) {
+        if (J < c.kb) {   // warp-uniform
+            const double gii = __shfl_sync(0xffffffffu, reg[J], J);
+            const int s = __shfl_sync(0xffffffffu, c.s_mine, J);
+            const double u = __shfl_sync(0xffffffffu, c.u_mine, J);
+            const double gamma = s > 0 ? c.gamma_p : c.gamma_m;
+            const double efac = s > 0 ? c.efac_p : c.efac_m;
+            const double rt = 1.0 + gamma * (1.0 - gii);
+            const double x = gamma * fast_rcp(rt);          // speculative: only used if accepted
+            const double p = efac * (rt * rt);
+            const bool accept = (p > 1.0 || u < p);
+            const double mu = x * reg[J];                    // -u of row `lane`: u = x (e_i - G[:, i])
+            if (accept) {
+#pragma unroll
+                for (int b = J + 1; b < KMAX; ++b) {
+                    const double rowjb = __shfl_sync(0xffffffffu, reg[b], J);
+                    if (c.lane > J) reg[b] = fma(mu, rowjb, reg[b]);
+                }
+                ++c.nacc;
+            }
+            // column J is final: keep it scaled by x_J (0 if rejected) for the row recurrence
+            if (c.lane > J) reg[J] = accept ? mu : 0.0;
+            if (c.lane == 0) { c.xs[J] = accept ? x : 0.0; c.s_out[c.i0 + J] = (int8_t)(accept ? -s : s); }
+            decide_site<J + 1>(reg, c);
+        }
+    }
+}
+
 __device__ __forceinline__ int decide_block(const SweepArgs& a, const double* Cc, int ld, int i0, int kb,
                                             const int8_t* s_in, int8_t* s_out, const double* unif, double* DD,
-                                            double* xs, int tid)
+                                            double* xs, int lane)
 {
-    const int ra = tid & 31, cg0 = tid >> 5;   // my row, my first column; columns cg0, cg0 + ndw, ... (ndw warps)
-    double* myrow = DD + ra * DLD;
+    double reg[KMAX];
 #pragma unroll
-    for (int q = 0; q < 32 / ndw; ++q) {
-        const int b = cg0 + ndw * q;
-        if (b < 32) myrow[b] = (ra < kb && b < kb) ? Cc[b * ld + i0 + ra] : 0.0;
-    }
-    dec_bar<32 * ndw>();
-    int nacc = 0;
-    for (int j = 0; j < kb; ++j) {
-        const int i = i0 + j;
-        const double* rowj = DD + j * DLD;
-        const double gii = rowj[j];
-        const int s = s_in[i];
-        const double gamma = s > 0 ? a.gamma_p : a.gamma_m;
-        const double efac = s > 0 ? a.efac_p : a.efac_m;
-        const double rt = 1.0 + gamma * (1.0 - gii);
-        const double x = gamma * fast_rcp(rt);          // speculative: only used if accepted
-        const double p = efac * (rt * rt);
-        const bool accept = (p > 1.0 || unif[i] < p);    // uniform over the deciding warps
-        if (accept) {
-            if (ra > j && ra < kb) {
-                const double mu = x * myrow[j];           // -u of row ra: u = x (e_i - G[:, i])
+    for (int b = 0; b < KMAX; ++b) reg[b] = (lane < kb && b < kb) ? Cc[b * ld + i0 + lane] : 0.0;
+    DecideCtx c{a.gamma_p, a.gamma_m, a.efac_p, a.efac_m, lane < kb ? (int)s_in[i0 + lane] : 1,
+                lane < kb ? unif[i0 + lane] : 2.0, kb, i0, lane, 0, xs, s_out};
+    decide_site<0>(reg, c);
+    {   // all 32 rows and columns of the table: the recurrences read (and discard) the padded ones
+        double* myrow = DD + lane * DLD;
 #pragma unroll
-                for (int q = 0; q < 32 / ndw; ++q) {
-                    const int b = cg0 + ndw * q;
-                    if (b > j && b < kb) myrow[b] = fma(mu, rowj[b], myrow[b]);
-                }
-            }
-            ++nacc;
-        }
-        if (tid == 0) { xs[j] = accept ? x : 0.0; s_out[i] = (int8_t)(accept ? -s : s); }
-        dec_bar<32 * ndw>();
-    }
-    // lower triangle: column j' of the block scaled by x_j' for the row recurrence
+        for (int b = 0; b < KMAX; ++b) myrow[b] = reg[b];
 #pragma unroll
-    for (int q = 0; q < 32 / ndw; ++q) {
-        const int b = cg0 + ndw * q;
-        if (b < ra && ra < kb) myrow[b] *= xs[b];
+        for (int b = KMAX; b < 32; ++b) myrow[b] = 0.0;
     }
-    return nacc;
+    return c.nacc;
 }
 
 // Both recurrences run in sub-blocks of 8 sites: the contributions of all earlier sub-blocks are plain sums with
@@ -262,8 +279,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             if (i0 == K) SWD_T(2);
             if (!(g.exp & 2)) {
                 const int kdec = (g.exp & 8) ? 1 : kb;
-                if (g.ndw == 8) { if (tid < 256) nacc += decide_block<8>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid); }
-                else if (tid < 128) nacc += decide_block<4>(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, tid);
+                if (warp == 0) nacc += decide_block(a, Cc, ld, i0, kdec, s_in, s_out, unif, DD, xs, lane);
                 __syncthreads();
                 if (i0 == K) SWD_T(3);
                 if (g.exp & 4) {
@@ -375,6 +391,23 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             for (int x = 0; x < 4; ++x)
 #pragma unroll
                 for (int y = 0; y < 2; ++y) c[x][y][0] = c[x][y][1] = 0.0;
+            // read-modify-write of the tile. Where the register budget allows (512 threads: 128 registers each) the old
+            // values are requested BEFORE the product, so that their L2 latency hides under the DMMAs; the 1024-thread
+            // variant (64 registers) loads them afterwards.
+            constexpr bool PREFETCH = MAXT <= 512;
+            double gold[4][2][2];
+            auto load_old = [&]() {
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 2; ++y)
+#pragma unroll
+                        for (int cc = 0; cc < 2; ++cc) {
+                            const int row = row0 + 8 * x + r, col = col0 + 8 * y + 2 * q + cc;
+                            gold[x][y][cc] = (row < n && col < n) ? __ldcg(Gg + row + (size_t)col * n) : 0.0;
+                        }
+            };
+            if (PREFETCH) load_old();
             for (int k0 = 0; k0 < kb4; k0 += 4) {
                 double av[4], bv[2];
 #pragma unroll
@@ -386,17 +419,7 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
 #pragma unroll
                     for (int y = 0; y < 2; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
             }
-            // read-modify-write of the tile: all loads first, then the stores
-            double gold[4][2][2];
-#pragma unroll
-            for (int x = 0; x < 4; ++x)
-#pragma unroll
-                for (int y = 0; y < 2; ++y)
-#pragma unroll
-                    for (int cc = 0; cc < 2; ++cc) {
-                        const int row = row0 + 8 * x + r, col = col0 + 8 * y + 2 * q + cc;
-                        gold[x][y][cc] = (row < n && col < n) ? Gg[row + (size_t)col * n] : 0.0;
-                    }
+            if (!PREFETCH) load_old();
 #pragma unroll
             for (int x = 0; x < 4; ++x)
 #pragma unroll
