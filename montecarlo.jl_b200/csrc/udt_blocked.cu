@@ -42,30 +42,33 @@ struct QrbArgs {
 };
 
 // ---------------------------------------------------------------------------------------------- panel
-template <int NW>
+// PW = warps that run the Householder steps, GW = warps of the Gram product
+template <int PW, int GW>
 size_t panel_smem(int n)
 {
     const size_t ldp = n + 8; // ldp % 16 == 8 for n % 16 == 0
-    return (2 * NB * ldp + NB * NB /*Ptop*/ + n /*nrm*/ + 2 * NW * NB + 2 * NB + NB * NB /*Ssm*/ +
-            (size_t)NW * NB * NB /*Sred*/ + NB /*taus*/ + 2 /*mbarrier*/) * sizeof(double) + (4 * NB + 4) * sizeof(int);
+    return (2 * NB * ldp + NB * NB /*Ptop*/ + n /*nrm*/ + 2 * PW * NB + 2 * NB + NB * NB /*Ssm*/ +
+            (size_t)GW * NB * NB /*Sred*/ + NB /*taus*/ + 2 /*mbarrier*/) * sizeof(double) + (4 * NB + 4) * sizeof(int);
 }
 
-template <int NW, int TPW>
-__global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
+// NT threads; the Householder steps run on warps 0 .. PW-1 (more warps only add redundant per-step work: 1425
+// cycles per step with 8 warps of a 256-thread CTA, 910 with 4), everything else on all of them
+template <int NT, int PW, int TPW, int GW>
+__global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
 {
     extern __shared__ __align__(16) double sm[];
     const int n = a.n, j = a.j, chain = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int T = NW * 32;
+    constexpr int T = NT, NW = NT / 32;
     const int ldp = n + 8;
     double* P = sm;                              // [NB][ldp] the panel, all n rows
     double* Dsp = P + (size_t)NB * ldp;          // [NB][ldp] staging of the displaced columns
     double* Ptop = Dsp + (size_t)NB * ldp;       // [NB][NB] raw top block of the factored panel
     double* nrm = Ptop + NB * NB;                // [n]
-    double* part = nrm + n;                      // [2][NW][NB]
-    double* rowk = part + 2 * NW * NB;           // [2][NB]
+    double* part = nrm + n;                      // [2][PW][NB]
+    double* rowk = part + 2 * PW * NB;           // [2][NB]
     double* Ssm = rowk + 2 * NB;                 // [NB][NB]
-    double* Sred = Ssm + NB * NB;                // [NW][NB*NB]
-    double* taus = Sred + (size_t)NW * NB * NB;  // [NB]
+    double* Sred = Ssm + NB * NB;                // [GW][NB*NB]; also the selection's rank table (n ints)
+    double* taus = Sred + (size_t)GW * NB * NB;  // [NB]
     uint64_t* mbar = reinterpret_cast<uint64_t*>(taus + NB);
     int* sel = reinterpret_cast<int*>(mbar + 2); // [NB] selected positions, [NB] displaced, [NB] holes, [NB] perm staging
     int* disp = sel + NB;
@@ -92,10 +95,8 @@ __global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
     } else {
         for (int c = j + tid; c < n; c += T) { const double s = __ldcg(gn + c); nrm[c] = (s == s) ? s : INFINITY; }
     }
-    __syncthreads();
-    // ---- the NB largest, by decreasing norm (ties: lower position first); `part` is free until the Householder steps
-    qrb::select_largest<NW, (400 + NW * 32 - 1) / (NW * 32)>(nrm, j, n, tid, reinterpret_cast<unsigned long long*>(part),
-                                                              reinterpret_cast<int*>(part + 2 * NW), sel);
+    // ---- the NB largest, by decreasing norm (ties: lower position first)
+    qrb::select_by_rank<NT>(nrm, j, n, tid, reinterpret_cast<int*>(Sred), sel);
     // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
     if (tid < NB) pstage[tid] = perm[sel[tid]];
     if (tid == 0) {
@@ -125,23 +126,25 @@ __global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
         for (int d = 0; d < nd; ++d) bulk_s2g(A + (size_t)hole[d] * n, Dsp + (size_t)d * ldp, (uint32_t)n * sizeof(double));
         bulk_commit();
     }
-    // ---- panel into registers, NB Householder steps
-    double x[TPW][4];
+    // ---- panel into the registers of PW warps, NB Householder steps (named barrier of these warps per step)
     const int q = lane & 3, rl = lane >> 2;
+    if (warp < PW) {
+        double x[TPW][4];
 #pragma unroll
-    for (int u = 0; u < TPW; ++u) {
-        const int t = warp + NW * u;
+        for (int u = 0; u < TPW; ++u) {
+            const int t = warp + PW * u;
 #pragma unroll
-        for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] : 0.0;
-    }
-    qrb::panel_steps<NW, TPW>(x, mt, warp, lane, part, rowk, taus, a.D + (size_t)chain * a.sD + j);
-    // ---- V back to P; the raw top block is kept aside while P carries the unit lower trapezoid for V'V
+            for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] : 0.0;
+        }
+        qrb::panel_steps<PW, TPW, 1>(x, mt, warp, lane, part, rowk, taus, a.D + (size_t)chain * a.sD + j);
+        // ---- V back to P; the raw top block is kept aside while P carries the unit lower trapezoid for V'V
 #pragma unroll
-    for (int u = 0; u < TPW; ++u) {
-        const int t = warp + NW * u;
-        if (t < mt) {
+        for (int u = 0; u < TPW; ++u) {
+            const int t = warp + PW * u;
+            if (t < mt) {
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc) P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] = x[u][cc];
+                for (int cc = 0; cc < 4; ++cc) P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] = x[u][cc];
+            }
         }
     }
     __syncthreads();
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(NW * 32) qrb_panel_kernel(QrbArgs a)
         P[(size_t)c * ldp + j + r] = r > c ? v : (r == c ? 1.0 : 0.0);
     }
     __syncthreads();
-    qrb::panel_gram<NW>(P, ldp, j, mt, warp, lane, T, tid, Sred, Ssm);
+    qrb::panel_gram<GW>(P, ldp, j, mt, warp, lane, T, tid, Sred, Ssm);
     if (warp == 0) qrb::panel_tfactor(Ssm, taus, lane, a.Tfac + ((size_t)chain * (n / NB) + j / NB) * NB * NB);
     for (int e = tid; e < NB * NB; e += T) P[(size_t)(e / NB) * ldp + j + e % NB] = Ptop[e];
     fence_async_smem();
@@ -298,8 +301,8 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
     ap.n = n; ap.A = X; ap.Tfac = Tfac; ap.norms = norms;
     for (int p = 0; p < npan; ++p) {
         a.j = p * NB;
-        if (small) qrb_panel_kernel<4, 6><<<batch, 128, panel_smem<4>(n), st>>>(a);
-        else qrb_panel_kernel<8, 7><<<batch, 256, panel_smem<8>(n), st>>>(a);
+        if (small) qrb_panel_kernel<128, 4, 6, 4><<<batch, 128, panel_smem<4, 4>(n), st>>>(a);
+        else qrb_panel_kernel<512, 8, 7, 8><<<batch, 512, panel_smem<8, 8>(n), st>>>(a);
         MCB_CUDA(cudaGetLastError());
         ap.j = a.j; ap.c_lo = a.j + NB; ap.mode = 0; ap.Cm = X;
         if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
@@ -325,8 +328,8 @@ bool udt_blocked_supported(int n) { return n % NB == 0 && n >= 128 && n <= 400; 
 
 int init_udt_blocked_kernels()
 {
-    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<4, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<4>(192)));
-    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<8, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<8>(400)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<128, 4, 6, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<4, 4>(192)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<512, 8, 7, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<8, 8>(400)));
     MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<24, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(192, 0)));
     MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<50, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(400, 0)));
     return 0;
