@@ -114,6 +114,20 @@ int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G);
  * stacks are rebuilt only if the configuration changed since the last call. Layout [chain][col][row]. */
 int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
 
+/* CombinedGreensIterator(mc, recalculate) (src/flavors/DQMC/unequal_time_stack.jl:746-885) on the device: yields, for
+ * l = 1 .. n_slices, G(0 <- l), G(l <- 0) and G(l <- l) of the current configuration by advancing three UDT triples one
+ * slice at a time (quick advance :862-885), re-factorising them every safe_mult slices (:824-861) and recomputing them from
+ * the UnequalTimeStack every `recalculate` slices (:795-822; recalculate <= 0 selects the reference's default 4 safe_mult).
+ * mcb_dqmc_cgi_begin needs the handle at its measurement point (current_slice == 1 on the way up, where mc.s.greens = G(0);
+ * the reference asserts the slice at :770) and fails with MCB_ERR_STATE otherwise. mcb_dqmc_cgi_next advances one slice:
+ * *slice receives l, or 0 once all n_slices steps have been produced; each non-NULL host pointer receives the matrix
+ * ([chain][col][row], after _greens! when physical != 0). The results also stay on the device until the next step:
+ * mcb_dqmc_cgi_device_results returns the three device pointers (same order: G0l, Gl0, Gll) for on-device consumers.
+ * Sweeping or changing the configuration invalidates an iteration in progress. The sweep state is not disturbed. */
+int mcb_dqmc_cgi_begin(mcb_dqmc* h, int32_t recalculate);
+int mcb_dqmc_cgi_next(mcb_dqmc* h, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll);
+int mcb_dqmc_cgi_device_results(mcb_dqmc* h, const double** G0l, const double** Gl0, const double** Gll);
+
 /* Recorded configurations in the reference's wire format compress(mc, model, conf) = BitArray(conf .== 1)
  * (src/models/HubbardModel/HubbardModel.jl:56-59, ConfigRecorder src/configurations.jl:24-43): per chain
  * mcb_dqmc_conf_chunks(h) = ceil(N*M/64) little-endian 64-bit chunks, bit b = spin i + N*l. */
@@ -230,6 +244,9 @@ int mcb_dqmc_rep_get_stats(mcb_dqmc_rep* h, mcb_dqmc_chain_stats* out);
 /* greens(mc, k, l), the recorded-configuration wire format and resume!(mc) for the two-block handle: as the
  * mcb_dqmc_* functions of the same names (the spin-down stack sees the complemented bits) */
 int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
+/* the CombinedGreensIterator on both blocks; host layout [chain][flavor][col][row] like mcb_dqmc_rep_greens_unequal */
+int mcb_dqmc_rep_cgi_begin(mcb_dqmc_rep* h, int32_t recalculate);
+int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* h, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll);
 int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* h);
 int mcb_dqmc_rep_get_conf_bits(mcb_dqmc_rep* h, uint64_t* chunks);
 int mcb_dqmc_rep_set_conf_bits(mcb_dqmc_rep* h, const uint64_t* chunks);

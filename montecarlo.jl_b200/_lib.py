@@ -57,6 +57,9 @@ SIGNATURES = {
     "mcb_dqmc_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
     "mcb_dqmc_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
     "mcb_dqmc_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
+    "mcb_dqmc_cgi_begin": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcb_dqmc_cgi_next": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mcb_dqmc_cgi_device_results": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 3),
     "mcb_dqmc_resume": (C.c_int, [C.c_void_p, C.c_int64]),
     "mcb_dqmc_conf_chunks": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_set_conf_bits": (C.c_int, [C.c_void_p, _u64]),
@@ -86,6 +89,8 @@ SIGNATURES = {
     "mcb_dqmc_rep_get_state": (C.c_int, [C.c_void_p, C.POINTER(DqmcState)]),
     "mcb_dqmc_rep_get_stats": (C.c_int, [C.c_void_p, C.POINTER(DqmcChainStats)]),
     "mcb_dqmc_rep_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
+    "mcb_dqmc_rep_cgi_begin": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcb_dqmc_rep_cgi_next": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_void_p, C.c_void_p, C.c_void_p]),
     "mcb_dqmc_rep_conf_chunks": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_rep_get_conf_bits": (C.c_int, [C.c_void_p, _u64]),
     "mcb_dqmc_rep_set_conf_bits": (C.c_int, [C.c_void_p, _u64]),

@@ -255,6 +255,44 @@ int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double*
     return MCB_OK;
 }
 
+int mcb_dqmc_cgi_begin(mcb_dqmc* h, int32_t recalculate)
+{
+    REQUIRE(h, "null handle");
+    if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
+    API_TRY(engine_cgi_begin(h, recalculate));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_cgi_next(mcb_dqmc* h, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll)
+{
+    REQUIRE(h && slice, "null argument");
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
+    int l = 0;
+    const double* res[3] = {nullptr, nullptr, nullptr};
+    API_TRY(engine_cgi_next(h, physical, &l, res));
+    *slice = l;
+    if (l > 0) {
+        double* dst[3] = {G0l, Gl0, Gll};
+        for (int w = 0; w < 3; ++w)
+            if (dst[w]) MCB_CUDA(cudaMemcpyAsync(dst[w], res[w], h->mat * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    }
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_cgi_device_results(mcb_dqmc* h, const double** G0l, const double** Gl0, const double** Gll)
+{
+    REQUIRE(h && G0l && Gl0 && Gll, "null argument");
+    const double* res[3];
+    if (engine_cgi_last(h, res) != 0) return MCB_ERR_STATE;
+    *G0l = res[0]; *Gl0 = res[1]; *Gll = res[2];
+    return MCB_OK;
+}
+
 int mcb_dqmc_conf_chunks(mcb_dqmc* h) { return h ? (int)(((size_t)h->N * h->M + 63) / 64) : 0; }
 
 static int upload_bits(mcb_dqmc* h, const uint64_t* chunks)

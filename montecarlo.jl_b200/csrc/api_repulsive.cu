@@ -330,6 +330,45 @@ int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* r, int32_t slice1, int32_t slice2,
     return MCB_OK;
 }
 
+// CombinedGreensIterator on both blocks (unequal_time_stack.jl:746-885)
+int mcb_dqmc_rep_cgi_begin(mcb_dqmc_rep* r, int32_t recalculate)
+{
+    REQUIRE(r, "null handle");
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    for (mcb_dqmc* h : {r->up, r->dn}) {
+        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+        API_TRY(engine_cgi_begin(h, recalculate));
+    }
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* r, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll)
+{
+    REQUIRE(r && slice, "null argument");
+    mcb_dqmc* hs[2] = {r->up, r->dn};
+    const size_t nn = r->up->nn;
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    double* dst[3] = {G0l, Gl0, Gll};
+    int ls[2] = {0, 0};
+    for (int f = 0; f < 2; ++f) {
+        mcb_dqmc* h = hs[f];
+        const double* res[3] = {nullptr, nullptr, nullptr};
+        API_TRY(engine_cgi_next(h, physical, &ls[f], res));
+        if (ls[f] == 0) continue;
+        for (int w = 0; w < 3; ++w)
+            if (dst[w])
+                MCB_CUDA(cudaMemcpy2DAsync(dst[w] + f * nn, 2 * nn * sizeof(double), res[w], nn * sizeof(double),
+                                           nn * sizeof(double), h->C, cudaMemcpyDeviceToHost, h->st));
+    }
+    if (ls[0] != ls[1]) { set_error("CombinedGreensIterator: the two blocks are out of step"); return MCB_ERR_STATE; }
+    *slice = ls[0];
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
 // compress / decompress (HubbardModel.jl:56-59): the field travels as BitArray(conf .== 1); the spin-down stack
 // lives on the negated field, i.e. on the complemented bits
 int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* r) { return r ? mcb_dqmc_conf_chunks(r->up) : 0; }

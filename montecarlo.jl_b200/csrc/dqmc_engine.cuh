@@ -93,6 +93,10 @@ int engine_measure(mcb_dqmc* h);
 int engine_greens_unequal(mcb_dqmc* h, int slice1, int slice2);
 void unequal_free(mcb_dqmc* h);
 double* unequal_result(mcb_dqmc* h);
+// CombinedGreensIterator on the device (unequal.cu)
+int engine_cgi_begin(mcb_dqmc* h, int recalculate);
+int engine_cgi_next(mcb_dqmc* h, int physical, int* l_out, const double* results[3]);
+int engine_cgi_last(mcb_dqmc* h, const double* results[3]);
 // add_slice_sequence_left/right on raw (U, D, T) triples
 int advance_raw(mcb_dqmc* h, bool left, const double* Usrc, const double* Dsrc, const double* Tsrc, double* Udst,
                 double* Ddst, double* Tdst, int lo, int hi);

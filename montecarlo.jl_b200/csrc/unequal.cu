@@ -21,6 +21,16 @@ struct UtStack {
     double* G = nullptr; // result (ut_stack.greens): the sweep's own G (h->G) is never touched
     std::vector<void*> all;
     int64_t built_version = -1;
+    // CombinedGreensIterator state: (Ul Dl Tl) -> G(l <- 0), (Ur Dr Tr) -> G(0 <- l), (U D T) -> G(l <- l); the triples of the
+    // iterator are its own (the stabilised evaluations above clobber Ul .. Tr). out[0..2] = G0l, Gl0, Gll (effective),
+    // phys[0..2] the same after _greens!.
+    double *cUl = nullptr, *cDl = nullptr, *cTl = nullptr, *cUr = nullptr, *cDr = nullptr, *cTr = nullptr;
+    double *cU = nullptr, *cD = nullptr, *cT = nullptr, *cX = nullptr;
+    double* out[3] = {nullptr, nullptr, nullptr};
+    double* phys[3] = {nullptr, nullptr, nullptr};
+    const double* last[3] = {nullptr, nullptr, nullptr};   // results of the last step
+    int cgi_l = 0, cgi_recalc = 0;   // next slice to produce (0: no iteration in progress)
+    int64_t cgi_version = -1;
 };
 
 namespace mcb {
@@ -44,7 +54,7 @@ __global__ void vec_op_kernel(double* out, const double* in, size_t total, int m
 }
 
 // mode 0: C = A + B ; 1: C = -A ; 2: C = diag(d) (d per chain) ; 3: C = A * diag(d) ; 4: C = identity, d = 1 ;
-// 5: C = diag(B) * A * diag(d) (B, d vectors per chain)
+// 5: C = diag(B) * A * diag(d) (B, d vectors per chain) ; 6: C = A - I ; 7: C = diag(d) * A
 __global__ void mat_op_kernel(double* C, const double* A, const double* B, double* d, int n, size_t total, int mode)
 {
     const size_t nn = (size_t)n * n;
@@ -57,6 +67,8 @@ __global__ void mat_op_kernel(double* C, const double* A, const double* B, doubl
         else if (mode == 2) v = i == j ? d[chain * n + i] : 0.0;
         else if (mode == 3) v = A[e] * d[chain * n + j];
         else if (mode == 5) v = B[chain * n + i] * A[e] * d[chain * n + j];
+        else if (mode == 6) v = A[e] - (i == j ? 1.0 : 0.0);
+        else if (mode == 7) v = d[chain * n + i] * A[e];
         else {
             v = i == j ? 1.0 : 0.0;
             if (d && j == 0) d[chain * n + i] = 1.0;
@@ -324,6 +336,131 @@ int full2(mcb_dqmc* h, int slice1, int slice2)
     return mat_op(h, G, G, nullptr, nullptr, 1);
 }
 
+int cgi_alloc(mcb_dqmc* h)
+{
+    UtStack* u = h->ut;
+    if (u->cUl) return 0;
+    auto mat = [&](double*& p) {
+        MCB_CUDA(cudaMalloc(&p, h->mat * sizeof(double)));
+        u->all.push_back(p);
+        return 0;
+    };
+    auto vec = [&](double*& p) {
+        MCB_CUDA(cudaMalloc(&p, h->vec * sizeof(double)));
+        u->all.push_back(p);
+        return 0;
+    };
+    for (double** p : {&u->cUl, &u->cTl, &u->cUr, &u->cTr, &u->cU, &u->cT, &u->cX, &u->out[0], &u->out[1], &u->out[2],
+                       &u->phys[0], &u->phys[1], &u->phys[2]})
+        MCB_TRY(mat(*p));
+    for (double** p : {&u->cDl, &u->cDr, &u->cD}) MCB_TRY(vec(*p));
+    return 0;
+}
+
+int copy_mat(mcb_dqmc* h, double* dst, const double* src)
+{
+    MCB_CUDA(cudaMemcpyAsync(dst, src, h->mat * sizeof(double), cudaMemcpyDeviceToDevice, h->st));
+    return 0;
+}
+int copy_vec(mcb_dqmc* h, double* dst, const double* src)
+{
+    MCB_CUDA(cudaMemcpyAsync(dst, src, h->vec * sizeof(double), cudaMemcpyDeviceToDevice, h->st));
+    return 0;
+}
+// (U, D, T) = udt(X) with X kept
+int udt_of(mcb_dqmc* h, const double* X, double* U, double* D, double* T)
+{
+    MCB_TRY(copy_mat(h, h->ut->cX, X));
+    return udt(h, h->ut->cX, U, D, T, 1);
+}
+// X <- B_l X (multiply_slice_matrix_left!) and X <- X B_l^-1 (multiply_slice_matrix_inv_right!), through cX
+int cgi_mul_left(mcb_dqmc* h, int l, double*& X)
+{
+    GemmArgs g = base_gemm(h, h->hop[2], true, X, false, h->ut->cX);
+    g.mid = conf_scale(h, l, true);
+    MCB_TRY(launch_gemm(g, h->st));
+    std::swap(X, h->ut->cX);
+    return 0;
+}
+int cgi_mul_inv_right(mcb_dqmc* h, int l, double*& X)
+{
+    GemmArgs g = base_gemm(h, X, false, h->hop[3], true, h->ut->cX);
+    g.mid = conf_scale(h, l, false);
+    MCB_TRY(launch_gemm(g, h->st));
+    std::swap(X, h->ut->cX);
+    return 0;
+}
+// C = A diag(d) B
+int mdm(mcb_dqmc* h, const double* A, const double* d, const double* B, double* C)
+{
+    GemmArgs g = base_gemm(h, A, false, B, false, C);
+    g.mid = vec_scale(d, h->N);
+    return launch_gemm(g, h->st);
+}
+
+// iterate(it::CombinedGreensIterator) (:768-787): the three triples from G(0) = mc.s.greens
+int cgi_begin(mcb_dqmc* h, int recalculate)
+{
+    UtStack* u = h->ut;
+    MCB_TRY(cgi_alloc(h));
+    MCB_TRY(udt_of(h, h->G, u->cUl, u->cDl, u->cTl));
+    MCB_TRY(copy_mat(h, u->cU, u->cUl));
+    MCB_TRY(copy_vec(h, u->cD, u->cDl));
+    MCB_TRY(copy_mat(h, u->cT, u->cTl));
+    MCB_TRY(mat_op(h, u->cX, h->G, nullptr, nullptr, 6));
+    MCB_TRY(udt(h, u->cX, u->cUr, u->cDr, u->cTr, 1));
+    u->cgi_l = 1;
+    u->last[0] = u->last[1] = u->last[2] = nullptr;
+    u->cgi_recalc = recalculate > 0 ? recalculate : 4 * h->s;
+    u->cgi_version = h->conf_version;
+    return 0;
+}
+
+// iterate(it, l) (:789-885): recalculation, stabilisation or quick advance
+int cgi_step(mcb_dqmc* h)
+{
+    UtStack* u = h->ut;
+    const int l = u->cgi_l;
+    double *G0l = u->out[0], *Gl0 = u->out[1], *Gll = u->out[2];
+    if (l % u->cgi_recalc == 0) {   // (:795-822)
+        MCB_TRY(full1(h, l, 0));
+        MCB_TRY(copy_mat(h, Gl0, u->G));
+        MCB_TRY(full2(h, 0, l));
+        MCB_TRY(copy_mat(h, G0l, u->G));
+        MCB_TRY(full1(h, l, l));
+        MCB_TRY(copy_mat(h, Gll, u->G));
+        MCB_TRY(udt_of(h, Gll, u->cU, u->cD, u->cT));
+        MCB_TRY(udt_of(h, Gl0, u->cUl, u->cDl, u->cTl));
+        MCB_TRY(udt_of(h, G0l, u->cUr, u->cDr, u->cTr));
+        return 0;
+    }
+    MCB_TRY(cgi_mul_left(h, l, u->cUl));
+    MCB_TRY(cgi_mul_inv_right(h, l, u->cTr));
+    MCB_TRY(cgi_mul_left(h, l, u->cU));
+    MCB_TRY(cgi_mul_inv_right(h, l, u->cT));
+    MCB_TRY(mdm(h, u->cUl, u->cDl, u->cTl, Gl0));
+    MCB_TRY(mdm(h, u->cUr, u->cDr, u->cTr, G0l));
+    MCB_TRY(mdm(h, u->cU, u->cD, u->cT, Gll));
+    if (l % h->s != 0) return 0;    // quick advance (:862-885)
+    // stabilisation (:824-861): re-factorise the large side of every triple
+    // Gl0: (Ul, Dl, t) = udt(Ul Dl), Tl = t Tl
+    MCB_TRY(mat_op(h, u->t1, u->cUl, nullptr, u->cDl, 3));
+    MCB_TRY(udt(h, u->t1, u->cUl, u->cDl, u->t2, 1));
+    MCB_TRY(mm(h, u->t2, false, u->cTl, false, u->cX));
+    std::swap(u->cTl, u->cX);
+    // G0l: (t, Dr, Tr) = udt(Dr Tr), Ur = Ur t
+    MCB_TRY(mat_op(h, u->t1, u->cTr, nullptr, u->cDr, 7));
+    MCB_TRY(udt(h, u->t1, u->t2, u->cDr, u->cTr, 1));
+    MCB_TRY(mm(h, u->cUr, false, u->t2, false, u->cX));
+    std::swap(u->cUr, u->cX);
+    // Gll: (Q, D, t) = udt(U D) ; (t', D, T) = udt(D (t T)) ; U = Q t'
+    MCB_TRY(mat_op(h, u->t1, u->cU, nullptr, u->cD, 3));
+    MCB_TRY(udt(h, u->t1, u->t2, u->cD, u->t3, 1));
+    MCB_TRY(mm(h, u->t3, false, u->cT, false, u->t1, u->cD));
+    MCB_TRY(udt(h, u->t1, u->t3, u->cD, u->cT, 1));
+    return mm(h, u->t2, false, u->t3, false, u->cU);
+}
+
 } // namespace
 
 int engine_greens_unequal(mcb_dqmc* h, int slice1, int slice2)
@@ -334,6 +471,59 @@ int engine_greens_unequal(mcb_dqmc* h, int slice1, int slice2)
 }
 
 double* unequal_result(mcb_dqmc* h) { return h->ut ? h->ut->G : nullptr; }
+
+// CombinedGreensIterator(mc, recalculate) (unequal_time_stack.jl:746-787): needs G = G(tau = 0), i.e. the measurement
+// point current_slice == 1 on the way up (the assertion of :770; DQMC.jl's run loop measures only there)
+int engine_cgi_begin(mcb_dqmc* h, int recalculate)
+{
+    if (!h->stack_built || h->current_slice != 1 || h->direction != 1) {
+        set_error("CombinedGreensIterator: the handle must be at current_slice == 1 on the way up (G = G(0))");
+        return MCB_ERR_STATE;
+    }
+    MCB_TRY(ut_alloc(h));
+    MCB_TRY(ut_build(h));
+    return cgi_begin(h, recalculate);
+}
+
+// one step: *l_out = the slice the results belong to (1 .. M), 0 when the iteration is over. results[0..2] = device
+// pointers to G(0 <- l), G(l <- 0), G(l <- l), [chain][col][row], valid until the next step.
+int engine_cgi_next(mcb_dqmc* h, int physical, int* l_out, const double* results[3])
+{
+    UtStack* u = h->ut;
+    if (!u || u->cgi_l == 0 || u->cgi_version != h->conf_version) {
+        set_error("CombinedGreensIterator: no iteration in progress for this configuration (call cgi_begin)");
+        return MCB_ERR_STATE;
+    }
+    if (u->cgi_l > h->M) {
+        u->cgi_l = 0;
+        *l_out = 0;
+        return 0;
+    }
+    MCB_TRY(cgi_step(h));
+    for (int w = 0; w < 3; ++w) {
+        if (physical) { // _greens! (DQMC.jl:721-730)
+            MCB_TRY(launch_gemm(base_gemm(h, u->out[w], false, h->hop[0], true, u->cX), h->st));
+            MCB_TRY(launch_gemm(base_gemm(h, h->hop[1], true, u->cX, false, u->phys[w]), h->st));
+            results[w] = u->phys[w];
+        } else {
+            results[w] = u->out[w];
+        }
+    }
+    for (int w = 0; w < 3; ++w) u->last[w] = results[w];
+    *l_out = u->cgi_l++;
+    return 0;
+}
+
+int engine_cgi_last(mcb_dqmc* h, const double* results[3])
+{
+    UtStack* u = h->ut;
+    if (!u || !u->last[0] || u->cgi_version != h->conf_version) {
+        set_error("CombinedGreensIterator: no step has been taken for this configuration");
+        return MCB_ERR_STATE;
+    }
+    for (int w = 0; w < 3; ++w) results[w] = u->last[w];
+    return 0;
+}
 
 void unequal_free(mcb_dqmc* h)
 {

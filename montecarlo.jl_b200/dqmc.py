@@ -314,14 +314,17 @@ def decompress(chunks, N, M):
 
 
 class CombinedGreensIterator:
-    """CombinedGreensIterator(mc) (unequal_time_stack.jl:746-883): yields, for l = 1..M, the physical Green's
-    functions (G(0 <- l), G(l <- 0), G(l <- l)), each of shape (C, N, N), for time-displaced measurements.
-    The reference propagates one slice at a time between stabilised recalculations (and checks the result
-    against greens(mc, l, 0) etc. to 1e-10, test/flavortests_DQMC.jl:143-160); here every l is the stabilised
-    evaluation itself, on stacks that are built once per configuration."""
+    """CombinedGreensIterator(mc, recalculate=4 safe_mult) (unequal_time_stack.jl:746-885): yields, for l = 1..M, the
+    Green's functions (G(0 <- l), G(l <- 0), G(l <- l)), each of shape (C, N, N), for time-displaced measurements.
+    The three UDT triples live on the device and advance one slice per step (mcb_dqmc_cgi_begin / _next); they are
+    re-factorised every safe_mult slices and recomputed from the UnequalTimeStack every `recalculate` slices, as in the
+    reference. The handle has to be at its measurement point (current_slice == 1 on the way up). The reference checks
+    the iterator against greens(mc, l, 0) etc. to 1e-14 (recalculate = safe_mult) and 1e-10 (default),
+    test/flavortests_DQMC.jl:143-160."""
 
-    def __init__(self, mc, physical=True):
+    def __init__(self, mc, recalculate=0, physical=True):
         self.mc = mc
+        self.recalculate = int(recalculate)
         self.physical = physical
 
     def __len__(self):
@@ -329,9 +332,16 @@ class CombinedGreensIterator:
 
     def __iter__(self):
         mc = self.mc
-        for l in range(1, mc.M + 1):
-            yield (mc.greens_unequal(0, l, self.physical), mc.greens_unequal(l, 0, self.physical),
-                   mc.greens_unequal(l, l, self.physical))
+        _lib.check(mc._f("cgi_begin")(mc.h, self.recalculate))
+        size = mc.n_chains * mc.model.flv * mc.N * mc.N
+        nxt = mc._f("cgi_next")
+        sl = C.c_int32(0)
+        while True:
+            bufs = [np.empty(size) for _ in range(3)]
+            _lib.check(nxt(mc.h, int(self.physical), C.byref(sl), *[b.ctypes.data_as(C.c_void_p) for b in bufs]))
+            if sl.value == 0:
+                return
+            yield tuple(mc._unbatch(b) for b in bufs)
 
 
 def mean_and_error(per_chain):

@@ -712,6 +712,102 @@ void orc_greens_unequal(void* h, int slice1, int slice2, double* out, int physic
     ref_vmul_nn(out, o.eTinv.data(), t.data(), o.N);
 }
 
+// CombinedGreensIterator (unequal_time_stack.jl:746-883), all M steps at once: out[(l-1)][0..2] = G(0 <- l), G(l <- 0),
+// G(l <- l) for l = 1..M (each n x n column-major), effective or after _greens! (physical != 0). The handle has to sit at
+// current_slice == 1 with a valid G(0) (the assertion of :770); recalculate <= 0 selects the default 4 safe_mult (:752).
+// Follows the three branches of iterate(it, l) operation for operation: recalculation (:795-822), stabilisation
+// (:824-861), quick advance (:862-885). Clobbers the work matrices like the reference.
+int orc_cgi(void* h, int recalculate, double* out, int physical)
+{
+    Oracle& o = *(Oracle*)h;
+    if (o.current_slice != 1) return -1;
+    const int n = o.N, M = o.M, s = o.safe_mult;
+    const size_t nn = (size_t)n * n;
+    if (recalculate <= 0) recalculate = 4 * s;
+    std::vector<double> uU(nn), uD(n), uT(nn), utmp(nn), phys(nn);
+    double *Ul = o.Ul.data(), *Dl = o.Dl.data(), *Tl = o.Tl.data(), *Ur = o.Ur.data(), *Dr = o.Dr.data(), *Tr = o.Tr.data();
+    double *tmp1 = o.tmp1.data(), *tmp2 = o.tmp2.data(), *cU = o.curr_U.data();
+    int64_t* piv = o.pivot.data();
+    double* tv = o.tempv.data();
+    auto emit = [&](int l, int which, const double* G) {
+        double* dst = out + ((size_t)(l - 1) * 3 + which) * nn;
+        if (!physical) { ref_copy(dst, G, n); return; }
+        ref_vmul_nn(phys.data(), G, o.eT.data(), n);
+        ref_vmul_nn(dst, o.eTinv.data(), phys.data(), n);
+    };
+    // iterate(it) (:768-787)
+    ref_copy(Tl, o.greens.data(), n);
+    ut_build(o);
+    double* ug = o.ut_greens.data();   // (re)allocated by ut_build
+    ref_udt_pivot(Ul, Dl, Tl, piv, tv, n, 1);
+    ref_copy(uU.data(), Ul, n);
+    for (int i = 0; i < n; ++i) uD[i] = Dl[i];
+    ref_copy(uT.data(), Tl, n);
+    ref_copy(Tr, o.greens.data(), n);
+    for (int i = 0; i < n; ++i) Tr[IDX(i, i, n)] -= 1.0;
+    ref_udt_pivot(Ur, Dr, Tr, piv, tv, n, 1);
+    for (int l = 1; l <= M; ++l) {
+        if (l % recalculate == 0) {
+            ut_full1(o, l, 0);
+            ref_copy(cU, ug, n);
+            ut_full2(o, 0, l);
+            ref_copy(utmp.data(), ug, n);
+            ut_full1(o, l, l);
+            ref_copy(uT.data(), ug, n);
+            emit(l, 2, uT.data());
+            ref_udt_pivot(uU.data(), uD.data(), uT.data(), piv, tv, n, 1);
+            emit(l, 1, cU);
+            ref_copy(Tl, cU, n);
+            ref_udt_pivot(Ul, Dl, Tl, piv, tv, n, 1);
+            emit(l, 0, utmp.data());
+            ref_copy(Tr, utmp.data(), n);
+            ref_udt_pivot(Ur, Dr, Tr, piv, tv, n, 1);
+            continue;
+        }
+        mul_slice_left(o, l, Ul);
+        mul_slice_inv_right(o, l, Tr);
+        mul_slice_left(o, l, uU.data());
+        mul_slice_inv_right(o, l, uT.data());
+        if (l % s == 0) {
+            // Gl0
+            ref_vmul_nd(tmp1, Ul, Dl, n);
+            ref_vmul_nn(tmp2, tmp1, Tl, n);
+            ref_udt_pivot(Ul, Dl, tmp1, piv, tv, n, 1);
+            ref_vmul_nn(cU, tmp1, Tl, n);
+            ref_copy(Tl, cU, n);
+            emit(l, 1, tmp2);
+            // G0l
+            ref_vmul_dn(cU, Dr, Tr, n);
+            ref_vmul_nn(ug, Ur, cU, n);
+            ref_copy(Tr, cU, n);
+            ref_udt_pivot(tmp2, Dr, Tr, piv, tv, n, 1);
+            ref_vmul_nn(cU, Ur, tmp2, n);
+            ref_copy(Ur, cU, n);
+            emit(l, 0, ug);
+            // Gll
+            ref_vmul_nd(utmp.data(), uU.data(), uD.data(), n);
+            ref_vmul_nn(ug, utmp.data(), uT.data(), n);
+            ref_udt_pivot(cU, uD.data(), utmp.data(), piv, tv, n, 1);
+            ref_vmul_nn(uU.data(), utmp.data(), uT.data(), n);
+            ref_vmul_dn(uT.data(), uD.data(), uU.data(), n);
+            ref_udt_pivot(utmp.data(), uD.data(), uT.data(), piv, tv, n, 1);
+            ref_vmul_nn(uU.data(), cU, utmp.data(), n);
+            emit(l, 2, ug);
+        } else {
+            ref_vmul_nd(cU, Ul, Dl, n);
+            ref_vmul_nn(tmp2, cU, Tl, n);
+            emit(l, 1, tmp2);
+            ref_vmul_nd(cU, Ur, Dr, n);
+            ref_vmul_nn(ug, cU, Tr, n);
+            emit(l, 0, ug);
+            ref_vmul_nd(cU, uU.data(), uD.data(), n);
+            ref_vmul_nn(ug, cU, uT.data(), n);
+            emit(l, 2, ug);
+        }
+    }
+    return 0;
+}
+
 // ---- bare linear-algebra entry points for the property tests (test/slice_matrices.jl:141-235)
 void orc_vmul(double* C, const double* A, const double* B, int n, int mode)
 {

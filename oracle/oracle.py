@@ -57,6 +57,8 @@ def lib(native=False):
     L.orc_get_state.argtypes = [C.c_void_p, _i64p, _f64p]
     L.orc_calculate_greens_at.argtypes = [C.c_void_p, C.c_int, _f64p]
     L.orc_greens_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _f64p, C.c_int]
+    L.orc_cgi.restype = C.c_int
+    L.orc_cgi.argtypes = [C.c_void_p, C.c_int, _f64p, C.c_int]
     L.orc_vmul.argtypes = [_f64p, _f64p, _f64p, C.c_int, C.c_int]
     L.orc_udt_pivot.argtypes = [_f64p, _f64p, _f64p, _i64p, C.c_int, C.c_int]
     L.orc_rdivp.argtypes = [_f64p, _f64p, _i64p, C.c_int]
@@ -187,11 +189,33 @@ class OracleDQMC:
         self.L.orc_calculate_greens_at(self.h, slice_, out)
         return unfmat(out, self.N)
 
+    def propagate_only(self):
+        """propagate(mc) without the local updates (stack.jl:502-620)."""
+        self.L.orc_propagate_only(self.h)
+
+    def propagate_to_measurement_point(self):
+        """Propagate until current_slice == 1 on the way up, where G = G(tau = 0) (the measurement point of
+        DQMC.jl's run loop and the precondition of the CombinedGreensIterator)."""
+        for _ in range(4 * self.M + 4):
+            st = self.state()
+            if st["current_slice"] == 1 and st["direction"] == 1:
+                return
+            self.propagate_only()
+        raise RuntimeError("measurement point not reached")
+
     def greens_unequal(self, slice1, slice2, physical=False):
         """G(slice1 <- slice2), 0 <= slice <= M (unequal_time_stack.jl:291-305). Clobbers the work matrices."""
         out = np.empty(self.N * self.N)
         self.L.orc_greens_unequal(self.h, slice1, slice2, out, 1 if physical else 0)
         return unfmat(out, self.N)
+
+    def combined_greens(self, recalculate=0, physical=True):
+        """CombinedGreensIterator (unequal_time_stack.jl:746-883) run to the end: array (M, 3, N, N) holding
+        G(0 <- l), G(l <- 0), G(l <- l) for l = 1..M. The handle has to be at current_slice == 1."""
+        out = np.empty(self.M * 3 * self.N * self.N)
+        if self.L.orc_cgi(self.h, recalculate, out, 1 if physical else 0) != 0:
+            raise RuntimeError("CombinedGreensIterator needs current_slice == 1")
+        return out.reshape(self.M, 3, self.N, self.N).transpose(0, 1, 3, 2).copy()
 
     def conf(self):
         out = np.empty(self.N * self.M, dtype=np.int8)

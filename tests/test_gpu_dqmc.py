@@ -428,17 +428,63 @@ def test_unequal_time_properties_and_sweep_state():
     mc.close()
 
 
-def test_combined_greens_iterator():
-    """test/flavortests_DQMC.jl:143-160: (G0l, Gl0, Gll) of the iterator against the direct evaluations."""
-    mc, oracles = _pair(4, 1.0, 1.0, 0.1, 5, 2)
-    it = mcb.CombinedGreensIterator(mc)
+def _to_measurement_point(mc, oracles):
+    """build_stack + M updates: current_slice == 1 on the way up, mc.s.greens = G(0) (where DQMC.jl's run loop measures)."""
+    mc.build_stack()
+    mc.update(mc.M)
+    for o in oracles:
+        o.build_stack()
+        o.update(mc.M)
+    st = mc.state()
+    assert st["current_slice"] == 1 and st["direction"] == 1
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("L,U,beta,safe_mult,recalculate", [(4, 1.0, 2.0, 5, 0), (4, 1.0, 2.0, 5, 5), (8, 2.0, 4.0, 4, 0),
+                                                            (8, 4.0, 2.0, 5, 10), (6, 4.0, 2.4, 4, 8), (2, 1.0, 15.0, 5, 0)])
+def test_combined_greens_iterator(L, U, beta, safe_mult, recalculate, general):
+    """CombinedGreensIterator on the device (unequal_time_stack.jl:746-885) against its step-for-step CPU restatement
+    and, as test/flavortests_DQMC.jl:143-160 does, against greens(mc, 0, l), greens(mc, l, 0), greens(mc, l, l).
+    The configurations are ones where the reference's scheme itself is accurate: at 8 x 8, beta = 4 with safe_mult = 10
+    and the default recalculate = 40 = M the restated reference is off by 5e-7 in G(0 <- l) and by O(10) in G(l <- l)
+    at l = 39 (39 unstabilised similarity transforms)"""
+    mc, oracles = _pair(L, U, beta, 0.1, safe_mult, 2, general=general)
+    _to_measurement_point(mc, oracles)
+    G0, st0 = mc.greens(physical=False), mc.state()
+    it = mcb.CombinedGreensIterator(mc, recalculate=recalculate)
     assert len(it) == mc.M
-    o = oracles[0]
-    for l, (G0l, Gl0, Gll) in enumerate(it, start=1):
-        assert relerr(G0l[0], o.greens_unequal(0, l, physical=True)) < RTOL_G, l
-        assert relerr(Gl0[0], o.greens_unequal(l, 0, physical=True)) < RTOL_G, l
-        want = mc.hop[1] @ o.greens_at(l) @ mc.hop[0]  # _greens!(calculate_greens(mc, l))
-        assert relerr(Gll[0], want) < RTOL_G, l
+    got = np.stack([np.stack(t, axis=1) for t in it])           # (M, C, 3, N, N)
+    assert got.shape == (mc.M, 2, 3, L * L, L * L)
+    assert np.array_equal(G0, mc.greens(physical=False)) and st0 == mc.state()   # sweep state untouched
+    direct = np.stack([np.stack([mc.greens_unequal(0, l), mc.greens_unequal(l, 0), mc.greens_unequal(l, l)], axis=1)
+                       for l in range(1, mc.M + 1)])
+    # recalculate = safe_mult: every stabilisation is a recalculation ("high precision"); otherwise G(l <- l) between
+    # recalculations is a similarity transform that amplifies rounding (see tests/test_oracle_unequal.py)
+    tol_ll = 1e-11 if recalculate == safe_mult else 1e-8
+    assert np.abs(got[:, :, :2] - direct[:, :, :2]).max() < 1e-10
+    assert np.abs(got[:, :, 2] - direct[:, :, 2]).max() < tol_ll
+    for c, o in enumerate(oracles):
+        want = o.combined_greens(recalculate=recalculate)        # (M, 3, N, N)
+        assert np.abs(got[:, c, :2] - want[:, :2]).max() < 1e-10, c
+        assert np.abs(got[:, c, 2] - want[:, 2]).max() < tol_ll, c
+    eff = [t for t in mcb.CombinedGreensIterator(mc, recalculate=recalculate, physical=False)]
+    assert np.allclose(mc.hop[1] @ eff[3][1][0] @ mc.hop[0], got[3, 0, 1], atol=1e-12)
+    mc.update(2)   # the sweep carries on
+    assert mc.state()["n_updates"] == st0["n_updates"] + 2
+    mc.close()
+
+
+def test_combined_greens_iterator_state_checks():
+    mc, oracles = _pair(4, 1.0, 1.0, 0.1, 5, 1)
+    mc.build_stack()   # current_slice == M on the way down: not the measurement point
+    with pytest.raises(RuntimeError, match="current_slice == 1"):
+        next(iter(mcb.CombinedGreensIterator(mc)))
+    mc.update(mc.M)
+    it = iter(mcb.CombinedGreensIterator(mc))
+    next(it)
+    mc.update(1)       # the field may have changed: the iteration in progress is void
+    with pytest.raises(RuntimeError, match="no iteration in progress"):
+        next(it)
     mc.close()
 
 

@@ -152,6 +152,32 @@ def test_unequal_time_greens_of_both_blocks():
     mc.close()
 
 
+def test_combined_greens_iterator_of_both_blocks():
+    """CombinedGreensIterator (unequal_time_stack.jl:746-885) per block against greens(mc, k, l) and the CPU restatement."""
+    mc, oracles = _pair(4, 4.0, 2.0, 0.1, 5, 2)
+    mc.build_stack()
+    mc.update(mc.M)
+    for o in oracles:
+        o.build_stack()
+        o.update(mc.M)
+    assert mc.state()["current_slice"] == 1 and mc.state()["direction"] == 1
+    # recalculate = 10: at U = 4 the default (20 = M, i.e. never) lets the reference's own scheme drift to 3e-7 in G(l <- l)
+    got = [t for t in mcb.CombinedGreensIterator(mc, recalculate=10)]
+    assert len(got) == mc.M and got[0][0].shape == (2, 2, 16, 16)
+    for l in (1, 4, 5, 6, 9, 10, 11, 19, 20):
+        G0l, Gl0, Gll = got[l - 1]
+        assert np.abs(G0l - mc.greens_unequal(0, l)).max() < 1e-10, l
+        assert np.abs(Gl0 - mc.greens_unequal(l, 0)).max() < 1e-10, l
+        assert np.abs(Gll - mc.greens_unequal(l, l)).max() < 1e-8, l
+    for c, o in enumerate(oracles):
+        for f, blk in enumerate((o.up, o.dn)):
+            want = blk.combined_greens(recalculate=10)
+            have = np.stack([np.stack([t[w][c, f] for w in range(3)]) for t in got])
+            assert np.abs(have[:, :2] - want[:, :2]).max() < 1e-10, (c, f)
+            assert np.abs(have[:, 2] - want[:, 2]).max() < 1e-8, (c, f)
+    mc.close()
+
+
 def test_checkpoint_and_resume_continue_the_same_chains():
     """save / resume! (FileIO.jl:38-156, DQMC.jl:517-521) for the two-block handle: a run that is stopped after two
     sweeps, saved as bit-packed field + sweep count and resumed in a new handle ends where the uninterrupted run does."""
