@@ -36,6 +36,7 @@ static int use_device(int dev)
         API_TRY(init_sweep_kernels());
         API_TRY(init_sweep_delayed_kernels());
         API_TRY(init_segment_kernels());
+        API_TRY(init_segment_resident_kernels());
         API_TRY(init_stab_kernels());
         inited[dev] = true;
     }
@@ -92,6 +93,12 @@ int mcb_dqmc_create(const mcb_dqmc_params* p, mcb_dqmc** out)
     h->N = p->n_sites; h->M = p->n_slices; h->s = p->safe_mult; h->C = p->n_chains;
     h->ne = h->M / h->s + 1;
     h->use_panel = segment_supported(h->N) && stab_supported(h->N) && p->general_path == 0;
+    {
+        // MCB_SEGMENT_RESIDENT=0: the GEMM + delayed-sweep launches per slice instead (comparisons)
+        const char* ev = getenv("MCB_SEGMENT_RESIDENT");
+        h->use_resident_segment = !h->use_panel && segment_resident_supported(h->N) && p->general_path == 0 &&
+                                  !(ev && atoi(ev) == 0);
+    }
     h->nn = (size_t)h->N * h->N;
     h->mat = h->nn * h->C;
     h->vec = (size_t)h->N * h->C;
@@ -130,6 +137,12 @@ int mcb_dqmc_destroy(mcb_dqmc* h)
     return MCB_OK;
 }
 
+__global__ void transpose_kernel(double* dst, const double* src, int n)
+{
+    const size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (e < (size_t)n * n) dst[e] = src[(e % n) * n + e / n];
+}
+
 int mcb_dqmc_set_hopping(mcb_dqmc* h, const double* eT_half_minus, const double* eT_half_plus,
                          const double* eT_minus, const double* eT_plus)
 {
@@ -138,6 +151,13 @@ int mcb_dqmc_set_hopping(mcb_dqmc* h, const double* eT_half_minus, const double*
     const double* src[4] = {eT_half_minus, eT_half_plus, eT_minus, eT_plus};
     for (int i = 0; i < 4; ++i)
         MCB_CUDA(cudaMemcpyAsync(h->hop[i], src[i], h->nn * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    if (h->use_resident_segment) {
+        for (int i = 0; i < 2; ++i) {
+            if (!h->hopT[i]) MCB_CUDA(cudaMalloc(&h->hopT[i], h->nn * sizeof(double)));
+            transpose_kernel<<<(unsigned)((h->nn + 255) / 256), 256, 0, h->st>>>(h->hopT[i], h->hop[2 + i], h->N);
+            MCB_CUDA(cudaGetLastError());
+        }
+    }
     MCB_CUDA(cudaStreamSynchronize(h->st));
     h->hopping_set = true;
     return MCB_OK;

@@ -261,6 +261,7 @@ void engine_free(mcb_dqmc* h)
 {
     unequal_free(h);
     for (int i = 0; i < 4; ++i) cudaFree(h->hop[i]);
+    for (int i = 0; i < 2; ++i) cudaFree(h->hopT[i]);
     cudaFree(h->conf); cudaFree(h->conf_bits); cudaFree(h->G); cudaFree(h->Gtmp);
     for (int i = 0; i < 8; ++i) cudaFree(h->W[i]);
     for (int i = 0; i < 2; ++i) cudaFree(h->Dw[i]);
@@ -394,7 +395,7 @@ int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_p
     h->conf_version++;
     *done = 0;
     if (max_updates <= 0) return 0;
-    if (!h->use_panel) {
+    if (!h->use_panel && !h->use_resident_segment) {
         MCB_TRY(engine_update(h));
         *done = 1;
         return 0;
@@ -429,7 +430,12 @@ int engine_update_batch(mcb_dqmc* h, int64_t max_updates, bool stop_at_measure_p
         const char* ev = getenv("MCB_PHASE_SYNC");
         a.phase_sync = ((!ev || atoi(ev)) && h->C % 4 == 0) ? 1 : 0;
     }
-    MCB_TRY(launch_segment(a, h->st));
+    if (h->use_panel) {
+        MCB_TRY(launch_segment(a, h->st));
+    } else {
+        a.eT2T = h->hopT[0]; a.eTinv2T = h->hopT[1];
+        MCB_TRY(launch_segment_resident(a, h->st));
+    }
     h->current_slice = start + d * (int)(visits - 1);
     h->n_updates += visits;
     *done = visits;

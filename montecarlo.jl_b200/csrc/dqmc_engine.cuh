@@ -46,6 +46,8 @@ struct mcb_dqmc {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
     bool use_panel = false; // chain-resident kernels (panel.cuh) exist for this N
+    bool use_resident_segment = false; // wrap + sweep with G in shared memory (segment_resident.cu), general stabilisation
+    double* hopT[2] = {nullptr, nullptr}; // transposes of hop[2], hop[3] for that kernel
     bool hopping_set = false, conf_set = false, stack_built = false;
     struct UtStack* ut = nullptr; // unequal-time stacks and work matrices, allocated on first use (unequal.cu)
     int64_t conf_version = 0;     // bumped whenever the configuration may have changed

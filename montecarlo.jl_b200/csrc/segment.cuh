@@ -11,6 +11,8 @@ struct SegmentArgs {
     int8_t* conf = nullptr; long long sConf = 0; // [chain][slice][site], per chain stride
     const double* eT2 = nullptr;    // e^{-dtau T}
     const double* eTinv2 = nullptr; // e^{+dtau T}
+    const double* eT2T = nullptr;   // their transposes (segment_resident.cu streams rows of the exponentials as columns)
+    const double* eTinv2T = nullptr;
     int n_slices = 0;
     int start_slice = 0; // 1-based slice of the first sweep_spatial
     int direction = 1;
@@ -30,5 +32,9 @@ struct SegmentArgs {
 bool segment_supported(int n);
 int launch_segment(const SegmentArgs& a, cudaStream_t st);
 int init_segment_kernels();
+// the same run of slice visits with G resident in one CTA's shared memory (segment_resident.cu): N = 144
+bool segment_resident_supported(int n);
+int launch_segment_resident(const SegmentArgs& a, cudaStream_t st);
+int init_segment_resident_kernels();
 
 } // namespace mcb
