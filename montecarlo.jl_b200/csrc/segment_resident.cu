@@ -7,7 +7,7 @@
 // Wrap: the two products of a wrap run on 12 warps (6 x 2 warp tiles of 24 x 72, the whole 144 x 144 result in DMMA
 // accumulators), one operand read as fragments straight out of the resident G, the other - the hopping exponential, the
 // same matrix for every chain and therefore L2-resident - streamed in panels of 8 columns by TMA bulk copies into a ring
-// of 4 stages, each guarded by an mbarrier that counts the bytes (refilled after a CTA barrier, as in gemm_tma.cu). The
+// of 4 stages guarded by full (byte-counting) and empty (one arrival per warp) mbarriers; no CTA barrier inside a product. The
 // exp(+-lambda s) diagonals are applied to the A fragments / at the write-back. The second product needs rows of the
 // exponential; the host uploads its transpose so that these are contiguous columns too.
 //
@@ -26,6 +26,13 @@ namespace mcb {
 namespace {
 
 using namespace swb;
+
+#ifdef SWD_TIMING
+__device__ long long sgr_clk[32];
+#define SGR_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) sgr_clk[i] = clock64(); } while (0)
+#else
+#define SGR_T(i) do { } while (0)
+#endif
 
 template <int N>
 struct RGeo {
@@ -52,6 +59,53 @@ struct RGeo {
     static_assert(SMEM <= 227 * 1024, "does not fit one SM");
 };
 
+// column_recurrence / row_recurrence (sweep_blocks.cuh) with the block's original columns / rows read from G itself
+// (column j of the block at Gcol + j * ldg, row k at Grow + k with column stride ldg) instead of from a copy
+__device__ __forceinline__ void column_recurrence_g(const double* Gcol, int ldg, double* U, int ld, int i0, int kb,
+                                                    const double* DD, const double* xs, int e)
+{
+    for (int j0 = 0; j0 < kb; j0 += 8) {
+        double c[8], u[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) c[q] = (j0 + q < kb) ? Gcol[(size_t)(j0 + q) * ldg + e] : 0.0;
+        for (int jp = 0; jp < j0; ++jp) {
+            const double up = U[jp * ld + e];
+            const double* d = DD + jp * DLD + j0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) c[q] = fma(-up, d[q], c[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            double cc = c[q];
+#pragma unroll
+            for (int p = 0; p < q; ++p) cc = fma(-u[p], DD[(j0 + p) * DLD + j0 + q], cc);
+            u[q] = (j0 + q < kb) ? xs[j0 + q] * ((e == i0 + j0 + q ? 1.0 : 0.0) - cc) : 0.0;
+            if (j0 + q < kb) U[(j0 + q) * ld + e] = u[q];
+        }
+    }
+}
+
+__device__ __forceinline__ void row_recurrence_g(const double* Grow, int ldg, double* Rc, int ld, int kb, const double* DD, int e)
+{
+    for (int j0 = 0; j0 < kb; j0 += 8) {
+        double r[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) r[q] = (j0 + q < kb) ? Grow[(size_t)e * ldg + j0 + q] : 0.0;
+        for (int jp = 0; jp < j0; ++jp) {
+            const double rp = Rc[jp * ld + e];
+            const double* d = DD + j0 * DLD + jp;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) r[q] = fma(d[q * DLD], rp, r[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+#pragma unroll
+            for (int p = 0; p < q; ++p) r[q] = fma(DD[(j0 + q) * DLD + j0 + p], r[p], r[q]);
+            if (j0 + q < kb) Rc[(j0 + q) * ld + e] = r[q];
+        }
+    }
+}
+
 // One product of a wrap. WHICH == 1: G <- diag(row) H (diag(mid) G)   (A = columns of H from the ring, B = G)
 //                        WHICH == 2: G <- ((G diag(mid)) H) diag(col)   (A = G, B = rows of H = columns of H' from the ring)
 // Hcols points at the matrix whose COLUMNS are streamed (H for 1, H' for 2). cnt counts the ring stages used so far (the
@@ -59,24 +113,24 @@ struct RGeo {
 template <int N, int WHICH>
 __device__ __forceinline__ void wrap_product(double* __restrict__ Gs, double* __restrict__ ring, const double* __restrict__ Hcols,
                                              const double* __restrict__ mid, const double* __restrict__ outsc, uint64_t* full,
-                                             uint32_t& cnt, int tid)
+                                             uint64_t* empty, uint32_t& cnt, int tid)
 {
     using R = RGeo<N>;
     constexpr int LD = R::LD, BK = R::BK, STAGES = R::STAGES, IT = R::IT, JT = R::JT, nk = N / BK;
     const int warp = tid >> 5, lane = tid & 31, r = lane >> 2, q = lane & 3;
     double acc[IT][JT][2];
     const int wm = (warp % 6) * R::WM, wn = (warp / 6) * R::WN;
-    // one bulk copy per column of a panel, issued by the first warp
+    // one bulk copy per column of a panel. The first panels go out from warp 0; stage s is refilled for panel kt + STAGES by
+    // warp kt % 12 once all twelve warps have released it (arrivals on empty[s]): no CTA-wide barrier inside the product.
     auto issue = [&](int kt) {
-        if (warp == 0) {
-            const uint32_t s = (cnt + kt) % STAGES;
-            if (lane == 0) mbar_expect_tx(full + s, BK * N * sizeof(double));
-            __syncwarp();
-            if (lane < BK)
-                bulk_g2s(ring + (size_t)(s * BK + lane) * LD, Hcols + (size_t)(kt * BK + lane) * N, N * sizeof(double), full + s);
-        }
+        const uint32_t s = (cnt + kt) % STAGES;
+        if (lane == 0) mbar_expect_tx(full + s, BK * N * sizeof(double));
+        __syncwarp();
+        if (lane < BK)
+            bulk_g2s(ring + (size_t)(s * BK + lane) * LD, Hcols + (size_t)(kt * BK + lane) * N, N * sizeof(double), full + s);
     };
-    for (int kt = 0; kt < STAGES; ++kt) issue(kt);
+    if (warp == 0)
+        for (int kt = 0; kt < STAGES; ++kt) issue(kt);
 #pragma unroll
     for (int i = 0; i < IT; ++i)
 #pragma unroll
@@ -101,8 +155,10 @@ __device__ __forceinline__ void wrap_product(double* __restrict__ Gs, double* __
 #pragma unroll
                 for (int j = 0; j < JT; ++j) dmma884(acc[i][j][0], acc[i][j][1], av[i], bv[j]);
         }
-        if (kt + STAGES < nk) {
-            __syncthreads();   // every warp is done with stage s: refill it
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + s);
+        if (kt + STAGES < nk && warp == kt % 12) {
+            mbar_wait(empty + s, (c / STAGES) & 1);
             issue(kt + STAGES);
         }
     }
@@ -144,7 +200,8 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
     double* sc_mid2 = sc_row1 + N;
     double* sc_col2 = sc_mid2 + N;
     uint64_t* full = reinterpret_cast<uint64_t*>(sm + R::OFF_BAR);
-    uint64_t* gbar = full + R::STAGES;
+    uint64_t* empty = full + R::STAGES;
+    uint64_t* gbar = empty + R::STAGES;
     int* tile_ctr = reinterpret_cast<int*>(sm + R::OFF_MISC);
     volatile int* decide_done = tile_ctr + 1;
     int8_t* s_in = reinterpret_cast<int8_t*>(sm + R::OFF_S);
@@ -157,7 +214,7 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
     const DecideConst dconst{a.gamma_p, a.gamma_m, a.efac_p, a.efac_m};
 
     if (tid == 0) {
-        for (int s = 0; s < R::STAGES; ++s) mbar_init(full + s, 1);
+        for (int s = 0; s < R::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 12); }
         mbar_init(gbar, 1);
     }
     __syncthreads();
@@ -165,6 +222,7 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
     if (tid == 0) mbar_expect_tx(gbar, (uint32_t)(N * N * sizeof(double)));
     if (tid < N) bulk_g2s(Gs + (size_t)tid * LD, Gg + (size_t)tid * N, N * sizeof(double), gbar);
     mbar_wait(gbar, 0);
+    SGR_T(0);
 
     int nacc = 0;
     bool bad = false;
@@ -195,8 +253,15 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
             }
             fence_async_smem();   // the ring area was written through the generic proxy by the previous sweep
             __syncthreads();
-            wrap_product<N, 1>(Gs, ring, a.direction > 0 ? a.eT2 : a.eTinv2, sc_mid1, sc_row1, full, cnt, tid);
-            wrap_product<N, 2>(Gs, ring, a.direction > 0 ? a.eTinv2T : a.eT2T, sc_mid2, sc_col2, full, cnt, tid);
+            if (v == 1) SGR_T(1);
+#ifdef SWD_TIMING
+            if (v == 2) SGR_T(25);
+            if (blockIdx.x == 0 && tid == 32 && v == 2) sgr_clk[26] = clock64();
+#endif
+            wrap_product<N, 1>(Gs, ring, a.direction > 0 ? a.eT2 : a.eTinv2, sc_mid1, sc_row1, full, empty, cnt, tid);
+            if (v == 1) SGR_T(2);
+            wrap_product<N, 2>(Gs, ring, a.direction > 0 ? a.eTinv2T : a.eT2T, sc_mid2, sc_col2, full, empty, cnt, tid);
+            if (v == 1) SGR_T(3);
         } else {
             __syncthreads();   // s_in, unif
         }
@@ -207,34 +272,36 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
 #pragma unroll
             for (int b = 0; b < K; ++b) reg[b] = lane < K ? Gs[(size_t)b * LD + lane] : 0.0;
             nacc += decide_rows<K>(dconst, reg, 0, K, s_in, s_out, unif, DD, xs, lane);
+            if (v == 1) SGR_T(4);
         }
         const bool last_visit = v == a.n_visits - 1;
         for (int i0 = 0; i0 < N; i0 += K) {
             const int i1 = i0 + K;
             const bool has_next = i1 < N;
             __syncthreads();   // the previous flush is complete, the decisions of this block are in DD / xs
-            // ---- copies of the block's columns and rows, the next block's diagonal block (all as they are BEFORE this flush)
-            for (int idx = tid; idx < K * N; idx += T) {
-                const int j = idx / N, row = idx - j * N;
-                Cc[j * LD + row] = Gs[(size_t)(i0 + j) * LD + row];
-            }
-            for (int idx = tid; idx < K * N; idx += T) {
-                const int l = idx / K, k = idx - l * K;
-                Rc[k * LD + l] = Gs[(size_t)l * LD + i0 + k];
-            }
-            if (has_next && tid < K * K) {
-                const int ra = tid % K, cb = tid / K;
-                Dn[cb * K + ra] = Gs[(size_t)(i1 + cb) * LD + i1 + ra];
-            }
-            if (tid == 0) { *tile_ctr = 0; *decide_done = 0; }
-            __syncthreads();
-            // ---- the update vectors of the block (two triangular recurrences, one element per thread)
+            if (v == 1 && i0 == K) SGR_T(5);
+            if (v == 1) SGR_T(12 + i0 / K);
+            if (v == 1 && i0 == 2 * K) SGR_T(9);
+            // ---- the update vectors of the block: two triangular recurrences, one element per thread, reading the block's
+            // columns and rows straight out of G (no copies) and writing u_j / the frozen rows into Cc / Rc. The threads
+            // left over fetch the next block's diagonal block as it is BEFORE this flush.
             {
                 constexpr int NV = (N + 31) / 32 * 32;
-                if (tid < NV) { if (tid < N) column_recurrence(Cc, LD, i0, K, DD, xs, tid); }
-                else if (tid < 2 * NV) { if (tid - NV < N) row_recurrence(Rc, LD, K, DD, tid - NV); }
+                if (tid < NV) { if (tid < N) column_recurrence_g(Gs + (size_t)i0 * LD, LD, Cc, LD, i0, K, DD, xs, tid); }
+                else if (tid < 2 * NV) { if (tid - NV < N) row_recurrence_g(Gs + i0, LD, Rc, LD, K, DD, tid - NV); }
+                else {
+                    if (tid == 2 * NV) { *tile_ctr = 0; *decide_done = 0; }
+                    if (has_next)
+                    for (int idx = tid - 2 * NV; idx < K * K; idx += T - 2 * NV) {
+                        const int ra = idx % K, cb = idx / K;
+                        Dn[cb * K + ra] = Gs[(size_t)(i1 + cb) * LD + i1 + ra];
+                    }
+                }
             }
             __syncthreads();
+            if (v == 1 && i0 == K) SGR_T(7);
+            if (v == 1 && i0 == 8 * K) SGR_T(21);
+            if (v == 1 && i0 == 7 * K) SGR_T(22);
             // ---- one warp: next diagonal block D' = D - U[blk', :] Rc[:, blk'] (2 x 2 DMMA tiles), then its decisions
             if (warp == 0 && has_next) {
                 double c[2][2][2];
@@ -266,61 +333,66 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
 #pragma unroll
                 for (int b = 0; b < K; ++b) reg[b] = lane < K ? Dn[b * K + lane] : 0.0;
                 nacc += decide_rows<K>(dconst, reg, i1, K, s_in, s_out, unif, DD, xs, lane);
+                if (v == 1 && i0 == K) SGR_T(8);
                 __syncwarp();
                 if (lane == 0) { __threadfence_block(); *decide_done = 1; }
-            } else if (has_next && (warp & 3) == 0) {
-                // the warps on the deciding warp's scheduler stay out of the flush until it is done (sweep_delayed.cu)
-                while (!*decide_done) __nanosleep(100);
             }
-            // ---- flush G -= U Rc in shared memory; warp tiles of 32 x 16 handed out by a counter
-            constexpr int TM = (N + 31) / 32, TN = N / 16;
-            const bool check = last_visit && !has_next;
-            for (;;) {
-                int tnext = 0;
-                if (lane == 0) tnext = atomicAdd(tile_ctr, 1);
-                tnext = __shfl_sync(0xffffffffu, tnext, 0);
-                if (tnext >= TM * TN) break;
-                const int row0 = (tnext % TM) * 32, col0 = (tnext / TM) * 16;
-                double c[4][2][2];
+            // ---- flush G -= U Rc in shared memory: 18 work items of 16 rows x 72 columns (2 x 9 DMMA tiles whose accumulators
+            // start as the G tile; the A operand is -U), handed out by a counter. The warps that share the deciding warp's
+            // scheduler join when it is done (their DMMAs would queue in front of its dependent FP64 chain, sweep_delayed.cu).
+            if (has_next && (warp & 3) == 0 && warp != 0) {
+                while (!*decide_done) __nanosleep(64);
+            }
+            {
+                const bool check = last_visit && !has_next;
+                for (;;) {
+                    int item = 0;
+                    if (lane == 0) item = atomicAdd(tile_ctr, 1);
+                    item = __shfl_sync(0xffffffffu, item, 0);
+                    if (item >= 18) break;
+                    const int row0 = (item >> 1) * 16, col0 = (item & 1) * (N / 2);
+                    double c[2][9][2];
 #pragma unroll
-                for (int x = 0; x < 4; ++x)
+                    for (int x = 0; x < 2; ++x)
 #pragma unroll
-                    for (int y = 0; y < 2; ++y) c[x][y][0] = c[x][y][1] = 0.0;
-                const double* ua[4];
-                const double* rb[2];
+                        for (int y = 0; y < 9; ++y)
 #pragma unroll
-                for (int x = 0; x < 4; ++x) ua[x] = Cc + q * LD + min(row0 + 8 * x + r, N - 1);
+                            for (int cc = 0; cc < 2; ++cc)
+                                c[x][y][cc] = Gs[(size_t)(col0 + 8 * y + 2 * q + cc) * LD + row0 + 8 * x + r];
 #pragma unroll
-                for (int y = 0; y < 2; ++y) rb[y] = Rc + q * LD + col0 + 8 * y + r;
+                    for (int k0 = 0; k0 < K; k0 += 4) {
+                        double av[2], bv[9];
 #pragma unroll
-                for (int k0 = 0; k0 < K; k0 += 4) {
-                    double av[4], bv[2];
+                        for (int x = 0; x < 2; ++x) av[x] = -Cc[(k0 + q) * LD + row0 + 8 * x + r];
 #pragma unroll
-                    for (int x = 0; x < 4; ++x) av[x] = ua[x][k0 * LD];
+                        for (int y = 0; y < 9; ++y) bv[y] = Rc[(k0 + q) * LD + col0 + 8 * y + r];
 #pragma unroll
-                    for (int y = 0; y < 2; ++y) bv[y] = rb[y][k0 * LD];
+                        for (int x = 0; x < 2; ++x)
 #pragma unroll
-                    for (int x = 0; x < 4; ++x)
+                            for (int y = 0; y < 9; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
+                    }
 #pragma unroll
-                        for (int y = 0; y < 2; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
-                }
+                    for (int x = 0; x < 2; ++x)
 #pragma unroll
-                for (int x = 0; x < 4; ++x)
+                        for (int y = 0; y < 9; ++y)
 #pragma unroll
-                    for (int y = 0; y < 2; ++y)
-#pragma unroll
-                        for (int cc = 0; cc < 2; ++cc) {
-                            const int row = row0 + 8 * x + r, col = col0 + 8 * y + 2 * q + cc;
-                            if (row < N) {
-                                double* gp = Gs + (size_t)col * LD + row;
-                                const double gnew = *gp - c[x][y][cc];
-                                *gp = gnew;
+                            for (int cc = 0; cc < 2; ++cc) {
+                                const double gnew = c[x][y][cc];
+                                Gs[(size_t)(col0 + 8 * y + 2 * q + cc) * LD + row0 + 8 * x + r] = gnew;
                                 if (check) bad |= (__double2hiint(gnew) & 0x7ff00000) == 0x7ff00000;
                             }
-                        }
+                }
+#ifdef SWD_TIMING
+                if (blockIdx.x == 0 && tid == 32 && v == 1 && i0 == 7 * K) sgr_clk[23] = clock64();
+                if (blockIdx.x == 0 && tid == 32 && v == 1 && i0 == 8 * K) sgr_clk[24] = clock64();
+#endif
             }
         }
         __syncthreads();   // last flush done; s_out complete
+        if (v == 1) SGR_T(10);
+#ifdef SWD_TIMING
+        if (blockIdx.x == 0 && tid == 32 && v == 1) sgr_clk[27] = clock64();
+#endif
         for (int i = tid; i < N; i += T) cg[(size_t)(slice - 1) * N + i] = s_out[i];
     }
     // ---- G back to global memory
@@ -331,6 +403,7 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
         bulk_commit();
         bulk_wait_all();
     }
+    SGR_T(11);
     if (tid == 0) {
         a.acc[chain] += nacc;
         a.prop[chain] += (long long)N * a.n_visits;
@@ -357,6 +430,24 @@ int launch_segment_resident(const SegmentArgs& a, cudaStream_t st)
     LaunchScope scope(LC_FUSED, st, 4.0 * a.n * (double)a.n * a.n * wraps * a.batch);
     segment_resident_kernel<144><<<a.batch, RGeo<144>::THREADS, RGeo<144>::SMEM, st>>>(a);
     MCB_CUDA(cudaGetLastError());
+#ifdef SWD_TIMING
+    {
+        static int shown = 0;
+        if (a.n_visits >= 2 && shown++ < 3) {
+            long long h[32];
+            cudaStreamSynchronize(st);
+            cudaMemcpyFromSymbol(h, sgr_clk, sizeof(h));
+            fprintf(stderr, "segment_resident visits=%d cycles: kernel (after the G load) %lld || visit 1: product 1 %lld product 2 %lld first decisions %lld "
+                    "| block 1: recurrences %lld next decisions %lld (under the flush) block total %lld | sweep of the visit %lld\n",
+                    a.n_visits, h[11] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[7] - h[5], h[8] - h[7], h[9] - h[5],
+                    h[10] - h[3]);
+            fprintf(stderr, "  block starts relative to the end of the wrap:");
+            for (int b = 0; b < 9; ++b) fprintf(stderr, " %lld", h[12 + b] - h[3]);
+            fprintf(stderr, " end %lld | block 7 recurrences done %lld, block 8 recurrences done %lld\n", h[10] - h[3], h[22] - h[3], h[21] - h[3]);
+            fprintf(stderr, "  warp 1 leaves the flush of block 7 at %lld, of block 8 at %lld; passes the end-of-visit barrier at %lld; next visit's pre-wrap barrier: thread 0 %lld, thread 32 %lld\n", h[23] - h[3], h[24] - h[3], h[27] - h[3], h[25] - h[3], h[26] - h[3]);
+        }
+    }
+#endif
     return 0;
 }
 

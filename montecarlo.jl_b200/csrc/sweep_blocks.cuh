@@ -25,7 +25,10 @@ constexpr int DLD = 33;        // row stride of DD (conflict-free column access)
 // One warp, the diagonal block in registers: lane a holds row a (KMAX entries), the pivot row travels by shuffles,
 // no shared-memory round trip and no barrier per site (the 8-warp shared-memory version took 670 cycles per site,
 // most of it the named barrier and the LDS -> FMA -> STS chain). Same operations in the same order, hence the same bits.
-constexpr int KMAX = 24;   // block size cap (delayed_geom): 24 entries of a row in registers
+#ifndef SWB_KMAX
+#define SWB_KMAX 24
+#endif
+constexpr int KMAX = SWB_KMAX;   // block size cap (delayed_geom): entries of a row in registers (24; 32 in experiments)
 
 struct DecideCtx {
     double gamma_p, gamma_m, efac_p, efac_m;

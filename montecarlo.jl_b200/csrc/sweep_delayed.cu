@@ -37,7 +37,7 @@ namespace mcb {
 namespace {
 
 constexpr int SMEM_LIMIT = 227 * 1024;
-constexpr size_t TABLE_BYTES = (32 * 33 + 32 + 24 * 24) * sizeof(double) + 16;   // DD, xs of the block-wise decisions, the next diagonal block, tile counter
+constexpr size_t TABLE_BYTES = (32 * 33 + 32 + SWB_KMAX * SWB_KMAX) * sizeof(double) + 16;   // DD, xs of the block-wise decisions, the next diagonal block, tile counter
 
 #ifdef SWD_TIMING
 __device__ long long swd_clk[32];
@@ -66,9 +66,9 @@ DelayedGeom delayed_geom(int n)
     int K = (int)((SMEM_LIMIT - 2048 - hdr - TABLE_BYTES) / (2 * (size_t)g.ld * sizeof(double)));
     K = K / 4 * 4;
     // block size: 24 measured best at N = 144 (196 against 204 us per slice with 32) and at N = 400 (1092 / 1124)
-    static const int kcap = getenv("MCB_SWEEP_K") ? atoi(getenv("MCB_SWEEP_K")) : 24;
+    static const int kcap = getenv("MCB_SWEEP_K") ? atoi(getenv("MCB_SWEEP_K")) : swb::KMAX;
     if (K > kcap) K = kcap;
-    if (K > 24) K = 24;   // the deciding warp keeps a row of the diagonal block in 24 registers (KMAX)
+    if (K > swb::KMAX) K = swb::KMAX;   // the deciding warp keeps a row of the diagonal block in KMAX registers
     if (K > round_up(n, 4)) K = round_up(n, 4);
     g.K = K;
     // 512 threads (128 registers each) for every N > 64: no spills in the deciding warp and the old tile values
@@ -219,32 +219,33 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             // ---- one warp: the next block's diagonal block brought up to date, D' = D - U[blk', :] Rc[:, blk'] (K^3 FMAs
             // instead of waiting for the N x K x N flush), then its decisions. The other warps start the flush at once.
             if (warp == 0 && kb1 > 0 && !(g.exp & 2)) {
-                {   // 3 x 3 DMMA tiles of the K x K x K product, subtracted from Dn in place
-                    const double* ua[3];
-                    const double* rb[3];
+                {   // KT x KT DMMA tiles of the K x K x K product, subtracted from Dn in place
+                    constexpr int KT = KMAX / 8;
+                    const double* ua[KT];
+                    const double* rb[KT];
 #pragma unroll
-                    for (int x = 0; x < 3; ++x) {
+                    for (int x = 0; x < KT; ++x) {
                         ua[x] = U + q * ld + min(i1 + 8 * x + r, g.np - 1);
                         rb[x] = Rc + q * ld + min(i1 + 8 * x + r, g.np - 1);
                     }
-                    double c[3][3][2];
+                    double c[KT][KT][2];
 #pragma unroll
-                    for (int x = 0; x < 3; ++x)
+                    for (int x = 0; x < KT; ++x)
 #pragma unroll
-                        for (int y = 0; y < 3; ++y) c[x][y][0] = c[x][y][1] = 0.0;
+                        for (int y = 0; y < KT; ++y) c[x][y][0] = c[x][y][1] = 0.0;
                     for (int k0 = 0; k0 < kb4; k0 += 4) {
-                        double av[3], bv[3];
+                        double av[KT], bv[KT];
 #pragma unroll
-                        for (int x = 0; x < 3; ++x) { av[x] = ua[x][k0 * ld]; bv[x] = rb[x][k0 * ld]; }
+                        for (int x = 0; x < KT; ++x) { av[x] = ua[x][k0 * ld]; bv[x] = rb[x][k0 * ld]; }
 #pragma unroll
-                        for (int x = 0; x < 3; ++x)
+                        for (int x = 0; x < KT; ++x)
 #pragma unroll
-                            for (int y = 0; y < 3; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
+                            for (int y = 0; y < KT; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
                     }
 #pragma unroll
-                    for (int x = 0; x < 3; ++x)
+                    for (int x = 0; x < KT; ++x)
 #pragma unroll
-                        for (int y = 0; y < 3; ++y)
+                        for (int y = 0; y < KT; ++y)
 #pragma unroll
                             for (int cc = 0; cc < 2; ++cc) {
                                 const int row = 8 * x + r, col = 8 * y + 2 * q + cc;
