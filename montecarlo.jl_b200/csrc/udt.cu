@@ -227,6 +227,7 @@ int init_udt_kernels()
     MCB_CUDA(cudaFuncSetAttribute(rdivp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     if (init_udt_blocked_kernels()) return -2;
     if (init_udt_resident_kernels()) return -2;
+    if (init_rdivp_blocked_kernels()) return -2;
     return init_udt_cluster_kernels();
 }
 
@@ -274,6 +275,10 @@ int launch_rdivp(int n, int batch, const double* in, long long sIn, double* out,
                  const double* T, long long sT, const int* pivot, long long sP, cudaStream_t st)
 {
     if (in == out) { set_error("rdivp: in-place call"); return -1; }
+    // MCB_RDIVP_BLOCKED=0: the row-by-row kernels below (comparisons)
+    static const bool blocked_on = !(getenv("MCB_RDIVP_BLOCKED") && atoi(getenv("MCB_RDIVP_BLOCKED")) == 0);
+    if (blocked_on && rdivp_blocked_supported(n) && !force_general_udt())
+        return launch_rdivp_blocked(n, batch, in, sIn, out, sOut, T, sT, pivot, sP, st);
     if (rdivp_panel_supported(n) && !force_general_udt() && sIn == (long long)n * n && sOut == sIn &&
         sT == sIn && sP == n)
         return launch_rdivp_panel(n, batch, in, out, T, pivot, st);

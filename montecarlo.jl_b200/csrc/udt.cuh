@@ -31,6 +31,11 @@ bool udt_resident_supported(int n);
 int init_udt_resident_kernels();
 int launch_udt_resident(int n, int batch, const double* X, double* U, double* D, long long sD, double* T, int* pivot,
                         long long sP, int apply_pivot, cudaStream_t st);
+// rdivp! as a blocked forward substitution on the tensor pipe (rdivp_blocked.cu): n % 16 == 0, 256 <= n <= 400
+bool rdivp_blocked_supported(int n);
+int init_rdivp_blocked_kernels();
+int launch_rdivp_blocked(int n, int batch, const double* in, long long sIn, double* out, long long sOut, const double* T,
+                         long long sT, const int* pivot, long long sP, cudaStream_t st);
 // testing aid: route every size through udt_kernel / rdivp_kernel
 void set_force_general_udt(bool on);
 bool force_general_udt();

@@ -107,7 +107,7 @@ def test_udt_contract(n, apply_pivot, linalg_path):
 
 
 @pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
-@pytest.mark.parametrize("n", [4, 16, 64, 144, 400])
+@pytest.mark.parametrize("n", [4, 16, 64, 144, 272, 400])   # 272, 400: blocked substitution on the tensor pipe
 def test_rdivp(n, linalg_path):
     rng = np.random.default_rng(7 + n)
     b = 2
