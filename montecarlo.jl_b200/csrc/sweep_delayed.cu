@@ -27,6 +27,7 @@
 // determinant is the product of the diagonal entries).
 #include "sweep.cuh"
 #include "sweep_blocks.cuh"
+#include "tma.cuh"
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
@@ -134,6 +135,21 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
     const bool worker = grp < ngrp && e < n;
     const int gstep = ngrp * ld;
     const DecideConst dconst{a.gamma_p, a.gamma_m, a.efac_p, a.efac_m};
+    // Cluster of CTAs on one chain (one spin sector): the decisions stay redundant, but the block's columns and rows are
+    // divided - every CTA loads elements [e0, e1) of the K columns and of the K rows, runs the two recurrences there and
+    // sends its part of u_j and of the frozen rows to the peers' shared memory as bulk copies (cp.async.bulk
+    // shared::cta -> shared::cluster, one per vector, peer and array), each CTA waiting on an mbarrier that counts the
+    // incoming bytes. Loads and recurrences shrink by the cluster size; the flush tiles stay interleaved as before.
+    // The exchange itself costs ~8 k cycles per block of 24 sites at N = 400 (115 KB out and in per CTA) whichever way it is
+    // done - per-thread st.shared::cluster, these bulk copies, or a round trip through an L2 scratch with multicast TMA
+    // loads were all measured within 10 % of each other - so the net gain is 8 % of the kernel, not the 25 % the divided
+    // work alone would give.
+    const bool split = blockwise && cls > 1 && !two;
+    const int echunk = (g.np + fcls - 1) / fcls;
+    const int e0 = split ? frank * echunk : 0, e1 = split ? min(g.np, e0 + echunk) : g.np, ne = e1 - e0;
+    uint64_t* xbar = reinterpret_cast<uint64_t*>(tile_ctr + 2);   // counts the bytes the peers send per block
+    uint32_t xphase = 0;
+    if (split && tid == 0) mbar_init(xbar, 1);   // (visible to the peers after the first cluster barrier)
 
     if constexpr (blockwise) {
         // The decisions of block b + 1 run on one warp UNDER the flush of block b (see below); those of the first block
@@ -153,11 +169,46 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
         const int kb4 = round_up(kb, 4);
         // previous flush done (G up to date in every CTA of the chain, buffers free)
         // (two sectors: also before the first block, the partner must be running before its shared memory is written)
-        if (cls > 1 && (i0 > 0 || two)) cluster.sync(); else __syncthreads();
+        if (cls > 1 && (i0 > 0 || two || split)) cluster.sync(); else __syncthreads();
+        if (split && tid == 0)   // the peers' shares of this block's vectors: everything but elements e0 .. e1, both arrays
+            mbar_expect_tx(xbar, (uint32_t)((size_t)round_up(min(K, n - i0), 4) * (g.np - ne) * 2 * sizeof(double)));
         if (i0 == K) SWD_T(1);
         // ---- load the block's columns and rows; zero the padding the flush will read. Flattened over the elements with
         // eight independent loads in flight per thread (a loop over columns per warp serialises the L2 latencies).
-        {
+        if (split) {
+            // this CTA's share of the columns (rows e0 .. e1) and of the rows (columns e0 .. e1) of the block
+            const int ncol = kb4 * ne;
+            for (int base = 0; base < ncol; base += 8 * T) {
+                double v[8];
+#pragma unroll
+                for (int z = 0; z < 8; ++z) {
+                    const int idx = base + z * T + tid;
+                    const int j = idx / ne, row = e0 + idx - j * ne;
+                    v[z] = (idx < ncol && j < kb && row < n) ? Gg[(size_t)(i0 + j) * n + row] : 0.0;
+                }
+#pragma unroll
+                for (int z = 0; z < 8; ++z) {
+                    const int idx = base + z * T + tid;
+                    const int j = idx / ne, row = e0 + idx - j * ne;
+                    if (idx < ncol) Cc[j * ld + row] = v[z];
+                }
+            }
+            for (int base = 0; base < ncol; base += 8 * T) {
+                double v[8];
+#pragma unroll
+                for (int z = 0; z < 8; ++z) {
+                    const int idx = base + z * T + tid;
+                    const int l = e0 + idx / kb4, k = idx % kb4;
+                    v[z] = (idx < ncol && k < kb && l < n) ? Gg[(size_t)l * n + i0 + k] : 0.0;
+                }
+#pragma unroll
+                for (int z = 0; z < 8; ++z) {
+                    const int idx = base + z * T + tid;
+                    const int l = e0 + idx / kb4, k = idx % kb4;
+                    if (idx < ncol) Rc[k * ld + l] = v[z];
+                }
+            }
+        } else {
             const int ncol = kb4 * ld;   // Cc: element (row, j) at Cc[j * ld + row], consecutive threads = consecutive rows
             for (int base = 0; base < ncol; base += 8 * T) {
                 double v[8];
@@ -204,6 +255,11 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             if (i0 == K) SWD_T(2);
             if (!(g.exp & 2)) {
                 if (g.exp & 4) {
+                } else if (split) {
+                    for (int it = tid; it < 2 * ne; it += T) {
+                        if (it < ne) { if (e0 + it < n) column_recurrence(Cc, ld, i0, kb, DD, xs, e0 + it); }
+                        else if (e0 + it - ne < n) row_recurrence(Rc, ld, kb, DD, e0 + it - ne);
+                    }
                 } else if (2 * nv <= T) {
                     if (tid < nv) { if (tid < n) column_recurrence(Cc, ld, i0, kb, DD, xs, tid); }
                     else if (tid < 2 * nv) { if (tid - nv < n) row_recurrence(Rc, ld, kb, DD, tid - nv); }
@@ -214,7 +270,23 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                     }
                 }
             }
-            __syncthreads();
+            if (split) {
+                // this CTA's elements of the update vectors (and the zero padding the flush reads) into the peers' copies
+                fence_async_smem();
+                __syncthreads();
+                if (i0 == K) SWD_T(8);
+                for (int w = tid; w < (fcls - 1) * 2 * kb4; w += T) {
+                    const int p = w / (2 * kb4), rem = w - p * 2 * kb4, arr = rem / kb4, j = rem - arr * kb4;
+                    const uint32_t peer = (uint32_t)((frank + 1 + p) % fcls);   // rank in the cluster
+                    const double* src = (arr ? Rc : Cc) + j * ld + e0;
+                    bulk_s2peer(mapa_u32(smem_u32(src), peer), src, (uint32_t)(ne * sizeof(double)), mapa_u32(smem_u32(xbar), peer));
+                }
+                if (i0 == K) SWD_T(9);
+                mbar_wait(xbar, xphase);
+                xphase ^= 1;
+            } else {
+                __syncthreads();
+            }
             if (i0 == K) SWD_T(3);
             // ---- one warp: the next block's diagonal block brought up to date, D' = D - U[blk', :] Rc[:, blk'] (K^3 FMAs
             // instead of waiting for the N x K x N flush), then its decisions. The other warps start the flush at once.
@@ -491,8 +563,8 @@ int launch_sweep_delayed(const SweepArgs& a, cudaStream_t st)
             long long h[32];
             cudaStreamSynchronize(st);
             cudaMemcpyFromSymbol(h, swd_clk, sizeof(h));
-            fprintf(stderr, "sweep_delayed n=%d K=%d cls=%d cycles: whole loop %lld | tail %lld || block 1: load %lld recurrences %lld next diagonal + decide %lld (under the flush) flush %lld\n",
-                    a.n, g.K, g.cls, h[6] - h[0], h[7] - h[6], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[3]);
+            fprintf(stderr, "sweep_delayed n=%d K=%d cls=%d cycles: whole loop %lld | tail %lld || block 1: load %lld recurrences %lld (of which push %lld, cluster barrier %lld) next diagonal + decide %lld (under the flush) flush %lld\n",
+                    a.n, g.K, g.cls, h[6] - h[0], h[7] - h[6], h[2] - h[1], h[3] - h[2], h[9] - h[8], h[3] - h[9], h[4] - h[3], h[5] - h[3]);
         }
     }
 #endif
