@@ -21,6 +21,8 @@
 // and the accuracy of the Green's functions built from it do not (profiles/experiments/panel_pivot_qr.py: 4e-12 /
 // 8e-13 relative to the step-wise CPU restatement at configs C / D, the same distance LAPACK's dgeqp3 has).
 #include "udt.cuh"
+#include <mutex>
+#include <stdlib.h>
 #include "prof.cuh"
 #include "qr_blocked.cuh"
 #include "tma.cuh"
@@ -335,6 +337,39 @@ int init_udt_blocked_kernels()
     return 0;
 }
 
+// Auxiliary streams for launch_udt_blocked: the panel kernel is a latency chain on one CTA per matrix (42 us per panel at
+// N = 400 whatever the batch), the apply kernel is throughput-bound. With the batch cut into groups that run on their own
+// streams, the panel kernels of one group overlap the apply kernels of the others.
+namespace {
+constexpr int MAX_GROUPS = 4;
+struct GroupStreams {
+    cudaStream_t s[MAX_GROUPS - 1] = {};
+    cudaEvent_t fork = nullptr, join[MAX_GROUPS - 1] = {};
+    bool ready = false;
+};
+GroupStreams g_groups[64];
+std::mutex g_groups_mutex;
+
+int group_streams(GroupStreams** out)
+{
+    int dev = 0;
+    MCB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("udt_blocked: device index out of range"); return -1; }
+    std::lock_guard<std::mutex> lock(g_groups_mutex);
+    GroupStreams& g = g_groups[dev];
+    if (!g.ready) {
+        for (int i = 0; i < MAX_GROUPS - 1; ++i) {
+            MCB_CUDA(cudaStreamCreateWithFlags(&g.s[i], cudaStreamNonBlocking));
+            MCB_CUDA(cudaEventCreateWithFlags(&g.join[i], cudaEventDisableTiming));
+        }
+        MCB_CUDA(cudaEventCreateWithFlags(&g.fork, cudaEventDisableTiming));
+        g.ready = true;
+    }
+    *out = &g;
+    return 0;
+}
+} // namespace
+
 // same contract as launch_udt (udt.cuh); X is the workspace the factorisation happens in
 int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
                        long long sP, int apply_pivot, cudaStream_t st)
@@ -344,10 +379,32 @@ int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long l
     MCB_CUDA(cudaMallocAsync(&norms, (size_t)batch * n * sizeof(double), st));
     MCB_CUDA(cudaMallocAsync(&perm, (size_t)batch * n * sizeof(int), st));
     MCB_CUDA(cudaMallocAsync(&Tfac, (size_t)batch * npan * NB * NB * sizeof(double), st));
-    int rc;
+    // MCB_UDT_GROUPS=1: one stream (comparisons)
+    static const int max_groups = getenv("MCB_UDT_GROUPS") ? atoi(getenv("MCB_UDT_GROUPS")) : MAX_GROUPS;
+    int groups = 1;
+    // two groups: 1558 us per batched 400 x 400 factorisation of 32 against 1750 on one stream; three or four groups (1620)
+    // lose to the host-side cost of issuing three or four times as many launches
+    if (n > 192 && batch >= 8) groups = 2;
+    if (groups > max_groups) groups = max_groups < 1 ? 1 : max_groups;
+    int rc = 0;
     {
         LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
-        rc = udt_blocked_on_scratch(n, batch, X, U, D, sD, T, pivot, sP, apply_pivot, norms, perm, Tfac, st);
+        GroupStreams* gs = nullptr;
+        if (groups > 1 && group_streams(&gs)) return -2;
+        if (groups > 1) MCB_CUDA(cudaEventRecord(gs->fork, st));
+        const size_t nn = (size_t)n * n;
+        for (int g = 0; g < groups && rc == 0; ++g) {
+            const int b0 = (int)((long long)batch * g / groups), b1 = (int)((long long)batch * (g + 1) / groups);
+            cudaStream_t s = g == 0 ? st : gs->s[g - 1];
+            if (g > 0) MCB_CUDA(cudaStreamWaitEvent(s, gs->fork, 0));
+            rc = udt_blocked_on_scratch(n, b1 - b0, X + b0 * nn, U + b0 * nn, D + (size_t)b0 * sD, sD, T + b0 * nn,
+                                        pivot + (size_t)b0 * sP, sP, apply_pivot, norms + (size_t)b0 * n, perm + (size_t)b0 * n,
+                                        Tfac + (size_t)b0 * npan * NB * NB, s);
+            if (g > 0) {
+                MCB_CUDA(cudaEventRecord(gs->join[g - 1], s));
+                MCB_CUDA(cudaStreamWaitEvent(st, gs->join[g - 1], 0));
+            }
+        }
     }
     MCB_CUDA(cudaFreeAsync(norms, st));
     MCB_CUDA(cudaFreeAsync(perm, st));
