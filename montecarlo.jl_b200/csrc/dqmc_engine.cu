@@ -192,6 +192,20 @@ int advance_raw(mcb_dqmc* h, bool left, const double* Usrc, const double* Dsrc, 
                            h->pivot, h->N, 1, h->st));
         return launch_gemm(base_gemm(h, h->W[2], false, Tsrc, false, Tdst), h->st);
     }
+    if (h->use_resident_segment && hi >= lo) {
+        // the whole chain of slice products in one launch (segment_resident.cu)
+        SliceChainArgs c;
+        c.n = h->N; c.batch = h->C;
+        c.Usrc = Usrc; c.Dsrc = Dsrc; c.dst = h->W[0];
+        c.conf = h->conf; c.sConf = (long long)h->M * h->N;
+        c.eT2 = h->hop[2]; c.eT2T = h->hopT[0];
+        c.lo = lo; c.hi = hi; c.left = left ? 1 : 0;
+        c.ep = h->eVp[0]; c.em = h->eVp[1];
+        MCB_TRY(launch_slice_chain_resident(c, h->st));
+        MCB_TRY(launch_udt(h->N, h->C, h->W[0], h->nn, Udst, h->nn, Ddst, h->N, h->W[2], h->nn,
+                           h->pivot, h->N, 1, h->st));
+        return launch_gemm(base_gemm(h, h->W[2], false, Tsrc, false, Tdst), h->st);
+    }
     const double* cur = Usrc;
     const Scale dcol = vec_scale(Dsrc, h->N);
     int pp = 0;

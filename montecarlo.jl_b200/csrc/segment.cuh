@@ -32,6 +32,19 @@ struct SegmentArgs {
 bool segment_supported(int n);
 int launch_segment(const SegmentArgs& a, cudaStream_t st);
 int init_segment_kernels();
+// the products of add_slice_sequence_left / _right with the running product resident in shared memory (segment_resident.cu)
+struct SliceChainArgs {
+    int n = 0, batch = 0;
+    const double* Usrc = nullptr;   // [batch][n][n]
+    const double* Dsrc = nullptr;   // [batch][n] column scaling applied at the end (null: none)
+    double* dst = nullptr;          // [batch][n][n]
+    const int8_t* conf = nullptr; long long sConf = 0;
+    const double* eT2 = nullptr;    // e^{-dtau T}
+    const double* eT2T = nullptr;   // its transpose
+    int lo = 0, hi = 0, left = 1;   // slices lo .. hi (1-based); left: B_hi ... B_lo, else B_lo' ... B_hi'
+    double ep = 1, em = 1;          // exp(+lambda s) for s = +1 / -1
+};
+int launch_slice_chain_resident(const SliceChainArgs& a, cudaStream_t st);
 // the same run of slice visits with G resident in one CTA's shared memory (segment_resident.cu): N = 144
 bool segment_resident_supported(int n);
 int launch_segment_resident(const SegmentArgs& a, cudaStream_t st);

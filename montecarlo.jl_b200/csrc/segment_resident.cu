@@ -411,6 +411,65 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
     }
 }
 
+// The slice-matrix chains of add_slice_sequence_left / _right (src/flavors/DQMC/stack.jl:242-311) with the running
+// product resident in shared memory: dst = (B_hi ... B_lo Usrc) diag(Dsrc) (left) or (B_lo' ... B_hi' Usrc) diag(Dsrc)
+// (right), B_l = e^{-dtau T} diag(e^{+lambda s_l}) (slice_matrices.jl:42-48, 70-76). One launch replaces hi - lo + 1
+// batched GEMM launches and their round trips of the product through L2.
+template <int N>
+__global__ void __launch_bounds__(RGeo<N>::THREADS, 1) slice_chain_resident_kernel(SliceChainArgs a)
+{
+    using R = RGeo<N>;
+    constexpr int LD = R::LD, T = R::THREADS;
+    extern __shared__ __align__(128) double sm[];
+    double* Gs = sm + R::OFF_G;
+    double* ring = sm + R::OFF_CC;
+    double* sc_mid = sm + R::OFF_SC;
+    double* sc_row = sc_mid + N;
+    double* dcol = sc_row + N;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sm + R::OFF_BAR);
+    uint64_t* empty = full + R::STAGES;
+    uint64_t* gbar = empty + R::STAGES;
+    const int chain = blockIdx.x, tid = threadIdx.x;
+    const double* src = a.Usrc + (size_t)chain * N * N;
+    double* dst = a.dst + (size_t)chain * N * N;
+    const int8_t* cg = a.conf + (size_t)chain * a.sConf;
+
+    if (tid == 0) {
+        for (int s = 0; s < R::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 12); }
+        mbar_init(gbar, 1);
+    }
+    __syncthreads();
+    if (tid == 0) mbar_expect_tx(gbar, (uint32_t)(N * N * sizeof(double)));
+    if (tid < N) bulk_g2s(Gs + (size_t)tid * LD, src + (size_t)tid * N, N * sizeof(double), gbar);
+    for (int i = tid; i < N; i += T) dcol[i] = a.Dsrc ? a.Dsrc[(size_t)chain * N + i] : 1.0;
+    mbar_wait(gbar, 0);
+
+    uint32_t cnt = 0;
+    const int count = a.hi - a.lo + 1;
+    for (int t = 0; t < count; ++t) {
+        const int slice = a.left ? a.lo + t : a.hi - t;
+        for (int i = tid; i < N; i += T) {
+            const double ev = cg[(size_t)(slice - 1) * N + i] > 0 ? a.ep : a.em;
+            sc_mid[i] = a.left ? ev : 1.0;
+            sc_row[i] = a.left ? 1.0 : ev;
+        }
+        __syncthreads();
+        wrap_product<N, 1>(Gs, ring, a.left ? a.eT2 : a.eT2T, sc_mid, sc_row, full, empty, cnt, tid);
+    }
+    // column scaling by Dsrc, then out (one bulk copy per column)
+    for (int idx = tid; idx < N * N; idx += T) {
+        const int col = idx / N, row = idx - col * N;
+        Gs[(size_t)col * LD + row] *= dcol[col];
+    }
+    fence_async_smem();
+    __syncthreads();
+    if (tid < N) {
+        bulk_s2g(dst + (size_t)tid * N, Gs + (size_t)tid * LD, N * sizeof(double));
+        bulk_commit();
+        bulk_wait_all();
+    }
+}
+
 } // namespace
 
 bool segment_resident_supported(int n) { return n == 144; }
@@ -418,6 +477,17 @@ bool segment_resident_supported(int n) { return n == 144; }
 int init_segment_resident_kernels()
 {
     MCB_CUDA(cudaFuncSetAttribute(segment_resident_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RGeo<144>::SMEM));
+    MCB_CUDA(cudaFuncSetAttribute(slice_chain_resident_kernel<144>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RGeo<144>::SMEM));
+    return 0;
+}
+
+int launch_slice_chain_resident(const SliceChainArgs& a, cudaStream_t st)
+{
+    if (a.n != 144) { set_error("slice_chain_resident: unsupported size"); return -1; }
+    if (a.hi < a.lo || a.batch <= 0) { set_error("slice_chain_resident: empty chain"); return -1; }
+    LaunchScope scope(LC_GEMM, st, 2.0 * a.n * (double)a.n * a.n * (a.hi - a.lo + 1) * a.batch);
+    slice_chain_resident_kernel<144><<<a.batch, RGeo<144>::THREADS, RGeo<144>::SMEM, st>>>(a);
+    MCB_CUDA(cudaGetLastError());
     return 0;
 }
 
