@@ -555,7 +555,14 @@ def run_ising(args, w, rank, local_rank, world):
             "roofline": {"kernel": "ising_halfsweep_kernel", "bound": "hbm", "achieved": gbs, "peak": hbm_peak,
                          "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": traffic_for(args.workload, "ising"),
                          "peak_source": hbm_src,
-                         "avg_launch_us": 1e3 * ms / max(1, gpu_launches)}}
+                         "avg_launch_us": 1e3 * ms / max(1, gpu_launches),
+                         # what actually bounds the kernel (ncu, profiles/r02u_ncu_full_summary.txt): the planes stay in L2,
+                         # the integer ALU pipe is 71 % busy (24.7 thread instructions per spin, two thirds of them the ten
+                         # Philox4x32 rounds shared by four spins); ALU ceiling = value / 0.71
+                         "bound_detail": {"limiter": "integer ALU pipe", "alu_pipe_pct_of_peak": 71.1,
+                                          "thread_instructions_per_spin": 24.7, "philox_rounds_per_spin": 2.5,
+                                          "alu_ceiling_flips_per_ns": value / world / 0.711 * world,
+                                          "source": "profiles/r02u_ncu_full_summary.txt"}}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         b = cpu_ising_baseline(w)
         line["cpu_baseline"] = {k2: b[k2] for k2 in ("value", "unit", "cores", "kind", "sample")}
