@@ -151,7 +151,7 @@ int mcb_dqmc_set_hopping(mcb_dqmc* h, const double* eT_half_minus, const double*
     const double* src[4] = {eT_half_minus, eT_half_plus, eT_minus, eT_plus};
     for (int i = 0; i < 4; ++i)
         MCB_CUDA(cudaMemcpyAsync(h->hop[i], src[i], h->nn * sizeof(double), cudaMemcpyHostToDevice, h->st));
-    if (h->use_resident_segment) {
+    if (h->use_resident_segment || gemm_tma_routes_abt(h->N, h->C)) {   // transposes of e^{-+dtau T} (streamed as columns)
         for (int i = 0; i < 2; ++i) {
             if (!h->hopT[i]) MCB_CUDA(cudaMalloc(&h->hopT[i], h->nn * sizeof(double)));
             transpose_kernel<<<(unsigned)((h->nn + 255) / 256), 256, 0, h->st>>>(h->hopT[i], h->hop[2 + i], h->N);

@@ -84,7 +84,11 @@ int wrap_greens(mcb_dqmc* h, double* Gx, double* Gt, int curr_slice, int directi
         a.row = conf_scale(h, l, false);
         MCB_TRY(launch_gemm(a, h->st));
         // multiply_slice_matrix_right!: G = Gt e^{-dtau T} diag(e^{+lambda s})
-        GemmArgs b = base_gemm(h, Gt, false, h->hop[2], true, Gx);
+        // (as Gt (e^{-dtau T})'' with the stored transpose where that form goes to the TMA-staged kernel: both tiles are then
+        // contiguous along their long side)
+        const bool abt = !h->use_resident_segment && h->hopT[0] && gemm_tma_routes_abt(h->N, h->C);
+        GemmArgs b = base_gemm(h, Gt, false, abt ? h->hopT[0] : h->hop[2], true, Gx);
+        b.transB = abt;
         b.col = conf_scale(h, l, true);
         MCB_TRY(launch_gemm(b, h->st));
     } else {
@@ -92,7 +96,9 @@ int wrap_greens(mcb_dqmc* h, double* Gx, double* Gt, int curr_slice, int directi
         // multiply_slice_matrix_left!: Gt = e^{-dtau T} diag(e^{+lambda s}) G
         MCB_TRY(mul_slice_left(h, l, Gx, Gt));
         // multiply_slice_matrix_inv_right!: G = Gt diag(e^{-lambda s}) e^{+dtau T}
-        GemmArgs b = base_gemm(h, Gt, false, h->hop[3], true, Gx);
+        const bool abt = !h->use_resident_segment && h->hopT[1] && gemm_tma_routes_abt(h->N, h->C);
+        GemmArgs b = base_gemm(h, Gt, false, abt ? h->hopT[1] : h->hop[3], true, Gx);
+        b.transB = abt;
         b.mid = conf_scale(h, l, false);
         MCB_TRY(launch_gemm(b, h->st));
     }

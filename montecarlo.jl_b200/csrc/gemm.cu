@@ -324,6 +324,12 @@ int set_gemm_attrs()
 
 static int g_sms = 148;
 
+bool gemm_tma_routes_abt(int n, int batch)
+{
+    static const int tma_on = getenv("MCB_GEMM_TMA") ? atoi(getenv("MCB_GEMM_TMA")) : 1;
+    return tma_on && n >= 144 && n % 16 == 0 && (n % 80 == 0 || n % 64 == 0 || n % 48 == 0) && !(n == 144 && batch >= g_sms / 2);
+}
+
 int init_gemm_kernels()
 {
     {

@@ -28,5 +28,7 @@ int init_gemm_kernels();
 bool gemm_tma_supported(const GemmArgs& g);
 int launch_gemm_tma(const GemmArgs& g, cudaStream_t st);
 int init_gemm_tma_kernels();
+// true if launch_gemm sends A B' products of this size and batch to the TMA-staged kernel
+bool gemm_tma_routes_abt(int n, int batch);
 
 } // namespace mcb
