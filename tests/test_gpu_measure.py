@@ -122,6 +122,25 @@ def test_run_follows_the_reference_measurement_schedule():
     mc.close()
 
 
+def test_run_schedule_on_the_chain_resident_n144_path():
+    """The same on a 12 x 12 lattice: wrap + sweep run inside segment_resident_kernel (runs of up to safe_mult slices, cut at
+    the measurement point), the stabilisation through the resident slice chains and the resident blocked QR."""
+    model = mcb.HubbardModelAttractive(L=12, U=2.0)
+    kw = dict(beta=1.0, delta_tau=0.1, safe_mult=5)
+    mc = mcb.DQMC(model, n_chains=2, seed=31, thermalization=1, sweeps=3, measure_rate=1, **kw)
+    conf0 = mc.conf()
+    obs = mc.run()
+    tables = orc.MeasurementTables(12, 5)
+    for c in range(2):
+        o = orc.OracleDQMC(144, 10, 5, 0.1, 2.0, mc.hop, conf0[c], seed=31, chain=c)
+        o.build_stack()
+        want = orc.run_measured(o, tables, thermalization=1, sweeps=3, measure_rate=1, T=model.hopping_matrix(), U=2.0)
+        assert want["count"] == obs["count"] == 3      # sweeps 2, 3, 4
+        for k in ("G", "occupation", "cdc", "sdc_x", "pc", "n", "double_occupancy", "e_kin", "e_int"):
+            assert np.abs(obs[k][c] - want[k]).max() < 1e-9, (k, c)
+    mc.close()
+
+
 def test_attractive_4x4_beta1_against_the_reference_literals():
     """test/integration_tests.jl:28-93 with 512 chains x (10 + 1000) sweeps."""
     g = _gold("attractive_4x4_beta1")
