@@ -17,7 +17,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $o/${tag}_launches_D.csv python profiles/microbench/sweep400.py > /dev/null 2>&1
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $o/${tag}_launches_A.csv python bench.py --steps 1 --warmup 1 --no-extra-configs --no-cpu-baseline > /dev/null 2>&1
 # full-set captures
-timeout 300 ncu --set full --import-source on --clock-control none -k regex:segment_resident -s 2 -c 1 -f -o $o/${tag}_C_segment_resident python profiles/microbench/sweep144.py > /dev/null 2>&1
+timeout 300 ncu --set full --import-source on --clock-control none -k regex:segment_resident -s 1 -c 1 -f -o $o/${tag}_C_segment_resident python profiles/microbench/sweep144.py > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:sweep_delayed -s 2 -c 1 -f -o $o/${tag}_D_sweep_delayed python profiles/microbench/sweep400.py > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:gemm_tma -s 2 -c 1 -f -o $o/${tag}_D_gemm_tma python profiles/microbench/sweep400.py > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:ising_halfsweep -s 4 -c 1 -f -o $o/${tag}_ising_halfsweep python bench.py --workload ising64 --steps 1 --warmup 1 --no-extra-configs --no-cpu-baseline > /dev/null 2>&1
