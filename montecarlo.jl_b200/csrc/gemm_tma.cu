@@ -30,20 +30,21 @@ struct TT {
     static constexpr int TILE = (BK * LDX > T * LDK) ? BK * LDX : T * LDK;   // doubles per operand per stage
     static constexpr int WT = T / 16;             // DMMA tiles per warp in each direction (2 x 2 warps of T/2 x T/2)
     static constexpr int LDC = T + 4;             // result tile [col][row]
-    static constexpr size_t SMEM = ((size_t)2 * STAGES * TILE + (size_t)STAGES * BK + 2 * STAGES) * sizeof(double);
+    static constexpr size_t SMEM = ((size_t)2 * STAGES * TILE + (size_t)STAGES * BK + 2 * STAGES) * sizeof(double);   // + full / empty barriers
     static_assert(T % 16 == 0 && LDX % 16 == 4 && (size_t)T * LDC <= (size_t)2 * STAGES * TILE, "unsupported tile");
 };
 
 // one stage of one operand: XC = the tile is contiguous in its non-K index in global memory (A: !transA, B: transB)
+// issued by one warp (lane = its lane index)
 template <int T, bool XC>
-__device__ __forceinline__ void issue_tile(double* S, const double* __restrict__ P, int n, int x0, int k0, int tid,
+__device__ __forceinline__ void issue_tile(double* S, const double* __restrict__ P, int n, int x0, int k0, int lane,
                                            uint64_t* bar)
 {
     constexpr int BK = TT<T>::BK;
     if (XC) {   // BK column segments of T doubles
-        if (tid < BK) bulk_g2s(S + tid * TT<T>::LDX, P + (size_t)x0 + (size_t)(k0 + tid) * n, T * sizeof(double), bar);
+        if (lane < BK) bulk_g2s(S + lane * TT<T>::LDX, P + (size_t)x0 + (size_t)(k0 + lane) * n, T * sizeof(double), bar);
     } else {    // T row segments of BK doubles
-        for (int x = tid; x < T; x += THREADS)
+        for (int x = lane; x < T; x += 32)
             bulk_g2s(S + x * TT<T>::LDK, P + (size_t)k0 + (size_t)(x0 + x) * n, BK * sizeof(double), bar);
     }
 }
@@ -76,19 +77,25 @@ __global__ void __launch_bounds__(THREADS) gemm_tma_kernel(GemmArgs g)
     const bool has_mid = g.mid.active();
     const int nk = n / BK;
 
+    uint64_t* empty = full + STAGES;   // one arrival per warp: the stage may be refilled
     if (tid == 0) {
-        for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, THREADS / 32); }
     }
     __syncthreads();
+    // one warp issues a stage: the diagonal `mid` first (ordered before the consumers by the barrier's arrival), then the
+    // byte count, then the copies. No CTA barrier inside the K loop: stage s is refilled for tile kt + STAGES by warp
+    // kt % 4 once all four warps have released it.
     auto issue = [&](int kt) {
         const int s = kt % STAGES, k0 = kt * BK;
-        if (tid == 0) mbar_expect_tx(full + s, 2u * T * BK * sizeof(double));
-        issue_tile<T, !TA>(As + (size_t)s * TILE, A, n, m0, k0, tid, full + s);
-        issue_tile<T, TB>(Bs + (size_t)s * TILE, B, n, n0, k0, tid, full + s);
-        if (has_mid && tid < BK) midv[s * BK + tid] = g.mid.at(chain, k0 + tid);
+        if (has_mid && lane < BK) midv[s * BK + lane] = g.mid.at(chain, k0 + lane);
+        __syncwarp();
+        if (lane == 0) mbar_expect_tx(full + s, 2u * T * BK * sizeof(double));
+        __syncwarp();
+        issue_tile<T, !TA>(As + (size_t)s * TILE, A, n, m0, k0, lane, full + s);
+        issue_tile<T, TB>(Bs + (size_t)s * TILE, B, n, n0, k0, lane, full + s);
     };
-    for (int kt = 0; kt < STAGES && kt < nk; ++kt) issue(kt);
-    __syncthreads();   // midv of the first stages is written with plain stores: the mbarrier orders only the copies
+    if (warp == 0)
+        for (int kt = 0; kt < STAGES && kt < nk; ++kt) issue(kt);
 
     double acc[WT][WT][2];
 #pragma unroll
@@ -118,9 +125,14 @@ __global__ void __launch_bounds__(THREADS) gemm_tma_kernel(GemmArgs g)
 #pragma unroll
                 for (int j = 0; j < WT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
-        __syncthreads();                      // every warp is done with stage s: refill it
-        if (kt + STAGES < nk) issue(kt + STAGES);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + s);
+        if (kt + STAGES < nk && warp == kt % (THREADS / 32)) {
+            mbar_wait(empty + s, (kt / STAGES) & 1);
+            issue(kt + STAGES);
+        }
     }
+    __syncthreads();   // every warp is done with the operand ring: it becomes the result tile
 
     // ---- epilogue: scalings in registers, the tile through shared memory, bulk stores of its column segments
     double* Cs = smem;                        // [T][LDC], the operand ring is free (barrier above)
