@@ -55,6 +55,13 @@ size_t panel_smem(int n)
 
 // NT threads; the Householder steps run on warps 0 .. PW-1 (more warps only add redundant per-step work: 1425
 // cycles per step with 8 warps of a 256-thread CTA, 910 with 4), everything else on all of them
+#ifdef SWD_TIMING
+__device__ long long qrb_clk[16];
+#define QRB_T(i) do { if (blockIdx.x == 0 && threadIdx.x == 0 && a.j == 5 * NB) qrb_clk[i] = clock64(); } while (0)
+#else
+#define QRB_T(i) do { } while (0)
+#endif
+
 template <int NT, int PW, int TPW, int GW>
 __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
 {
@@ -82,6 +89,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     int* perm = a.perm + (size_t)chain * n;
     const int m = n - j, mt = m / 8;
 
+    QRB_T(0);
     if (tid == 0) mbar_init(mbar, 1);
     // ---- squared norms of the trailing columns (rows >= j): exact, from the previous update; computed here at j = 0
     if (j == 0) {
@@ -97,8 +105,11 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     } else {
         for (int c = j + tid; c < n; c += T) { const double s = __ldcg(gn + c); nrm[c] = (s == s) ? s : INFINITY; }
     }
+    __syncthreads();
+    QRB_T(1);
     // ---- the NB largest, by decreasing norm (ties: lower position first)
     qrb::select_by_rank<NT>(nrm, j, n, tid, reinterpret_cast<int*>(Sred), sel);
+    QRB_T(2);
     // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
     if (tid < NB) pstage[tid] = perm[sel[tid]];
     if (tid == 0) {
@@ -122,6 +133,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     if (tid < nd) moved = perm[disp[tid]];
     mbar_wait(mbar, 0);
     __syncthreads();   // every thread has read its perm entries; the staged columns are complete
+    QRB_T(3);
     if (tid < nd) perm[hole[tid]] = moved;
     if (tid < NB) perm[j + tid] = pstage[tid];
     if (tid == 0 && nd > 0) {
@@ -150,6 +162,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
         }
     }
     __syncthreads();
+    QRB_T(4);
     for (int e = tid; e < NB * NB; e += T) {
         const int c = e / NB, r = e % NB;
         const double v = P[(size_t)c * ldp + j + r];
@@ -162,11 +175,13 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     for (int e = tid; e < NB * NB; e += T) P[(size_t)(e / NB) * ldp + j + e % NB] = Ptop[e];
     fence_async_smem();
     __syncthreads();
+    QRB_T(5);
     if (tid == 0) {
         for (int s = 0; s < NB; ++s) bulk_s2g(A + (size_t)(j + s) * n, P + (size_t)s * ldp, (uint32_t)n * sizeof(double));
         bulk_commit();
         bulk_wait_all();
     }
+    QRB_T(6);
 }
 
 // ---------------------------------------------------------------------------------------------- apply
@@ -310,6 +325,18 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
         if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
         else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
     }
+#ifdef SWD_TIMING
+    {
+        static int shown = 0;
+        if (!small && shown++ < 2) {
+            long long h[16];
+            cudaStreamSynchronize(st);
+            cudaMemcpyFromSymbol(h, qrb_clk, sizeof(h));
+            fprintf(stderr, "qrb_panel n=%d panel 5 cycles: norms %lld select %lld lists+gather %lld steps %lld top+gram+T %lld store %lld | total %lld\n",
+                    n, h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[4], h[6] - h[5], h[6] - h[0]);
+        }
+    }
+#endif
     // explicit Q: the block reflectors in reverse order on the identity; panel p leaves columns < p*NB alone
     qrb_identity_kernel<<<dim3(8, batch), 256, 0, st>>>(U, n);
     MCB_CUDA(cudaGetLastError());

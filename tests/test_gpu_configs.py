@@ -66,6 +66,22 @@ def test_config_C_128_chains_as_benched():
     mc.close()
 
 
+def test_config_C_propagation_canary_on_the_resident_path():
+    """The same lattice with check_propagation_error on (stack.jl:540-550): the wrapped G of the chain-resident kernel
+    against the freshly stabilised one at every stabilisation of a full sweep, and the oracle's own canary for one chain."""
+    mc, oracles = _run_against_oracle(12, 4.0, 10.0, 0.1, 128, watch=(5,), checkpoints=(10, 11, 21), check=True)
+    mc.sweep(1)
+    for o in oracles.values():
+        o.sweep(1)
+    err = mc.stats()["max_propagation_error"]
+    assert np.all(np.isfinite(err)) and err.max() < 1e-6, err.max()
+    want = oracles[5].state()["max_prop_err"]
+    # (rounding noise amplified by ten wraps: the two implementations agree in magnitude, not in digits)
+    assert want < 1e-6 and err[5] < 10 * want + 1e-8, (err[5], want)
+    assert np.all(mc.stats()["n_nonfinite"] == 0)
+    mc.close()
+
+
 def test_config_D_32_chains_real_beta():
     """20 x 20, U = 4, beta = 16, dtau = 0.05 (M = 320, 33 stack slots, singular values spanning tens of decades),
     32 chains, propagation check on: build_stack + the first 21 updates (two stabilisations) of chains 0 / 31, then
