@@ -203,7 +203,6 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
     uint64_t* empty = full + R::STAGES;
     uint64_t* gbar = empty + R::STAGES;
     int* tile_ctr = reinterpret_cast<int*>(sm + R::OFF_MISC);
-    volatile int* decide_done = tile_ctr + 1;
     int8_t* s_in = reinterpret_cast<int8_t*>(sm + R::OFF_S);
     int8_t* s_out = s_in + (N + 15) / 16 * 16;
 
@@ -290,7 +289,7 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
                 if (tid < NV) { if (tid < N) column_recurrence_g(Gs + (size_t)i0 * LD, LD, Cc, LD, i0, K, DD, xs, tid); }
                 else if (tid < 2 * NV) { if (tid - NV < N) row_recurrence_g(Gs + i0, LD, Rc, LD, K, DD, tid - NV); }
                 else {
-                    if (tid == 2 * NV) { *tile_ctr = 0; *decide_done = 0; }
+                    if (tid == 2 * NV) *tile_ctr = 0;
                     if (has_next)
                     for (int idx = tid - 2 * NV; idx < K * K; idx += T - 2 * NV) {
                         const int ra = idx % K, cb = idx / K;
@@ -334,26 +333,27 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
                 for (int b = 0; b < K; ++b) reg[b] = lane < K ? Dn[b * K + lane] : 0.0;
                 nacc += decide_rows<K>(dconst, reg, i1, K, s_in, s_out, unif, DD, xs, lane);
                 if (v == 1 && i0 == K) SGR_T(8);
-                __syncwarp();
-                if (lane == 0) { __threadfence_block(); *decide_done = 1; }
+                // the two warps on this scheduler were parked on a named barrier (no polling: a spinning warp takes issue
+                // slots from the decisions); let them into the flush
+                asm volatile("bar.arrive 1, 96;" ::: "memory");
             }
             // ---- flush G -= U Rc in shared memory: 18 work items of 16 rows x 72 columns (2 x 9 DMMA tiles whose accumulators
             // start as the G tile; the A operand is -U), handed out by a counter. The warps that share the deciding warp's
             // scheduler join when it is done (their DMMAs would queue in front of its dependent FP64 chain, sweep_delayed.cu).
-            if (has_next && (warp & 3) == 0 && warp != 0) {
-                while (!*decide_done) __nanosleep(64);
-            }
+            if (has_next && (warp & 3) == 0 && warp != 0) asm volatile("bar.sync 1, 96;" ::: "memory");
             {
                 const bool check = last_visit && !has_next;
+                constexpr int FR = 1;                  // row tiles (of 8) per work item
+                constexpr int FI = 2 * N / (8 * FR);   // work items
                 for (;;) {
                     int item = 0;
                     if (lane == 0) item = atomicAdd(tile_ctr, 1);
                     item = __shfl_sync(0xffffffffu, item, 0);
-                    if (item >= 18) break;
-                    const int row0 = (item >> 1) * 16, col0 = (item & 1) * (N / 2);
-                    double c[2][9][2];
+                    if (item >= FI) break;
+                    const int row0 = (item >> 1) * (8 * FR), col0 = (item & 1) * (N / 2);
+                    double c[FR][9][2];
 #pragma unroll
-                    for (int x = 0; x < 2; ++x)
+                    for (int x = 0; x < FR; ++x)
 #pragma unroll
                         for (int y = 0; y < 9; ++y)
 #pragma unroll
@@ -361,18 +361,18 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
                                 c[x][y][cc] = Gs[(size_t)(col0 + 8 * y + 2 * q + cc) * LD + row0 + 8 * x + r];
 #pragma unroll
                     for (int k0 = 0; k0 < K; k0 += 4) {
-                        double av[2], bv[9];
+                        double av[FR], bv[9];
 #pragma unroll
-                        for (int x = 0; x < 2; ++x) av[x] = -Cc[(k0 + q) * LD + row0 + 8 * x + r];
+                        for (int x = 0; x < FR; ++x) av[x] = -Cc[(k0 + q) * LD + row0 + 8 * x + r];
 #pragma unroll
                         for (int y = 0; y < 9; ++y) bv[y] = Rc[(k0 + q) * LD + col0 + 8 * y + r];
 #pragma unroll
-                        for (int x = 0; x < 2; ++x)
+                        for (int x = 0; x < FR; ++x)
 #pragma unroll
                             for (int y = 0; y < 9; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
                     }
 #pragma unroll
-                    for (int x = 0; x < 2; ++x)
+                    for (int x = 0; x < FR; ++x)
 #pragma unroll
                         for (int y = 0; y < 9; ++y)
 #pragma unroll

@@ -331,12 +331,16 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
                 nacc += decide_rows<KMAX>(dconst, reg, i1, kb1, s_in, s_out, unif, DD, xs, lane);
                 if (i0 == K) SWD_T(4);
                 __syncwarp();
-                if (lane == 0) { __threadfence_block(); *decide_done = 1; }
-            } else if (kb1 > 0 && !(g.exp & 2) && ((!(g.exp & 64) && (warp & 3) == 0) || (g.exp & 128))) {
+                if (g.exp & 128) { if (lane == 0) { __threadfence_block(); *decide_done = 1; } }
+                else if (!(g.exp & 64)) asm volatile("bar.arrive 1, %0;" ::"r"(T / 4) : "memory");
+            } else if (kb1 > 0 && !(g.exp & 2) && (g.exp & 128)) {
+                while (!*decide_done) __nanosleep(100);   // experiment: every warp waits for the decisions
+            } else if (kb1 > 0 && !(g.exp & 2) && !(g.exp & 64) && (warp & 3) == 0) {
                 // The warps that share the deciding warp's scheduler stay out of the flush until it is done: their DMMAs
                 // would queue in front of its dependent FP64 chain (decisions 32 k cycles with them, 24 k without, at
-                // N = 144). Experiments: bit 64 lets them in, bit 128 makes every warp wait.
-                while (!*decide_done) __nanosleep(100);
+                // N = 144). They park on a named barrier (a polling loop takes issue slots from the decisions).
+                // Experiment bit 64 lets them in.
+                asm volatile("bar.sync 1, %0;" ::"r"(T / 4) : "memory");
             }
         } else {
             // ---- site by site (two spin sectors: the partner's G_ii arrives through distributed shared memory)
