@@ -114,6 +114,26 @@ int mcb_dqmc_calculate_greens_at(mcb_dqmc* h, int32_t slice, double* G);
  * stacks are rebuilt only if the configuration changed since the last call. Layout [chain][col][row]. */
 int mcb_dqmc_greens_unequal(mcb_dqmc* h, int32_t slice1, int32_t slice2, double* G, int32_t physical);
 
+/* The one collective of a multi-GPU run (dqmc_allreduce_observables): the reference runs one
+ * independent Markov chain per process (src/flavors/DQMC/DQMC.jl:369-515) and combines results afterwards; here the ranks
+ * of a run sum the moments of the per-chain observable means at the end. NCCL is loaded at run time (dlopen of
+ * libnccl.so.2, or of the file named by the environment variable MCB_NCCL_LIB); the library does not link against it.
+ *   mcb_comm_unique_id   rank 0 obtains the 128-byte id and hands it to the other ranks (file, MPI, socket ...)
+ *   mcb_comm_create      every rank, after cudaSetDevice-able device_id is known; collective over the n_ranks ranks
+ *   mcb_dqmc_allreduce_observables   moments[mcb_dqmc_moments_len(h)] =
+ *        [ sum_c x_c (R) | sum_c x_c^2 (R) | sum_c G_c (F N^2) | sum_c G_c^2 (F N^2) | number of chains ]
+ *        over the chains c of ALL ranks, x_c / G_c = chain c's means over the measurements taken so far (record layout R =
+ *        mcb_dqmc_observable_len as in mcb_dqmc_get_observables, G as in mcb_dqmc_get_greens_sum, F = 1). A rank without
+ *        measurements contributes zeros and zero chains. comm == NULL: the moments of this rank alone, no NCCL needed.
+ *        mean = sum / chains, standard error^2 = (sumsq / chains - mean^2) / (chains - 1). */
+typedef struct mcb_comm mcb_comm;
+#define MCB_UNIQUE_ID_BYTES 128
+int mcb_comm_unique_id(void* id);
+int mcb_comm_create(const void* id, int32_t n_ranks, int32_t rank, int32_t device_id, mcb_comm** out);
+int mcb_comm_destroy(mcb_comm* c);
+int32_t mcb_dqmc_moments_len(mcb_dqmc* h);
+int mcb_dqmc_allreduce_observables(mcb_dqmc* h, mcb_comm* c, double* moments);
+
 /* CombinedGreensIterator(mc, recalculate) (src/flavors/DQMC/unequal_time_stack.jl:746-885) on the device: yields, for
  * l = 1 .. n_slices, G(0 <- l), G(l <- 0) and G(l <- l) of the current configuration by advancing three UDT triples one
  * slice at a time (quick advance :862-885), re-factorising them every safe_mult slices (:824-861) and recomputing them from

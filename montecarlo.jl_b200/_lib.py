@@ -57,6 +57,11 @@ SIGNATURES = {
     "mcb_dqmc_get_greens": (C.c_int, [C.c_void_p, _f64, C.c_int32]),
     "mcb_dqmc_calculate_greens_at": (C.c_int, [C.c_void_p, C.c_int32, _f64]),
     "mcb_dqmc_greens_unequal": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, _f64, C.c_int32]),
+    "mcb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "mcb_comm_create": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "mcb_comm_destroy": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_moments_len": (C.c_int32, [C.c_void_p]),
+    "mcb_dqmc_allreduce_observables": (C.c_int, [C.c_void_p, C.c_void_p, _f64]),
     "mcb_dqmc_cgi_begin": (C.c_int, [C.c_void_p, C.c_int32]),
     "mcb_dqmc_cgi_next": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_void_p, C.c_void_p, C.c_void_p]),
     "mcb_dqmc_cgi_device_results": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 3),

@@ -269,6 +269,24 @@ class DQMC:
             out["mz"] = rec[:, o_occ + 2 * N:o_occ + 3 * N]
         return out
 
+    def allreduce_moments(self, comm=None):
+        """Moments of the per-chain observable means summed over the chains of all ranks of `comm` (an
+        `sharding.NcclComm`; None = this handle alone): the C-ABI collective mcb_dqmc_allreduce_observables.
+        Returns (record_sum, record_sumsq, G_sum, G_sumsq, n_chains) with the record in the layout of
+        mcb_dqmc_get_observables and G as (N, N)."""
+        if self.model.flv != 1:
+            raise NotImplementedError("allreduce_moments: one-flavor handles only")
+        L = self.L
+        n = L.mcb_dqmc_moments_len(self.h)
+        if n <= 0:
+            raise RuntimeError("enable_measurements first")
+        buf = np.empty(n)
+        _lib.check(L.mcb_dqmc_allreduce_observables(self.h, comm.h if comm is not None else None, buf))
+        R, NN = self._f("observable_len")(self.h), self.N * self.N
+        g = lambda a: a.reshape(self.N, self.N).T.copy()
+        return (buf[:R].copy(), buf[R:2 * R].copy(), g(buf[2 * R:2 * R + NN]), g(buf[2 * R + NN:2 * R + 2 * NN]),
+                int(round(buf[-1])))
+
     @staticmethod
     def observable_shapes(model, K=None):
         """Trailing shapes (without the chain axis) of everything observables() returns as an array; lets a rank

@@ -13,6 +13,35 @@ import os
 import numpy as np
 
 
+class NcclComm:
+    """Communicator of the C-ABI collective (mcb_comm_*, csrc/comm.cu): NCCL loaded by the library itself, no torch.
+    Rank 0 calls NcclComm.unique_id() and passes the 128 bytes to the other ranks by any means."""
+
+    @staticmethod
+    def unique_id():
+        import ctypes as C
+        from . import _lib
+        buf = C.create_string_buffer(128)
+        _lib.check(_lib.lib().mcb_comm_unique_id(buf))
+        return buf.raw
+
+    def __init__(self, unique_id, n_ranks, rank, device=0):
+        import ctypes as C
+        from . import _lib
+        self.L = _lib.lib()
+        self.h = C.c_void_p()
+        _lib.check(self.L.mcb_comm_create(C.c_char_p(bytes(unique_id)), n_ranks, rank, device, C.byref(self.h)))
+        self.n_ranks, self.rank = n_ranks, rank
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.L.mcb_comm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
 def dist_env():
     """(rank, local_rank, world_size) from the torchrun environment; (0, 0, 1) when run alone."""
     return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)),
