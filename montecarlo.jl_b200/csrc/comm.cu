@@ -38,8 +38,11 @@ int load_nccl()
 {
     std::lock_guard<std::mutex> lock(g_nccl_mutex);
     if (g_nccl.lib) return 0;
+    // an NCCL that the process has loaded already (a host with torch) is reused: two different libnccl.so.2 in one process
+    // do not mix (the loader resolves the later one's symbols against the first)
     const char* path = getenv("MCB_NCCL_LIB");
-    void* lib = dlopen(path ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+    if (!lib) lib = dlopen(path ? path : "libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
     if (!lib) {
         mcb::set_error(std::string("NCCL not found (dlopen: ") + dlerror() + "); set MCB_NCCL_LIB to the path of libnccl.so.2");
         return MCB_ERR_STATE;

@@ -451,6 +451,50 @@ __global__ void __launch_bounds__(MAXT) sweep_delayed_kernel(SweepArgs a, Delaye
             // variant (64 registers) loads them afterwards.
             constexpr bool PREFETCH = MAXT <= 512;
             double gold[4][2][2];
+            if ((n & 1) == 0) {
+                // Even n: the product is formed TRANSPOSED (the fragments of Rc as the A operand, those of U as B), so that
+                // the two accumulator elements of a thread are G(row, col), G(row + 1, col): adjacent in the column-major G,
+                // one 16-byte load and store instead of two of 8 bytes. c[x][y][cc] <-> row0 + 8x + 2q + cc, col0 + 8y + r.
+                auto load_old2 = [&]() {
+#pragma unroll
+                    for (int x = 0; x < 4; ++x)
+#pragma unroll
+                        for (int y = 0; y < 2; ++y) {
+                            const int row = row0 + 8 * x + 2 * q, col = col0 + 8 * y + r;
+                            double2 v = make_double2(0.0, 0.0);
+                            if (row < n && col < n) v = __ldcg(reinterpret_cast<const double2*>(Gg + row + (size_t)col * n));
+                            gold[x][y][0] = v.x; gold[x][y][1] = v.y;
+                        }
+                };
+                if (PREFETCH) load_old2();
+                for (int k0 = 0; k0 < kb4; k0 += 4) {
+                    double av[4], bv[2];
+#pragma unroll
+                    for (int x = 0; x < 4; ++x) av[x] = ua[x][k0 * ld];
+#pragma unroll
+                    for (int y = 0; y < 2; ++y) bv[y] = rb[y][k0 * ld];
+#pragma unroll
+                    for (int x = 0; x < 4; ++x)
+#pragma unroll
+                        for (int y = 0; y < 2; ++y) dmma884(c[x][y][0], c[x][y][1], bv[y], av[x]);
+                }
+                if (!PREFETCH) load_old2();
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 2; ++y) {
+                        const int row = row0 + 8 * x + 2 * q, col = col0 + 8 * y + r;
+                        const double2 gnew = make_double2(gold[x][y][0] - c[x][y][0], gold[x][y][1] - c[x][y][1]);
+                        if (row < n && col < n) {
+                            *reinterpret_cast<double2*>(Gg + row + (size_t)col * n) = gnew;
+                            // exponent field all ones = Inf / NaN (integer test: the FP64 pipe is the busy one here)
+                            if (last_block)
+                                bad |= ((__double2hiint(gnew.x) & 0x7ff00000) == 0x7ff00000) |
+                                       ((__double2hiint(gnew.y) & 0x7ff00000) == 0x7ff00000);
+                        }
+                    }
+                continue;
+            }
             auto load_old = [&]() {
 #pragma unroll
                 for (int x = 0; x < 4; ++x)

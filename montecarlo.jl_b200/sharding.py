@@ -13,6 +13,20 @@ import os
 import numpy as np
 
 
+def _prefer_bundled_nccl():
+    """If the NCCL wheel that torch links against is installed, point the library at it (MCB_NCCL_LIB): a process that
+    loads the system libnccl.so.2 first and imports torch afterwards would resolve torch's NCCL symbols against it."""
+    if os.environ.get("MCB_NCCL_LIB"):
+        return
+    import importlib.util
+    spec = importlib.util.find_spec("nvidia")
+    for root in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+        cand = os.path.join(root, "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            os.environ["MCB_NCCL_LIB"] = cand
+            return
+
+
 class NcclComm:
     """Communicator of the C-ABI collective (mcb_comm_*, csrc/comm.cu): NCCL loaded by the library itself, no torch.
     Rank 0 calls NcclComm.unique_id() and passes the 128 bytes to the other ranks by any means."""
@@ -21,6 +35,7 @@ class NcclComm:
     def unique_id():
         import ctypes as C
         from . import _lib
+        _prefer_bundled_nccl()
         buf = C.create_string_buffer(128)
         _lib.check(_lib.lib().mcb_comm_unique_id(buf))
         return buf.raw
@@ -28,6 +43,7 @@ class NcclComm:
     def __init__(self, unique_id, n_ranks, rank, device=0):
         import ctypes as C
         from . import _lib
+        _prefer_bundled_nccl()
         self.L = _lib.lib()
         self.h = C.c_void_p()
         _lib.check(self.L.mcb_comm_create(C.c_char_p(bytes(unique_id)), n_ranks, rank, device, C.byref(self.h)))
