@@ -351,14 +351,17 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
                     item = __shfl_sync(0xffffffffu, item, 0);
                     if (item >= FI) break;
                     const int row0 = (item >> 1) * (8 * FR), col0 = (item & 1) * (N / 2);
+                    // The product is formed transposed (fragments of Rc as the A operand, of -U as B): a thread's two
+                    // accumulator elements are then G(row, col), G(row + 1, col), adjacent in the column-major resident G:
+                    // 16-byte shared-memory loads and stores. c[x][y][cc] <-> row0 + 8x + 2q + cc, col0 + 8y + r.
                     double c[FR][9][2];
 #pragma unroll
                     for (int x = 0; x < FR; ++x)
 #pragma unroll
-                        for (int y = 0; y < 9; ++y)
-#pragma unroll
-                            for (int cc = 0; cc < 2; ++cc)
-                                c[x][y][cc] = Gs[(size_t)(col0 + 8 * y + 2 * q + cc) * LD + row0 + 8 * x + r];
+                        for (int y = 0; y < 9; ++y) {
+                            const double2 v = *reinterpret_cast<const double2*>(Gs + (size_t)(col0 + 8 * y + r) * LD + row0 + 8 * x + 2 * q);
+                            c[x][y][0] = v.x; c[x][y][1] = v.y;
+                        }
 #pragma unroll
                     for (int k0 = 0; k0 < K; k0 += 4) {
                         double av[FR], bv[9];
@@ -369,18 +372,18 @@ __global__ void __launch_bounds__(RGeo<N>::THREADS, 1) segment_resident_kernel(S
 #pragma unroll
                         for (int x = 0; x < FR; ++x)
 #pragma unroll
-                            for (int y = 0; y < 9; ++y) dmma884(c[x][y][0], c[x][y][1], av[x], bv[y]);
+                            for (int y = 0; y < 9; ++y) dmma884(c[x][y][0], c[x][y][1], bv[y], av[x]);
                     }
 #pragma unroll
                     for (int x = 0; x < FR; ++x)
 #pragma unroll
-                        for (int y = 0; y < 9; ++y)
-#pragma unroll
-                            for (int cc = 0; cc < 2; ++cc) {
-                                const double gnew = c[x][y][cc];
-                                Gs[(size_t)(col0 + 8 * y + 2 * q + cc) * LD + row0 + 8 * x + r] = gnew;
-                                if (check) bad |= (__double2hiint(gnew) & 0x7ff00000) == 0x7ff00000;
-                            }
+                        for (int y = 0; y < 9; ++y) {
+                            *reinterpret_cast<double2*>(Gs + (size_t)(col0 + 8 * y + r) * LD + row0 + 8 * x + 2 * q) =
+                                make_double2(c[x][y][0], c[x][y][1]);
+                            if (check)
+                                bad |= ((__double2hiint(c[x][y][0]) & 0x7ff00000) == 0x7ff00000) |
+                                       ((__double2hiint(c[x][y][1]) & 0x7ff00000) == 0x7ff00000);
+                        }
                 }
 #ifdef SWD_TIMING
                 if (blockIdx.x == 0 && tid == 32 && v == 1 && i0 == 7 * K) sgr_clk[23] = clock64();
