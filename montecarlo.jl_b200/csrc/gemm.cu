@@ -118,9 +118,11 @@ __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
 #pragma unroll
             for (int j = 0; j < WT; ++j) b[j] = frag<T, TB>(bs, wn + j * 8 + r, kk + q);
 #pragma unroll
+            // the product is formed transposed (B fragments as the A operand): a thread's two accumulator elements are then
+            // C(row, col), C(row + 1, col), adjacent in the column-major result: one 16-byte store instead of two of 8
             for (int i = 0; i < WT; ++i)
 #pragma unroll
-                for (int j = 0; j < WT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                for (int j = 0; j < WT; ++j) dmma884(acc[i][j][0], acc[i][j][1], b[j], a[i]);
         }
         if (kt + 1 < nk) {
             const int nxt = cur ^ 1;
@@ -131,24 +133,37 @@ __global__ void __launch_bounds__(THREADS) gemm_kernel(GemmArgs g)
         __syncthreads();
     }
 
+    // acc[i][j][c] = C(m0 + wm + 8 i + 2 q + c, n0 + wn + 8 j + r)
     const bool has_row = g.row.active(), has_col = g.col.active();
+    const bool vec_ok = (n & 1) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0;
+    double cs[WT];
+#pragma unroll
+    for (int j = 0; j < WT; ++j) {
+        const int gn = n0 + wn + j * 8 + r;
+        cs[j] = (has_col && gn < n) ? g.col.at(chain, gn) : 1.0;
+    }
 #pragma unroll
     for (int i = 0; i < WT; ++i) {
-        const int gm = m0 + wm + i * 8 + r;
+        const int gm = m0 + wm + i * 8 + 2 * q;
         if (gm >= n) continue;
-        const double rs = has_row ? g.row.at(chain, gm) : 1.0;
+        const bool two = gm + 1 < n;
+        const double rs0 = has_row ? g.row.at(chain, gm) : 1.0;
+        const double rs1 = (has_row && two) ? g.row.at(chain, gm + 1) : 1.0;
 #pragma unroll
-        for (int j = 0; j < WT; ++j)
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const int gn = n0 + wn + j * 8 + 2 * q + c;
-                if (gn >= n) continue;
-                double v = acc[i][j][c];
-                if (has_row) v *= rs;
-                if (has_col) v *= g.col.at(chain, gn);
-                if (g.add && gm == gn) v += g.add[(size_t)chain * g.stride_add + gm];
-                C[(size_t)gm + (size_t)gn * n] = v;
+        for (int j = 0; j < WT; ++j) {
+            const int gn = n0 + wn + j * 8 + r;
+            if (gn >= n) continue;
+            double v0 = acc[i][j][0], v1 = acc[i][j][1];
+            if (has_row) { v0 *= rs0; v1 *= rs1; }
+            if (has_col) { v0 *= cs[j]; v1 *= cs[j]; }
+            if (g.add) {
+                if (gm == gn) v0 += g.add[(size_t)chain * g.stride_add + gm];
+                if (gm + 1 == gn) v1 += g.add[(size_t)chain * g.stride_add + gn];
             }
+            double* dst = C + (size_t)gm + (size_t)gn * n;
+            if (vec_ok) *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);   // (n even: gm + 1 < n)
+            else { dst[0] = v0; if (two) dst[1] = v1; }
+        }
     }
 }
 
