@@ -267,9 +267,9 @@ __global__ void __launch_bounds__(Full<NN>::THREADS, 1) gemm_full_kernel(GemmArg
                 b[j] = TB ? bs[k * F::LDX + x] : bs[x * F::LDK + k];
             }
 #pragma unroll
-            for (int i = 0; i < IT; ++i)
+            for (int i = 0; i < IT; ++i)   // (transposed product, as in gemm_kernel: 16-byte stores in the epilogue)
 #pragma unroll
-                for (int j = 0; j < JT; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                for (int j = 0; j < JT; ++j) dmma884(acc[i][j][0], acc[i][j][1], b[j], a[i]);
         }
         if (kt + 1 < nk) {
             const int nxt = cur ^ 1;
@@ -279,22 +279,28 @@ __global__ void __launch_bounds__(Full<NN>::THREADS, 1) gemm_full_kernel(GemmArg
         }
         __syncthreads();
     }
+    // acc[i][j][c] = C(wm + 8 i + 2 q + c, wn + 8 j + r); NN is even and C is 16-byte aligned whenever the stride is even
     const bool has_row = g.row.active(), has_col = g.col.active();
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(C) & 15) == 0;
 #pragma unroll
     for (int i = 0; i < IT; ++i) {
-        const int gm = wm + i * 8 + r;
-        const double rs = has_row ? g.row.at(chain, gm) : 1.0;
+        const int gm = wm + i * 8 + 2 * q;
+        const double rs0 = has_row ? g.row.at(chain, gm) : 1.0;
+        const double rs1 = has_row ? g.row.at(chain, gm + 1) : 1.0;
 #pragma unroll
-        for (int j = 0; j < JT; ++j)
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const int gn = wn + j * 8 + 2 * q + c;
-                double v = acc[i][j][c];
-                if (has_row) v *= rs;
-                if (has_col) v *= g.col.at(chain, gn);
-                if (g.add && gm == gn) v += g.add[(size_t)chain * g.stride_add + gm];
-                C[(size_t)gm + (size_t)gn * NN] = v;
+        for (int j = 0; j < JT; ++j) {
+            const int gn = wn + j * 8 + r;
+            double v0 = acc[i][j][0], v1 = acc[i][j][1];
+            if (has_row) { v0 *= rs0; v1 *= rs1; }
+            if (has_col) { const double cv = g.col.at(chain, gn); v0 *= cv; v1 *= cv; }
+            if (g.add) {
+                if (gm == gn) v0 += g.add[(size_t)chain * g.stride_add + gm];
+                if (gm + 1 == gn) v1 += g.add[(size_t)chain * g.stride_add + gn];
             }
+            double* dst = C + (size_t)gm + (size_t)gn * NN;
+            if (vec_ok) *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+            else { dst[0] = v0; dst[1] = v1; }
+        }
     }
 }
 
