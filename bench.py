@@ -404,7 +404,7 @@ def run_dqmc(args, w, rank, local_rank, world):
     # the other BASELINE.json configs, so that the driver's records (N = 1, 2, 4, 8) carry them too
     if args.workload == "dqmc_A512" and not args.no_extra_configs:
         line["configs"] = {
-            "dqmc_C128": quick_dqmc("dqmc_C128", rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps=3),
+            "dqmc_C128": quick_dqmc("dqmc_C128", rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps=8, warmup=4),
             "dqmc_D32": quick_dqmc("dqmc_D32", rank, local_rank, world, max_over_ranks, barrier, fp64_peak, steps=2),
             "ising64": quick_ising("ising64", rank, local_rank, world, max_over_ranks, barrier, steps=5),
         }
