@@ -1,6 +1,7 @@
 // extern "C" entry points of the DQMC engine and of the batched linear algebra (include/mcb200.h).
 #include "dqmc_engine.cuh"
 #include <math.h>
+#include <mutex>
 #include <string.h>
 #include <stdlib.h>
 
@@ -30,6 +31,8 @@ static int use_device(int dev)
     }
     MCB_CUDA(cudaSetDevice(dev));
     static bool inited[64] = {};
+    static std::mutex init_mutex;   // handles may be created from several host threads
+    std::lock_guard<std::mutex> lock(init_mutex);
     if (dev >= 0 && dev < 64 && !inited[dev]) {
         API_TRY(init_gemm_kernels());
         API_TRY(init_udt_kernels());

@@ -21,8 +21,10 @@
 // and the accuracy of the Green's functions built from it do not (profiles/experiments/panel_pivot_qr.py: 4e-12 /
 // 8e-13 relative to the step-wise CPU restatement at configs C / D, the same distance LAPACK's dgeqp3 has).
 #include "udt.cuh"
+#include <map>
 #include <mutex>
 #include <stdlib.h>
+#include <utility>
 #include "prof.cuh"
 #include "qr_blocked.cuh"
 #include "tma.cuh"
@@ -108,7 +110,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     __syncthreads();
     QRB_T(1);
     // ---- the NB largest, by decreasing norm (ties: lower position first)
-    qrb::select_by_rank<NT>(nrm, j, n, tid, reinterpret_cast<int*>(Sred), sel);
+    qrb::select_by_rank<NT>(nrm, j, n, tid, Sred, sel);
     QRB_T(2);
     // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
     if (tid < NB) pstage[tid] = perm[sel[tid]];
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
         for (int u = 0; u < TPW; ++u) {
             const int t = warp + PW * u;
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] : 0.0;
+            for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? P[(size_t)qrb::panel_col(q, cc) * ldp + j + 8 * t + rl] : 0.0;
         }
         qrb::panel_steps<PW, TPW, 1>(x, mt, warp, lane, part, rowk, taus, a.D + (size_t)chain * a.sD + j);
         // ---- V back to P; the raw top block is kept aside while P carries the unit lower trapezoid for V'V
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
             const int t = warp + PW * u;
             if (t < mt) {
 #pragma unroll
-                for (int cc = 0; cc < 4; ++cc) P[(size_t)(4 * q + cc) * ldp + j + 8 * t + rl] = x[u][cc];
+                for (int cc = 0; cc < 4; ++cc) P[(size_t)qrb::panel_col(q, cc) * ldp + j + 8 * t + rl] = x[u][cc];
             }
         }
     }
@@ -367,32 +369,35 @@ int init_udt_blocked_kernels()
 // Auxiliary streams for launch_udt_blocked: the panel kernel is a latency chain on one CTA per matrix (42 us per panel at
 // N = 400 whatever the batch), the apply kernel is throughput-bound. With the batch cut into groups that run on their own
 // streams, the panel kernels of one group overlap the apply kernels of the others.
+// One set of auxiliary streams and events per (device, caller's stream): two handles driven from two host threads must
+// not share the fork / join events (a wait would pick up the other thread's record and let a group start before its own
+// stream's earlier work is done), and sharing the streams would serialise them. A set lives until the process exits; a
+// stream handle value that the runtime hands out again after a destroy simply finds its set.
 namespace {
 constexpr int MAX_GROUPS = 4;
 struct GroupStreams {
     cudaStream_t s[MAX_GROUPS - 1] = {};
     cudaEvent_t fork = nullptr, join[MAX_GROUPS - 1] = {};
-    bool ready = false;
 };
-GroupStreams g_groups[64];
+std::map<std::pair<int, cudaStream_t>, GroupStreams> g_groups;
 std::mutex g_groups_mutex;
 
-int group_streams(GroupStreams** out)
+int group_streams(cudaStream_t st, GroupStreams** out)
 {
     int dev = 0;
     MCB_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64) { set_error("udt_blocked: device index out of range"); return -1; }
     std::lock_guard<std::mutex> lock(g_groups_mutex);
-    GroupStreams& g = g_groups[dev];
-    if (!g.ready) {
+    auto it = g_groups.find({dev, st});
+    if (it == g_groups.end()) {
+        GroupStreams g;
         for (int i = 0; i < MAX_GROUPS - 1; ++i) {
             MCB_CUDA(cudaStreamCreateWithFlags(&g.s[i], cudaStreamNonBlocking));
             MCB_CUDA(cudaEventCreateWithFlags(&g.join[i], cudaEventDisableTiming));
         }
         MCB_CUDA(cudaEventCreateWithFlags(&g.fork, cudaEventDisableTiming));
-        g.ready = true;
+        it = g_groups.emplace(std::make_pair(dev, st), g).first;
     }
-    *out = &g;
+    *out = &it->second;   // std::map nodes do not move
     return 0;
 }
 } // namespace
@@ -417,7 +422,7 @@ int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long l
     {
         LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
         GroupStreams* gs = nullptr;
-        if (groups > 1 && group_streams(&gs)) return -2;
+        if (groups > 1 && group_streams(st, &gs)) return -2;
         if (groups > 1) MCB_CUDA(cudaEventRecord(gs->fork, st));
         const size_t nn = (size_t)n * n;
         for (int g = 0; g < groups && rc == 0; ++g) {

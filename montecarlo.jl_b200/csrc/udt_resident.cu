@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
         __syncthreads();
         if (p == 1) UDTR_T(10);
         // ---- the NB largest remaining columns, by decreasing norm (ties: lower position first)
-        qrb::select_by_rank<RTH>(nrm, j, n, tid, reinterpret_cast<int*>(part), sel);
+        qrb::select_by_rank<RTH>(nrm, j, n, tid, Sred, sel);   // Sred is free until the Gram product
         if (p == 1) UDTR_T(11);
         // ---- gather the selected columns (all rows: rows < j carry R of earlier panels) into the reflector buffer
         int ps = 0;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
             for (int u = 0; u < RTPW; ++u) {
                 const int t = warp + PW * u;
 #pragma unroll
-                for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] : 0.0;
+                for (int cc = 0; cc < 4; ++cc) x[u][cc] = (t < mt) ? Vs[vs_index(qrb::panel_col(q, cc), j + 8 * t + rl, ld)] : 0.0;
             }
             qrb::panel_steps<PW, RTPW, 1>(x, mt, warp, lane, part, rowk, taus, dvec + j);
 #pragma unroll
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
                 const int t = warp + PW * u;
                 if (t < mt) {
 #pragma unroll
-                    for (int cc = 0; cc < 4; ++cc) Vs[vs_index(4 * q + cc, j + 8 * t + rl, ld)] = x[u][cc];
+                    for (int cc = 0; cc < 4; ++cc) Vs[vs_index(qrb::panel_col(q, cc), j + 8 * t + rl, ld)] = x[u][cc];
                 }
             }
         }

@@ -133,3 +133,42 @@ def test_unequal_time_greens_large(L, beta, dtau, chains):
         G = mc.greens_unequal(k, l, physical=False)
         assert relerr(G[1], o.greens_unequal(k, l)) < 1e-9, (k, l)
     mc.close()
+
+
+def test_two_handles_from_two_host_threads():
+    """Handles are independent: two of them driven from two host threads (each on its own stream, both going through the
+    two-stream blocked UDT, whose auxiliary streams and events are per caller stream) give what each gives alone."""
+    import threading
+    L, beta, dtau, chains, n_upd = 16, 1.0, 0.1, 8, 12
+
+    def make(offset):
+        mc = mcb.DQMC(mcb.HubbardModelAttractive(L=L, U=4.0), n_chains=chains, seed=123, chain_offset=offset, beta=beta,
+                      delta_tau=dtau, safe_mult=5, check_propagation_error=False)
+        mc.build_stack()
+        return mc
+
+    alone = []
+    for off in (0, chains):
+        mc = make(off)
+        mc.update(n_upd)
+        alone.append((mc.greens(physical=False), mc.conf()))
+        mc.close()
+    mcs = [make(0), make(chains)]
+    errs = []
+
+    def work(mc):
+        try:
+            mc.update(n_upd)
+        except Exception as e:   # surfaced below: an exception in a thread would otherwise pass silently
+            errs.append(e)
+
+    ths = [threading.Thread(target=work, args=(mc,)) for mc in mcs]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for mc, (G, conf) in zip(mcs, alone):
+        assert np.array_equal(mc.conf(), conf)
+        assert relerr(mc.greens(physical=False), G) <= 1e-12
+        mc.close()

@@ -104,6 +104,31 @@ def test_udt_contract(n, apply_pivot, linalg_path):
             assert np.linalg.cond(Tt) < 50 * np.linalg.cond(np.triu(To) if not apply_pivot else To)
             lead = D[k].reshape(-1, 16)[:, 0]                  # the largest column of every panel: non-increasing
             assert np.all(np.diff(lead) <= 1e-9 * lead[0])
+            # the first panel = the 16 columns of largest norm, in decreasing order
+            assert np.array_equal(piv[k][:16], np.argsort(-(X[k] ** 2).sum(0), kind="stable")[:16])
+
+
+@pytest.mark.parametrize("n", [144, 256, 400])
+def test_udt_equal_norms(n):
+    """Pivot selection when every column norm is EXACTLY equal (identity, a +-1 matrix): every column passes the
+    selection's threshold, ties go to the lower position, the factorisation still reconstructs."""
+    rng = np.random.default_rng(n)
+    b = 2
+    X = np.empty((b, n, n))
+    X[0] = np.eye(n)
+    X[1] = rng.choice([-1.0, 1.0], size=(n, n))
+    L = _lib.lib()
+    U, T = np.empty(b * n * n), np.empty(b * n * n)
+    D, piv = np.empty(b * n), np.empty(b * n, dtype=np.int32)
+    _lib.check(L.mcb_linalg_udt(n, b, _cm(X), U, D, T, piv, 1, 0))
+    U, T = _uncm(U, b, n), _uncm(T, b, n)
+    D, piv = D.reshape(b, n), piv.reshape(b, n)
+    for k in range(b):
+        assert sorted(piv[k]) == list(range(n))
+        assert np.array_equal(piv[k][:16], np.arange(16))
+        assert np.abs(U[k] @ U[k].T - np.eye(n)).max() < 1e-12
+        assert np.abs(U[k] @ np.diag(D[k]) @ T[k] - X[k]).max() < 1e-12 * n
+    assert np.array_equal(piv[0], np.arange(n))   # the identity never moves a column
 
 
 @pytest.mark.parametrize("linalg_path", [False, True], indirect=True)
