@@ -331,22 +331,29 @@ __device__ __forceinline__ void panel_tfactor(const double* Ssm, const double* t
 //   Vt [m][TLD]    V[r][k] at r * TLD + k
 //   Ts [NB][TLD]   op(T)[k][k2] at k2 * TLD + k   (op(T) = T' for Q' C, T for Q C; the caller fills it)
 // Returns the squared norm of the rows >= 8 * t_norm of the thread's column (partial: sum over the 4 lanes of a column).
-template <int RT>
+// BOTTOM: the tiles are counted from the last row upwards (c[t] = rows m - 8 (t + 1) + 2q + {0,1} of the m active
+// ones), so that a strip kept in registers across panels of growing height always uses a prefix of its tiles (form Q).
+template <int RT, bool BOTTOM = false>
 __device__ __forceinline__ double apply_strip(double (&c)[RT][2], int mt, int t_norm, const double* Vs, int ldv,
-                                              const double* Vt, const double* Ts, int lane)
+                                              const double* Vt, const double* Ts, int lane, int m = 0)
 {
     const int q = lane & 3, rl = lane >> 2;
     double w[2][2];
     {
         double wh[2][2][2] = {}; // even / odd row tiles: four independent DMMA chains
+        // BOTTOM walks its tiles from the highest index down, i.e. through the rows from the top like the other mode, and
+        // mt is even there (m % 16 == 0), so tile t is the (t + 1) & 1 -th chain: the same sums in the same order, bit for bit
 #pragma unroll
-        for (int t = 0; t < RT; ++t) {
+        for (int tt = 0; tt < RT; ++tt) {
+            const int t = BOTTOM ? RT - 1 - tt : tt;
+            const int h = BOTTOM ? (t + 1) & 1 : t & 1;
             if (t < mt) {
 #pragma unroll
                 for (int kt = 0; kt < 2; ++kt) {
-                    const double2 b = *reinterpret_cast<const double2*>(Vs + (size_t)(kt * 8 + rl) * ldv + 8 * t + 2 * q);
-                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][0], b.x);
-                    dmma884(wh[t & 1][kt][0], wh[t & 1][kt][1], c[t][1], b.y);
+                    const int r0 = BOTTOM ? m - 8 * (t + 1) : 8 * t;
+                    const double2 b = *reinterpret_cast<const double2*>(Vs + (size_t)(kt * 8 + rl) * ldv + r0 + 2 * q);
+                    dmma884(wh[h][kt][0], wh[h][kt][1], c[t][0], b.x);
+                    dmma884(wh[h][kt][0], wh[h][kt][1], c[t][1], b.y);
                 }
             }
         }
@@ -370,7 +377,8 @@ __device__ __forceinline__ double apply_strip(double (&c)[RT][2], int mt, int t_
         if (t < mt) {
 #pragma unroll
             for (int kt = 0; kt < 2; ++kt) {
-                const double2 b = *reinterpret_cast<const double2*>(Vt + (size_t)(8 * t + rl) * TLD + kt * 8 + 2 * q);
+                const int r0 = BOTTOM ? m - 8 * (t + 1) : 8 * t;
+                const double2 b = *reinterpret_cast<const double2*>(Vt + (size_t)(r0 + rl) * TLD + kt * 8 + 2 * q);
                 dmma884(c[t][0], c[t][1], y[kt][0], b.x);
                 dmma884(c[t][0], c[t][1], y[kt][1], b.y);
             }

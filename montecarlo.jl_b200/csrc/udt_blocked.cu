@@ -264,6 +264,84 @@ __global__ void __launch_bounds__(NWARPS * 32) qrb_apply_kernel(ApplyArgs a)
     }
 }
 
+// ---------------------------------------------------------------------------------------------- form Q in one launch
+// Q = H_0 H_1 ... H_{npan-1} I. The columns of Q are independent, so a warp keeps its 8-column strip in registers for
+// ALL block reflectors (25 at N = 400) instead of one launch of the apply kernel per reflector: no launch gaps, the
+// strip never travels, and the next reflector block arrives by TMA while the current one is applied. The strip's tiles
+// are counted from the last row upwards (apply_strip<RT, true>): the block of panel p acts on the rows >= 16 p, a prefix
+// of the tiles that grows as p falls. Panels p > (c0 + 7) / 16 leave the strip at column c0 alone (it is still e_c there).
+template <int RT, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32) qrb_formq_kernel(int n, const double* __restrict__ Afac,
+                                                                const double* __restrict__ Tfac, double* __restrict__ U)
+{
+    extern __shared__ __align__(16) double sm[];
+    const int chain = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q = lane & 3, rl = lane >> 2;
+    const int ldv = n + 8, npan = n / NB;            // n % 16 == 0: ldv % 16 == 8
+    double* Vs = sm;                                  // [2][NB][ldv]  V[r][k] at k * ldv + r, r relative to the panel's first row
+    double* Vt = Vs + (size_t)2 * NB * ldv;           // [n][TLD]      V[r][k] at r * TLD + k
+    double* Ts = Vt + (size_t)n * TLD;                // [NB][TLD]     T[k][k2] at k * TLD + k2
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Ts + (size_t)NB * TLD);   // [2]
+    const double* A = Afac + (size_t)chain * n * n;
+    const int cta_c0 = blockIdx.x * NWARPS * 8, c0 = cta_c0 + 8 * warp;
+    const bool active = c0 < n;
+    const int p_hi = (min(n, cta_c0 + NWARPS * 8) - 1) / NB;
+    const int p_w = active ? (c0 + 7) / NB : -1;
+    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); }
+    double c[RT][2];
+#pragma unroll
+    for (int t = 0; t < RT; ++t) {
+        const int row = n - 8 * (t + 1) + 2 * q;
+        c[t][0] = (active && row == c0 + rl) ? 1.0 : 0.0;
+        c[t][1] = (active && row + 1 == c0 + rl) ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    auto issue = [&](int p, int buf) {
+        const int j = p * NB;
+        const uint32_t colbytes = (uint32_t)(n - j) * sizeof(double);
+        mbar_expect_tx(mbar + buf, NB * colbytes);
+        for (int k = 0; k < NB; ++k) bulk_g2s(Vs + (size_t)(buf * NB + k) * ldv, A + (size_t)(j + k) * n + j, colbytes, mbar + buf);
+    };
+    if (tid == 0) issue(p_hi, 0);
+    int it = 0;
+    for (int p = p_hi; p >= 0; --p, ++it) {
+        const int buf = it & 1, m = n - p * NB, mt = m / 8;
+        double* V = Vs + (size_t)buf * NB * ldv;
+        {
+            const double* Tg = Tfac + ((size_t)chain * npan + p) * NB * NB;   // Tg[k + k2 * NB] = T[k][k2]
+            for (int e = tid; e < NB * NB; e += NWARPS * 32) Ts[(e % NB) * TLD + e / NB] = __ldcg(Tg + e);
+        }
+        mbar_wait(mbar + buf, (it >> 1) & 1);
+        // unit lower trapezoid: the top NB x NB block still carries R on and above its diagonal
+        for (int e = tid; e < NB * NB; e += NWARPS * 32) {
+            const int k = e / NB, r = e % NB;
+            if (r <= k) V[(size_t)k * ldv + r] = (r == k) ? 1.0 : 0.0;
+        }
+        __syncthreads();
+        for (int e = tid; e < (NB / 2) * m; e += NWARPS * 32) {
+            const int kp = e / m, r = e - kp * m;
+            *reinterpret_cast<double2*>(Vt + (size_t)r * TLD + 2 * kp) =
+                make_double2(V[(size_t)(2 * kp) * ldv + r], V[(size_t)(2 * kp + 1) * ldv + r]);
+        }
+        __syncthreads();
+        // the other buffer was last read by the strips of the previous panel: free since the barriers above
+        if (tid == 0 && p > 0) issue(p - 1, buf ^ 1);
+        if (p <= p_w) qrb::apply_strip<RT, true>(c, mt, 1 << 30, V, ldv, Vt, Ts, lane, m);
+        __syncthreads();   // Vt and Ts are free
+    }
+    if (active) {
+        double* Ucol = U + (size_t)chain * n * n + (size_t)(c0 + rl) * n + 2 * q;
+#pragma unroll
+        for (int t = 0; t < RT; ++t)
+            if (8 * (t + 1) <= n) *reinterpret_cast<double2*>(Ucol + n - 8 * (t + 1)) = make_double2(c[t][0], c[t][1]);
+    }
+}
+
+size_t formq_smem(int n)
+{
+    return ((size_t)2 * NB * (n + 8) + (size_t)n * TLD + (size_t)NB * TLD + 2) * sizeof(double);
+}
+
 __global__ void qrb_identity_kernel(double* U, int n)
 {
     double* u = U + (size_t)blockIdx.y * n * n;
@@ -340,13 +418,20 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
     }
 #endif
     // explicit Q: the block reflectors in reverse order on the identity; panel p leaves columns < p*NB alone
-    qrb_identity_kernel<<<dim3(8, batch), 256, 0, st>>>(U, n);
-    MCB_CUDA(cudaGetLastError());
-    ap.mode = 1; ap.Cm = U;
-    for (int p = npan - 1; p >= 0; --p) {
-        ap.j = p * NB; ap.c_lo = p * NB;
-        if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
-        else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
+    // MCB_FORMQ_FUSED=0: one launch of the apply kernel per reflector block (comparisons)
+    static const bool fused_formq = !(getenv("MCB_FORMQ_FUSED") && atoi(getenv("MCB_FORMQ_FUSED")) == 0);
+    if (!small && fused_formq) {
+        qrb_formq_kernel<50, AW><<<dim3((n + AW * 8 - 1) / (AW * 8), batch), AW * 32, formq_smem(n), st>>>(n, X, Tfac, U);
+        MCB_CUDA(cudaGetLastError());
+    } else {
+        qrb_identity_kernel<<<dim3(8, batch), 256, 0, st>>>(U, n);
+        MCB_CUDA(cudaGetLastError());
+        ap.mode = 1; ap.Cm = U;
+        for (int p = npan - 1; p >= 0; --p) {
+            ap.j = p * NB; ap.c_lo = p * NB;
+            if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
+            else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
+        }
     }
     qrb_emit_kernel<<<dim3(n < 64 ? n : 64, batch), 128, 0, st>>>(X, D, sD, perm, T, pivot, sP, n, apply_pivot);
     MCB_CUDA(cudaGetLastError());
@@ -363,6 +448,7 @@ int init_udt_blocked_kernels()
     MCB_CUDA(cudaFuncSetAttribute(qrb_panel_kernel<512, 8, 7, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem<8, 8>(400)));
     MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<24, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(192, 0)));
     MCB_CUDA(cudaFuncSetAttribute(qrb_apply_kernel<50, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)apply_smem(400, 0)));
+    MCB_CUDA(cudaFuncSetAttribute(qrb_formq_kernel<50, AW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)formq_smem(400)));
     return 0;
 }
 
