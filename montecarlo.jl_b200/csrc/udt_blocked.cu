@@ -93,6 +93,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
 
     QRB_T(0);
     if (tid == 0) mbar_init(mbar, 1);
+    griddep_wait();   // the trailing update of the previous panel
     // ---- squared norms of the trailing columns (rows >= j): exact, from the previous update; computed here at j = 0
     if (j == 0) {
         for (int c = warp; c < n; c += NW) {
@@ -165,6 +166,7 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     }
     __syncthreads();
     QRB_T(4);
+    griddep_launch();   // what is left takes about as long as the next kernel's launch
     for (int e = tid; e < NB * NB; e += T) {
         const int c = e / NB, r = e % NB;
         const double v = P[(size_t)c * ldp + j + r];
@@ -211,6 +213,7 @@ __global__ void __launch_bounds__(NWARPS * 32) qrb_apply_kernel(ApplyArgs a)
     double* Ts = Vt + (size_t)m * TLD;                // [NB][TLD]   op(T)[k][k2] at k2 * TLD + k
     uint64_t* mbar = reinterpret_cast<uint64_t*>(Ts + (size_t)NB * TLD);
     const double* A = a.A + (size_t)chain * n * n;
+    griddep_wait();
     if (tid == 0) {
         mbar_init(mbar, 1);
         const uint32_t colbytes = (uint32_t)m * sizeof(double);
@@ -254,6 +257,7 @@ __global__ void __launch_bounds__(NWARPS * 32) qrb_apply_kernel(ApplyArgs a)
     __syncthreads();
     if (!active) return;
     double nrm = qrb::apply_strip<RT>(c, mt, NB / 8, Vs, ldv, Vt, Ts, lane);
+    griddep_launch();
 #pragma unroll
     for (int t = 0; t < RT; ++t)
         if (t < mt) *reinterpret_cast<double2*>(Ccol + 8 * t) = make_double2(c[t][0], c[t][1]);
@@ -288,6 +292,7 @@ __global__ void __launch_bounds__(NWARPS * 32) qrb_formq_kernel(int n, const dou
     const int p_hi = (min(n, cta_c0 + NWARPS * 8) - 1) / NB;
     const int p_w = active ? (c0 + 7) / NB : -1;
     if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); }
+    griddep_wait();
     double c[RT][2];
 #pragma unroll
     for (int t = 0; t < RT; ++t) {
@@ -329,6 +334,7 @@ __global__ void __launch_bounds__(NWARPS * 32) qrb_formq_kernel(int n, const dou
         if (p <= p_w) qrb::apply_strip<RT, true>(c, mt, 1 << 30, V, ldv, Vt, Ts, lane, m);
         __syncthreads();   // Vt and Ts are free
     }
+    griddep_launch();
     if (active) {
         double* Ucol = U + (size_t)chain * n * n + (size_t)(c0 + rl) * n + 2 * q;
 #pragma unroll
@@ -354,6 +360,7 @@ __global__ void qrb_emit_kernel(const double* A, const double* D, long long sD, 
                                 long long sP, int n, int apply_pivot)
 {
     const int chain = blockIdx.y;
+    griddep_wait();
     const double* a = A + (size_t)chain * n * n;
     const double* d = D + (size_t)chain * sD;
     const int* pm = perm + (size_t)chain * n;
@@ -363,6 +370,20 @@ __global__ void qrb_emit_kernel(const double* A, const double* D, long long sD, 
         for (int i = threadIdx.x; i < n; i += blockDim.x) t[i + (size_t)dst * n] = (i <= pos) ? a[i + (size_t)pos * n] / d[i] : 0.0;
         if (threadIdx.x == 0) pivot[(size_t)chain * sP + pos] = pm[pos];
     }
+}
+
+// launch with programmatic dependent launch allowed (tma.cuh: griddep_wait / griddep_launch); MCB_PDL=0: plain launches
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args)
+{
+    static const bool pdl = !(getenv("MCB_PDL") && atoi(getenv("MCB_PDL")) == 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
 size_t apply_smem(int n, int j)
@@ -378,8 +399,7 @@ int launch_apply(const ApplyArgs& a, int batch, cudaStream_t st)
     const int strips = (a.n - a.c_lo) / 8;
     if (strips <= 0) return 0;
     dim3 grid((strips + NWARPS - 1) / NWARPS, batch);
-    qrb_apply_kernel<RT, NWARPS><<<grid, NWARPS * 32, apply_smem(a.n, a.j), st>>>(a);
-    MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(launch_pdl(qrb_apply_kernel<RT, NWARPS>, grid, dim3(NWARPS * 32), apply_smem(a.n, a.j), st, a));
     return 0;
 }
 
@@ -398,9 +418,8 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
     ap.n = n; ap.A = X; ap.Tfac = Tfac; ap.norms = norms;
     for (int p = 0; p < npan; ++p) {
         a.j = p * NB;
-        if (small) qrb_panel_kernel<128, 4, 6, 4><<<batch, 128, panel_smem<4, 4>(n), st>>>(a);
-        else qrb_panel_kernel<512, 8, 7, 8><<<batch, 512, panel_smem<8, 8>(n), st>>>(a);
-        MCB_CUDA(cudaGetLastError());
+        if (small) MCB_CUDA(launch_pdl(qrb_panel_kernel<128, 4, 6, 4>, dim3(batch), dim3(128), panel_smem<4, 4>(n), st, a));
+        else MCB_CUDA(launch_pdl(qrb_panel_kernel<512, 8, 7, 8>, dim3(batch), dim3(512), panel_smem<8, 8>(n), st, a));
         ap.j = a.j; ap.c_lo = a.j + NB; ap.mode = 0; ap.Cm = X;
         if (small) { if (launch_apply<24, AW>(ap, batch, st)) return -2; }
         else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
@@ -421,8 +440,8 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
     // MCB_FORMQ_FUSED=0: one launch of the apply kernel per reflector block (comparisons)
     static const bool fused_formq = !(getenv("MCB_FORMQ_FUSED") && atoi(getenv("MCB_FORMQ_FUSED")) == 0);
     if (!small && fused_formq) {
-        qrb_formq_kernel<50, AW><<<dim3((n + AW * 8 - 1) / (AW * 8), batch), AW * 32, formq_smem(n), st>>>(n, X, Tfac, U);
-        MCB_CUDA(cudaGetLastError());
+        MCB_CUDA(launch_pdl(qrb_formq_kernel<50, AW>, dim3((n + AW * 8 - 1) / (AW * 8), batch), dim3(AW * 32), formq_smem(n), st, n,
+                            (const double*)X, (const double*)Tfac, U));
     } else {
         qrb_identity_kernel<<<dim3(8, batch), 256, 0, st>>>(U, n);
         MCB_CUDA(cudaGetLastError());
@@ -433,8 +452,8 @@ int udt_blocked_on_scratch(int n, int batch, double* X, double* U, double* D, lo
             else { if (launch_apply<50, AW>(ap, batch, st)) return -2; }
         }
     }
-    qrb_emit_kernel<<<dim3(n < 64 ? n : 64, batch), 128, 0, st>>>(X, D, sD, perm, T, pivot, sP, n, apply_pivot);
-    MCB_CUDA(cudaGetLastError());
+    MCB_CUDA(launch_pdl(qrb_emit_kernel, dim3(n < 64 ? n : 64, batch), dim3(128), 0, st, (const double*)X, (const double*)D, sD,
+                        (const int*)perm, T, pivot, sP, n, apply_pivot));
     return 0;
 }
 

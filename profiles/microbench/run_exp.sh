@@ -4,4 +4,4 @@ timeout 900 python -m pytest tests -m gpu -x -q -k "udt or rdivp or calculate_gr
 tail -3 gpurun_out/exp_tests.txt
 timeout 300 python profiles/microbench/canary_D.py 1 > gpurun_out/exp_canary_fused.txt 2>&1
 cat gpurun_out/exp_canary_fused.txt
-timeout 300 python bench.py --workload dqmc_D32 --steps 4 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.readlines()[-1]); print(d['config']['workload'], d['value'], d['ms_per_step'], {k:round(v['ms_per_step'],1) for k,v in d['kernels'].items()})"
+for v in 1 0; do MCB_PDL=$v timeout 300 python bench.py --workload dqmc_D32 --steps 4 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.readlines()[-1]); print('pdl $v', d['config']['workload'], d['value'], d['ms_per_step'], {k:round(v['ms_per_step'],1) for k,v in d['kernels'].items()})"; done
