@@ -336,17 +336,28 @@ def run_dqmc(args, w, rank, local_rank, world):
     _lib.check(L.mcb_dqmc_get_conf(mc.h, conf_np))
     e2e_steps = max(3, min(args.steps, 10))
 
+    e2e_calls = {}   # slowest wall time of each call of the step, ms (diagnostic: host-side stalls show up here)
+
+    def timed_call(name, rc_of):
+        t = time.perf_counter()
+        _lib.check(rc_of())
+        e2e_calls[name] = max(e2e_calls.get(name, 0.0), 1e3 * (time.perf_counter() - t))
+
     def e2e_step():
-        _lib.check(L.mcb_dqmc_set_conf(mc.h, conf_np))       # H2D: this step's HS field
-        _lib.check(L.mcb_dqmc_build_stack(mc.h))             # run!'s prologue (DQMC.jl:412-414)
-        _lib.check(L.mcb_dqmc_sweep(mc.h, 1, 0))             # the sweep
-        _lib.check(L.mcb_dqmc_get_greens(mc.h, g_np, 0))     # D2H: mc.s.greens
-        _lib.check(L.mcb_dqmc_get_conf(mc.h, conf_np))       # D2H: mc.conf
+        timed_call("set_conf", lambda: L.mcb_dqmc_set_conf(mc.h, conf_np))        # H2D: this step's HS field
+        timed_call("build_stack", lambda: L.mcb_dqmc_build_stack(mc.h))           # run!'s prologue (DQMC.jl:412-414)
+        timed_call("sweep", lambda: L.mcb_dqmc_sweep(mc.h, 1, 0))                 # the sweep
+        timed_call("get_greens", lambda: L.mcb_dqmc_get_greens(mc.h, g_np, 0))    # D2H: mc.s.greens
+        timed_call("get_conf", lambda: L.mcb_dqmc_get_conf(mc.h, conf_np))        # D2H: mc.conf
     e2e_step()
+    e2e_calls.clear()
     barrier()
     t0 = time.perf_counter()
+    e2e_step_ms = []
     for _ in range(e2e_steps):
+        ts = time.perf_counter()
         e2e_step()
+        e2e_step_ms.append(1e3 * (time.perf_counter() - ts))
     barrier()
     e2e_dt = max_over_ranks(time.perf_counter() - t0)
     e2e_value = world * C_ * e2e_steps / e2e_dt
@@ -362,6 +373,7 @@ def run_dqmc(args, w, rank, local_rank, world):
         "gpu_launches": gpu_launches,
         "e2e": {"value": e2e_value, "unit": "chain-sweeps/s", "h2d_bytes_per_step": int(conf_np.nbytes),
                 "d2h_bytes_per_step": int(conf_np.nbytes + g_np.nbytes), "steps": e2e_steps,
+                "step_ms": [round(x, 2) for x in e2e_step_ms], "slowest_call_ms": {k: round(v, 2) for k, v in e2e_calls.items()},
                 "what": "set_conf(H2D) + build_stack + sweep(1) + get_greens + get_conf (D2H), wall clock, pinned host buffers"},
         "clocks": clk.summary(),
         "whole_sweep_fp64": {"algorithmic_flop_per_chain_sweep": F_sweep,

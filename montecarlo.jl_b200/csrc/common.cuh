@@ -3,7 +3,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string>
+#include <utility>
 #include "prof.cuh"
 
 namespace mcb {
@@ -132,6 +134,32 @@ __device__ __forceinline__ double warp_sum(double v)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
+}
+
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute (launch_pdl) may
+// be scheduled while its predecessor on the stream still runs (once every CTA of the predecessor has executed
+// griddep_launch or exited). Nothing before griddep_wait() may read or write global memory that the predecessor
+// touches; the wait returns when the predecessor has completed and its writes are visible. Both instructions are no-ops
+// in a kernel launched the plain way. Used where it was measured to pay: the chain-resident kernels of N <= 64 (segment.cu,
+// stab.cu: wait and trigger first thing, 16.38 -> 16.20 ms per sweep of dqmc_A512) and the panel / apply / form-Q chain of
+// the blocked QR (udt_blocked.cu: trigger late, so that a waiting grid does not hold SMs the other stream group needs;
+// 257 -> 241 ms per sweep of dqmc_D32). The N = 144 / 400 GEMM, sweep and rdivp kernels gained nothing (one CTA per SM
+// and kernels of 40 - 500 us) and stay plain launches.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// host side: the launch; MCB_PDL=0 makes it a plain launch (comparisons). Only for kernels that call griddep_wait().
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args)
+{
+    static const bool pdl = !(getenv("MCB_PDL") && atoi(getenv("MCB_PDL")) == 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
 } // namespace mcb

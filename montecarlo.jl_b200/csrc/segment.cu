@@ -273,6 +273,7 @@ __device__ __forceinline__ void site_block(double (&acc)[SGeo<N>::MT][CW][2], Ch
 template <int N>
 __global__ void __launch_bounds__(SGeo<N>::THREADS, 1) segment_kernel(SegmentArgs a)
 {
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     constexpr int MT = SGeo<N>::MT, TPC = SGeo<N>::TPC, LD = SGeo<N>::LD;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SegSmem<N>& sm = *reinterpret_cast<SegSmem<N>*>(smem_raw);
@@ -392,7 +393,7 @@ int launch_t(const SegmentArgs& a, cudaStream_t st)
     // acceptance counters
     const int wraps = a.n_visits - 1 + (a.first_wrap ? 1 : 0);
     LaunchScope scope(LC_FUSED, st, 4.0 * N * (double)N * N * wraps * a.batch);
-    segment_kernel<N><<<(a.batch + CH - 1) / CH, SGeo<N>::THREADS, sizeof(SegSmem<N>), st>>>(a);
+    MCB_CUDA(launch_pdl(segment_kernel<N>, dim3((a.batch + CH - 1) / CH), dim3(SGeo<N>::THREADS), sizeof(SegSmem<N>), st, a));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

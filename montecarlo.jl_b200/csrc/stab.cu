@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(Geo<N>::THREADS) slice_products_kernel(Advance
 {
     constexpr int MT = Geo<N>::MT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     MultSmem<N>& sm = *reinterpret_cast<MultSmem<N>*>(smem_raw);
     const Lane t;
     const int chain = blockIdx.x;
@@ -108,6 +109,7 @@ udt2_kernel(UdtFused a)
 {
     constexpr int MT = Geo2<N, CW>::MT, LD = Geo2<N, CW>::LD, NT = Geo2<N, CW>::NT, KC = 2 * CW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     UdtSmem<N>& sm = *reinterpret_cast<UdtSmem<N>*>(smem_raw);
     const Lane2 t(CW);
     const int tid = threadIdx.x;
@@ -251,6 +253,7 @@ rdivp_big_kernel(const double* Ag, double* Og, const double* Tg, const int* pivg
 {
     constexpr int MT = Geo<N>::MT, LD = Geo<N>::LD;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     double* Tt = reinterpret_cast<double*>(smem_raw);       // T[j][k] at Tt[k + j*LD]
     int* piv = reinterpret_cast<int*>(Tt + N * LD);
     const Lane t;
@@ -374,6 +377,7 @@ greens_mid_kernel(const double* Ulg, const double* Q1g, const double* T1g, const
 {
     constexpr int MT = Geo<N>::MT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     GlueSmem<N>& sm = *reinterpret_cast<GlueSmem<N>*>(smem_raw);
     const Lane t;
     const int chain = blockIdx.x;
@@ -407,6 +411,7 @@ greens_end_kernel(const double* W3g, const double* Q2g, const double* T2g, const
 {
     constexpr int MT = Geo<N>::MT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     GlueSmem<N>& sm = *reinterpret_cast<GlueSmem<N>*>(smem_raw);
     const Lane t;
     const int chain = blockIdx.x;
@@ -478,6 +483,7 @@ rdivp_rows_kernel(const double* Ag, double* Og, const double* Tg, const int* piv
 {
     constexpr int MT = N / 8, LDT = N + 4, WARPS = 4;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    griddep_wait(); griddep_launch();   // programmatic dependent launch (common.cuh)
     double (*Tt)[8][LDT] = reinterpret_cast<double (*)[8][LDT]>(smem_raw); // Tt[buffer][row in block][k]
     int* piv = reinterpret_cast<int*>(smem_raw + 2 * 8 * LDT * sizeof(double));
     const int tid = threadIdx.x, wl = tid >> 5, l = tid & 31, r = l >> 2, q = l & 3;
@@ -539,7 +545,7 @@ int launch_slice_products(const AdvanceArgs& a, double* Xout, cudaStream_t st)
     if (a.batch <= 0) return 0;
     const double n3 = (double)a.n * a.n * a.n;
     LaunchScope scope(LC_ADVANCE, st, 2.0 * (a.hi - a.lo + 1) * n3 * a.batch);
-    STAB_DISPATCH(a.n, (slice_products_kernel<N><<<a.batch, Geo<N>::THREADS, sizeof(MultSmem<N>), st>>>(a, Xout)));
+    STAB_DISPATCH(a.n, MCB_CUDA(launch_pdl(slice_products_kernel<N>, dim3(a.batch), dim3(Geo<N>::THREADS), sizeof(MultSmem<N>), st, a, Xout)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -549,7 +555,7 @@ int launch_greens_mid(int n, int batch, const double* Ul, const double* Q1, cons
 {
     if (batch <= 0) return 0;
     LaunchScope scope(LC_GREENS, st, 5.0 * n * (double)n * n * batch);
-    STAB_DISPATCH(n, (greens_mid_kernel<N><<<batch, Geo<N>::THREADS, sizeof(GlueSmem<N>), st>>>(Ul, Q1, T1, piv1, D1, Ur, W3, W4, A2)));
+    STAB_DISPATCH(n, MCB_CUDA(launch_pdl(greens_mid_kernel<N>, dim3(batch), dim3(Geo<N>::THREADS), sizeof(GlueSmem<N>), st, Ul, Q1, T1, piv1, D1, Ur, W3, W4, A2)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -559,7 +565,7 @@ int launch_greens_end(int n, int batch, const double* W3, const double* Q2, cons
 {
     if (batch <= 0) return 0;
     LaunchScope scope(LC_GREENS, st, 5.0 * n * (double)n * n * batch);
-    STAB_DISPATCH(n, (greens_end_kernel<N><<<batch, Geo<N>::THREADS, sizeof(GlueSmem<N>), st>>>(W3, Q2, T2, piv2, D2, W4, G)));
+    STAB_DISPATCH(n, MCB_CUDA(launch_pdl(greens_end_kernel<N>, dim3(batch), dim3(Geo<N>::THREADS), sizeof(GlueSmem<N>), st, W3, Q2, T2, piv2, D2, W4, G)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -569,11 +575,10 @@ static int launch_udt2(int n, int batch, const UdtFused& a, double flops, cudaSt
     if (batch <= 0) return 0;
     LaunchScope scope(LC_UDT, st, flops * batch);
     if (n == 144) {
-        udt2_kernel<144, 2><<<batch, Geo2<144>::NT, sizeof(UdtSmem<144>), st>>>(a);
-        MCB_CUDA(cudaGetLastError());
+        MCB_CUDA(launch_pdl(udt2_kernel<144, 2>, dim3(batch), dim3(Geo2<144>::NT), sizeof(UdtSmem<144>), st, a));
         return 0;
     }
-    STAB_DISPATCH(n, (udt2_kernel<N, UdtCw<N>::value><<<batch, Geo2<N, UdtCw<N>::value>::NT, sizeof(UdtSmem<N>), st>>>(a)));
+    STAB_DISPATCH(n, MCB_CUDA(launch_pdl(udt2_kernel<N, UdtCw<N>::value>, dim3(batch), dim3(Geo2<N, UdtCw<N>::value>::NT), sizeof(UdtSmem<N>), st, a)));
     MCB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -615,8 +620,8 @@ int launch_rdivp_panel(int n, int batch, const double* in, double* out, const do
     }
 #define RDIVP_CASE(NN)                                                                                  \
     case NN:                                                                                            \
-        rdivp_big_kernel<NN><<<batch, Geo<NN>::THREADS, NN * Geo<NN>::LD * sizeof(double) + NN * sizeof(int), st>>>( \
-            in, out, T, pivot);                                                                         \
+        MCB_CUDA(launch_pdl(rdivp_big_kernel<NN>, dim3(batch), dim3(Geo<NN>::THREADS),                  \
+                            NN * Geo<NN>::LD * sizeof(double) + NN * sizeof(int), st, in, out, T, pivot));   \
         break;
     switch (n) {
         RDIVP_CASE(16) RDIVP_CASE(32) RDIVP_CASE(64) RDIVP_CASE(144)

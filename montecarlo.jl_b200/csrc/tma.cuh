@@ -84,11 +84,4 @@ __device__ __forceinline__ void bulk_s2peer(uint32_t dst_cluster_addr, const voi
 // writes made through the generic proxy (st.shared) before an async-proxy read of the same shared memory
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may be scheduled
-// while its predecessor on the stream still runs (after every CTA of the predecessor has executed griddep_launch or
-// exited). Nothing before griddep_wait() may read or write global memory that the predecessor touches; the wait returns
-// when the predecessor has completed and its writes are visible. Both are no-ops in a kernel launched the plain way.
-__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-
 } // namespace mcb

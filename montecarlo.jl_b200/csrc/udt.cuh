@@ -22,6 +22,11 @@ int init_udt_cluster_kernels();
 int launch_udt_cluster(int n, int batch, double* X, double* U, double* D, double* T, int* pivot, int apply_pivot,
                        cudaStream_t st);
 // blocked panel-pivoted QR on the tensor pipe (udt_blocked.cu): n % 16 == 0, 128 <= n <= 400
+// Stream-ordered scratch of the blocked / resident factorisations: cudaMallocAsync from a pool of the library's own, one
+// per device, that keeps what it has been given (release threshold = max). The device's default pool hands its memory
+// back to the driver at every synchronisation, so a host that synchronises after each call paid a fresh allocation in
+// the next one. MCB_SCRATCH_POOL=0: the default pool (comparisons).
+int scratch_alloc(void** p, size_t bytes, cudaStream_t st);
 bool udt_blocked_supported(int n);
 int init_udt_blocked_kernels();
 int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,

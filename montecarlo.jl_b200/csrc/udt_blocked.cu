@@ -372,20 +372,6 @@ __global__ void qrb_emit_kernel(const double* A, const double* D, long long sD, 
     }
 }
 
-// launch with programmatic dependent launch allowed (tma.cuh: griddep_wait / griddep_launch); MCB_PDL=0: plain launches
-template <typename... KArgs, typename... Args>
-cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args)
-{
-    static const bool pdl = !(getenv("MCB_PDL") && atoi(getenv("MCB_PDL")) == 0);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
-}
-
 size_t apply_smem(int n, int j)
 {
     const int m = n - j;
@@ -507,15 +493,43 @@ int group_streams(cudaStream_t st, GroupStreams** out)
 }
 } // namespace
 
+int scratch_alloc(void** p, size_t bytes, cudaStream_t st)
+{
+    static const bool own = !(getenv("MCB_SCRATCH_POOL") && atoi(getenv("MCB_SCRATCH_POOL")) == 0);
+    if (!own) { MCB_CUDA(cudaMallocAsync(p, bytes, st)); return 0; }
+    static cudaMemPool_t pools[64] = {};
+    static std::mutex pool_mutex;
+    int dev = 0;
+    MCB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("scratch pool: device index out of range"); return -1; }
+    cudaMemPool_t pool = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(pool_mutex);
+        if (!pools[dev]) {
+            cudaMemPoolProps props = {};
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = dev;
+            MCB_CUDA(cudaMemPoolCreate(&pools[dev], &props));
+            unsigned long long keep = ~0ull;
+            MCB_CUDA(cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep));
+        }
+        pool = pools[dev];
+    }
+    MCB_CUDA(cudaMallocFromPoolAsync(p, bytes, pool, st));
+    return 0;
+}
+
 // same contract as launch_udt (udt.cuh); X is the workspace the factorisation happens in
 int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long long sD, double* T, int* pivot,
                        long long sP, int apply_pivot, cudaStream_t st)
 {
     const int npan = n / NB;
     double* norms = nullptr; int* perm = nullptr; double* Tfac = nullptr;
-    MCB_CUDA(cudaMallocAsync(&norms, (size_t)batch * n * sizeof(double), st));
-    MCB_CUDA(cudaMallocAsync(&perm, (size_t)batch * n * sizeof(int), st));
-    MCB_CUDA(cudaMallocAsync(&Tfac, (size_t)batch * npan * NB * NB * sizeof(double), st));
+    if (scratch_alloc((void**)&norms, (size_t)batch * n * sizeof(double), st)) return -2;
+    if (scratch_alloc((void**)&perm, (size_t)batch * n * sizeof(int), st)) return -2;
+    if (scratch_alloc((void**)&Tfac, (size_t)batch * npan * NB * NB * sizeof(double), st)) return -2;
     // MCB_UDT_GROUPS=1: one stream (comparisons)
     static const int max_groups = getenv("MCB_UDT_GROUPS") ? atoi(getenv("MCB_UDT_GROUPS")) : MAX_GROUPS;
     int groups = 1;

@@ -299,7 +299,7 @@ int launch_udt_resident(int n, int batch, const double* X, double* U, double* D,
 {
     ResArgs a;
     a.n = n; a.X = X; a.U = U; a.D = D; a.sD = sD; a.T = T; a.pivot = pivot; a.sP = sP; a.apply_pivot = apply_pivot;
-    MCB_CUDA(cudaMallocAsync(&a.Tfac, (size_t)batch * (n / NB) * NB * NB * sizeof(double), st));
+    if (scratch_alloc((void**)&a.Tfac, (size_t)batch * (n / NB) * NB * NB * sizeof(double), st)) return -2;
     {
         LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
         udt_resident_kernel<<<batch, RTH, resident_smem(n), st>>>(a);

@@ -1,7 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q -k "udt or rdivp or calculate_greens or noalloc or config" > gpurun_out/exp_tests.txt 2>&1
-tail -3 gpurun_out/exp_tests.txt
-timeout 300 python profiles/microbench/canary_D.py 1 > gpurun_out/exp_canary_fused.txt 2>&1
-cat gpurun_out/exp_canary_fused.txt
-for v in 1 0; do MCB_PDL=$v timeout 300 python bench.py --workload dqmc_D32 --steps 4 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.readlines()[-1]); print('pdl $v', d['config']['workload'], d['value'], d['ms_per_step'], {k:round(v['ms_per_step'],1) for k,v in d['kernels'].items()})"; done
+for v in 1 0 1 0; do echo "== own pool $v"; MCB_SCRATCH_POOL=$v timeout 300 python profiles/microbench/e2e_breakdown.py dqmc_C128 24 2>&1 | awk '{print $10}' | sort -n | tr '\n' ' '; echo; done 2>&1 | tee gpurun_out/exp_e2e.txt
