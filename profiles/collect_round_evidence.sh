@@ -20,5 +20,8 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:segment_resident -s 1 -c 1 -f -o $o/${tag}_C_segment_resident python profiles/microbench/sweep144.py > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:sweep_delayed -s 2 -c 1 -f -o $o/${tag}_D_sweep_delayed python profiles/microbench/sweep400.py > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:gemm_tma -s 2 -c 1 -f -o $o/${tag}_D_gemm_tma python profiles/microbench/sweep400.py > /dev/null 2>&1
+timeout 300 ncu --set full --import-source on --clock-control none -k regex:qrb_panel -s 5 -c 1 -f -o $o/${tag}_D_qrb_panel python profiles/microbench/udt400.py 400 32 > /dev/null 2>&1
+timeout 300 ncu --set full --import-source on --clock-control none -k regex:qrb_formq -s 1 -c 1 -f -o $o/${tag}_D_qrb_formq python profiles/microbench/udt400.py 400 32 > /dev/null 2>&1
+timeout 300 ncu --set full --import-source on --clock-control none -k regex:segment_kernel -s 4 -c 1 -f -o $o/${tag}_A_segment_kernel python bench.py --steps 1 --warmup 1 --no-extra-configs --no-cpu-baseline > /dev/null 2>&1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:ising_halfsweep -s 4 -c 1 -f -o $o/${tag}_ising_halfsweep python bench.py --workload ising64 --steps 1 --warmup 1 --no-extra-configs --no-cpu-baseline > /dev/null 2>&1
 ls -la $o | grep ${tag}_ | awk '{print $5, $9}'
