@@ -115,20 +115,22 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     QRB_T(2);
     // ---- gather the panel (all rows: rows < j carry R entries of earlier panels) and the displaced columns
     if (tid < NB) pstage[tid] = perm[sel[tid]];
-    if (tid == 0) {
-        int nd = 0, nh = 0;
-        for (int p = j; p < j + NB; ++p) {
-            bool chosen = false;
-            for (int s = 0; s < NB; ++s) chosen |= (sel[s] == p);
-            if (!chosen) disp[nd++] = p;
-        }
-        for (int s = 0; s < NB; ++s)                   // holes: selected positions beyond the panel (as many as displaced)
-            if (sel[s] >= j + NB) hole[nh++] = sel[s];
-        *ndisp = nd;
+    if (warp == 0) {
+        // the lists by ballots (lane = slot s / panel position), the copies issued by the lanes in parallel
+        const int sv = lane < NB ? sel[lane] : 0x7fffffff;
+        const bool inside = lane < NB && sv < j + NB;                       // selected and already inside the panel
+        const unsigned chosen = __reduce_or_sync(0xffffffffu, inside ? 1u << (sv - j) : 0u);
+        const unsigned outside = __ballot_sync(0xffffffffu, lane < NB && !inside);
+        const unsigned freed = ~chosen & 0xffffu;                           // panel positions whose column is displaced
+        const bool displaced = lane < NB && ((freed >> lane) & 1u);
+        const int dslot = __popc(freed & ((1u << lane) - 1u));              // displaced: by increasing position
+        if (displaced) disp[dslot] = j + lane;
+        if (lane < NB && !inside) hole[__popc(outside & ((1u << lane) - 1u))] = sv;   // holes: by increasing slot
         const uint32_t colbytes = (uint32_t)n * sizeof(double);
-        mbar_expect_tx(mbar, (uint32_t)(NB + nd) * colbytes);
-        for (int s = 0; s < NB; ++s) bulk_g2s(P + (size_t)s * ldp, A + (size_t)sel[s] * n, colbytes, mbar);
-        for (int d = 0; d < nd; ++d) bulk_g2s(Dsp + (size_t)d * ldp, A + (size_t)disp[d] * n, colbytes, mbar);
+        if (lane == 0) { *ndisp = __popc(freed); mbar_expect_tx(mbar, (uint32_t)(NB + __popc(freed)) * colbytes); }
+        __syncwarp();
+        if (lane < NB) bulk_g2s(P + (size_t)lane * ldp, A + (size_t)sv * n, colbytes, mbar);
+        if (displaced) bulk_g2s(Dsp + (size_t)dslot * ldp, A + (size_t)(j + lane) * n, colbytes, mbar);
     }
     __syncthreads();
     const int nd = *ndisp;
@@ -139,8 +141,8 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     QRB_T(3);
     if (tid < nd) perm[hole[tid]] = moved;
     if (tid < NB) perm[j + tid] = pstage[tid];
-    if (tid == 0 && nd > 0) {
-        for (int d = 0; d < nd; ++d) bulk_s2g(A + (size_t)hole[d] * n, Dsp + (size_t)d * ldp, (uint32_t)n * sizeof(double));
+    if (tid < nd) {   // one copy per thread; every issuing thread waits for its own groups before the CTA ends (below)
+        bulk_s2g(A + (size_t)hole[tid] * n, Dsp + (size_t)tid * ldp, (uint32_t)n * sizeof(double));
         bulk_commit();
     }
     // ---- panel into the registers of PW warps, NB Householder steps (named barrier of these warps per step)
@@ -180,8 +182,8 @@ __global__ void __launch_bounds__(NT) qrb_panel_kernel(QrbArgs a)
     fence_async_smem();
     __syncthreads();
     QRB_T(5);
-    if (tid == 0) {
-        for (int s = 0; s < NB; ++s) bulk_s2g(A + (size_t)(j + s) * n, P + (size_t)s * ldp, (uint32_t)n * sizeof(double));
+    if (tid < NB) {   // threads 0 .. nd - 1 also issued a displaced column above
+        bulk_s2g(A + (size_t)(j + tid) * n, P + (size_t)tid * ldp, (uint32_t)n * sizeof(double));
         bulk_commit();
         bulk_wait_all();
     }
