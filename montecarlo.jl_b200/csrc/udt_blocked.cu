@@ -532,13 +532,13 @@ int launch_udt_blocked(int n, int batch, double* X, double* U, double* D, long l
     if (scratch_alloc((void**)&norms, (size_t)batch * n * sizeof(double), st)) return -2;
     if (scratch_alloc((void**)&perm, (size_t)batch * n * sizeof(int), st)) return -2;
     if (scratch_alloc((void**)&Tfac, (size_t)batch * npan * NB * NB * sizeof(double), st)) return -2;
-    // MCB_UDT_GROUPS=1: one stream (comparisons)
-    static const int max_groups = getenv("MCB_UDT_GROUPS") ? atoi(getenv("MCB_UDT_GROUPS")) : MAX_GROUPS;
+    // MCB_UDT_GROUPS=k: k groups (1 .. 4) instead of the default (comparisons)
+    static const int env_groups = getenv("MCB_UDT_GROUPS") ? atoi(getenv("MCB_UDT_GROUPS")) : 0;
     int groups = 1;
-    // two groups: 1558 us per batched 400 x 400 factorisation of 32 against 1750 on one stream; three or four groups (1620)
-    // lose to the host-side cost of issuing three or four times as many launches
-    if (n > 192 && batch >= 8) groups = 2;
-    if (groups > max_groups) groups = max_groups < 1 ? 1 : max_groups;
+    // two groups: 1558 us per batched 400 x 400 factorisation of 32 against 1750 on one stream. Three or four groups give
+    // the same time as two: the factorisation is the latency chain of one group (25 x (panel + apply) + form Q) as soon as
+    // the apply kernels of a group fit the SMs in one wave
+    if (n > 192 && batch >= 8) groups = env_groups >= 1 && env_groups <= MAX_GROUPS ? env_groups : 2;
     int rc = 0;
     {
         LaunchScope scope(LC_UDT, st, 8.0 / 3.0 * n * (double)n * n * batch);
