@@ -119,16 +119,18 @@ __global__ void __launch_bounds__(RTH, 1) udt_resident_kernel(ResArgs a)
             const double* col = A + (size_t)sel[k] * ld;
             for (int i = lane; i < n; i += 32) Vs[vs_index(k, i, ld)] = col[i];
         }
-        if (tid == 0) {
-            int nd = 0, nh = 0;
-            for (int pp = j; pp < j + NB; ++pp) {
-                bool chosen = false;
-                for (int s = 0; s < NB; ++s) chosen |= (sel[s] == pp);
-                if (!chosen) disp[nd++] = pp;
-            }
-            for (int s = 0; s < NB; ++s)               // holes: selected positions beyond the panel
-                if (sel[s] >= j + NB) hole[nh++] = sel[s];
-            *ndisp = nd;
+        if (warp == RW - 1) {
+            // displaced panel positions (by increasing position) and holes = selected positions beyond the panel (by
+            // increasing slot), by ballots: lane = slot / panel position (one thread walking the 16 x 16 comparisons took
+            // about 1.5 k cycles while the other warps waited at the barrier)
+            const int sv = lane < NB ? sel[lane] : 0x7fffffff;
+            const bool inside = lane < NB && sv < j + NB;
+            const unsigned chosen = __reduce_or_sync(0xffffffffu, inside ? 1u << (sv - j) : 0u);
+            const unsigned outside = __ballot_sync(0xffffffffu, lane < NB && !inside);
+            const unsigned freed = ~chosen & 0xffffu;
+            if (lane < NB && ((freed >> lane) & 1u)) disp[__popc(freed & ((1u << lane) - 1u))] = j + lane;
+            if (lane < NB && !inside) hole[__popc(outside & ((1u << lane) - 1u))] = sv;
+            if (lane == 0) *ndisp = __popc(freed);
         }
         __syncthreads();
         // ---- displaced columns fill the holes
