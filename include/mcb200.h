@@ -177,6 +177,18 @@ int mcb_dqmc_set_measurement_tables(mcb_dqmc* h, const int32_t* trg_of, int32_t 
 /* accumulate the observables of the current G now (what apply!(groups) does, generic.jl:194-243) */
 int mcb_dqmc_measure(mcb_dqmc* h);
 int mcb_dqmc_reset_observables(mcb_dqmc* h);
+/* Time-displaced measurements: charge_density_susceptibility, spin_density_susceptibility, pairing_susceptibility
+ * (src/flavors/DQMC/measurements/measurements.jl:56-58, 144-146, 207) through apply!(::CombinedGreensIterator, ...)
+ * (src/flavors/DQMC/measurements/generic.jl:227-243): with G00 = greens!(mc), for every slice l = 1..M of the iterator the
+ * kernels of HubbardModelAttractive for packed Green's functions (HubbardModelAttractive.jl:225-229, 239-241, 246-248) are
+ * summed over the lattice iterators of mcb_dqmc_set_measurement_tables, then scaled by delta_tau / N (finish!, :272-286).
+ * The handle has to be at its measurement point (as for mcb_dqmc_cgi_begin; `recalculate` as there); the sweep state is
+ * left untouched. One call = one measurement; per chain the record [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K]]
+ * (ps column-major (dir12, dir1, dir2); sds = the x, y and z components, equal for this model) accumulates as a SUM over
+ * calls, reset by mcb_dqmc_reset_observables. One-flavor handles only. */
+int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate);
+int32_t mcb_dqmc_susceptibility_len(mcb_dqmc* h);
+int mcb_dqmc_get_susceptibilities(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t* count);
 /* Length of one chain's observable record, and the records: per chain the SUM over measurements of
  *   [ n = mean_i 2(1-G_ii), double occupancy mean_i (1-G_ii)^2, E_kin/N, E_int/N          
  *   | cdc[n_dirs] | sdc_x[n_dirs] (= sdc_y) | sdc_z[n_dirs]                                (outputs of EachSitePairByDistance, /N)

@@ -75,6 +75,9 @@ SIGNATURES = {
     "mcb_dqmc_set_measurement_tables": (C.c_int, [C.c_void_p, _i32, C.c_int32, C.c_int32, _f64]),
     "mcb_dqmc_measure": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_reset_observables": (C.c_int, [C.c_void_p]),
+    "mcb_dqmc_measure_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcb_dqmc_susceptibility_len": (C.c_int32, [C.c_void_p]),
+    "mcb_dqmc_get_susceptibilities": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_observable_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_get_observables": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_get_greens_sum": (C.c_int, [C.c_void_p, _f64]),

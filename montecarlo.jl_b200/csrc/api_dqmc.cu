@@ -428,6 +428,30 @@ int mcb_dqmc_measure(mcb_dqmc* h)
     return MCB_OK;
 }
 
+int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate)
+{
+    REQUIRE(h, "null handle");
+    if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    ProfBind bind(h);
+    API_TRY(engine_measure_td(h, recalculate));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int32_t mcb_dqmc_susceptibility_len(mcb_dqmc* h) { return (h && h->ms.ready()) ? h->ms.td_len() : 0; }
+
+int mcb_dqmc_get_susceptibilities(mcb_dqmc* h, double* sums, int64_t* count)
+{
+    REQUIRE(h && sums && count, "null argument");
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(sums, h->ms.td, (size_t)h->C * h->ms.td_len() * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    MCB_CUDA(cudaStreamSynchronize(h->st));
+    *count = h->ms.n_td;
+    return MCB_OK;
+}
+
 int mcb_dqmc_profile(mcb_dqmc* h, int32_t enable_timing, int32_t reset)
 {
     REQUIRE(h, "null handle");

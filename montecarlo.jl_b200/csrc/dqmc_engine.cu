@@ -537,4 +537,26 @@ int engine_measure(mcb_dqmc* h)
     return measure_accumulate(h->ms, h->W[1], h->W[1], h->st);
 }
 
+// apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243): G00 = greens!(mc), then for every slice of the
+// iterator the time-displaced kernels of the group on (G00, G0l, Gl0, Gll); finish! scales by delta_tau / N. The iterator
+// runs on the device (unequal.cu) and leaves the sweep state as it found it.
+int engine_measure_td(mcb_dqmc* h, int recalculate)
+{
+    if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (h->ms.flavors != 1) { set_error("two-flavor tables on a one-flavor handle"); return MCB_ERR_STATE; }
+    MCB_TRY(engine_cgi_begin(h, recalculate));   // checks the measurement point
+    if (!h->ms.G00) MCB_CUDA(cudaMalloc(&h->ms.G00, h->mat * sizeof(double)));
+    MCB_TRY(engine_physical_greens(h, h->ms.G00));
+    const double factor = h->p.delta_tau / (double)h->N;
+    for (;;) {
+        int l = 0;
+        const double* res[3] = {nullptr, nullptr, nullptr};
+        MCB_TRY(engine_cgi_next(h, 1, &l, res));
+        if (l == 0) break;
+        MCB_TRY(measure_td_accumulate(h->ms, h->ms.G00, res[0], res[1], res[2], factor, h->st));
+    }
+    h->ms.n_td += 1;
+    return 0;
+}
+
 } // namespace mcb

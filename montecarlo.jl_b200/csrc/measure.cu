@@ -130,6 +130,57 @@ __global__ void __launch_bounds__(MT) measure_kernel(const double* __restrict__ 
     }
 }
 
+// One slice of apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for charge_density_susceptibility,
+// spin_density_susceptibility and pairing_susceptibility (measurements.jl:56-58, 144-146, 207) with the
+// HubbardModelAttractive kernels for packed Green's functions (HubbardModelAttractive.jl:225-229, 239-241, 246-248):
+//   cdc  4 (1 - Gll[i,i]) (1 - G00[j,j]) - 2 G0l[j,i] Gl0[i,j]     sdc  -2 G0l[j,i] Gl0[i,j]  (x = y = z)
+//   pc   Gl0[src1,src2] Gl0[trg1,trg2]
+// over the same iterator tables as the equal-time kernel; factor = delta_tau / N (finish!, generic.jl:272-286) is applied
+// per slice (the sum over l is linear). A thread owns one bin: fixed order, no atomics.
+__global__ void __launch_bounds__(MT) measure_td_kernel(const double* __restrict__ G00_all, const double* __restrict__ G0l_all,
+                                                        const double* __restrict__ Gl0_all, const double* __restrict__ Gll_all,
+                                                        const int32_t* __restrict__ trg_of, int n, int n_dirs, int K,
+                                                        double factor, int td_len, double* __restrict__ td_all)
+{
+    const int chain = blockIdx.x;
+    const size_t nn = (size_t)n * n;
+    const double* g00 = G00_all + (size_t)chain * nn;
+    const double* g0l = G0l_all + (size_t)chain * nn;
+    const double* gl0 = Gl0_all + (size_t)chain * nn;
+    const double* gll = Gll_all + (size_t)chain * nn;
+    double* td = td_all + (size_t)chain * td_len;
+    const int gtid = blockIdx.y * MT + threadIdx.x, gthreads = gridDim.y * MT;
+    const int n_pair_bins = 2 * n_dirs, n_bins = n_pair_bins + n_dirs * K * K;
+    for (int b = gtid; b < n_bins; b += gthreads) {
+        double acc = 0.0;
+        if (b < n_pair_bins) {
+            const int kind = b / n_dirs, d = b - kind * n_dirs;
+            const int32_t* trg = trg_of + (size_t)d * n;
+            for (int i = 0; i < n; ++i) {           // i = src, j = trg; G[i, j] at i + j * n
+                const int j = trg[i];
+                if (j < 0) continue;
+                const double ex = -2.0 * g0l[j + (size_t)i * n] * gl0[i + (size_t)j * n];
+                if (kind == 0) acc += 4.0 * (1.0 - gll[i + (size_t)i * n]) * (1.0 - g00[j + (size_t)j * n]) + ex;
+                else acc += ex;
+            }
+        } else {
+            const int q = b - n_pair_bins;          // q = dir12 + n_dirs * (dir1 + K * dir2)
+            const int d12 = q % n_dirs, k1 = (q / n_dirs) % K, k2 = q / (n_dirs * K);
+            const int32_t* t12 = trg_of + (size_t)d12 * n;
+            const int32_t* t1 = trg_of + (size_t)k1 * n;
+            const int32_t* t2 = trg_of + (size_t)k2 * n;
+            for (int s1 = 0; s1 < n; ++s1) {
+                const int s2 = t12[s1];
+                if (s2 < 0) continue;
+                const int r1 = t1[s1], r2 = t2[s2];
+                if (r1 < 0 || r2 < 0) continue;
+                acc += gl0[s1 + (size_t)s2 * n] * gl0[r1 + (size_t)r2 * n];
+            }
+        }
+        td[b] += acc * factor;
+    }
+}
+
 } // namespace
 
 int measure_setup(MeasureState& m, int N, int C, int flavors, const int32_t* trg_of_host, int n_dirs, int K,
@@ -142,6 +193,7 @@ int measure_setup(MeasureState& m, int N, int C, int flavors, const int32_t* trg
     MCB_CUDA(cudaMalloc(&m.hopT, nn * sizeof(double)));
     MCB_CUDA(cudaMalloc(&m.obs, (size_t)C * m.obs_len() * sizeof(double)));
     MCB_CUDA(cudaMalloc(&m.Gsum, (size_t)C * flavors * nn * sizeof(double)));
+    MCB_CUDA(cudaMalloc(&m.td, (size_t)C * (m.td_len() > 0 ? m.td_len() : 1) * sizeof(double)));
     MCB_CUDA(cudaMemcpyAsync(m.trg_of, trg_of_host, (size_t)n_dirs * N * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     MCB_CUDA(cudaMemcpyAsync(m.hopT, hop_host, nn * sizeof(double), cudaMemcpyHostToDevice, st));
     MCB_CUDA(cudaStreamSynchronize(st));
@@ -150,17 +202,18 @@ int measure_setup(MeasureState& m, int N, int C, int flavors, const int32_t* trg
 
 void measure_free(MeasureState& m)
 {
-    cudaFree(m.trg_of); cudaFree(m.hopT); cudaFree(m.obs); cudaFree(m.Gsum);
-    m.trg_of = nullptr; m.hopT = nullptr; m.obs = nullptr; m.Gsum = nullptr;
-    m.n_meas = 0;
+    cudaFree(m.trg_of); cudaFree(m.hopT); cudaFree(m.obs); cudaFree(m.Gsum); cudaFree(m.td); cudaFree(m.G00);
+    m.trg_of = nullptr; m.hopT = nullptr; m.obs = nullptr; m.Gsum = nullptr; m.td = nullptr; m.G00 = nullptr;
+    m.n_meas = 0; m.n_td = 0;
 }
 
 int measure_reset(MeasureState& m, cudaStream_t st)
 {
     MCB_CUDA(cudaMemsetAsync(m.obs, 0, (size_t)m.C * m.obs_len() * sizeof(double), st));
     MCB_CUDA(cudaMemsetAsync(m.Gsum, 0, (size_t)m.C * m.flavors * m.N * m.N * sizeof(double), st));
+    if (m.td) MCB_CUDA(cudaMemsetAsync(m.td, 0, (size_t)m.C * (m.td_len() > 0 ? m.td_len() : 1) * sizeof(double), st));
     MCB_CUDA(cudaStreamSynchronize(st));
-    m.n_meas = 0;
+    m.n_meas = 0; m.n_td = 0;
     return 0;
 }
 
@@ -178,6 +231,19 @@ int measure_accumulate(MeasureState& m, const double* Gu, const double* Gd, cuda
         measure_kernel<false><<<grid, MT, 0, st>>>(Gu, Gu, m.trg_of, m.hopT, m.N, m.n_dirs, m.K, m.U_signed, m.obs_len(), m.obs, m.Gsum);
     MCB_CUDA(cudaGetLastError());
     m.n_meas += 1;
+    return 0;
+}
+
+int measure_td_accumulate(MeasureState& m, const double* G00, const double* G0l, const double* Gl0, const double* Gll,
+                          double factor, cudaStream_t st)
+{
+    const int n_bins = m.td_len();
+    if (n_bins <= 0) return 0;
+    int gy = (n_bins + MT - 1) / MT;
+    if (gy > 64) gy = 64;
+    LaunchScope scope(LC_MEASURE, st, 0.0);
+    measure_td_kernel<<<dim3(m.C, gy), MT, 0, st>>>(G00, G0l, Gl0, Gll, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
+    MCB_CUDA(cudaGetLastError());
     return 0;
 }
 

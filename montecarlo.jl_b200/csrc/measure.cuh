@@ -17,6 +17,11 @@ struct MeasureState {
     double* obs = nullptr;       // [C][obs_len()] sums over measurements
     double* Gsum = nullptr;      // [C][flavors][N*N] sums of the physical G
     int64_t n_meas = 0;
+    // time-displaced measurements (one flavor): per chain [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K]] sums over measurements
+    double* td = nullptr;        // [C][td_len()]
+    double* G00 = nullptr;       // [C][N*N] the equal-time physical G of the measurement in progress
+    int64_t n_td = 0;
+    int td_len() const { return n_dirs * (2 + K * K); }
 
     // record of one chain: [n, double occupancy, E_kin/N, E_int/N | cdc[n_dirs] | sdc_x[n_dirs] | sdc_z[n_dirs] |
     //                       pc[n_dirs*K*K] (column-major (dir12, dir1, dir2)) | occupation[flavors*N] | mz[N] (2 flavors)]
@@ -36,5 +41,8 @@ void measure_free(MeasureState& m);
 int measure_reset(MeasureState& m, cudaStream_t st);
 // accumulate the observables of the physical Green's functions Gu (and Gd; pass Gu for one flavor), [C][N*N]
 int measure_accumulate(MeasureState& m, const double* Gu, const double* Gd, cudaStream_t st);
+// one slice l of a time-displaced measurement: td += factor * kernel(G00, G0l, Gl0, Gll) per output bin (measure.cu)
+int measure_td_accumulate(MeasureState& m, const double* G00, const double* G0l, const double* Gl0, const double* Gll,
+                          double factor, cudaStream_t st);
 
 } // namespace mcb

@@ -8,6 +8,7 @@ Restates the reference's ED test helper test/ED/ED.jl in matrix form (numpy):
   expectation_value              test/ED/ED.jl:441-475  Tr(e^{-beta H} O) / Z
   Greens / calculate_Greens_matrix  :146-155, 479-500   G[i, j] = <c_j c+_i>  (note the index order)
   charge_density_correlation, m_z, spin_density_correlation_{x,z}, pairing_correlation  :180-400
+  expectation_value_integrated   test/ED/ED.jl:625-675  step * sum_{tau = step .. beta} <A(tau) B(0)>
 Fermion operators are Jordan-Wigner matrices over the mode order lin = 2*site + substate (ED.jl:44-46).
 Only tests/ may import this module.
 """
@@ -49,6 +50,7 @@ class HubbardED:
         w, V = np.linalg.eigh(H)
         wts = np.exp(-beta * (w - w.min()))
         self.rho = (V * (wts / wts.sum())) @ V.T
+        self.w, self.V = w - w.min(), V
 
     def mode(self, site, sub):
         return 2 * site + sub
@@ -100,3 +102,21 @@ class HubbardED:
 
     def occupation(self, site):
         return self.ev(self.n(site, UP) + self.n(site, DOWN))
+
+    def integrated(self, A, B, step):
+        """expectation_value_integrated (ED.jl:625-675): step * sum over tau = beta, beta - step, .., step of
+        Tr(e^{-(beta - tau) H} A e^{-tau H} B) / Z = <A(tau) B(0)>, A(tau) = e^{tau H} A e^{-tau H}."""
+        Ae, Be = self.V.T @ A @ self.V, self.V.T @ B @ self.V
+        Z = np.exp(-self.beta * self.w).sum()
+        total = 0.0
+        for l in range(1, int(round(self.beta / step)) + 1):
+            tau = l * step
+            total += step * float(np.sum(np.exp(-(self.beta - tau) * self.w)[:, None] * Ae
+                                         * np.exp(-tau * self.w)[None, :] * Be.T)) / Z
+        return total
+
+    def number(self, site):
+        return self.n(site, UP) + self.n(site, DOWN)
+
+    def mz_operator(self, site):
+        return self.n(site, UP) - self.n(site, DOWN)

@@ -157,7 +157,7 @@ class OracleDQMC:
     def __init__(self, N, M, safe_mult, dtau, U, hop, conf, seed=123, chain=0,
                  check_propagation=False, native=False):
         self.L = lib(native)
-        self.N, self.M = N, M
+        self.N, self.M, self.dtau = N, M, dtau
         eTm, eTp, eT2m, eT2p = hop
         cbuf = np.ascontiguousarray(np.asarray(conf, dtype=np.int8).T).reshape(-1)
         self.h = self.L.orc_create(N, M, safe_mult, dtau, U, fmat(eTm), fmat(eTp), fmat(eT2m),
@@ -356,3 +356,29 @@ def run_measured(chain, tables, thermalization, sweeps, measure_rate=10, T=None,
         out.update(n=acc["o5"][0] / k, double_occupancy=acc["o5"][1] / k, e_kin=acc["o5"][2] / k,
                    e_int=acc["o5"][3] / k)
     return out
+
+
+def susceptibilities(chain, tables, recalculate=0):
+    """One time-displaced measurement of an OracleDQMC chain at its measurement point: apply!(::CombinedGreensIterator, ...)
+    (src/flavors/DQMC/measurements/generic.jl:227-243) for charge_density_susceptibility, spin_density_susceptibility and
+    pairing_susceptibility (measurements.jl:56-58, 144-146, 207) with the HubbardModelAttractive kernels for packed
+    Green's functions (G00, G0l, Gl0, Gll) (HubbardModelAttractive.jl:225-229, 239-241, 246-248):
+        cdc  4 (1 - Gll[i,i]) (1 - G00[j,j]) - 2 G0l[j,i] Gl0[i,j]      over EachSitePairByDistance
+        sdc  -2 G0l[j,i] Gl0[i,j]                                        (x = y = z)
+        pc   Gl0[src1,src2] Gl0[trg1,trg2]                               over EachLocalQuadByDistance{K}
+    summed over l = 1..M, then finish!(..., delta_tau): times delta_tau / N (generic.jl:272-286).
+    Plain numpy loops over the iterator tuples (small lattices). Returns dict cds, sds (n_dirs), ps (n_dirs, K, K)."""
+    N, nd, K = tables.N, tables.n_dirs, tables.K
+    G00 = chain.greens(physical=True)
+    cg = chain.combined_greens(recalculate, physical=True)   # (M, 3, N, N): G0l, Gl0, Gll
+    cds, sds, ps = np.zeros(nd), np.zeros(nd), np.zeros(tables.n_pc)
+    d_, i_, j_ = tables.trip[:, 0], tables.trip[:, 1], tables.trip[:, 2]
+    lin, s1, t1, s2, t2 = (tables.quint[:, k] for k in range(5))
+    for l in range(cg.shape[0]):
+        G0l, Gl0, Gll = cg[l]
+        ex = -2.0 * G0l[j_, i_] * Gl0[i_, j_]
+        np.add.at(sds, d_, ex)
+        np.add.at(cds, d_, 4.0 * (1.0 - Gll[i_, i_]) * (1.0 - G00[j_, j_]) + ex)
+        np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1, t2])
+    f = chain.dtau / N
+    return dict(cds=cds * f, sds=sds * f, ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())

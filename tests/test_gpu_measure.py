@@ -260,3 +260,52 @@ def test_repulsive_2x2_against_exact_diagonalisation():
     assert np.all(np.abs(mz - [ed.m_z(i) for i in range(N)]) <= 0.02 + 4 * mz_e)
     d_ed = np.mean([ed.double_occupancy(i) for i in range(N)])
     assert _close(_mean_err(obs, "double_occupancy")[0], d_ed)
+
+
+@pytest.mark.parametrize("L,U,mu,beta,safe_mult,recalculate,K", [(2, 1.0, 1.0, 1.0, 5, 5, 4), (4, 1.0, 0.3, 2.0, 5, 0, 5),
+                                                                   (8, 2.0, 0.0, 2.0, 5, 10, 5), (12, 4.0, 0.0, 1.0, 5, 5, 5)])
+def test_susceptibilities_match_the_oracle(L, U, mu, beta, safe_mult, recalculate, K):
+    """Time-displaced measurements (charge / spin density and pairing susceptibility, measurements.jl:56-58, 144-146,
+    207) accumulated on the device from the device-side CombinedGreensIterator, against the oracle's restatement of
+    apply!(::CombinedGreensIterator, ...) on the same HS field; the oracle side is pinned against exact
+    diagonalisation in tests/test_oracle_measure.py. Tolerance: the iterator's own (1e-10 on G(0 <- l), G(l <- 0),
+    1e-8 on G(l <- l) between recalculations) carried through sums of products of O(1) entries."""
+    n_chains = 3
+    model = mcb.HubbardModelAttractive(L=L, U=U, mu=mu)
+    mc = mcb.DQMC(model, n_chains=n_chains, seed=31, beta=beta, delta_tau=0.1, safe_mult=safe_mult)
+    mc.enable_measurements(K)
+    conf0 = mc.conf()
+    oracles = [orc.OracleDQMC(L * L, mc.M, safe_mult, 0.1, U, mc.hop, conf0[c], seed=31, chain=c) for c in range(n_chains)]
+    mc.build_stack()
+    with pytest.raises(RuntimeError, match="current_slice == 1"):
+        mc.measure_susceptibilities(recalculate)           # not at the measurement point
+    mc.update(mc.M)
+    for o in oracles:
+        o.build_stack()
+        o.update(mc.M)
+    tables = orc.MeasurementTables(L, K)
+    G0, st0 = mc.greens(physical=False), mc.state()
+    mc.measure_susceptibilities(recalculate)
+    assert np.array_equal(G0, mc.greens(physical=False)) and st0 == mc.state()   # sweep state untouched
+    got = mc.susceptibilities()
+    assert got["count"] == 1 and got["ps"].shape == (n_chains, L * L, K, K)
+    want = [orc.susceptibilities(o, tables, recalculate) for o in oracles]
+    for c in range(n_chains):
+        for k in ("cds", "sds", "ps"):
+            scale = max(1.0, np.abs(want[c][k]).max())
+            assert np.abs(got[k][c] - want[c][k]).max() < 1e-8 * scale, (c, k)
+    assert np.abs(want[0]["cds"]).max() > 0.1
+    # a second measurement after two more sweeps: the record is the mean over calls
+    mc.sweep(2)
+    mc.measure_susceptibilities(recalculate)
+    two = mc.susceptibilities()
+    assert two["count"] == 2
+    for c, o in enumerate(oracles):
+        o.sweep(2)
+        w2 = orc.susceptibilities(o, tables, recalculate)
+        for k in ("cds", "sds", "ps"):
+            scale = max(1.0, np.abs(w2[k]).max())
+            assert np.abs(two[k][c] - 0.5 * (want[c][k] + w2[k])).max() < 1e-8 * scale, (c, k)
+    mc.reset_observables()
+    assert mc.susceptibilities()["count"] == 0
+    mc.close()

@@ -189,6 +189,40 @@ def test_attractive_2x2_against_exact_diagonalisation():
     assert _close(_mean_err(recs, "e_int")[0], -1.0 * (d_ed - 0.5 * n_ed + 0.25))
 
 
+def test_attractive_2x2_susceptibilities_against_exact_diagonalisation():
+    """The time-displaced measurements (charge / spin density and pairing susceptibility through the
+    CombinedGreensIterator) of the same model against expectation_value_integrated, as ED_tests.jl:272-345 does
+    (atol = rtol = 2 dtau^2)."""
+    lat = mcb.SquareLattice(2)
+    ed = HubbardED(lat.neighs, U_signed=-1.0, mu=1.0, t=1.0, beta=1.0)
+    t = orc.MeasurementTables(2, 4)
+    N, K, dtau = 4, 4, 0.1
+    model, chains = _attractive_chains(2, 1.0, 1.0, 1.0, dtau, 5, n_chains=16, seed=77)
+    recs = []
+    for o in chains:
+        o.propagate_to_measurement_point()
+        o.sweep(50)
+        acc, n = None, 0
+        for _ in range(250):
+            o.sweep(2)
+            r = orc.susceptibilities(o, t, recalculate=5)
+            acc = r if acc is None else {k: acc[k] + r[k] for k in r}
+            n += 1
+        recs.append({k: v / n for k, v in acc.items()})
+    cds, sds, ps = np.zeros(t.n_dirs), np.zeros(t.n_dirs), np.zeros((t.n_dirs, K, K))
+    for d, s, g in t.trip:                                                # ED_tests.jl:275-320
+        cds[d] += ed.integrated(ed.number(g), ed.number(s), dtau)
+        sds[d] += ed.integrated(ed.mz_operator(g), ed.mz_operator(s), dtau)
+    for lin, s1, t1, s2, t2 in t.quint:                                   # ED_tests.jl:322-343
+        A = ed.c[ed.mode(s1, 0)] @ ed.c[ed.mode(t1, 1)]                   # annihilate (trg1, dn), then (src1, up)
+        B = ed.cd[ed.mode(t2, 1)] @ ed.cd[ed.mode(s2, 0)]                 # create (src2, up), then (trg2, dn)
+        ps[lin % t.n_dirs, (lin // t.n_dirs) % K, lin // (K * t.n_dirs)] += ed.integrated(A, B, dtau)
+    assert _close(_mean_err(recs, "cds")[0], cds / N)
+    assert _close(_mean_err(recs, "sds")[0], sds / N)
+    assert _close(_mean_err(recs, "ps")[0], ps / N)
+    assert np.abs(cds).max() > 0.5 and np.abs(ps).max() > 0.05             # the comparison is not between zeros
+
+
 def test_repulsive_2x2_against_exact_diagonalisation():
     """HubbardModelRepulsive(2, 2, U = 1), same run parameters (ED_tests.jl:92)."""
     lat = mcb.SquareLattice(2)
