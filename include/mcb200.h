@@ -185,7 +185,7 @@ int mcb_dqmc_reset_observables(mcb_dqmc* h);
  * The handle has to be at its measurement point (as for mcb_dqmc_cgi_begin; `recalculate` as there); the sweep state is
  * left untouched. One call = one measurement; per chain the record [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K]]
  * (ps column-major (dir12, dir1, dir2); sds = the x, y and z components, equal for this model) accumulates as a SUM over
- * calls, reset by mcb_dqmc_reset_observables. One-flavor handles only. */
+ * calls, reset by mcb_dqmc_reset_observables. (Two-flavor handles: mcb_dqmc_rep_measure_susceptibilities.) */
 int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate);
 int32_t mcb_dqmc_susceptibility_len(mcb_dqmc* h);
 int mcb_dqmc_get_susceptibilities(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t* count);
@@ -279,6 +279,12 @@ int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* h, int32_t slice1, int32_t slice2,
 /* the CombinedGreensIterator on both blocks; host layout [chain][flavor][col][row] like mcb_dqmc_rep_greens_unequal */
 int mcb_dqmc_rep_cgi_begin(mcb_dqmc_rep* h, int32_t recalculate);
 int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* h, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll);
+/* the time-displaced measurements of mcb_dqmc_measure_susceptibilities with the reference's general (two-flavor) kernels for
+ * packed Green's functions (src/flavors/DQMC/measurements/measurements.jl:75-90 cdc, :157-196 sdc_x/y/z, :215-219 pc) on the
+ * BlockDiagonal matrices. Record per chain: [cds[n_dirs] | sds_x[n_dirs] (= sds_y) | sds_z[n_dirs] | ps[n_dirs*K*K]]. */
+int mcb_dqmc_rep_measure_susceptibilities(mcb_dqmc_rep* h, int32_t recalculate);
+int32_t mcb_dqmc_rep_susceptibility_len(mcb_dqmc_rep* h);
+int mcb_dqmc_rep_get_susceptibilities(mcb_dqmc_rep* h, double* sums /*[chain][len]*/, int64_t* count);
 int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* h);
 int mcb_dqmc_rep_get_conf_bits(mcb_dqmc_rep* h, uint64_t* chunks);
 int mcb_dqmc_rep_set_conf_bits(mcb_dqmc_rep* h, const uint64_t* chunks);

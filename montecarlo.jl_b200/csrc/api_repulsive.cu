@@ -369,6 +369,57 @@ int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* r, int32_t physical, int32_t* slice, dou
     return MCB_OK;
 }
 
+// apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for the two-block handle: charge / spin density
+// and pairing susceptibility from the iterators of both blocks, advanced in step (measure.cu: measure_td_kernel<true>)
+int mcb_dqmc_rep_measure_susceptibilities(mcb_dqmc_rep* r, int32_t recalculate)
+{
+    REQUIRE(r, "null handle");
+    mcb_dqmc* u = r->up;
+    mcb_dqmc* d = r->dn;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (u->ms.flavors != 2) { set_error("one-flavor tables on a two-flavor handle"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    ProfBind bind(u);
+    for (mcb_dqmc* h : {u, d}) {
+        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+        API_TRY(engine_cgi_begin(h, recalculate));
+    }
+    double* g00[2];
+    API_TRY(measure_td_g00(u->ms, g00));
+    API_TRY(engine_physical_greens(u, g00[0]));
+    API_TRY(engine_physical_greens(d, g00[1]));
+    const double factor = u->p.delta_tau / (double)u->N;
+    for (;;) {
+        int lu = 0, ld = 0;
+        const double* ru[3] = {nullptr, nullptr, nullptr};
+        const double* rd[3] = {nullptr, nullptr, nullptr};
+        API_TRY(engine_cgi_next(u, 1, &lu, ru));
+        API_TRY(engine_cgi_next(d, 1, &ld, rd));
+        if (lu != ld) { set_error("CombinedGreensIterator: the two blocks are out of step"); return MCB_ERR_STATE; }
+        if (lu == 0) break;
+        const double* const mu[4] = {g00[0], ru[0], ru[1], ru[2]};
+        const double* const md[4] = {g00[1], rd[0], rd[1], rd[2]};
+        API_TRY(measure_td_accumulate(u->ms, mu, md, factor, u->st));
+    }
+    u->ms.n_td += 1;
+    MCB_CUDA(cudaStreamSynchronize(u->st));
+    return MCB_OK;
+}
+
+int32_t mcb_dqmc_rep_susceptibility_len(mcb_dqmc_rep* r) { return (r && r->up->ms.ready()) ? r->up->ms.td_len() : 0; }
+
+int mcb_dqmc_rep_get_susceptibilities(mcb_dqmc_rep* r, double* sums, int64_t* count)
+{
+    REQUIRE(r && sums && count, "null argument");
+    mcb_dqmc* u = r->up;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    MCB_CUDA(cudaSetDevice(u->p.device_id));
+    MCB_CUDA(cudaMemcpyAsync(sums, u->ms.td, (size_t)u->C * u->ms.td_len() * sizeof(double), cudaMemcpyDeviceToHost, u->st));
+    MCB_CUDA(cudaStreamSynchronize(u->st));
+    *count = u->ms.n_td;
+    return MCB_OK;
+}
+
 // compress / decompress (HubbardModel.jl:56-59): the field travels as BitArray(conf .== 1); the spin-down stack
 // lives on the negated field, i.e. on the complemented bits
 int mcb_dqmc_rep_conf_chunks(mcb_dqmc_rep* r) { return r ? mcb_dqmc_conf_chunks(r->up) : 0; }

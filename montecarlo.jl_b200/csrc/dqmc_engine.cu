@@ -545,15 +545,17 @@ int engine_measure_td(mcb_dqmc* h, int recalculate)
     if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     if (h->ms.flavors != 1) { set_error("two-flavor tables on a one-flavor handle"); return MCB_ERR_STATE; }
     MCB_TRY(engine_cgi_begin(h, recalculate));   // checks the measurement point
-    if (!h->ms.G00) MCB_CUDA(cudaMalloc(&h->ms.G00, h->mat * sizeof(double)));
-    MCB_TRY(engine_physical_greens(h, h->ms.G00));
+    double* g00[2];
+    MCB_TRY(measure_td_g00(h->ms, g00));
+    MCB_TRY(engine_physical_greens(h, g00[0]));
     const double factor = h->p.delta_tau / (double)h->N;
     for (;;) {
         int l = 0;
         const double* res[3] = {nullptr, nullptr, nullptr};
         MCB_TRY(engine_cgi_next(h, 1, &l, res));
         if (l == 0) break;
-        MCB_TRY(measure_td_accumulate(h->ms, h->ms.G00, res[0], res[1], res[2], factor, h->st));
+        const double* const mats[4] = {g00[0], res[0], res[1], res[2]};
+        MCB_TRY(measure_td_accumulate(h->ms, mats, mats, factor, h->st));
     }
     h->ms.n_td += 1;
     return 0;

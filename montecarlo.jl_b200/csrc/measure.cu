@@ -131,26 +131,33 @@ __global__ void __launch_bounds__(MT) measure_kernel(const double* __restrict__ 
 }
 
 // One slice of apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for charge_density_susceptibility,
-// spin_density_susceptibility and pairing_susceptibility (measurements.jl:56-58, 144-146, 207) with the
-// HubbardModelAttractive kernels for packed Green's functions (HubbardModelAttractive.jl:225-229, 239-241, 246-248):
-//   cdc  4 (1 - Gll[i,i]) (1 - G00[j,j]) - 2 G0l[j,i] Gl0[i,j]     sdc  -2 G0l[j,i] Gl0[i,j]  (x = y = z)
-//   pc   Gl0[src1,src2] Gl0[trg1,trg2]
+// spin_density_susceptibility and pairing_susceptibility (measurements.jl:56-58, 144-146, 207). Kernels for packed Green's
+// functions (G00, G0l, Gl0, Gll):
+//   one flavor (HubbardModelAttractive.jl:225-229, 239-241, 246-248)
+//     cdc  4 (1 - Gll[i,i]) (1 - G00[j,j]) - 2 G0l[j,i] Gl0[i,j]     sdc  -2 G0l[j,i] Gl0[i,j]  (x = y = z)
+//     pc   Gl0[src1,src2] Gl0[trg1,trg2]
+//   two flavors (measurements.jl:75-90, 157-196, 215-219 with the off-diagonal blocks of the BlockDiagonal matrices dropped;
+//   u / d = spin-up / spin-down block)
+//     cdc    sum over the four spin pairs of (1 - Gll_s[i,i]) (1 - G00_s'[j,j]), minus G0l_u[j,i] Gl0_u[i,j] + G0l_d[j,i] Gl0_d[i,j]
+//     sdc_x  -G0l_u[j,i] Gl0_d[i,j] - G0l_d[j,i] Gl0_u[i,j]           (= sdc_y)
+//     sdc_z  the cdc terms with a minus sign on the up-down and down-up products
+//     pc     Gl0_u[src1,src2] Gl0_d[trg1,trg2]
 // over the same iterator tables as the equal-time kernel; factor = delta_tau / N (finish!, generic.jl:272-286) is applied
 // per slice (the sum over l is linear). A thread owns one bin: fixed order, no atomics.
-__global__ void __launch_bounds__(MT) measure_td_kernel(const double* __restrict__ G00_all, const double* __restrict__ G0l_all,
-                                                        const double* __restrict__ Gl0_all, const double* __restrict__ Gll_all,
-                                                        const int32_t* __restrict__ trg_of, int n, int n_dirs, int K,
-                                                        double factor, int td_len, double* __restrict__ td_all)
+struct TdMats { const double* m[4]; };   // G00, G0l, Gl0, Gll of one spin block, [C][N*N]
+
+template <bool TWO>
+__global__ void __launch_bounds__(MT) measure_td_kernel(TdMats up, TdMats dn, const int32_t* __restrict__ trg_of, int n,
+                                                        int n_dirs, int K, double factor, int td_len,
+                                                        double* __restrict__ td_all)
 {
     const int chain = blockIdx.x;
-    const size_t nn = (size_t)n * n;
-    const double* g00 = G00_all + (size_t)chain * nn;
-    const double* g0l = G0l_all + (size_t)chain * nn;
-    const double* gl0 = Gl0_all + (size_t)chain * nn;
-    const double* gll = Gll_all + (size_t)chain * nn;
+    const size_t nn = (size_t)n * n, off = (size_t)chain * nn;
+    const double *u00 = up.m[0] + off, *u0l = up.m[1] + off, *ul0 = up.m[2] + off, *ull = up.m[3] + off;
+    const double *d00 = dn.m[0] + off, *d0l = dn.m[1] + off, *dl0 = dn.m[2] + off, *dll = dn.m[3] + off;
     double* td = td_all + (size_t)chain * td_len;
     const int gtid = blockIdx.y * MT + threadIdx.x, gthreads = gridDim.y * MT;
-    const int n_pair_bins = 2 * n_dirs, n_bins = n_pair_bins + n_dirs * K * K;
+    const int n_pair_bins = (TWO ? 3 : 2) * n_dirs, n_bins = n_pair_bins + n_dirs * K * K;
     for (int b = gtid; b < n_bins; b += gthreads) {
         double acc = 0.0;
         if (b < n_pair_bins) {
@@ -159,9 +166,18 @@ __global__ void __launch_bounds__(MT) measure_td_kernel(const double* __restrict
             for (int i = 0; i < n; ++i) {           // i = src, j = trg; G[i, j] at i + j * n
                 const int j = trg[i];
                 if (j < 0) continue;
-                const double ex = -2.0 * g0l[j + (size_t)i * n] * gl0[i + (size_t)j * n];
-                if (kind == 0) acc += 4.0 * (1.0 - gll[i + (size_t)i * n]) * (1.0 - g00[j + (size_t)j * n]) + ex;
-                else acc += ex;
+                const size_t ji = j + (size_t)i * n, ij = i + (size_t)j * n, ii = i + (size_t)i * n, jj = j + (size_t)j * n;
+                if (!TWO) {
+                    const double ex = -2.0 * u0l[ji] * ul0[ij];
+                    acc += kind == 0 ? 4.0 * (1.0 - ull[ii]) * (1.0 - u00[jj]) + ex : ex;
+                } else if (kind == 1) {
+                    acc += -u0l[ji] * dl0[ij] - d0l[ji] * ul0[ij];
+                } else {
+                    const double nui = 1.0 - ull[ii], ndi = 1.0 - dll[ii], nuj = 1.0 - u00[jj], ndj = 1.0 - d00[jj];
+                    const double same = nui * nuj - u0l[ji] * ul0[ij] + ndi * ndj - d0l[ji] * dl0[ij];
+                    const double mixed = nui * ndj + ndi * nuj;
+                    acc += kind == 0 ? same + mixed : same - mixed;
+                }
             }
         } else {
             const int q = b - n_pair_bins;          // q = dir12 + n_dirs * (dir1 + K * dir2)
@@ -174,7 +190,7 @@ __global__ void __launch_bounds__(MT) measure_td_kernel(const double* __restrict
                 if (s2 < 0) continue;
                 const int r1 = t1[s1], r2 = t2[s2];
                 if (r1 < 0 || r2 < 0) continue;
-                acc += gl0[s1 + (size_t)s2 * n] * gl0[r1 + (size_t)r2 * n];
+                acc += ul0[s1 + (size_t)s2 * n] * dl0[r1 + (size_t)r2 * n];
             }
         }
         td[b] += acc * factor;
@@ -234,15 +250,28 @@ int measure_accumulate(MeasureState& m, const double* Gu, const double* Gd, cuda
     return 0;
 }
 
-int measure_td_accumulate(MeasureState& m, const double* G00, const double* G0l, const double* Gl0, const double* Gll,
-                          double factor, cudaStream_t st)
+int measure_td_g00(MeasureState& m, double* g00[2])
+{
+    const size_t per = (size_t)m.C * m.N * m.N;
+    if (!m.G00) MCB_CUDA(cudaMalloc(&m.G00, (size_t)m.flavors * per * sizeof(double)));
+    g00[0] = m.G00;
+    g00[1] = m.flavors == 2 ? m.G00 + per : m.G00;
+    return 0;
+}
+
+int measure_td_accumulate(MeasureState& m, const double* const up[4], const double* const dn[4], double factor, cudaStream_t st)
 {
     const int n_bins = m.td_len();
     if (n_bins <= 0) return 0;
     int gy = (n_bins + MT - 1) / MT;
     if (gy > 64) gy = 64;
+    TdMats u, d;
+    for (int w = 0; w < 4; ++w) { u.m[w] = up[w]; d.m[w] = dn[w]; }
     LaunchScope scope(LC_MEASURE, st, 0.0);
-    measure_td_kernel<<<dim3(m.C, gy), MT, 0, st>>>(G00, G0l, Gl0, Gll, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
+    if (m.flavors == 2)
+        measure_td_kernel<true><<<dim3(m.C, gy), MT, 0, st>>>(u, d, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
+    else
+        measure_td_kernel<false><<<dim3(m.C, gy), MT, 0, st>>>(u, u, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

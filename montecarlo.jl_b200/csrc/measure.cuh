@@ -17,11 +17,14 @@ struct MeasureState {
     double* obs = nullptr;       // [C][obs_len()] sums over measurements
     double* Gsum = nullptr;      // [C][flavors][N*N] sums of the physical G
     int64_t n_meas = 0;
-    // time-displaced measurements (one flavor): per chain [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K]] sums over measurements
+    // time-displaced measurements, per chain sums over measurements:
+    //   one flavor   [cds[n_dirs] | sds[n_dirs] (x = y = z) | ps[n_dirs*K*K]]
+    //   two flavors  [cds[n_dirs] | sds_x[n_dirs] (= y) | sds_z[n_dirs] | ps[n_dirs*K*K]]
     double* td = nullptr;        // [C][td_len()]
-    double* G00 = nullptr;       // [C][N*N] the equal-time physical G of the measurement in progress
+    double* G00 = nullptr;       // [flavors][C][N*N] the equal-time physical G of the measurement in progress
     int64_t n_td = 0;
-    int td_len() const { return n_dirs * (2 + K * K); }
+    int td_pairs() const { return flavors == 2 ? 3 : 2; }
+    int td_len() const { return n_dirs * (td_pairs() + K * K); }
 
     // record of one chain: [n, double occupancy, E_kin/N, E_int/N | cdc[n_dirs] | sdc_x[n_dirs] | sdc_z[n_dirs] |
     //                       pc[n_dirs*K*K] (column-major (dir12, dir1, dir2)) | occupation[flavors*N] | mz[N] (2 flavors)]
@@ -42,7 +45,9 @@ int measure_reset(MeasureState& m, cudaStream_t st);
 // accumulate the observables of the physical Green's functions Gu (and Gd; pass Gu for one flavor), [C][N*N]
 int measure_accumulate(MeasureState& m, const double* Gu, const double* Gd, cudaStream_t st);
 // one slice l of a time-displaced measurement: td += factor * kernel(G00, G0l, Gl0, Gll) per output bin (measure.cu)
-int measure_td_accumulate(MeasureState& m, const double* G00, const double* G0l, const double* Gl0, const double* Gll,
-                          double factor, cudaStream_t st);
+// up[4] / dn[4] = {G00, G0l, Gl0, Gll} of the spin-up / spin-down block, [C][N*N] each (dn = up for one flavor)
+int measure_td_accumulate(MeasureState& m, const double* const up[4], const double* const dn[4], double factor, cudaStream_t st);
+// the buffer(s) for G00 of the measurement in progress, allocated on first use: g00[f] for f < flavors
+int measure_td_g00(MeasureState& m, double* g00[2]);
 
 } // namespace mcb

@@ -273,26 +273,30 @@ class DQMC:
         """One time-displaced measurement (charge_density_susceptibility, spin_density_susceptibility,
         pairing_susceptibility: measurements.jl:56-58, 144-146, 207 through apply!(::CombinedGreensIterator, ...),
         generic.jl:227-243), accumulated on the device. The handle has to be at its measurement point, as for
-        CombinedGreensIterator; one-flavor models."""
-        if self.model.flv != 1:
-            raise NotImplementedError("measure_susceptibilities: one-flavor handles only")
+        CombinedGreensIterator."""
         self.enable_measurements()
-        _lib.check(self.L.mcb_dqmc_measure_susceptibilities(self.h, int(recalculate)))
+        _lib.check(self._f("measure_susceptibilities")(self.h, int(recalculate)))
 
     def susceptibilities(self):
-        """Per-chain means over the time-displaced measurements taken so far: cds, sds (C, n_dirs) — the charge and
-        spin (x = y = z) density susceptibilities by direction — and ps (C, n_dirs, K, K), the pairing susceptibility
-        in the layout of pc."""
-        n = self.L.mcb_dqmc_susceptibility_len(self.h)
+        """Per-chain means over the time-displaced measurements taken so far: cds (C, n_dirs), sds_x = sds_y and sds_z
+        (C, n_dirs; all equal, also as `sds`, for a one-flavor model) — the charge and spin density susceptibilities by
+        direction — and ps (C, n_dirs, K, K), the pairing susceptibility in the layout of pc."""
+        n = self._f("susceptibility_len")(self.h)
         if n <= 0:
             raise RuntimeError("enable_measurements first")
         buf = np.empty(self.n_chains * n)
         cnt = C.c_int64()
-        _lib.check(self.L.mcb_dqmc_get_susceptibilities(self.h, buf, C.byref(cnt)))
+        _lib.check(self._f("get_susceptibilities")(self.h, buf, C.byref(cnt)))
         rec = buf.reshape(self.n_chains, n) / max(cnt.value, 1)
         nd, K = self.n_dirs, self.K
-        ps = rec[:, 2 * nd:].reshape(self.n_chains, K, K, nd).transpose(0, 3, 2, 1)
-        return dict(count=cnt.value, cds=rec[:, :nd], sds=rec[:, nd:2 * nd], ps=ps)
+        npair = 3 if self.model.flv == 2 else 2
+        ps = rec[:, npair * nd:].reshape(self.n_chains, K, K, nd).transpose(0, 3, 2, 1)
+        sx = rec[:, nd:2 * nd]
+        sz = rec[:, 2 * nd:3 * nd] if npair == 3 else sx
+        out = dict(count=cnt.value, cds=rec[:, :nd], sds_x=sx, sds_y=sx, sds_z=sz, ps=ps)
+        if npair == 2:
+            out["sds"] = sx
+        return out
 
     def allreduce_moments(self, comm=None):
         """Moments of the per-chain observable means summed over the chains of all ranks of `comm` (an

@@ -359,26 +359,66 @@ def run_measured(chain, tables, thermalization, sweeps, measure_rate=10, T=None,
 
 
 def susceptibilities(chain, tables, recalculate=0):
-    """One time-displaced measurement of an OracleDQMC chain at its measurement point: apply!(::CombinedGreensIterator, ...)
+    """One time-displaced measurement of a chain at its measurement point: apply!(::CombinedGreensIterator, ...)
     (src/flavors/DQMC/measurements/generic.jl:227-243) for charge_density_susceptibility, spin_density_susceptibility and
-    pairing_susceptibility (measurements.jl:56-58, 144-146, 207) with the HubbardModelAttractive kernels for packed
-    Green's functions (G00, G0l, Gl0, Gll) (HubbardModelAttractive.jl:225-229, 239-241, 246-248):
+    pairing_susceptibility (measurements.jl:56-58, 144-146, 207), summed over l = 1..M, then finish!(..., delta_tau):
+    times delta_tau / N (generic.jl:272-286). Kernels for packed Green's functions (G00, G0l, Gl0, Gll):
+      OracleDQMC (HubbardModelAttractive.jl:225-229, 239-241, 246-248)
         cdc  4 (1 - Gll[i,i]) (1 - G00[j,j]) - 2 G0l[j,i] Gl0[i,j]      over EachSitePairByDistance
         sdc  -2 G0l[j,i] Gl0[i,j]                                        (x = y = z)
         pc   Gl0[src1,src2] Gl0[trg1,trg2]                               over EachLocalQuadByDistance{K}
-    summed over l = 1..M, then finish!(..., delta_tau): times delta_tau / N (generic.jl:272-286).
-    Plain numpy loops over the iterator tuples (small lattices). Returns dict cds, sds (n_dirs), ps (n_dirs, K, K)."""
+      OracleDQMCRepulsive: the general kernels (measurements.jl:75-90, 157-196, 215-219) evaluated literally on the
+        2N x 2N block-diagonal matrices.
+    Plain numpy over the iterator tuples (small lattices). Returns dict cds, sds_x, sds_y, sds_z (n_dirs; also `sds` for
+    one flavor), ps (n_dirs, K, K)."""
     N, nd, K = tables.N, tables.n_dirs, tables.K
-    G00 = chain.greens(physical=True)
-    cg = chain.combined_greens(recalculate, physical=True)   # (M, 3, N, N): G0l, Gl0, Gll
-    cds, sds, ps = np.zeros(nd), np.zeros(nd), np.zeros(tables.n_pc)
     d_, i_, j_ = tables.trip[:, 0], tables.trip[:, 1], tables.trip[:, 2]
     lin, s1, t1, s2, t2 = (tables.quint[:, k] for k in range(5))
-    for l in range(cg.shape[0]):
-        G0l, Gl0, Gll = cg[l]
-        ex = -2.0 * G0l[j_, i_] * Gl0[i_, j_]
-        np.add.at(sds, d_, ex)
-        np.add.at(cds, d_, 4.0 * (1.0 - Gll[i_, i_]) * (1.0 - G00[j_, j_]) + ex)
-        np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1, t2])
-    f = chain.dtau / N
-    return dict(cds=cds * f, sds=sds * f, ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())
+    cds, sx, sy, sz, ps = np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(tables.n_pc)
+    if isinstance(chain, OracleDQMCRepulsive):
+        def full(u, d):
+            g = np.zeros((2 * N, 2 * N))
+            g[:N, :N], g[N:, N:] = u, d
+            return g
+        gu, gd = chain.greens(physical=True)
+        G00 = full(gu, gd)
+        cu = chain.up.combined_greens(recalculate, physical=True)
+        cd = chain.dn.combined_greens(recalculate, physical=True)
+        iN, jN = i_ + N, j_ + N
+        for l in range(cu.shape[0]):
+            G0l, Gl0, Gll = (full(cu[l, w], cd[l, w]) for w in range(3))
+            np.add.at(cds, d_, (1 - Gll[i_, i_]) * (1 - G00[j_, j_]) - G0l[j_, i_] * Gl0[i_, j_]
+                      + (1 - Gll[i_, i_]) * (1 - G00[jN, jN]) - G0l[jN, i_] * Gl0[i_, jN]
+                      + (1 - Gll[iN, iN]) * (1 - G00[j_, j_]) - G0l[j_, iN] * Gl0[iN, j_]
+                      + (1 - Gll[iN, iN]) * (1 - G00[jN, jN]) - G0l[jN, iN] * Gl0[iN, jN])
+            np.add.at(sx, d_, Gll[iN, i_] * G00[jN, j_] - G0l[jN, i_] * Gl0[iN, j_]
+                      + Gll[iN, i_] * G00[j_, jN] - G0l[j_, i_] * Gl0[iN, jN]
+                      + Gll[i_, iN] * G00[jN, j_] - G0l[jN, iN] * Gl0[i_, j_]
+                      + Gll[i_, iN] * G00[j_, jN] - G0l[j_, iN] * Gl0[i_, jN])
+            np.add.at(sy, d_, -Gll[iN, i_] * G00[jN, j_] + G0l[jN, i_] * Gl0[iN, j_]
+                      + Gll[iN, i_] * G00[j_, jN] - G0l[j_, i_] * Gl0[iN, jN]
+                      + Gll[i_, iN] * G00[jN, j_] - G0l[jN, iN] * Gl0[i_, j_]
+                      - Gll[i_, iN] * G00[j_, jN] + G0l[j_, iN] * Gl0[i_, jN])
+            np.add.at(sz, d_, (1 - Gll[i_, i_]) * (1 - G00[j_, j_]) - G0l[j_, i_] * Gl0[i_, j_]
+                      - (1 - Gll[i_, i_]) * (1 - G00[jN, jN]) + G0l[jN, i_] * Gl0[i_, jN]
+                      - (1 - Gll[iN, iN]) * (1 - G00[j_, j_]) + G0l[j_, iN] * Gl0[iN, j_]
+                      + (1 - Gll[iN, iN]) * (1 - G00[jN, jN]) - G0l[jN, iN] * Gl0[iN, jN])
+            np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1 + N, t2 + N] - Gl0[s1, t2 + N] * Gl0[t1 + N, s2])
+        dtau = chain.up.dtau
+    else:
+        G00 = chain.greens(physical=True)
+        cg = chain.combined_greens(recalculate, physical=True)   # (M, 3, N, N): G0l, Gl0, Gll
+        for l in range(cg.shape[0]):
+            G0l, Gl0, Gll = cg[l]
+            ex = -2.0 * G0l[j_, i_] * Gl0[i_, j_]
+            np.add.at(sx, d_, ex)
+            np.add.at(cds, d_, 4.0 * (1.0 - Gll[i_, i_]) * (1.0 - G00[j_, j_]) + ex)
+            np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1, t2])
+        sy, sz = sx, sx
+        dtau = chain.dtau
+    f = dtau / N
+    out = dict(cds=cds * f, sds_x=sx * f, sds_y=sy * f, sds_z=sz * f,
+               ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())
+    if not isinstance(chain, OracleDQMCRepulsive):
+        out["sds"] = out["sds_x"]
+    return out

@@ -178,6 +178,34 @@ def test_combined_greens_iterator_of_both_blocks():
     mc.close()
 
 
+@pytest.mark.parametrize("L,U,beta,K", [(2, 1.0, 1.0, 4), (4, 4.0, 2.0, 5)])
+def test_susceptibilities_of_the_two_block_handle(L, U, beta, K):
+    """Charge / spin density and pairing susceptibility (measurements.jl:56-58, 144-146, 207) with the reference's general
+    two-flavor kernels for packed Green's functions, accumulated on the device from the iterators of both blocks, against
+    the oracle's literal evaluation on the 2N x 2N matrices (pinned against exact diagonalisation on the CPU,
+    tests/test_oracle_measure.py). sds_x couples the two blocks."""
+    mc, oracles = _pair(L, U, beta, 0.1, 5, 2)
+    mc.enable_measurements(K)
+    mc.build_stack()
+    mc.update(mc.M)
+    for o in oracles:
+        o.build_stack()
+        o.update(mc.M)
+    tables = orc.MeasurementTables(L, K)
+    G0, st0 = mc.greens(physical=False), mc.state()
+    mc.measure_susceptibilities(recalculate=10)
+    assert np.array_equal(G0, mc.greens(physical=False)) and st0 == mc.state()
+    got = mc.susceptibilities()
+    assert got["count"] == 1
+    for c, o in enumerate(oracles):
+        want = orc.susceptibilities(o, tables, recalculate=10)
+        for k in ("cds", "sds_x", "sds_y", "sds_z", "ps"):
+            scale = max(1.0, np.abs(want[k]).max())
+            assert np.abs(got[k][c] - want[k]).max() < 1e-8 * scale, (c, k)
+        assert np.abs(want["sds_x"]).max() > 0.05 and np.abs(want["sds_x"] - want["sds_z"]).max() > 1e-6
+    mc.close()
+
+
 def test_checkpoint_and_resume_continue_the_same_chains():
     """save / resume! (FileIO.jl:38-156, DQMC.jl:517-521) for the two-block handle: a run that is stopped after two
     sweeps, saved as bit-packed field + sweep count and resumed in a new handle ends where the uninterrupted run does."""

@@ -252,3 +252,43 @@ def test_repulsive_2x2_against_exact_diagonalisation():
     assert _close(_mean_err(recs, "pc")[0], pc / N)
     mz, mz_e = _mean_err(recs, "mz")
     assert np.all(np.abs(mz - [ed.m_z(i) for i in range(N)]) <= 0.02 + 4 * mz_e)
+
+
+def test_repulsive_2x2_susceptibilities_against_exact_diagonalisation():
+    """The same comparison (ED_tests.jl:272-345) for HubbardModelRepulsive(2, 2, U = 1): the general two-flavor kernels
+    for packed Green's functions, including sds_x, which couples the two spin blocks."""
+    lat = mcb.SquareLattice(2)
+    ed = HubbardED(lat.neighs, U_signed=+1.0, mu=0.0, t=1.0, beta=1.0)
+    t = orc.MeasurementTables(2, 4)
+    N, K, dtau, M = 4, 4, 0.1, 10
+    model = mcb.HubbardModelRepulsive(L=2, U=1.0)
+    hop = model.hopping_exponentials(dtau)
+    recs = []
+    for c in range(16):
+        o = orc.OracleDQMCRepulsive(N, M, 5, dtau, 1.0, hop, model.rand_conf(M, 9, c), seed=9, chain=c)
+        o.build_stack()
+        o.update(M)                      # the measurement point: current_slice == 1 on the way up
+        o.sweep(50)
+        acc, n = None, 0
+        for _ in range(250):
+            o.sweep(2)
+            r = orc.susceptibilities(o, t, recalculate=5)
+            acc = r if acc is None else {k: acc[k] + r[k] for k in r}
+            n += 1
+        recs.append({k: v / n for k, v in acc.items()})
+    sx_op = lambda s: ed.cd[ed.mode(s, 0)] @ ed.c[ed.mode(s, 1)] + ed.cd[ed.mode(s, 1)] @ ed.c[ed.mode(s, 0)]
+    cds, sdx, sdz, ps = np.zeros(t.n_dirs), np.zeros(t.n_dirs), np.zeros(t.n_dirs), np.zeros((t.n_dirs, K, K))
+    for d, s, g in t.trip:
+        cds[d] += ed.integrated(ed.number(g), ed.number(s), dtau)
+        sdx[d] += ed.integrated(sx_op(g), sx_op(s), dtau)
+        sdz[d] += ed.integrated(ed.mz_operator(g), ed.mz_operator(s), dtau)
+    for lin, s1, t1, s2, t2 in t.quint:
+        A = ed.c[ed.mode(s1, 0)] @ ed.c[ed.mode(t1, 1)]
+        B = ed.cd[ed.mode(t2, 1)] @ ed.cd[ed.mode(s2, 0)]
+        ps[lin % t.n_dirs, (lin // t.n_dirs) % K, lin // (K * t.n_dirs)] += ed.integrated(A, B, dtau)
+    assert _close(_mean_err(recs, "cds")[0], cds / N)
+    assert _close(_mean_err(recs, "sds_x")[0], sdx / N, 0.03)
+    assert _close(_mean_err(recs, "sds_y")[0], sdx / N, 0.03)
+    assert _close(_mean_err(recs, "sds_z")[0], sdz / N, 0.03)
+    assert _close(_mean_err(recs, "ps")[0], ps / N)
+    assert np.abs(sdx).max() > 0.3 and np.abs(ps).max() > 0.05
