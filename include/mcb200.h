@@ -183,8 +183,10 @@ int mcb_dqmc_reset_observables(mcb_dqmc* h);
  * kernels of HubbardModelAttractive for packed Green's functions (HubbardModelAttractive.jl:225-229, 239-241, 246-248) are
  * summed over the lattice iterators of mcb_dqmc_set_measurement_tables, then scaled by delta_tau / N (finish!, :272-286).
  * The handle has to be at its measurement point (as for mcb_dqmc_cgi_begin; `recalculate` as there); the sweep state is
- * left untouched. One call = one measurement; per chain the record [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K]]
- * (ps column-major (dir12, dir1, dir2); sds = the x, y and z components, equal for this model) accumulates as a SUM over
+ * left untouched. One call = one measurement; per chain the record [cds[n_dirs] | sds[n_dirs] | ps[n_dirs*K*K] | ccs[n_dirs*K]]
+ * (ps column-major (dir12, dir1, dir2); sds = the x, y and z components, equal for this model; ccs =
+ * current_current_susceptibility, measurements.jl:254-262, cc_kernel HubbardModelAttractive.jl:249-266 over
+ * EachLocalQuadBySyncedDistance{K}, column-major (dir12, dir1), with the hopping matrix of the tables) accumulates as a SUM over
  * calls, reset by mcb_dqmc_reset_observables. (Two-flavor handles: mcb_dqmc_rep_measure_susceptibilities.) */
 int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate);
 int32_t mcb_dqmc_susceptibility_len(mcb_dqmc* h);
@@ -280,8 +282,9 @@ int mcb_dqmc_rep_greens_unequal(mcb_dqmc_rep* h, int32_t slice1, int32_t slice2,
 int mcb_dqmc_rep_cgi_begin(mcb_dqmc_rep* h, int32_t recalculate);
 int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* h, int32_t physical, int32_t* slice, double* G0l, double* Gl0, double* Gll);
 /* the time-displaced measurements of mcb_dqmc_measure_susceptibilities with the reference's general (two-flavor) kernels for
- * packed Green's functions (src/flavors/DQMC/measurements/measurements.jl:75-90 cdc, :157-196 sdc_x/y/z, :215-219 pc) on the
- * BlockDiagonal matrices. Record per chain: [cds[n_dirs] | sds_x[n_dirs] (= sds_y) | sds_z[n_dirs] | ps[n_dirs*K*K]]. */
+ * packed Green's functions (src/flavors/DQMC/measurements/measurements.jl:75-90 cdc, :157-196 sdc_x/y/z, :215-219 pc,
+ * :268-300 cc) on the BlockDiagonal matrices. Record per chain:
+ * [cds[n_dirs] | sds_x[n_dirs] (= sds_y) | sds_z[n_dirs] | ps[n_dirs*K*K] | ccs[n_dirs*K]]. */
 int mcb_dqmc_rep_measure_susceptibilities(mcb_dqmc_rep* h, int32_t recalculate);
 int32_t mcb_dqmc_rep_susceptibility_len(mcb_dqmc_rep* h);
 int mcb_dqmc_rep_get_susceptibilities(mcb_dqmc_rep* h, double* sums /*[chain][len]*/, int64_t* count);

@@ -142,13 +142,20 @@ __global__ void __launch_bounds__(MT) measure_kernel(const double* __restrict__ 
 //     sdc_x  -G0l_u[j,i] Gl0_d[i,j] - G0l_d[j,i] Gl0_u[i,j]           (= sdc_y)
 //     sdc_z  the cdc terms with a minus sign on the up-down and down-up products
 //     pc     Gl0_u[src1,src2] Gl0_d[trg1,trg2]
+// and current_current_susceptibility (measurements.jl:254-262) over EachLocalQuadBySyncedDistance{K} (both targets in the
+// same direction, lattice_iterators.jl:390-464) with cc_kernel (HubbardModelAttractive.jl:249-266; general form
+// measurements.jl:268-300), T = mc.s.hopping_matrix: with A_s = T[s1,t1] Gll_s[t1,s1] - T[t1,s1] Gll_s[s1,t1],
+// B_s = T[s2,t2] G00_s[t2,s2] - T[t2,s2] G00_s[s2,t2] the kernel is (A_u + A_d)(B_u + B_d) + X_u + X_d,
+//     X_s = - T[t1,s1] T[t2,s2] G0l_s[s2,t1] Gl0_s[s1,t2] + T[s1,t1] T[t2,s2] G0l_s[s2,s1] Gl0_s[t1,t2]
+//           + T[t1,s1] T[s2,t2] G0l_s[t2,t1] Gl0_s[s1,s2] - T[s1,t1] T[s2,t2] G0l_s[t2,s1] Gl0_s[t1,s2]
+// (one flavor: d = u, i.e. 4 A B + 2 X).
 // over the same iterator tables as the equal-time kernel; factor = delta_tau / N (finish!, generic.jl:272-286) is applied
 // per slice (the sum over l is linear). A thread owns one bin: fixed order, no atomics.
 struct TdMats { const double* m[4]; };   // G00, G0l, Gl0, Gll of one spin block, [C][N*N]
 
 template <bool TWO>
-__global__ void __launch_bounds__(MT) measure_td_kernel(TdMats up, TdMats dn, const int32_t* __restrict__ trg_of, int n,
-                                                        int n_dirs, int K, double factor, int td_len,
+__global__ void __launch_bounds__(MT) measure_td_kernel(TdMats up, TdMats dn, const int32_t* __restrict__ trg_of,
+                                                        const double* __restrict__ hop, int n, int n_dirs, int K, double factor, int td_len,
                                                         double* __restrict__ td_all)
 {
     const int chain = blockIdx.x;
@@ -157,10 +164,36 @@ __global__ void __launch_bounds__(MT) measure_td_kernel(TdMats up, TdMats dn, co
     const double *d00 = dn.m[0] + off, *d0l = dn.m[1] + off, *dl0 = dn.m[2] + off, *dll = dn.m[3] + off;
     double* td = td_all + (size_t)chain * td_len;
     const int gtid = blockIdx.y * MT + threadIdx.x, gthreads = gridDim.y * MT;
-    const int n_pair_bins = (TWO ? 3 : 2) * n_dirs, n_bins = n_pair_bins + n_dirs * K * K;
+    const int n_pair_bins = (TWO ? 3 : 2) * n_dirs, n_quad_bins = n_dirs * K * K, n_bins = n_pair_bins + n_quad_bins + n_dirs * K;
     for (int b = gtid; b < n_bins; b += gthreads) {
         double acc = 0.0;
-        if (b < n_pair_bins) {
+        if (b >= n_pair_bins + n_quad_bins) {
+            const int q = b - n_pair_bins - n_quad_bins;   // q = dir12 + n_dirs * dir1
+            const int d12 = q % n_dirs, k1 = q / n_dirs;
+            const int32_t* t12 = trg_of + (size_t)d12 * n;
+            const int32_t* tk = trg_of + (size_t)k1 * n;
+            auto at = [n](const double* g, int a, int c) { return g[a + (size_t)c * n]; };   // g[a, c]
+            for (int s1 = 0; s1 < n; ++s1) {
+                const int s2 = t12[s1];
+                if (s2 < 0) continue;
+                const int t1 = tk[s1], t2 = tk[s2];
+                if (t1 < 0 || t2 < 0) continue;
+                const double T11 = at(hop, s1, t1), T11r = at(hop, t1, s1), T22 = at(hop, s2, t2), T22r = at(hop, t2, s2);
+                double A = T11 * at(ull, t1, s1) - T11r * at(ull, s1, t1);
+                double B = T22 * at(u00, t2, s2) - T22r * at(u00, s2, t2);
+                double X = -T11r * T22r * at(u0l, s2, t1) * at(ul0, s1, t2) + T11 * T22r * at(u0l, s2, s1) * at(ul0, t1, t2)
+                           + T11r * T22 * at(u0l, t2, t1) * at(ul0, s1, s2) - T11 * T22 * at(u0l, t2, s1) * at(ul0, t1, s2);
+                if (TWO) {
+                    A += T11 * at(dll, t1, s1) - T11r * at(dll, s1, t1);
+                    B += T22 * at(d00, t2, s2) - T22r * at(d00, s2, t2);
+                    X += -T11r * T22r * at(d0l, s2, t1) * at(dl0, s1, t2) + T11 * T22r * at(d0l, s2, s1) * at(dl0, t1, t2)
+                         + T11r * T22 * at(d0l, t2, t1) * at(dl0, s1, s2) - T11 * T22 * at(d0l, t2, s1) * at(dl0, t1, s2);
+                    acc += A * B + X;
+                } else {
+                    acc += 4.0 * A * B + 2.0 * X;
+                }
+            }
+        } else if (b < n_pair_bins) {
             const int kind = b / n_dirs, d = b - kind * n_dirs;
             const int32_t* trg = trg_of + (size_t)d * n;
             for (int i = 0; i < n; ++i) {           // i = src, j = trg; G[i, j] at i + j * n
@@ -269,9 +302,9 @@ int measure_td_accumulate(MeasureState& m, const double* const up[4], const doub
     for (int w = 0; w < 4; ++w) { u.m[w] = up[w]; d.m[w] = dn[w]; }
     LaunchScope scope(LC_MEASURE, st, 0.0);
     if (m.flavors == 2)
-        measure_td_kernel<true><<<dim3(m.C, gy), MT, 0, st>>>(u, d, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
+        measure_td_kernel<true><<<dim3(m.C, gy), MT, 0, st>>>(u, d, m.trg_of, m.hopT, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
     else
-        measure_td_kernel<false><<<dim3(m.C, gy), MT, 0, st>>>(u, u, m.trg_of, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
+        measure_td_kernel<false><<<dim3(m.C, gy), MT, 0, st>>>(u, u, m.trg_of, m.hopT, m.N, m.n_dirs, m.K, factor, n_bins, m.td);
     MCB_CUDA(cudaGetLastError());
     return 0;
 }

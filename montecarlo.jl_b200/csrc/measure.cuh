@@ -18,13 +18,14 @@ struct MeasureState {
     double* Gsum = nullptr;      // [C][flavors][N*N] sums of the physical G
     int64_t n_meas = 0;
     // time-displaced measurements, per chain sums over measurements:
-    //   one flavor   [cds[n_dirs] | sds[n_dirs] (x = y = z) | ps[n_dirs*K*K]]
-    //   two flavors  [cds[n_dirs] | sds_x[n_dirs] (= y) | sds_z[n_dirs] | ps[n_dirs*K*K]]
+    //   one flavor   [cds[n_dirs] | sds[n_dirs] (x = y = z) | ps[n_dirs*K*K] | ccs[n_dirs*K]]
+    //   two flavors  [cds[n_dirs] | sds_x[n_dirs] (= y) | sds_z[n_dirs] | ps[n_dirs*K*K] | ccs[n_dirs*K]]
+    //   (ps column-major (dir12, dir1, dir2), ccs column-major (dir12, dir1))
     double* td = nullptr;        // [C][td_len()]
     double* G00 = nullptr;       // [flavors][C][N*N] the equal-time physical G of the measurement in progress
     int64_t n_td = 0;
     int td_pairs() const { return flavors == 2 ? 3 : 2; }
-    int td_len() const { return n_dirs * (td_pairs() + K * K); }
+    int td_len() const { return n_dirs * (td_pairs() + K * K + K); }
 
     // record of one chain: [n, double occupancy, E_kin/N, E_int/N | cdc[n_dirs] | sdc_x[n_dirs] | sdc_z[n_dirs] |
     //                       pc[n_dirs*K*K] (column-major (dir12, dir1, dir2)) | occupation[flavors*N] | mz[N] (2 flavors)]

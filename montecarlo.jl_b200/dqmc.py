@@ -280,7 +280,8 @@ class DQMC:
     def susceptibilities(self):
         """Per-chain means over the time-displaced measurements taken so far: cds (C, n_dirs), sds_x = sds_y and sds_z
         (C, n_dirs; all equal, also as `sds`, for a one-flavor model) — the charge and spin density susceptibilities by
-        direction — and ps (C, n_dirs, K, K), the pairing susceptibility in the layout of pc."""
+        direction —, ps (C, n_dirs, K, K), the pairing susceptibility in the layout of pc, and ccs (C, n_dirs, K), the
+        current-current susceptibility over EachLocalQuadBySyncedDistance{K}."""
         n = self._f("susceptibility_len")(self.h)
         if n <= 0:
             raise RuntimeError("enable_measurements first")
@@ -290,10 +291,11 @@ class DQMC:
         rec = buf.reshape(self.n_chains, n) / max(cnt.value, 1)
         nd, K = self.n_dirs, self.K
         npair = 3 if self.model.flv == 2 else 2
-        ps = rec[:, npair * nd:].reshape(self.n_chains, K, K, nd).transpose(0, 3, 2, 1)
+        ps = rec[:, npair * nd:(npair + K * K) * nd].reshape(self.n_chains, K, K, nd).transpose(0, 3, 2, 1)
+        ccs = rec[:, (npair + K * K) * nd:].reshape(self.n_chains, K, nd).transpose(0, 2, 1)
         sx = rec[:, nd:2 * nd]
         sz = rec[:, 2 * nd:3 * nd] if npair == 3 else sx
-        out = dict(count=cnt.value, cds=rec[:, :nd], sds_x=sx, sds_y=sx, sds_z=sz, ps=ps)
+        out = dict(count=cnt.value, cds=rec[:, :nd], sds_x=sx, sds_y=sx, sds_z=sz, ps=ps, ccs=ccs)
         if npair == 2:
             out["sds"] = sx
         return out

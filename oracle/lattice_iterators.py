@@ -108,3 +108,28 @@ def quad_quintuplets(implied, K):
                 for q in implied[dir12][dir1][dir2]:
                     rows.append((lin,) + q)
     return np.array(rows, dtype=np.int32).reshape(-1, 5)
+
+
+def synced_quad_quintuplets(pairs, n_sites, K):
+    """EachLocalQuadBySyncedDistance{K}(lattice) and its iteration (lattice_iterators.jl:390-464): the quadruples
+    (src1, trg1, src2, trg2) with src2 - src1 in direction dir12 and BOTH targets in the same direction dir1 < K of their
+    source, as rows (lin, src1, trg1, src2, trg2), lin = the column-major linear index of (dir12, dir1) in an array of
+    size (n_dirs, K). Order: dir1-major, then dir12, then the reference's push order (pair, trg1, trg2)."""
+    trg_from_src = [[] for _ in range(n_sites)]
+    for d in range(K):
+        for (src, trg) in pairs[d]:
+            trg_from_src[src].append((d, trg))
+    nd = len(pairs)
+    implied = [[[] for _ in range(K)] for _ in range(nd)]
+    for dir12 in range(nd):
+        for (src1, src2) in pairs[dir12]:
+            for (dir1, trg1) in trg_from_src[src1]:
+                for (dir2, trg2) in trg_from_src[src2]:
+                    if dir1 == dir2:
+                        implied[dir12][dir1].append((src1, trg1, src2, trg2))
+    rows = []
+    for dir1 in range(K):
+        for dir12 in range(nd):
+            for q in implied[dir12][dir1]:
+                rows.append((dir12 + nd * dir1,) + q)
+    return np.array(rows, dtype=np.int32).reshape(-1, 5)

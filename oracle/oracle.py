@@ -301,6 +301,7 @@ class MeasurementTables:
         self.implied = li.each_local_quad_by_distance(self.pairs, self.N, K)
         self.quint = np.ascontiguousarray(li.quad_quintuplets(self.implied, K))
         self.n_pc = self.n_dirs * K * K
+        self.synced = np.ascontiguousarray(li.synced_quad_quintuplets(self.pairs, self.N, K))
 
 
 def measure(G, tables, flavors=1, T=None, U=0.0):
@@ -358,7 +359,7 @@ def run_measured(chain, tables, thermalization, sweeps, measure_rate=10, T=None,
     return out
 
 
-def susceptibilities(chain, tables, recalculate=0):
+def susceptibilities(chain, tables, recalculate=0, T=None):
     """One time-displaced measurement of a chain at its measurement point: apply!(::CombinedGreensIterator, ...)
     (src/flavors/DQMC/measurements/generic.jl:227-243) for charge_density_susceptibility, spin_density_susceptibility and
     pairing_susceptibility (measurements.jl:56-58, 144-146, 207), summed over l = 1..M, then finish!(..., delta_tau):
@@ -369,12 +370,17 @@ def susceptibilities(chain, tables, recalculate=0):
         pc   Gl0[src1,src2] Gl0[trg1,trg2]                               over EachLocalQuadByDistance{K}
       OracleDQMCRepulsive: the general kernels (measurements.jl:75-90, 157-196, 215-219) evaluated literally on the
         2N x 2N block-diagonal matrices.
+    current_current_susceptibility (measurements.jl:254-262) over EachLocalQuadBySyncedDistance{K} needs the hopping matrix
+    T (mc.s.hopping_matrix) and is evaluated when T is given: cc_kernel of HubbardModelAttractive.jl:249-266 / the general
+    one of measurements.jl:268-300.
     Plain numpy over the iterator tuples (small lattices). Returns dict cds, sds_x, sds_y, sds_z (n_dirs; also `sds` for
-    one flavor), ps (n_dirs, K, K)."""
+    one flavor), ps (n_dirs, K, K) and, with T, ccs (n_dirs, K)."""
     N, nd, K = tables.N, tables.n_dirs, tables.K
     d_, i_, j_ = tables.trip[:, 0], tables.trip[:, 1], tables.trip[:, 2]
     lin, s1, t1, s2, t2 = (tables.quint[:, k] for k in range(5))
     cds, sx, sy, sz, ps = np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(tables.n_pc)
+    cc = np.zeros(nd * K)
+    clin, c1, e1, c2, e2 = (tables.synced[:, k] for k in range(5))   # (lin, src1, trg1, src2, trg2)
     if isinstance(chain, OracleDQMCRepulsive):
         def full(u, d):
             g = np.zeros((2 * N, 2 * N))
@@ -404,6 +410,17 @@ def susceptibilities(chain, tables, recalculate=0):
                       - (1 - Gll[iN, iN]) * (1 - G00[j_, j_]) + G0l[j_, iN] * Gl0[iN, j_]
                       + (1 - Gll[iN, iN]) * (1 - G00[jN, jN]) - G0l[jN, iN] * Gl0[iN, jN])
             np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1 + N, t2 + N] - Gl0[s1, t2 + N] * Gl0[t1 + N, s2])
+            if T is not None:
+                Tf = full(T, T)
+                for o1 in (0, N):
+                    for o2 in (0, N):
+                        a1, b1, a2, b2 = c1 + o1, e1 + o1, c2 + o2, e2 + o2       # s1, t1, s2, t2
+                        np.add.at(cc, clin, (Tf[a1, b1] * Gll[b1, a1] - Tf[b1, a1] * Gll[a1, b1])
+                                  * (Tf[a2, b2] * G00[b2, a2] - Tf[b2, a2] * G00[a2, b2])
+                                  + Tf[b1, a1] * Tf[b2, a2] * (-G0l[a2, b1]) * Gl0[a1, b2]
+                                  - Tf[a1, b1] * Tf[b2, a2] * (-G0l[a2, a1]) * Gl0[b1, b2]
+                                  - Tf[b1, a1] * Tf[a2, b2] * (-G0l[b2, b1]) * Gl0[a1, a2]
+                                  + Tf[a1, b1] * Tf[a2, b2] * (-G0l[b2, a1]) * Gl0[b1, a2])
         dtau = chain.up.dtau
     else:
         G00 = chain.greens(physical=True)
@@ -414,6 +431,13 @@ def susceptibilities(chain, tables, recalculate=0):
             np.add.at(sx, d_, ex)
             np.add.at(cds, d_, 4.0 * (1.0 - Gll[i_, i_]) * (1.0 - G00[j_, j_]) + ex)
             np.add.at(ps, lin, Gl0[s1, s2] * Gl0[t1, t2])
+            if T is not None:
+                np.add.at(cc, clin, 4.0 * (T[c1, e1] * Gll[e1, c1] - T[e1, c1] * Gll[c1, e1])
+                          * (T[c2, e2] * G00[e2, c2] - T[e2, c2] * G00[c2, e2])
+                          + 2.0 * T[e1, c1] * T[e2, c2] * (-G0l[c2, e1]) * Gl0[c1, e2]
+                          - 2.0 * T[c1, e1] * T[e2, c2] * (-G0l[c2, c1]) * Gl0[e1, e2]
+                          - 2.0 * T[e1, c1] * T[c2, e2] * (-G0l[e2, e1]) * Gl0[c1, c2]
+                          + 2.0 * T[c1, e1] * T[c2, e2] * (-G0l[e2, c1]) * Gl0[e1, c2])
         sy, sz = sx, sx
         dtau = chain.dtau
     f = dtau / N
@@ -421,4 +445,6 @@ def susceptibilities(chain, tables, recalculate=0):
                ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())
     if not isinstance(chain, OracleDQMCRepulsive):
         out["sds"] = out["sds_x"]
+    if T is not None:
+        out["ccs"] = (cc * f).reshape(K, nd).T.copy()   # column-major (n_dirs, K)
     return out

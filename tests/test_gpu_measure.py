@@ -289,12 +289,14 @@ def test_susceptibilities_match_the_oracle(L, U, mu, beta, safe_mult, recalculat
     assert np.array_equal(G0, mc.greens(physical=False)) and st0 == mc.state()   # sweep state untouched
     got = mc.susceptibilities()
     assert got["count"] == 1 and got["ps"].shape == (n_chains, L * L, K, K)
-    want = [orc.susceptibilities(o, tables, recalculate) for o in oracles]
+    T = model.hopping_matrix()
+    want = [orc.susceptibilities(o, tables, recalculate, T=T) for o in oracles]
+    assert got["ccs"].shape == (n_chains, L * L, K)
     for c in range(n_chains):
-        for k in ("cds", "sds", "ps"):
+        for k in ("cds", "sds", "ps", "ccs"):
             scale = max(1.0, np.abs(want[c][k]).max())
             assert np.abs(got[k][c] - want[c][k]).max() < 1e-8 * scale, (c, k)
-    assert np.abs(want[0]["cds"]).max() > 0.1
+    assert np.abs(want[0]["cds"]).max() > 0.1 and np.abs(want[0]["ccs"]).max() > 0.1
     # a second measurement after two more sweeps: the record is the mean over calls
     mc.sweep(2)
     mc.measure_susceptibilities(recalculate)
@@ -302,8 +304,8 @@ def test_susceptibilities_match_the_oracle(L, U, mu, beta, safe_mult, recalculat
     assert two["count"] == 2
     for c, o in enumerate(oracles):
         o.sweep(2)
-        w2 = orc.susceptibilities(o, tables, recalculate)
-        for k in ("cds", "sds", "ps"):
+        w2 = orc.susceptibilities(o, tables, recalculate, T=T)
+        for k in ("cds", "sds", "ps", "ccs"):
             scale = max(1.0, np.abs(w2[k]).max())
             assert np.abs(two[k][c] - 0.5 * (want[c][k] + w2[k])).max() < 1e-8 * scale, (c, k)
     mc.reset_observables()

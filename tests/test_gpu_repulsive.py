@@ -198,8 +198,8 @@ def test_susceptibilities_of_the_two_block_handle(L, U, beta, K):
     got = mc.susceptibilities()
     assert got["count"] == 1
     for c, o in enumerate(oracles):
-        want = orc.susceptibilities(o, tables, recalculate=10)
-        for k in ("cds", "sds_x", "sds_y", "sds_z", "ps"):
+        want = orc.susceptibilities(o, tables, recalculate=10, T=mc.model.hopping_matrix())
+        for k in ("cds", "sds_x", "sds_y", "sds_z", "ps", "ccs"):
             scale = max(1.0, np.abs(want[k]).max())
             assert np.abs(got[k][c] - want[k]).max() < 1e-8 * scale, (c, k)
         assert np.abs(want["sds_x"]).max() > 0.05 and np.abs(want["sds_x"] - want["sds_z"]).max() > 1e-6

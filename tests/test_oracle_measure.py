@@ -189,6 +189,23 @@ def test_attractive_2x2_against_exact_diagonalisation():
     assert _close(_mean_err(recs, "e_int")[0], -1.0 * (d_ed - 0.5 * n_ed + 0.25))
 
 
+def _ed_current(ed, T, src, trg):
+    """current_density (test/ED/ED.jl:403-435): sum over spins of T[trg, src] c+_trg c_src - T[src, trg] c+_src c_trg."""
+    J = np.zeros((ed.dim, ed.dim))
+    for sub in (0, 1):
+        J += T[trg, src] * ed.cd[ed.mode(trg, sub)] @ ed.c[ed.mode(src, sub)]
+        J -= T[src, trg] * ed.cd[ed.mode(src, sub)] @ ed.c[ed.mode(trg, sub)]
+    return J
+
+
+def _ed_ccs(ed, T, t, K, dtau):
+    """ED_tests.jl:346-358 over EachLocalQuadBySyncedDistance{K}."""
+    ccs = np.zeros((t.n_dirs, K))
+    for lin, s1, t1, s2, t2 in t.synced:
+        ccs[lin % t.n_dirs, lin // t.n_dirs] += ed.integrated(_ed_current(ed, T, s1, t1), _ed_current(ed, T, s2, t2), dtau)
+    return ccs
+
+
 def test_attractive_2x2_susceptibilities_against_exact_diagonalisation():
     """The time-displaced measurements (charge / spin density and pairing susceptibility through the
     CombinedGreensIterator) of the same model against expectation_value_integrated, as ED_tests.jl:272-345 does
@@ -205,7 +222,7 @@ def test_attractive_2x2_susceptibilities_against_exact_diagonalisation():
         acc, n = None, 0
         for _ in range(250):
             o.sweep(2)
-            r = orc.susceptibilities(o, t, recalculate=5)
+            r = orc.susceptibilities(o, t, recalculate=5, T=model.hopping_matrix())
             acc = r if acc is None else {k: acc[k] + r[k] for k in r}
             n += 1
         recs.append({k: v / n for k, v in acc.items()})
@@ -220,7 +237,9 @@ def test_attractive_2x2_susceptibilities_against_exact_diagonalisation():
     assert _close(_mean_err(recs, "cds")[0], cds / N)
     assert _close(_mean_err(recs, "sds")[0], sds / N)
     assert _close(_mean_err(recs, "ps")[0], ps / N)
-    assert np.abs(cds).max() > 0.5 and np.abs(ps).max() > 0.05             # the comparison is not between zeros
+    ccs = _ed_ccs(ed, model.hopping_matrix(), t, K, dtau)
+    assert _close(_mean_err(recs, "ccs")[0], ccs / N)
+    assert np.abs(cds).max() > 0.5 and np.abs(ps).max() > 0.05 and np.abs(ccs).max() > 1.0   # not between zeros
 
 
 def test_repulsive_2x2_against_exact_diagonalisation():
@@ -272,7 +291,7 @@ def test_repulsive_2x2_susceptibilities_against_exact_diagonalisation():
         acc, n = None, 0
         for _ in range(250):
             o.sweep(2)
-            r = orc.susceptibilities(o, t, recalculate=5)
+            r = orc.susceptibilities(o, t, recalculate=5, T=model.hopping_matrix()[:N, :N])
             acc = r if acc is None else {k: acc[k] + r[k] for k in r}
             n += 1
         recs.append({k: v / n for k, v in acc.items()})
@@ -291,4 +310,6 @@ def test_repulsive_2x2_susceptibilities_against_exact_diagonalisation():
     assert _close(_mean_err(recs, "sds_y")[0], sdx / N, 0.03)
     assert _close(_mean_err(recs, "sds_z")[0], sdz / N, 0.03)
     assert _close(_mean_err(recs, "ps")[0], ps / N)
-    assert np.abs(sdx).max() > 0.3 and np.abs(ps).max() > 0.05
+    ccs = _ed_ccs(ed, model.hopping_matrix()[:N, :N], t, K, dtau)
+    assert _close(_mean_err(recs, "ccs")[0], ccs / N)
+    assert np.abs(sdx).max() > 0.3 and np.abs(ps).max() > 0.05 and np.abs(ccs).max() > 1.0
