@@ -76,6 +76,7 @@ SIGNATURES = {
     "mcb_dqmc_measure": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_reset_observables": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_measure_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcb_dqmc_schedule_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "mcb_dqmc_susceptibility_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_get_susceptibilities": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_rep_measure_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32]),

@@ -221,7 +221,10 @@ int mcb_dqmc_update(mcb_dqmc* h, int64_t n_updates, int32_t measure_every)
         left -= done;
         if (measure_every > 0 && h->current_slice == 1 && h->direction == 1) {
             const int64_t sweep = (h->n_updates - 1) / (2 * (int64_t)h->M) + 1; // 1-based like DQMC.jl:420
-            if (sweep % measure_every == 0) API_TRY(engine_measure(h));
+            if (sweep % measure_every == 0) {
+                API_TRY(engine_measure(h));
+                if (h->td_scheduled) API_TRY(engine_measure_td(h, h->td_recalculate));
+            }
         }
     }
     MCB_CUDA(cudaEventRecord(h->ev1, h->st));
@@ -436,6 +439,14 @@ int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate)
     ProfBind bind(h);
     API_TRY(engine_measure_td(h, recalculate));
     MCB_CUDA(cudaStreamSynchronize(h->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_schedule_susceptibilities(mcb_dqmc* h, int32_t enable, int32_t recalculate)
+{
+    REQUIRE(h, "null handle");
+    h->td_scheduled = enable != 0;
+    h->td_recalculate = recalculate;
     return MCB_OK;
 }
 

@@ -46,6 +46,8 @@ struct mcb_dqmc {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
     bool use_panel = false; // chain-resident kernels (panel.cuh) exist for this N
+    bool td_scheduled = false;         // time-displaced measurements ride along with the scheduled equal-time ones
+    int td_recalculate = 0;
     bool use_resident_segment = false; // wrap + sweep with G in shared memory (segment_resident.cu), general stabilisation
     double* hopT[2] = {nullptr, nullptr}; // transposes of hop[2], hop[3] for that kernel
     bool hopping_set = false, conf_set = false, stack_built = false;

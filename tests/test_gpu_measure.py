@@ -311,3 +311,33 @@ def test_susceptibilities_match_the_oracle(L, U, mu, beta, safe_mult, recalculat
     mc.reset_observables()
     assert mc.susceptibilities()["count"] == 0
     mc.close()
+
+
+def test_scheduled_susceptibilities_ride_along_with_the_measurement_schedule():
+    """run!'s measurement point (DQMC.jl:423-438): with schedule_susceptibilities the time-displaced group is measured
+    wherever the equal-time one is; the sums equal those of the same measurements taken by hand."""
+    def make():
+        mc = mcb.DQMC(mcb.HubbardModelAttractive(L=4, U=2.0, mu=0.2), n_chains=3, seed=5, beta=1.0, delta_tau=0.1, safe_mult=5)
+        mc.enable_measurements(5)
+        mc.build_stack()
+        mc.update(mc.M)           # to the measurement point; sweeps counted from here end there
+        return mc
+    a = make()
+    a.schedule_susceptibilities(True, recalculate=5)
+    a.sweep(6, measure_every=2)
+    sa, oa = a.susceptibilities(), a.observables()
+    b = make()
+    for k in range(1, 7):
+        b.sweep(1)
+        # the update that ends a visit of the measurement point belongs to sweep k + 1 here (the handle started half a
+        # sweep in): DQMC.jl:420-423 counts sweeps from the start of the run
+        if (k + 1) % 2 == 0:
+            b.measure()
+            b.measure_susceptibilities(recalculate=5)
+    sb, ob = b.susceptibilities(), b.observables()
+    assert sa["count"] == sb["count"] == oa["count"] == 3
+    for k in ("cds", "sds", "ps", "ccs"):
+        assert np.array_equal(sa[k], sb[k]), k
+    assert np.array_equal(oa["cdc"], ob["cdc"])
+    a.close()
+    b.close()
