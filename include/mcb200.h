@@ -133,6 +133,9 @@ int mcb_comm_create(const void* id, int32_t n_ranks, int32_t rank, int32_t devic
 int mcb_comm_destroy(mcb_comm* c);
 int32_t mcb_dqmc_moments_len(mcb_dqmc* h);
 int mcb_dqmc_allreduce_observables(mcb_dqmc* h, mcb_comm* c, double* moments);
+/* the same for the time-displaced records: moments[2 L + 1] = [ sum_c x_c | sum_c x_c^2 | number of chains ],
+ * L = mcb_dqmc_susceptibility_len(h), x_c = chain c's mean record of mcb_dqmc_get_susceptibilities */
+int mcb_dqmc_allreduce_susceptibilities(mcb_dqmc* h, mcb_comm* c, double* moments);
 
 /* CombinedGreensIterator(mc, recalculate) (src/flavors/DQMC/unequal_time_stack.jl:746-885) on the device: yields, for
  * l = 1 .. n_slices, G(0 <- l), G(l <- 0) and G(l <- l) of the current configuration by advancing three UDT triples one

@@ -62,6 +62,7 @@ SIGNATURES = {
     "mcb_comm_destroy": (C.c_int, [C.c_void_p]),
     "mcb_dqmc_moments_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_allreduce_observables": (C.c_int, [C.c_void_p, C.c_void_p, _f64]),
+    "mcb_dqmc_allreduce_susceptibilities": (C.c_int, [C.c_void_p, C.c_void_p, _f64]),
     "mcb_dqmc_cgi_begin": (C.c_int, [C.c_void_p, C.c_int32]),
     "mcb_dqmc_cgi_next": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_void_p, C.c_void_p, C.c_void_p]),
     "mcb_dqmc_cgi_device_results": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 3),

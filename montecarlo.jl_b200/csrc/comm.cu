@@ -186,4 +186,49 @@ int mcb_dqmc_allreduce_observables(mcb_dqmc* h, mcb_comm* c, double* moments)
     return rc;
 }
 
+// The same reduction for the time-displaced records (mcb_dqmc_get_susceptibilities): moments, length 2 L + 1 with
+// L = mcb_dqmc_susceptibility_len(h): [ sum_c x_c (L) | sum_c x_c^2 (L) | number of chains ], x_c = chain c's mean over the
+// time-displaced measurements taken so far; a rank without such measurements contributes zeros and zero chains.
+int mcb_dqmc_allreduce_susceptibilities(mcb_dqmc* h, mcb_comm* c, double* moments)
+{
+    if (!h || !moments) { mcb::set_error("null argument"); return MCB_ERR_ARG; }
+    if (!h->ms.ready()) { mcb::set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (c && c->device != h->p.device_id) { mcb::set_error("communicator and handle live on different devices"); return MCB_ERR_ARG; }
+    MCB_CUDA(cudaSetDevice(h->p.device_id));
+    const int L = h->ms.td_len();
+    const size_t len = (size_t)2 * L + 1;
+    double* buf = nullptr;
+    double* own = nullptr;
+    if (c) {
+        if (c->buf_len < len) {
+            if (c->buf) cudaFree(c->buf);
+            c->buf = nullptr; c->buf_len = 0;
+            MCB_CUDA(cudaMalloc(&c->buf, len * sizeof(double)));
+            c->buf_len = len;
+        }
+        buf = c->buf;
+    } else {
+        MCB_CUDA(cudaMalloc(&own, len * sizeof(double)));
+        buf = own;
+    }
+    const bool measured = h->ms.n_td > 0;
+    MCB_CUDA(cudaMemsetAsync(buf, 0, len * sizeof(double), h->st));
+    if (measured && L > 0) {
+        moments_kernel<<<(L + 127) / 128, 128, 0, h->st>>>(h->ms.td, h->C, L, 1.0 / (double)h->ms.n_td, buf);
+        MCB_CUDA(cudaGetLastError());
+        const double count = (double)h->C;
+        MCB_CUDA(cudaMemcpyAsync(buf + len - 1, &count, sizeof(double), cudaMemcpyHostToDevice, h->st));
+    }
+    int rc = MCB_OK;
+    if (c && c->n_ranks > 1)
+        rc = nccl_check(g_nccl.all_reduce(buf, buf, len, NCCL_FLOAT64, NCCL_SUM, c->comm, h->st), "ncclAllReduce");
+    if (rc == MCB_OK) {
+        cudaError_t e = cudaMemcpyAsync(moments, buf, len * sizeof(double), cudaMemcpyDeviceToHost, h->st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
+        if (e != cudaSuccess) { mcb::set_error(cudaGetErrorString(e)); rc = MCB_ERR_CUDA; }
+    }
+    if (own) cudaFree(own);
+    return rc;
+}
+
 } // extern "C"

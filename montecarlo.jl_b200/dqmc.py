@@ -326,6 +326,18 @@ class DQMC:
         return (buf[:R].copy(), buf[R:2 * R].copy(), g(buf[2 * R:2 * R + NN]), g(buf[2 * R + NN:2 * R + 2 * NN]),
                 int(round(buf[-1])))
 
+    def allreduce_susceptibility_moments(self, comm=None):
+        """The same collective for the time-displaced records (mcb_dqmc_allreduce_susceptibilities): returns
+        (record_sum, record_sumsq, n_chains), the record in the layout of mcb_dqmc_get_susceptibilities."""
+        if self.model.flv != 1:
+            raise NotImplementedError("allreduce_susceptibility_moments: one-flavor handles only")
+        n = self.L.mcb_dqmc_susceptibility_len(self.h)
+        if n <= 0:
+            raise RuntimeError("enable_measurements first")
+        buf = np.empty(2 * n + 1)
+        _lib.check(self.L.mcb_dqmc_allreduce_susceptibilities(self.h, comm.h if comm is not None else None, buf))
+        return buf[:n].copy(), buf[n:2 * n].copy(), int(round(buf[-1]))
+
     @staticmethod
     def observable_shapes(model, K=None):
         """Trailing shapes (without the chain axis) of everything observables() returns as an array; lets a rank

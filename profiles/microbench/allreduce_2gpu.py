@@ -29,8 +29,18 @@ dist.all_gather_object(gathered, [np.asarray(x) for x in own])
 for i in range(5):
     want = sum(np.asarray(g[i], dtype=np.float64) for g in gathered)
     assert np.allclose(np.asarray(tot[i], dtype=np.float64), want, rtol=1e-13, atol=1e-15), (rank, i)
+# the time-displaced records travel the same way
+mc.update(mc.M)
+mc.measure_susceptibilities(recalculate=5)
+own_td = mc.allreduce_susceptibility_moments(None)
+tot_td = mc.allreduce_susceptibility_moments(comm)
+gathered = [None] * world
+dist.all_gather_object(gathered, [np.asarray(x) for x in own_td])
+for i in range(3):
+    want = sum(np.asarray(g[i], dtype=np.float64) for g in gathered)
+    assert np.allclose(np.asarray(tot_td[i], dtype=np.float64), want, rtol=1e-13, atol=1e-15), (rank, "td", i)
 if rank == 0:
-    print(f"allreduce over {world} ranks ok: chains {tot[4]}, <n> = {tot[0][0] / tot[4]:.6f}")
+    print(f"allreduce over {world} ranks ok: chains {tot[4]}, <n> = {tot[0][0] / tot[4]:.6f}; susceptibilities: chains {tot_td[2]}, cds[0] = {tot_td[0][0] / tot_td[2]:.6f}")
 comm.close()
 mc.close()
 dist.destroy_process_group()

@@ -48,6 +48,29 @@ def test_moments_of_one_rank(with_comm):
     mc.close()
 
 
+@pytest.mark.parametrize("with_comm", [False, True])
+def test_susceptibility_moments_of_one_rank(with_comm):
+    import ctypes as C
+    mc = _measured_handle(chains=4)
+    s, s2, chains = mc.allreduce_susceptibility_moments()
+    assert chains == 0 and not s.any()                      # nothing time-displaced measured yet
+    mc.update(mc.M)                                         # to the measurement point
+    for _ in range(2):
+        mc.measure_susceptibilities(recalculate=5)
+        mc.sweep(1)
+    comm = sharding.NcclComm(sharding.NcclComm.unique_id(), 1, 0, 0) if with_comm else None
+    s, s2, chains = mc.allreduce_susceptibility_moments(comm)
+    n = mc.L.mcb_dqmc_susceptibility_len(mc.h)
+    buf, cnt = np.empty(mc.n_chains * n), C.c_int64()
+    mcb._lib.check(mc.L.mcb_dqmc_get_susceptibilities(mc.h, buf, C.byref(cnt)))
+    rec = buf.reshape(mc.n_chains, n) / cnt.value
+    assert chains == 4 and cnt.value == 2
+    assert np.allclose(s, rec.sum(0), rtol=1e-13, atol=1e-15) and np.allclose(s2, (rec * rec).sum(0), rtol=1e-13, atol=1e-15)
+    if comm is not None:
+        comm.close()
+    mc.close()
+
+
 def test_rank_without_measurements_contributes_nothing():
     model = mcb.HubbardModelAttractive(L=4, U=2.0)
     mc = mcb.DQMC(model, n_chains=2, seed=5, beta=1.0, delta_tau=0.1, safe_mult=5)
