@@ -193,7 +193,8 @@ int mcb_dqmc_reset_observables(mcb_dqmc* h);
  * calls, reset by mcb_dqmc_reset_observables. (Two-flavor handles: mcb_dqmc_rep_measure_susceptibilities.) */
 int mcb_dqmc_measure_susceptibilities(mcb_dqmc* h, int32_t recalculate);
 /* enable != 0: every scheduled measurement of mcb_dqmc_update / mcb_dqmc_sweep (measure_every > 0) also takes one
- * time-displaced measurement, as run! does for a measurement group on the CombinedGreensIterator (DQMC.jl:423-438) */
+ * time-displaced measurement, as run! does for a measurement group on the CombinedGreensIterator (DQMC.jl:423-438), and so
+ * does every configuration of mcb_dqmc_replay (DQMC.jl:649-660) */
 int mcb_dqmc_schedule_susceptibilities(mcb_dqmc* h, int32_t enable, int32_t recalculate);
 int32_t mcb_dqmc_susceptibility_len(mcb_dqmc* h);
 int mcb_dqmc_get_susceptibilities(mcb_dqmc* h, double* sums /*[chain][len]*/, int64_t* count);

@@ -369,6 +369,7 @@ int mcb_dqmc_replay(mcb_dqmc* h, const uint64_t* chunks, int64_t n_confs)
         API_TRY(upload_bits(h, chunks + (size_t)b * h->C * nch));
         API_TRY(engine_calculate_greens_at(h, 0));
         API_TRY(engine_measure(h));
+        if (h->td_scheduled) API_TRY(engine_measure_td(h, h->td_recalculate, true));
         MCB_CUDA(cudaStreamSynchronize(h->st)); // the staging buffer is reused by the next batch
     }
     return MCB_OK;

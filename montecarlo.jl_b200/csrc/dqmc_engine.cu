@@ -540,11 +540,12 @@ int engine_measure(mcb_dqmc* h)
 // apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243): G00 = greens!(mc), then for every slice of the
 // iterator the time-displaced kernels of the group on (G00, G0l, Gl0, Gll); finish! scales by delta_tau / N. The iterator
 // runs on the device (unequal.cu) and leaves the sweep state as it found it.
-int engine_measure_td(mcb_dqmc* h, int recalculate)
+int engine_measure_td(mcb_dqmc* h, int recalculate, bool from_g0)
 {
     if (!h->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
     if (h->ms.flavors != 1) { set_error("two-flavor tables on a one-flavor handle"); return MCB_ERR_STATE; }
-    MCB_TRY(engine_cgi_begin(h, recalculate));   // checks the measurement point
+    if (from_g0) MCB_TRY(engine_cgi_begin_from_g0(h, recalculate));   // replay!: G = G(0) of the recorded configuration
+    else MCB_TRY(engine_cgi_begin(h, recalculate));                   // checks the measurement point
     double* g00[2];
     MCB_TRY(measure_td_g00(h->ms, g00));
     MCB_TRY(engine_physical_greens(h, g00[0]));

@@ -98,7 +98,8 @@ int engine_greens_unequal(mcb_dqmc* h, int slice1, int slice2);
 void unequal_free(mcb_dqmc* h);
 double* unequal_result(mcb_dqmc* h);
 // CombinedGreensIterator on the device (unequal.cu)
-int engine_measure_td(mcb_dqmc* h, int recalculate);
+int engine_measure_td(mcb_dqmc* h, int recalculate, bool from_g0 = false);
+int engine_cgi_begin_from_g0(mcb_dqmc* h, int recalculate);
 int engine_cgi_begin(mcb_dqmc* h, int recalculate);
 int engine_cgi_next(mcb_dqmc* h, int physical, int* l_out, const double* results[3]);
 int engine_cgi_last(mcb_dqmc* h, const double* results[3]);

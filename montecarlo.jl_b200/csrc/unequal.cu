@@ -485,6 +485,15 @@ int engine_cgi_begin(mcb_dqmc* h, int recalculate)
     return cgi_begin(h, recalculate);
 }
 
+// the same start for replay!, where calculate_greens(mc, 0) has just put G(0) of a recorded configuration into mc.s.greens
+// and there is no sweep state to check (DQMC.jl:649-660)
+int engine_cgi_begin_from_g0(mcb_dqmc* h, int recalculate)
+{
+    MCB_TRY(ut_alloc(h));
+    MCB_TRY(ut_build(h));
+    return cgi_begin(h, recalculate);
+}
+
 // one step: *l_out = the slice the results belong to (1 .. M), 0 when the iteration is over. results[0..2] = device
 // pointers to G(0 <- l), G(l <- 0), G(l <- l), [chain][col][row], valid until the next step.
 int engine_cgi_next(mcb_dqmc* h, int physical, int* l_out, const double* results[3])

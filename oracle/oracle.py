@@ -423,8 +423,12 @@ def susceptibilities(chain, tables, recalculate=0, T=None):
                                   + Tf[a1, b1] * Tf[a2, b2] * (-G0l[b2, a1]) * Gl0[b1, a2])
         dtau = chain.up.dtau
     else:
-        G00 = chain.greens(physical=True)
-        cg = chain.combined_greens(recalculate, physical=True)   # (M, 3, N, N): G0l, Gl0, Gll
+        if isinstance(chain, tuple):   # (G00, cg, dtau): Green's functions from elsewhere, e.g. stabilised evaluations
+            G00, cg, dtau_given = chain
+        else:
+            G00 = chain.greens(physical=True)
+            cg = chain.combined_greens(recalculate, physical=True)   # (M, 3, N, N): G0l, Gl0, Gll
+            dtau_given = chain.dtau
         for l in range(cg.shape[0]):
             G0l, Gl0, Gll = cg[l]
             ex = -2.0 * G0l[j_, i_] * Gl0[i_, j_]
@@ -439,7 +443,7 @@ def susceptibilities(chain, tables, recalculate=0, T=None):
                           - 2.0 * T[e1, c1] * T[c2, e2] * (-G0l[e2, e1]) * Gl0[c1, c2]
                           + 2.0 * T[c1, e1] * T[c2, e2] * (-G0l[e2, c1]) * Gl0[e1, c2])
         sy, sz = sx, sx
-        dtau = chain.dtau
+        dtau = dtau_given
     f = dtau / N
     out = dict(cds=cds * f, sds_x=sx * f, sds_y=sy * f, sds_z=sz * f,
                ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())

@@ -341,3 +341,36 @@ def test_scheduled_susceptibilities_ride_along_with_the_measurement_schedule():
     assert np.array_equal(oa["cdc"], ob["cdc"])
     a.close()
     b.close()
+
+
+def test_replay_takes_the_time_displaced_group_along():
+    """replay! (DQMC.jl:649-660) with a measurement group on the CombinedGreensIterator: per recorded configuration
+    calculate_greens(mc, 0), then the iterator from that G(0). Reference values: the same kernels on the STABILISED
+    G(0 <- l), G(l <- 0), G(l <- l) of every slice (greens(mc, k, l)), which the iterator reproduces to 1e-10 / 1e-8."""
+    L, U, K = 4, 2.0, 5
+    model = mcb.HubbardModelAttractive(L=L, U=U, mu=0.1)
+    kw = dict(beta=1.0, delta_tau=0.1, safe_mult=5)
+    mc = mcb.DQMC(model, n_chains=3, seed=9, **kw)
+    mc.enable_measurements(K)
+    mc.schedule_susceptibilities(True, recalculate=5)
+    N, M = mc.N, mc.M
+    confs = np.random.default_rng(4).choice(np.array([-1, 1], dtype=np.int8), size=(6, N, M))
+    res = mc.replay(np.stack([mcb.compress(c) for c in confs]))
+    assert res[0]["count"] == 2
+    got = mc.susceptibilities()
+    assert got["count"] == 2
+    tables = orc.MeasurementTables(L, K)
+    one = mcb.DQMC(model, n_chains=1, seed=9, **kw)
+    want = []
+    for c in confs:
+        one.set_conf(c[None])
+        one.greens_at(0)                                     # leaves G(0) as the handle's Green's function
+        G00 = one.greens(physical=True)[0]
+        cg = np.stack([np.stack([one.greens_unequal(0, l)[0], one.greens_unequal(l, 0)[0], one.greens_unequal(l, l)[0]])
+                       for l in range(1, M + 1)])
+        want.append(orc.susceptibilities((G00, cg, 0.1), tables, T=model.hopping_matrix()))
+    for slot in range(3):
+        for k in ("cds", "sds", "ps", "ccs"):
+            w = 0.5 * (want[slot][k] + want[3 + slot][k])    # batch b holds configurations 3 b .. 3 b + 2
+            assert np.abs(got[k][slot] - w).max() < 1e-7 * max(1.0, np.abs(w).max()), (slot, k)
+    mc.close(); one.close()
