@@ -81,6 +81,7 @@ SIGNATURES = {
     "mcb_dqmc_susceptibility_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_get_susceptibilities": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_rep_measure_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32]),
+    "mcb_dqmc_rep_schedule_susceptibilities": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "mcb_dqmc_rep_susceptibility_len": (C.c_int32, [C.c_void_p]),
     "mcb_dqmc_rep_get_susceptibilities": (C.c_int, [C.c_void_p, _f64, C.POINTER(C.c_int64)]),
     "mcb_dqmc_observable_len": (C.c_int32, [C.c_void_p]),

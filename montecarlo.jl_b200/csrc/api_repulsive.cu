@@ -144,6 +144,40 @@ static int rep_measure(mcb_dqmc_rep* r)
     return measure_accumulate(u->ms, u->W[1], d->W[1], u->st);
 }
 
+// apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for the two-block handle: charge / spin density,
+// pairing and current-current susceptibility from the iterators of both blocks, advanced in step (measure.cu:
+// measure_td_kernel<true>). Enqueues only.
+static int rep_measure_td(mcb_dqmc_rep* r, int recalculate)
+{
+    mcb_dqmc* u = r->up;
+    mcb_dqmc* d = r->dn;
+    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
+    if (u->ms.flavors != 2) { set_error("one-flavor tables on a two-flavor handle"); return MCB_ERR_STATE; }
+    for (mcb_dqmc* h : {u, d}) {
+        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
+        API_TRY(engine_cgi_begin(h, recalculate));
+    }
+    double* g00[2];
+    API_TRY(measure_td_g00(u->ms, g00));
+    API_TRY(engine_physical_greens(u, g00[0]));
+    API_TRY(engine_physical_greens(d, g00[1]));
+    const double factor = u->p.delta_tau / (double)u->N;
+    for (;;) {
+        int lu = 0, ld = 0;
+        const double* ru[3] = {nullptr, nullptr, nullptr};
+        const double* rd[3] = {nullptr, nullptr, nullptr};
+        API_TRY(engine_cgi_next(u, 1, &lu, ru));
+        API_TRY(engine_cgi_next(d, 1, &ld, rd));
+        if (lu != ld) { set_error("CombinedGreensIterator: the two blocks are out of step"); return MCB_ERR_STATE; }
+        if (lu == 0) break;
+        const double* const mu[4] = {g00[0], ru[0], ru[1], ru[2]};
+        const double* const md[4] = {g00[1], rd[0], rd[1], rd[2]};
+        API_TRY(measure_td_accumulate(u->ms, mu, md, factor, u->st));
+    }
+    u->ms.n_td += 1;
+    return MCB_OK;
+}
+
 int mcb_dqmc_rep_update(mcb_dqmc_rep* r, int64_t n_updates, int32_t measure_every)
 {
     REQUIRE(r && n_updates >= 0, "bad argument");
@@ -157,7 +191,10 @@ int mcb_dqmc_rep_update(mcb_dqmc_rep* r, int64_t n_updates, int32_t measure_ever
         API_TRY(rep_update(r));
         if (measure_every > 0 && u->current_slice == 1 && u->direction == 1) { // DQMC.jl:429-436
             const int64_t sweep = (u->n_updates - 1) / (2 * (int64_t)u->M) + 1;
-            if (sweep % measure_every == 0) API_TRY(rep_measure(r));
+            if (sweep % measure_every == 0) {
+                API_TRY(rep_measure(r));
+                if (u->td_scheduled) API_TRY(rep_measure_td(r, u->td_recalculate));
+            }
         }
     }
     MCB_CUDA(cudaEventRecord(u->ev1, u->st));
@@ -369,40 +406,21 @@ int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* r, int32_t physical, int32_t* slice, dou
     return MCB_OK;
 }
 
-// apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for the two-block handle: charge / spin density
-// and pairing susceptibility from the iterators of both blocks, advanced in step (measure.cu: measure_td_kernel<true>)
 int mcb_dqmc_rep_measure_susceptibilities(mcb_dqmc_rep* r, int32_t recalculate)
 {
     REQUIRE(r, "null handle");
-    mcb_dqmc* u = r->up;
-    mcb_dqmc* d = r->dn;
-    if (!u->ms.ready()) { set_error("measurement tables not set"); return MCB_ERR_STATE; }
-    if (u->ms.flavors != 2) { set_error("one-flavor tables on a two-flavor handle"); return MCB_ERR_STATE; }
-    MCB_CUDA(cudaSetDevice(u->p.device_id));
-    ProfBind bind(u);
-    for (mcb_dqmc* h : {u, d}) {
-        if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
-        API_TRY(engine_cgi_begin(h, recalculate));
-    }
-    double* g00[2];
-    API_TRY(measure_td_g00(u->ms, g00));
-    API_TRY(engine_physical_greens(u, g00[0]));
-    API_TRY(engine_physical_greens(d, g00[1]));
-    const double factor = u->p.delta_tau / (double)u->N;
-    for (;;) {
-        int lu = 0, ld = 0;
-        const double* ru[3] = {nullptr, nullptr, nullptr};
-        const double* rd[3] = {nullptr, nullptr, nullptr};
-        API_TRY(engine_cgi_next(u, 1, &lu, ru));
-        API_TRY(engine_cgi_next(d, 1, &ld, rd));
-        if (lu != ld) { set_error("CombinedGreensIterator: the two blocks are out of step"); return MCB_ERR_STATE; }
-        if (lu == 0) break;
-        const double* const mu[4] = {g00[0], ru[0], ru[1], ru[2]};
-        const double* const md[4] = {g00[1], rd[0], rd[1], rd[2]};
-        API_TRY(measure_td_accumulate(u->ms, mu, md, factor, u->st));
-    }
-    u->ms.n_td += 1;
-    MCB_CUDA(cudaStreamSynchronize(u->st));
+    MCB_CUDA(cudaSetDevice(r->up->p.device_id));
+    ProfBind bind(r->up);
+    API_TRY(rep_measure_td(r, recalculate));
+    MCB_CUDA(cudaStreamSynchronize(r->up->st));
+    return MCB_OK;
+}
+
+int mcb_dqmc_rep_schedule_susceptibilities(mcb_dqmc_rep* r, int32_t enable, int32_t recalculate)
+{
+    REQUIRE(r, "null handle");
+    r->up->td_scheduled = enable != 0;
+    r->up->td_recalculate = recalculate;
     return MCB_OK;
 }
 

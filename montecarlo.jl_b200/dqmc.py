@@ -279,11 +279,10 @@ class DQMC:
 
     def schedule_susceptibilities(self, enable=True, recalculate=0):
         """Let every scheduled measurement of update / sweep / run (measure_every > 0) also take one time-displaced
-        measurement, as run! does for a measurement group on the CombinedGreensIterator. One-flavor handles."""
-        if self.model.flv != 1:
-            raise NotImplementedError("schedule_susceptibilities: one-flavor handles only (call measure_susceptibilities)")
+        measurement, as run! does for a measurement group on the CombinedGreensIterator (and, for the one-flavor handle,
+        every configuration of replay)."""
         self.enable_measurements()
-        _lib.check(self.L.mcb_dqmc_schedule_susceptibilities(self.h, int(bool(enable)), int(recalculate)))
+        _lib.check(self._f("schedule_susceptibilities")(self.h, int(bool(enable)), int(recalculate)))
 
     def susceptibilities(self):
         """Per-chain means over the time-displaced measurements taken so far: cds (C, n_dirs), sds_x = sds_y and sds_z

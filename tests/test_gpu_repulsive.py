@@ -206,6 +206,32 @@ def test_susceptibilities_of_the_two_block_handle(L, U, beta, K):
     mc.close()
 
 
+def test_scheduled_susceptibilities_of_the_two_block_handle():
+    """With schedule_susceptibilities the time-displaced group is measured wherever the equal-time one is (run!,
+    DQMC.jl:423-438): same sums as the same measurements taken by hand."""
+    def make():
+        mc, _ = _pair(4, 4.0, 1.0, 0.1, 5, 2)
+        mc.enable_measurements(5)
+        mc.build_stack()
+        mc.update(mc.M)
+        return mc
+    a = make()
+    a.schedule_susceptibilities(True, recalculate=5)
+    a.sweep(4, measure_every=2)
+    b = make()
+    for k in range(1, 5):
+        b.sweep(1)
+        if (k + 1) % 2 == 0:          # the handle started half a sweep in (see tests/test_gpu_measure.py)
+            b.measure()
+            b.measure_susceptibilities(recalculate=5)
+    sa, sb = a.susceptibilities(), b.susceptibilities()
+    assert sa["count"] == sb["count"] == 2
+    for k in ("cds", "sds_x", "sds_z", "ps", "ccs"):
+        assert np.array_equal(sa[k], sb[k]), k
+    a.close()
+    b.close()
+
+
 def test_checkpoint_and_resume_continue_the_same_chains():
     """save / resume! (FileIO.jl:38-156, DQMC.jl:517-521) for the two-block handle: a run that is stopped after two
     sweeps, saved as bit-packed field + sweep count and resumed in a new handle ends where the uninterrupted run does."""
