@@ -293,6 +293,8 @@ int mcb_dqmc_rep_cgi_next(mcb_dqmc_rep* h, int32_t physical, int32_t* slice, dou
  * :268-300 cc) on the BlockDiagonal matrices. Record per chain:
  * [cds[n_dirs] | sds_x[n_dirs] (= sds_y) | sds_z[n_dirs] | ps[n_dirs*K*K] | ccs[n_dirs*K]]. */
 int mcb_dqmc_rep_measure_susceptibilities(mcb_dqmc_rep* h, int32_t recalculate);
+/* as mcb_dqmc_schedule_susceptibilities: scheduled measurements of mcb_dqmc_rep_update / _sweep and every configuration of
+ * mcb_dqmc_rep_replay take the time-displaced group along */
 int mcb_dqmc_rep_schedule_susceptibilities(mcb_dqmc_rep* h, int32_t enable, int32_t recalculate);
 int32_t mcb_dqmc_rep_susceptibility_len(mcb_dqmc_rep* h);
 int mcb_dqmc_rep_get_susceptibilities(mcb_dqmc_rep* h, double* sums /*[chain][len]*/, int64_t* count);

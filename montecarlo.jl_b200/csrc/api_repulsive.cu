@@ -147,7 +147,7 @@ static int rep_measure(mcb_dqmc_rep* r)
 // apply!(::CombinedGreensIterator, ...) (measurements/generic.jl:227-243) for the two-block handle: charge / spin density,
 // pairing and current-current susceptibility from the iterators of both blocks, advanced in step (measure.cu:
 // measure_td_kernel<true>). Enqueues only.
-static int rep_measure_td(mcb_dqmc_rep* r, int recalculate)
+static int rep_measure_td(mcb_dqmc_rep* r, int recalculate, bool from_g0 = false)
 {
     mcb_dqmc* u = r->up;
     mcb_dqmc* d = r->dn;
@@ -155,7 +155,9 @@ static int rep_measure_td(mcb_dqmc_rep* r, int recalculate)
     if (u->ms.flavors != 2) { set_error("one-flavor tables on a two-flavor handle"); return MCB_ERR_STATE; }
     for (mcb_dqmc* h : {u, d}) {
         if (!h->hopping_set || !h->conf_set) { set_error("set_hopping and set_conf first"); return MCB_ERR_STATE; }
-        API_TRY(engine_cgi_begin(h, recalculate));
+        // replay!: G = G(0) of the recorded configuration, no sweep state to check
+        if (from_g0) API_TRY(engine_cgi_begin_from_g0(h, recalculate));
+        else API_TRY(engine_cgi_begin(h, recalculate));
     }
     double* g00[2];
     API_TRY(measure_td_g00(u->ms, g00));
@@ -276,6 +278,7 @@ int mcb_dqmc_rep_replay(mcb_dqmc_rep* r, const uint64_t* chunks, int64_t n_confs
         API_TRY(engine_calculate_greens_at(u, 0));
         API_TRY(engine_calculate_greens_at(r->dn, 0));
         API_TRY(rep_measure(r));
+        if (u->td_scheduled) API_TRY(rep_measure_td(r, u->td_recalculate, true));
         MCB_CUDA(cudaStreamSynchronize(u->st));
     }
     return MCB_OK;

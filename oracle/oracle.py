@@ -381,15 +381,19 @@ def susceptibilities(chain, tables, recalculate=0, T=None):
     cds, sx, sy, sz, ps = np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(nd), np.zeros(tables.n_pc)
     cc = np.zeros(nd * K)
     clin, c1, e1, c2, e2 = (tables.synced[:, k] for k in range(5))   # (lin, src1, trg1, src2, trg2)
-    if isinstance(chain, OracleDQMCRepulsive):
+    two = isinstance(chain, (OracleDQMCRepulsive, dict))
+    if two:
         def full(u, d):
             g = np.zeros((2 * N, 2 * N))
             g[:N, :N], g[N:, N:] = u, d
             return g
-        gu, gd = chain.greens(physical=True)
+        if isinstance(chain, dict):   # Green's functions from elsewhere: G00 (2, N, N), cu / cd (M, 3, N, N), dtau
+            (gu, gd), cu, cd = chain["G00"], chain["cu"], chain["cd"]
+        else:
+            gu, gd = chain.greens(physical=True)
+            cu = chain.up.combined_greens(recalculate, physical=True)
+            cd = chain.dn.combined_greens(recalculate, physical=True)
         G00 = full(gu, gd)
-        cu = chain.up.combined_greens(recalculate, physical=True)
-        cd = chain.dn.combined_greens(recalculate, physical=True)
         iN, jN = i_ + N, j_ + N
         for l in range(cu.shape[0]):
             G0l, Gl0, Gll = (full(cu[l, w], cd[l, w]) for w in range(3))
@@ -421,7 +425,7 @@ def susceptibilities(chain, tables, recalculate=0, T=None):
                                   - Tf[a1, b1] * Tf[b2, a2] * (-G0l[a2, a1]) * Gl0[b1, b2]
                                   - Tf[b1, a1] * Tf[a2, b2] * (-G0l[b2, b1]) * Gl0[a1, a2]
                                   + Tf[a1, b1] * Tf[a2, b2] * (-G0l[b2, a1]) * Gl0[b1, a2])
-        dtau = chain.up.dtau
+        dtau = chain["dtau"] if isinstance(chain, dict) else chain.up.dtau
     else:
         if isinstance(chain, tuple):   # (G00, cg, dtau): Green's functions from elsewhere, e.g. stabilised evaluations
             G00, cg, dtau_given = chain
@@ -447,7 +451,7 @@ def susceptibilities(chain, tables, recalculate=0, T=None):
     f = dtau / N
     out = dict(cds=cds * f, sds_x=sx * f, sds_y=sy * f, sds_z=sz * f,
                ps=(ps * f).reshape(K, K, nd).transpose(2, 1, 0).copy())
-    if not isinstance(chain, OracleDQMCRepulsive):
+    if not two:
         out["sds"] = out["sds_x"]
     if T is not None:
         out["ccs"] = (cc * f).reshape(K, nd).T.copy()   # column-major (n_dirs, K)

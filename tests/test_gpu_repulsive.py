@@ -232,6 +232,38 @@ def test_scheduled_susceptibilities_of_the_two_block_handle():
     b.close()
 
 
+def test_replay_takes_the_time_displaced_group_along():
+    """replay! (DQMC.jl:649-660) of the two-block handle with the time-displaced group scheduled: per recorded
+    configuration the iterators start from G(0) of both blocks. Reference: the general kernels on the stabilised
+    greens(mc, k, l) of every slice."""
+    L, U, K = 2, 1.0, 4
+    mc, _ = _pair(L, U, 1.0, 0.1, 5, 2)
+    mc.enable_measurements(K)
+    mc.schedule_susceptibilities(True, recalculate=5)
+    N, M = mc.N, mc.M
+    confs = np.random.default_rng(8).choice(np.array([-1, 1], dtype=np.int8), size=(4, N, M))
+    res = mc.replay(np.stack([mcb.compress(c) for c in confs]))
+    assert res[0]["count"] == 2
+    got = mc.susceptibilities()
+    assert got["count"] == 2
+    tables = orc.MeasurementTables(L, K)
+    one, _ = _pair(L, U, 1.0, 0.1, 5, 1)
+    want = []
+    for c in confs:
+        one.set_conf(c[None])
+        one.greens_at(0)
+        G00 = one.greens(physical=True)[0]                       # (2, N, N)
+        tri = [[one.greens_unequal(0, l)[0], one.greens_unequal(l, 0)[0], one.greens_unequal(l, l)[0]] for l in range(1, M + 1)]
+        cu = np.stack([np.stack([t[w][0] for w in range(3)]) for t in tri])
+        cd = np.stack([np.stack([t[w][1] for w in range(3)]) for t in tri])
+        want.append(orc.susceptibilities(dict(G00=G00, cu=cu, cd=cd, dtau=0.1), tables, T=mc.model.hopping_matrix()))
+    for slot in range(2):
+        for k in ("cds", "sds_x", "sds_z", "ps", "ccs"):
+            w = 0.5 * (want[slot][k] + want[2 + slot][k])
+            assert np.abs(got[k][slot] - w).max() < 1e-7 * max(1.0, np.abs(w).max()), (slot, k)
+    mc.close(); one.close()
+
+
 def test_checkpoint_and_resume_continue_the_same_chains():
     """save / resume! (FileIO.jl:38-156, DQMC.jl:517-521) for the two-block handle: a run that is stopped after two
     sweeps, saved as bit-packed field + sweep count and resumed in a new handle ends where the uninterrupted run does."""
